@@ -1,0 +1,184 @@
+"""K1 — feature binning / encoding (host implementation + shared metadata).
+
+The reference discovers split candidates with ``np.unique(X[:, f])`` at every
+node (``mpitree/tree/decision_tree.py:73``).  Here candidates are discovered
+**once per fit**: every feature is mapped to small integer *bin codes* whose
+order equals the order of the raw values, so ``x <= t`` on raw values is
+``code <= bin`` on codes.  The code->value table is kept so a split threshold is
+still reported as a data value (``decision_tree.py:88-91`` returns
+``possible_thresholds[argmin]``).
+
+* ``<= max_bins`` distinct values  -> lossless: one bin per distinct value, the
+  histogram search examines exactly the reference's candidate set.
+* more distinct values             -> quantile bins; the bin's upper edge (a
+  data value) is the threshold.
+* string / object columns          -> ordinal codes in sorted-unique order, the
+  same order Python's ``<=`` gives the reference on object arrays.
+
+The CUDA counterpart (``mpitree_b200/csrc/binning.cu``) implements the encode
+pass; edges are always computed from (a sample of) the data with the code here
+or with its device twin in :mod:`mpitree_b200.ops.cuda_engine`.
+"""
+
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import List, Optional, Sequence
+
+import numpy as np
+
+__all__ = ["BinMapper", "FEATURE_GROUP", "padded_features"]
+
+#: features per device tile row chunk (16 one-byte codes = one 128-bit load)
+FEATURE_GROUP = 16
+
+
+def padded_features(n_features: int) -> int:
+    return ((n_features + FEATURE_GROUP - 1) // FEATURE_GROUP) * FEATURE_GROUP
+
+
+def _column_uniques(col: np.ndarray) -> np.ndarray:
+    if col.dtype == object:
+        try:
+            return np.array(sorted(set(col.tolist())), dtype=object)
+        except TypeError as exc:  # mixed str/int in one column, like the reference
+            raise TypeError(f"cannot order the values of a mixed-type column: {exc}") from None
+    return np.unique(col)
+
+
+@dataclass
+class BinMapper:
+    """Per-feature ascending upper edges; ``code = first edge >= value``.
+
+    Attributes
+    ----------
+    edges : list of 1-D arrays (one per feature), ascending data values
+    lossless : bool array, True where each bin holds exactly one distinct value
+    max_bins : int (<= 256 so codes fit one byte)
+    """
+
+    edges: List[np.ndarray]
+    lossless: np.ndarray
+    max_bins: int = 256
+
+    # ----------------------------------------------------------------- build
+    @classmethod
+    def fit(
+        cls,
+        X: np.ndarray,
+        max_bins: int = 256,
+        *,
+        summaries: Optional[Sequence[Sequence[np.ndarray]]] = None,
+    ) -> "BinMapper":
+        """Compute edges from ``X`` (n_rows, n_features).
+
+        ``summaries`` optionally carries, per *other* rank, a list of per-feature
+        value arrays (uniques or quantile sketches) to merge with the local
+        ones so that every rank derives identical edges (the cross-rank "edge
+        agreement" step of K1).
+        """
+        if not 2 <= max_bins <= 256:
+            raise ValueError("max_bins must be in [2, 256]")
+        n_features = X.shape[1]
+        edges, lossless = [], np.zeros(n_features, dtype=bool)
+        for f in range(n_features):
+            values = _column_uniques(X[:, f]) if X.shape[0] else np.zeros(0, X.dtype)
+            if summaries:
+                parts = [values] + [np.asarray(s[f]) for s in summaries]
+                parts = [p for p in parts if len(p)]
+                if parts:
+                    values = _column_uniques(np.concatenate(parts))
+            if len(values) <= max_bins:
+                edges.append(values)
+                lossless[f] = True
+            else:
+                edges.append(_quantile_edges(values, X[:, f], max_bins))
+        return cls(edges=edges, lossless=lossless, max_bins=max_bins)
+
+    @staticmethod
+    def local_summary(X: np.ndarray, cap: int = 4096) -> List[np.ndarray]:
+        """Per-feature value summary small enough to all-gather between ranks."""
+        out = []
+        for f in range(X.shape[1]):
+            u = _column_uniques(X[:, f]) if X.shape[0] else np.zeros(0, X.dtype)
+            if len(u) > cap:
+                idx = np.unique(np.linspace(0, len(u) - 1, cap).round().astype(np.int64))
+                u = u[idx]
+            out.append(u)
+        return out
+
+    # ------------------------------------------------------------- transform
+    @property
+    def n_features(self) -> int:
+        return len(self.edges)
+
+    @property
+    def n_bins(self) -> np.ndarray:
+        return np.array([max(len(e), 1) for e in self.edges], dtype=np.int32)
+
+    @property
+    def is_numeric(self) -> bool:
+        return all(e.dtype != object for e in self.edges)
+
+    def transform(self, X: np.ndarray) -> np.ndarray:
+        """Raw values -> ``uint8`` codes ``(n_rows, n_features)`` (row-major)."""
+        n, F = X.shape
+        if F != self.n_features:
+            raise ValueError(f"X has {F} features, the bin mapper was fitted on {self.n_features}")
+        codes = np.empty((n, F), dtype=np.uint8)
+        for f in range(F):
+            e = self.edges[f]
+            if len(e) == 0:
+                codes[:, f] = 0
+                continue
+            col = X[:, f]
+            if e.dtype == object:
+                lut = {v: i for i, v in enumerate(e.tolist())}
+                try:
+                    codes[:, f] = [lut[v] for v in col.tolist()]
+                except KeyError:
+                    codes[:, f] = [_bisect_obj(e, v) for v in col.tolist()]
+            else:
+                c = np.searchsorted(e, col, side="left")
+                np.minimum(c, len(e) - 1, out=c)
+                codes[:, f] = c
+        return codes
+
+    def threshold_of(self, feature: int, bin_code: int):
+        """Raw-value threshold for ``code <= bin_code`` as a plain Python object."""
+        v = self.edges[feature][bin_code]
+        return v.item() if isinstance(v, np.generic) else v
+
+    def edges_matrix(self, dtype=np.float32) -> np.ndarray:
+        """(n_features, max_bins) array of edges padded with +inf (device encode table)."""
+        out = np.full((self.n_features, self.max_bins), np.inf, dtype=dtype)
+        for f, e in enumerate(self.edges):
+            if e.dtype == object:
+                raise TypeError("object/string features are encoded on the host")
+            out[f, : len(e)] = e
+        return out
+
+
+def _quantile_edges(uniques: np.ndarray, col: np.ndarray, max_bins: int) -> np.ndarray:
+    """``max_bins`` ascending data values; the last edge is the column maximum."""
+    if col.dtype == object:
+        idx = np.linspace(0, len(uniques) - 1, max_bins).round().astype(np.int64)
+        return uniques[np.unique(idx)]
+    qs = np.linspace(0.0, 1.0, max_bins + 1)[1:]
+    # 'higher' keeps every edge an actual data value
+    e = np.quantile(col, qs, method="higher")
+    e = np.unique(e)
+    if e[-1] < uniques[-1]:
+        e[-1] = uniques[-1]
+    return e.astype(col.dtype, copy=False)
+
+
+def _bisect_obj(edges: np.ndarray, v) -> int:
+    lo, hi = 0, len(edges) - 1
+    while lo < hi:
+        mid = (lo + hi) // 2
+        if edges[mid] >= v:
+            hi = mid
+        else:
+            lo = mid + 1
+    return lo

@@ -1,0 +1,314 @@
+"""Host (numpy) engine: exact split search and the level-wise builder.
+
+This is the correctness scaffold and the CPU product path (small inputs, the
+``iris / 2 ranks on CPU`` parity configuration, the CPU half of subtree
+hand-off).  It runs the *same algorithm* as the CUDA engine — per-node
+feature x bin x class count histograms, cross-rank sum, prefix over bins,
+entropy gain, argmax — and reproduces the reference's choices bit for bit:
+
+* criterion: Shannon entropy in base 2, ``-sum(p * log2 p)`` over the classes
+  present, float64 (reference ``mpitree/tree/decision_tree.py:37-51``);
+* split cost: ``np.dot([nL/n, nR/n], [H(yL), H(yR)])`` (``:79-86``); gain is
+  ``H(y) - min(cost)`` and the threshold is the *first* arg-min over ascending
+  candidates (``:88-91``); the feature is the *first* arg-max gain (``:140``);
+* candidates: every distinct value present in the node (``:73``), except the
+  largest one, whose right side is empty — the reference can only crash after
+  choosing it (``:150-164``), so dropping it changes no successful fit;
+* stop rules (``:118-123``): one class, all rows identical (== no feature has
+  two non-empty bins), ``depth == max_depth``, ``n < min_samples_split``.
+
+Bit-exactness strategy: costs are first evaluated vectorised, then every
+candidate within a tiny tolerance of the best is re-evaluated with the same
+scalar numpy calls the reference makes, so rounding-level ties resolve the same
+way without paying a Python loop over all candidates.
+"""
+
+from __future__ import annotations
+
+import functools
+from dataclasses import dataclass
+from fractions import Fraction
+from typing import List, Optional, Tuple
+
+import numpy as np
+
+from ..models.flat_tree import FlatTree
+
+__all__ = [
+    "exact_entropy",
+    "exact_cost",
+    "best_split",
+    "build_tree_cpu",
+    "probe_dot_mode",
+    "SplitParams",
+]
+
+_TOL = 1e-9
+
+
+@dataclass(frozen=True)
+class SplitParams:
+    max_depth: Optional[int] = None
+    min_samples_split: int = 2
+    criterion: str = "entropy"  # "entropy" (reference) or "gini" (extension)
+
+
+# --------------------------------------------------------------------------
+# float model probes (which rounding does this host's 2-element np.dot use?)
+# --------------------------------------------------------------------------
+@functools.lru_cache(maxsize=1)
+def probe_dot_mode() -> int:
+    """0: a*c + b*d, 1: fma(b, d, a*c), 2: fma(a, c, b*d) for a 2-element ``np.dot``.
+
+    The device gain kernel is told which one the host BLAS uses so that GPU and
+    reference costs round identically.
+    """
+    rng = np.random.default_rng(12345)
+    score = [0, 0, 0]
+
+    def fma(x, y, z):
+        return float(Fraction(x) * Fraction(y) + Fraction(z))
+
+    for _ in range(64):
+        a, b, c, d = (float(v) for v in rng.random(4))
+        r = float(np.dot(np.array([a, b]), np.array([c, d])))
+        score[0] += r == a * c + b * d
+        score[1] += r == fma(b, d, a * c)
+        score[2] += r == fma(a, c, b * d)
+    return int(np.argmax(score))
+
+
+# --------------------------------------------------------------------------
+# exact scalar formulas (same numpy calls as the reference)
+# --------------------------------------------------------------------------
+def exact_entropy(counts: np.ndarray) -> float:
+    """Entropy of a class-count vector, computed like ``_compute_entropy``."""
+    present = counts[counts > 0]
+    n = int(present.sum())
+    proba = present / n
+    return -np.sum(proba * np.log2(proba))
+
+
+def exact_gini(counts: np.ndarray) -> float:
+    present = counts[counts > 0]
+    n = int(present.sum())
+    proba = present / n
+    return 1.0 - np.sum(proba * proba)
+
+
+def exact_cost(left: np.ndarray, right: np.ndarray, criterion: str = "entropy") -> float:
+    """Weighted child impurity, computed like ``_compute_information_gain``."""
+    imp = exact_entropy if criterion == "entropy" else exact_gini
+    n_left, n_right = int(left.sum()), int(right.sum())
+    n = n_left + n_right
+    weights = np.array([n_left / n, n_right / n])
+    impurity = np.array([imp(left), imp(right)])
+    return np.dot(weights, impurity)
+
+
+# --------------------------------------------------------------------------
+# vectorised approximate impurity
+# --------------------------------------------------------------------------
+def _impurity_rows(counts: np.ndarray, totals: np.ndarray, criterion: str) -> np.ndarray:
+    """Impurity of each row of ``counts`` (..., C) with row sums ``totals`` (...)."""
+    safe = np.where(totals > 0, totals, 1).astype(np.float64)
+    p = counts / safe[..., None]
+    if criterion == "entropy":
+        with np.errstate(divide="ignore", invalid="ignore"):
+            t = np.where(counts > 0, p * np.log2(np.where(counts > 0, p, 1.0)), 0.0)
+        return -t.sum(axis=-1)
+    return 1.0 - (p * p).sum(axis=-1)
+
+
+def best_split(
+    hist: np.ndarray, n_bins: np.ndarray, criterion: str = "entropy"
+) -> Optional[Tuple[int, int, float, np.ndarray]]:
+    """Best ``(feature, bin, gain, left_counts)`` of one node, or ``None``.
+
+    ``hist`` is the node's (F, B, C) count histogram.  ``None`` means no feature
+    has two non-empty bins, i.e. all rows are identical -> the node is a leaf.
+    """
+    F, B, C = hist.shape
+    total = hist[0].sum(axis=0)
+    n = int(total.sum())
+    left = np.cumsum(hist, axis=1)  # (F, B, C)
+    n_left = left.sum(axis=-1)  # (F, B)
+    n_right = n - n_left
+    present = hist.sum(axis=-1) > 0
+    cand = present & (n_right > 0)
+    if not cand.any():
+        return None
+    right = total[None, None, :] - left
+    h_left = _impurity_rows(left, n_left, criterion)
+    h_right = _impurity_rows(right, n_right, criterion)
+    cost = (n_left / n) * h_left + (n_right / n) * h_right
+    cost = np.where(cand, cost, np.inf)
+    fmin = cost.min(axis=1)  # per feature
+    best_approx = fmin.min()
+    tol = _TOL * (1.0 + abs(best_approx))
+
+    imp = exact_entropy if criterion == "entropy" else exact_gini
+    h_parent = imp(total)
+    best = None  # (gain, feature, bin)
+    for f in np.flatnonzero(fmin <= best_approx + tol):
+        bins = np.flatnonzero(cost[f] <= fmin[f] + tol)
+        costs = [exact_cost(left[f, b], right[f, b], criterion) for b in bins]
+        k = int(np.argmin(costs))  # first arg-min over ascending thresholds
+        gain = h_parent - costs[k]
+        if best is None or gain > best[0]:  # strict: first arg-max over features
+            best = (gain, int(f), int(bins[k]))
+    gain, f, b = best
+    return f, b, float(gain), left[f, b].copy()
+
+
+# --------------------------------------------------------------------------
+# level-wise builder
+# --------------------------------------------------------------------------
+def _is_terminal(counts: np.ndarray, depth: int, params: SplitParams) -> bool:
+    n = int(counts.sum())
+    return bool(
+        (counts > 0).sum() <= 1
+        or (params.max_depth is not None and depth >= params.max_depth)
+        or n < params.min_samples_split
+    )
+
+
+def _level_histograms(codes, y, slot, n_slots, B, C, comm) -> np.ndarray:
+    """(n_slots, F, B, C) int64 histogram of the rows with ``slot >= 0``."""
+    F = codes.shape[1]
+    hist = np.zeros((n_slots, F, B, C), dtype=np.int64)
+    rows = np.flatnonzero(slot >= 0)
+    if rows.size:
+        base = (slot[rows].astype(np.int64) * F) * (B * C) + y[rows]
+        sub = codes[rows]
+        flat = hist.reshape(-1)
+        for f in range(F):
+            idx = base + (f * B + sub[:, f].astype(np.int64)) * C
+            flat += np.bincount(idx, minlength=flat.size)
+    if comm is not None and comm.size > 1:
+        hist = comm.allreduce_sum(hist)
+    return hist
+
+
+def build_tree_cpu(
+    codes: np.ndarray,
+    y: np.ndarray,
+    n_bins: np.ndarray,
+    n_classes: int,
+    params: SplitParams,
+    comm=None,
+    *,
+    max_level_entries: int = 1 << 24,
+    handoff_rows: int = 0,
+    pending_out: Optional[dict] = None,
+) -> FlatTree:
+    """Grow a tree level by level from this rank's row shard.
+
+    ``codes`` (n_local, F) uint8 bin codes, ``y`` (n_local,) class codes.  With
+    a communicator of size > 1 every rank ends with the identical ``FlatTree``
+    (counts are global).  Node ids are breadth-first.
+
+    With ``handoff_rows > 0`` a non-terminal child whose global row count is
+    ``<= handoff_rows`` is not expanded here: it stays a leaf of the returned
+    trunk and ``pending_out[node_id]`` receives this rank's local row indices
+    for it (phase 2 of the scheduler finishes those subtrees on owner ranks).
+    """
+    codes = np.ascontiguousarray(codes)
+    y = np.asarray(y, dtype=np.int64)
+    n_local, F = codes.shape
+    B = int(max(int(np.max(n_bins)) if len(n_bins) else 1, 1))
+    C = int(n_classes)
+
+    root_counts = np.bincount(y, minlength=C).astype(np.int64)
+    if comm is not None and comm.size > 1:
+        root_counts = comm.allreduce_sum(root_counts)
+
+    feature, bin_, left_, right_, parent, depth, counts, gain = [], [], [], [], [], [], [], []
+
+    def new_node(par: int, dep: int, cnt: np.ndarray) -> int:
+        feature.append(-1)
+        bin_.append(-1)
+        left_.append(-1)
+        right_.append(-1)
+        parent.append(par)
+        depth.append(dep)
+        counts.append(cnt)
+        gain.append(np.nan)
+        return len(feature) - 1
+
+    new_node(-1, 0, root_counts)
+    slot = np.zeros(n_local, dtype=np.int32)
+    pending_ids: List[int] = []  # node ids handed off; rows carry slot = -2 - index
+    frontier: List[int] = [] if _is_terminal(root_counts, 0, params) else [0]
+    if not frontier:
+        slot[:] = -1
+
+    per_node = max(F * B * C, 1)
+    chunk = max(1, max_level_entries // per_node)
+
+    while frontier:
+        # (node id -> decision) for this level, histogram built in bounded chunks
+        decisions = {}
+        for c0 in range(0, len(frontier), chunk):
+            ids = frontier[c0 : c0 + chunk]
+            local_slot = np.where((slot >= c0) & (slot < c0 + len(ids)), slot - c0, -1)
+            hist = _level_histograms(codes, y, local_slot, len(ids), B, C, comm)
+            for j, nid in enumerate(ids):
+                decisions[nid] = best_split(hist[j], n_bins, params.criterion)
+
+        next_frontier: List[int] = []
+        # per current slot: (feature, bin, left slot or -1, right slot or -1)
+        route_f = np.full(len(frontier), -1, dtype=np.int64)
+        route_b = np.zeros(len(frontier), dtype=np.int64)
+        route_l = np.full(len(frontier), -1, dtype=np.int32)
+        route_r = np.full(len(frontier), -1, dtype=np.int32)
+        for s, nid in enumerate(frontier):
+            dec = decisions[nid]
+            if dec is None:
+                continue  # all rows identical -> stays a leaf
+            f, b, g, left_counts = dec
+            right_counts = counts[nid] - left_counts
+            feature[nid], bin_[nid], gain[nid] = f, b, g
+            d = depth[nid] + 1
+            lid = new_node(nid, d, left_counts)
+            rid = new_node(nid, d, right_counts)
+            left_[nid], right_[nid] = lid, rid
+            route_f[s], route_b[s] = f, b
+            for cid, cnt, route in ((lid, left_counts, route_l), (rid, right_counts, route_r)):
+                if _is_terminal(cnt, d, params):
+                    continue
+                if handoff_rows and int(cnt.sum()) <= handoff_rows:
+                    route[s] = -2 - len(pending_ids)
+                    pending_ids.append(cid)
+                else:
+                    route[s] = len(next_frontier)
+                    next_frontier.append(cid)
+
+        rows = np.flatnonzero(slot >= 0)
+        if rows.size:
+            s = slot[rows]
+            f = route_f[s]
+            split = f >= 0
+            go_left = np.zeros(rows.size, dtype=bool)
+            go_left[split] = codes[rows[split], f[split]] <= route_b[s[split]]
+            new_slot = np.where(go_left, route_l[s], route_r[s])
+            new_slot[~split] = -1
+            slot[rows] = new_slot
+        frontier = next_frontier
+
+    if pending_out is not None:
+        for k, nid in enumerate(pending_ids):
+            pending_out[nid] = np.flatnonzero(slot == -2 - k)
+
+    m = len(feature)
+    return FlatTree(
+        feature=np.asarray(feature, np.int32),
+        bin=np.asarray(bin_, np.int32),
+        left=np.asarray(left_, np.int32),
+        right=np.asarray(right_, np.int32),
+        parent=np.asarray(parent, np.int32),
+        depth=np.asarray(depth, np.int32),
+        counts=np.asarray(counts, np.int64).reshape(m, C),
+        gain=np.asarray(gain, np.float64),
+        thresholds=[None] * m,
+    )

@@ -1,0 +1,116 @@
+"""Level-wise scheduler: engine selection, phase 1 (cooperative) + phase 2 (hand-off).
+
+The reference builds depth-first with Python recursion and parallelises only by
+giving subtrees to halves of the communicator
+(``mpitree/tree/decision_tree.py:93-166`` serial, ``:364-479`` parallel).  This
+scheduler is breadth-first:
+
+1. **phase 1 — cooperative levels.**  All frontier nodes of a depth are
+   processed together; every rank contributes the count histogram of its own
+   row shard and the cross-rank sum gives every rank the same split decisions.
+   On GPUs one fused kernel per level does histogram + peer reduction + gain +
+   arg-max, one kernel partitions the rows (see :mod:`mpitree_b200.ops.cuda_engine`).
+2. **phase 2 — hand-off.**  Frontier nodes whose global row count fell below
+   ``handoff_rows`` are assigned to owner ranks (sized bin-packing), their rows
+   are gathered there, owners finish those subtrees alone, and the finished
+   subtrees are exchanged as flat arrays and stitched with deterministic ids.
+"""
+
+from __future__ import annotations
+
+from typing import Optional
+
+import numpy as np
+
+from ..models.flat_tree import FlatTree
+from ..ops.cpu_engine import SplitParams, build_tree_cpu
+from .handoff import Graft, assign_owners, default_handoff_rows, stitch_subtrees
+
+__all__ = ["fit_flat_tree_host", "resolve_engine"]
+
+
+def resolve_engine(device: Optional[str], *, numeric: bool, n_classes: int, is_cuda_input: bool = False) -> str:
+    """Pick ``"cuda"`` or ``"cpu"``.  ``auto`` never silently falls back on a GPU box."""
+    device = (device or "auto").lower()
+    if device not in ("auto", "cpu", "cuda"):
+        raise ValueError("device must be 'auto', 'cpu' or 'cuda'")
+    if device == "cpu":
+        if is_cuda_input:
+            raise ValueError("device='cpu' was requested but X lives on a CUDA device")
+        return "cpu"
+    import torch
+
+    have = torch.cuda.is_available()
+    if device == "cuda" and not have:
+        raise RuntimeError("device='cuda' requested but no CUDA device is available")
+    if not have:
+        return "cpu"
+    from ..ops import cuda_engine
+
+    ok, why = cuda_engine.supports(numeric=numeric, n_classes=n_classes)
+    if not ok:
+        if device == "cuda":
+            raise RuntimeError(f"the CUDA engine cannot run this problem: {why}")
+        return "cpu"
+    return "cuda"
+
+
+def fit_flat_tree_host(
+    codes: np.ndarray,
+    y: np.ndarray,
+    n_bins: np.ndarray,
+    n_classes: int,
+    params: SplitParams,
+    comm=None,
+    *,
+    handoff_rows: Optional[int] = None,
+) -> FlatTree:
+    """Host engine entry: phase 1 + phase 2 over ``comm`` (row-sharded input)."""
+    world = 1 if comm is None else comm.size
+    if handoff_rows is None:
+        handoff_rows = default_handoff_rows(codes.shape[1], int(np.max(n_bins, initial=1)), n_classes, world)
+    if world <= 1 or handoff_rows <= 0:
+        return build_tree_cpu(codes, y, n_bins, n_classes, params, comm)
+
+    pending: dict = {}
+    trunk = build_tree_cpu(
+        codes, y, n_bins, n_classes, params, comm, handoff_rows=handoff_rows, pending_out=pending
+    )
+    node_ids = sorted(pending)
+    if not node_ids:
+        return trunk
+
+    # phase 2a: owners, decided identically on every rank from global counts
+    node_rows = [int(trunk.counts[nid].sum()) for nid in node_ids]
+    owners = assign_owners(node_rows, world)
+
+    # phase 2b: gather each pending node's rows on its owner
+    outbox = {
+        nid: (owners[k], codes[pending[nid]], y[pending[nid]])
+        for k, nid in enumerate(node_ids)
+        if len(pending[nid])
+    }
+    inbox = comm.allgather_object({nid: v for nid, v in outbox.items()})
+
+    # phase 2c: owners finish their subtrees with no communication
+    mine = []
+    for k, nid in enumerate(node_ids):
+        if owners[k] != comm.rank:
+            continue
+        parts = [box[nid] for box in inbox if nid in box]
+        sub_codes = np.concatenate([p[1] for p in parts]) if parts else codes[:0]
+        sub_y = np.concatenate([p[2] for p in parts]) if parts else y[:0]
+        depth0 = int(trunk.depth[nid])
+        sub_params = SplitParams(
+            max_depth=None if params.max_depth is None else params.max_depth - depth0,
+            min_samples_split=params.min_samples_split,
+            criterion=params.criterion,
+        )
+        sub = build_tree_cpu(sub_codes, sub_y, n_bins, n_classes, sub_params, None)
+        mine.append((nid, sub))
+
+    # phase 2d: exchange finished subtrees (flat arrays) and stitch
+    everyone = comm.allgather_object([(nid, sub.to_bytes()) for nid, sub in mine])
+    grafts = [Graft(nid, FlatTree.from_bytes(blob)) for box in everyone for nid, blob in box]
+    grafts.sort(key=lambda g: g.node_id)
+    return stitch_subtrees(trunk, grafts)

@@ -1,0 +1,458 @@
+"""Estimators: ``DecisionTreeClassifier`` and ``ParallelDecisionTreeClassifier``.
+
+Public surface and behaviour follow the reference
+(``mpitree/tree/decision_tree.py``): keyword-only ``max_depth`` /
+``min_samples_split`` (``:33-35``), ``fit`` (``:168-190`` serial, ``:340-362``
+parallel), ``predict_proba`` returning the reached leaf's raw class counts
+(``:192-227``), ``predict`` = arg-max of those counts (``:229-248``),
+``export_text`` (``:250-307``), fitted attributes ``n_features_``, ``classes_``,
+``tree_`` (``:186-189``), plus what ``BaseEstimator``/``ClassifierMixin`` give
+(``get_params``, ``set_params``, ``clone``, ``score``).
+
+What is different is everything underneath: features are binned once, trees are
+grown level by level from count histograms, on B200s by hand-written sm_100a
+kernels (:mod:`mpitree_b200.ops.cuda_engine`), on hosts by the numpy engine
+(:mod:`mpitree_b200.ops.cpu_engine`).  The parallel class shards *rows* across
+ranks (one rank per GPU) instead of replicating the data set and splitting the
+communicator by subtree.
+
+Deliberate, documented deviations from reference *defects* (outputs are
+unchanged wherever the reference succeeds; see DESIGN.md "Quirk policy"):
+
+* a split whose right side would be empty is never chosen (the reference then
+  recurses forever or raises ``IndexError``, ``:150-164``);
+* ``count`` always has ``max(label) + 1`` entries, so gappy labels predict
+  (the reference's ``predict`` raises, ``:126`` / ``:227``);
+* ``export_text`` prints string thresholds instead of raising (``:276``);
+* base-class order makes ``sklearn.base.is_classifier`` true (``:17``);
+* importing the package needs neither MPI nor a GPU (``:313`` imports mpi4py in
+  the class body).
+"""
+
+from __future__ import annotations
+
+import numbers
+from typing import Optional
+
+import numpy as np
+from sklearn.base import BaseEstimator, ClassifierMixin
+from sklearn.utils.validation import check_array, check_is_fitted, check_X_y
+
+from ..models.export import render_text
+from ..models.flat_tree import FlatTree
+from ..ops.binning import BinMapper
+from ..ops.cpu_engine import SplitParams, best_split, exact_entropy
+from ..parallel import comm as _comm
+from ..parallel.scheduler import fit_flat_tree_host, resolve_engine
+from ._base import Node
+
+__all__ = ["DecisionTreeClassifier", "ParallelDecisionTreeClassifier"]
+
+
+def _is_torch_tensor(x) -> bool:
+    return type(x).__module__.startswith("torch") and hasattr(x, "is_cuda")
+
+
+def _validate_labels(y: np.ndarray) -> np.ndarray:
+    """Labels must be non-negative integers, as ``np.bincount`` demands (``:125``)."""
+    y = np.asarray(y)
+    if y.dtype == object:
+        try:
+            as_int = y.astype(np.int64)
+        except (TypeError, ValueError):
+            raise TypeError("class labels must be non-negative integers") from None
+        if not np.array_equal(as_int, y):
+            raise TypeError("class labels must be non-negative integers")
+        y = as_int
+    if y.dtype == bool:
+        y = y.astype(np.int64)
+    if not np.issubdtype(y.dtype, np.integer):
+        raise TypeError(
+            f"Cannot cast array data from dtype('{y.dtype}') to dtype('int64') according to the rule 'safe'"
+        )
+    if y.size and y.min() < 0:
+        raise ValueError("'list' argument must have no negative elements")
+    return y.astype(np.int64, copy=False)
+
+
+def _as_feature_matrix(X: np.ndarray) -> np.ndarray:
+    """Keep numeric dtypes numeric; leave genuine object/string columns as objects."""
+    if X.dtype.kind in "US":
+        return X.astype(object)
+    if X.dtype == object:
+        try:
+            return X.astype(np.float64)
+        except (TypeError, ValueError):
+            return X
+    return X
+
+
+class DecisionTreeClassifier(ClassifierMixin, BaseEstimator):
+    """Exact-candidate / histogram decision tree classifier (entropy criterion).
+
+    Parameters
+    ----------
+    max_depth : int, optional
+        Maximum depth; ``None`` grows until every leaf is pure, constant or
+        smaller than ``min_samples_split``.
+    min_samples_split : int, default=2
+        A node with fewer rows is not split.
+    criterion : {"entropy", "gini"}, default="entropy"
+        ``"entropy"`` is the reference's criterion; ``"gini"`` is an extension.
+    max_bins : int, default=256
+        Features with at most this many distinct values are searched exactly
+        (every distinct value is a candidate, like the reference); others are
+        quantile-binned.
+    device : {"auto", "cpu", "cuda"}, default="auto"
+        ``auto`` uses the CUDA engine whenever a GPU is present.
+    """
+
+    def __init__(
+        self,
+        *,
+        max_depth: Optional[int] = None,
+        min_samples_split: int = 2,
+        criterion: str = "entropy",
+        max_bins: int = 256,
+        device: str = "auto",
+    ):
+        self.max_depth = max_depth
+        self.min_samples_split = min_samples_split
+        self.criterion = criterion
+        self.max_bins = max_bins
+        self.device = device
+
+    # ------------------------------------------------------------------ util
+    def _params(self, depth_offset: int = 0) -> SplitParams:
+        if self.criterion not in ("entropy", "gini"):
+            raise ValueError("criterion must be 'entropy' or 'gini'")
+        md = self.max_depth
+        if md is not None:
+            if not isinstance(md, numbers.Integral) or md < 0:
+                raise ValueError("max_depth must be a non-negative integer or None")
+            md = max(int(md) - depth_offset, 0)
+        return SplitParams(max_depth=md, min_samples_split=int(self.min_samples_split), criterion=self.criterion)
+
+    def _communicator(self):
+        return None
+
+    def _shard(self, X, y, comm):
+        return X, y
+
+    # --------------------------------------------------- reference internals
+    def _compute_entropy(self, x):
+        """Shannon entropy (base 2) of a label array (reference ``:37-51``)."""
+        x = np.asarray(x)
+        if x.size == 0:
+            return -0.0
+        _, counts = np.unique(x, return_counts=True)
+        return exact_entropy(counts)
+
+    def _compute_information_gain(self, X, y, feature_idx):
+        """``(gain, threshold)`` of the best split on one feature (reference ``:53-91``).
+
+        The reference also admits the column maximum as a candidate (gain 0, empty
+        right side); it is returned only when the column is constant.
+        """
+        X = np.asarray(X)
+        y = _validate_labels(np.asarray(y))
+        col = _as_feature_matrix(X[:, [feature_idx]])
+        mapper = BinMapper.fit(col, max_bins=256)
+        codes = mapper.transform(col)[:, 0]
+        classes, y_codes = np.unique(y, return_inverse=True)
+        B, C = int(mapper.n_bins[0]), len(classes)
+        hist = np.zeros((1, B, C), dtype=np.int64)
+        np.add.at(hist[0], (codes, y_codes), 1)
+        res = best_split(hist, mapper.n_bins, self.criterion)
+        if res is None:
+            return 0.0, mapper.threshold_of(0, B - 1)
+        _, b, gain, _ = res
+        return max(gain, 0.0) if gain < 0 else gain, mapper.threshold_of(0, b)
+
+    def _make_tree(self, X, y, *, parent=None, depth=0):
+        """Build the subtree for ``(X, y)`` and return its root ``Node`` (reference ``:93-166``)."""
+        flat = self._fit_flat(np.asarray(X), np.asarray(y), depth_offset=depth, comm=None, local=True)
+        root = flat.to_nodes()
+        if parent is not None or depth:
+            _reparent(root, parent, depth)
+        return root
+
+    # ------------------------------------------------------------------- fit
+    def _fit_flat(self, X, y, *, depth_offset=0, comm=None, local=False) -> FlatTree:
+        y = _validate_labels(y)
+        X = _as_feature_matrix(X)
+        classes = self.classes_ if hasattr(self, "classes_") else np.unique(y)
+        # class code = index into classes_
+        y_codes = np.searchsorted(classes, y)
+        numeric = X.dtype != object
+        engine = resolve_engine(self.device, numeric=numeric, n_classes=len(classes))
+        params = self._params(depth_offset)
+
+        if engine == "cuda":
+            from ..ops import cuda_engine
+
+            flat, mapper = cuda_engine.fit_from_host(
+                X, y_codes, len(classes), params, max_bins=self.max_bins, comm=comm
+            )
+        else:
+            summaries = None
+            if comm is not None and comm.size > 1:
+                mine = BinMapper.local_summary(X)
+                summaries = [s for r, s in enumerate(comm.allgather_object(mine)) if r != comm.rank]
+            mapper = BinMapper.fit(X, max_bins=self.max_bins, summaries=summaries)
+            codes = mapper.transform(X)
+            flat = fit_flat_tree_host(
+                codes,
+                y_codes,
+                mapper.n_bins,
+                len(classes),
+                params,
+                comm,
+                handoff_rows=getattr(self, "handoff_rows", None),
+            )
+        flat.class_labels = np.asarray(classes, dtype=np.int64)
+        flat.thresholds = [
+            None if flat.feature[i] < 0 else mapper.threshold_of(int(flat.feature[i]), int(flat.bin[i]))
+            for i in range(flat.n_nodes)
+        ]
+        if not local:
+            self.bin_mapper_ = mapper
+            self.engine_ = engine
+        return flat
+
+    def fit(self, X, y):
+        """Train the classifier on ``X`` (n_samples, n_features) and integer labels ``y``."""
+        comm = self._communicator()
+        if _is_torch_tensor(X):
+            return self._fit_torch(X, y, comm)
+        X, y = check_X_y(X, y, dtype=None, ensure_all_finite=True)
+        y = _validate_labels(y)
+        self.n_features_ = X.shape[1]
+        self.n_features_in_ = X.shape[1]
+        self.classes_ = np.unique(y)
+        X, y = self._shard(X, y, comm)
+        self.flat_tree_ = self._fit_flat(X, y, comm=comm)
+        self.tree_ = self.flat_tree_.to_nodes()
+        return self
+
+    def _fit_torch(self, X, y, comm):
+        """``fit`` for torch tensors (host-pinned or CUDA): no numpy round trip."""
+        from ..ops import cuda_engine
+
+        if X.dim() != 2:
+            raise ValueError("X must be 2-dimensional")
+        resolve_engine(
+            "cuda" if self.device == "auto" else self.device,
+            numeric=True,
+            n_classes=2,
+            is_cuda_input=bool(X.is_cuda),
+        )
+        flat, mapper, classes = cuda_engine.fit_from_torch(
+            X, y, self._params(), max_bins=self.max_bins, comm=comm,
+            replicated=getattr(self, "data_layout", "sharded") == "replicated",
+        )
+        self.n_features_ = int(X.shape[1])
+        self.n_features_in_ = int(X.shape[1])
+        self.classes_ = classes
+        flat.class_labels = np.asarray(classes, dtype=np.int64)
+        flat.thresholds = [
+            None if flat.feature[i] < 0 else mapper.threshold_of(int(flat.feature[i]), int(flat.bin[i]))
+            for i in range(flat.n_nodes)
+        ]
+        self.bin_mapper_ = mapper
+        self.engine_ = "cuda"
+        self.flat_tree_ = flat
+        self.tree_ = flat.to_nodes()
+        return self
+
+    # --------------------------------------------------------------- predict
+    def _leaf_ids(self, X) -> np.ndarray:
+        flat = self._flat()
+        if _is_torch_tensor(X):
+            from ..ops import cuda_engine
+
+            return cuda_engine.predict_leaf_ids(flat, X)
+        X = _as_feature_matrix(check_array(X, dtype=None, ensure_all_finite=True))
+        if X.dtype != object and getattr(self, "engine_", "cpu") == "cuda" and self.device != "cpu":
+            from ..ops import cuda_engine
+
+            if cuda_engine.available():
+                return cuda_engine.predict_leaf_ids(flat, X)
+        return flat.apply_raw(X)
+
+    def _flat(self) -> FlatTree:
+        check_is_fitted(self, "tree_")
+        flat = getattr(self, "flat_tree_", None)
+        if flat is None:  # e.g. tree_ assigned by hand or unpickled from an older object
+            flat = FlatTree.from_nodes(self.tree_)
+            self.flat_tree_ = flat
+        return flat
+
+    def apply(self, X) -> np.ndarray:
+        """Index (breadth-first node id) of the leaf each row ends in."""
+        ids = self._leaf_ids(X)
+        return ids.cpu().numpy() if _is_torch_tensor(ids) else ids
+
+    def predict_proba(self, X):
+        """Raw per-class training counts of the leaf each row reaches (int64).
+
+        Like the reference these are counts, not normalised probabilities.
+        """
+        ids = self._leaf_ids(X)
+        counts = self._flat().expanded_counts()
+        if _is_torch_tensor(ids):
+            import torch
+
+            return torch.as_tensor(counts, device=ids.device)[ids]
+        return counts[ids]
+
+    def predict(self, X):
+        """Predicted class label per row (arg-max of the leaf counts, ties -> lowest label)."""
+        ids = self._leaf_ids(X)
+        labels = self._flat().expanded_counts().argmax(axis=1)
+        if _is_torch_tensor(ids):
+            import torch
+
+            return torch.as_tensor(labels, device=ids.device)[ids]
+        return labels[ids]
+
+    # ---------------------------------------------------------------- export
+    def export_text(self, *, feature_names=None, class_names=None, precision=2):
+        """Text rendering of the fitted tree (grammar in :mod:`mpitree_b200.models.export`)."""
+        check_is_fitted(self, "tree_")
+        return render_text(
+            self.tree_, feature_names=feature_names, class_names=class_names, precision=precision
+        )
+
+    # ------------------------------------------------------------ inspection
+    def get_depth(self) -> int:
+        return self._flat().max_depth
+
+    def get_n_leaves(self) -> int:
+        return self._flat().n_leaves
+
+    def __sklearn_tags__(self):
+        tags = super().__sklearn_tags__()
+        tags.input_tags.string = True
+        return tags
+
+
+def _reparent(root: Node, parent: Optional[Node], depth: int) -> None:
+    root.parent = parent
+    base = parent.depth + 1 if parent is not None else depth
+    for n in root.iter_preorder():
+        n.depth = base if n is root else n.parent.depth + 1
+
+
+class _WorldAttr:
+    """Class attribute resolved lazily from the live process group.
+
+    The reference evaluates ``MPI.COMM_WORLD`` in the class body, i.e. at import
+    time (``:313-317``); resolving on access keeps ``clf.WORLD_RANK`` working in
+    user scripts without making ``import`` depend on a launcher.
+    """
+
+    def __init__(self, what: str):
+        self.what = what
+
+    def __get__(self, obj, owner):
+        w = _comm.world()
+        return {"comm": w, "rank": w.rank, "size": w.size}[self.what]
+
+
+class ParallelDecisionTreeClassifier(DecisionTreeClassifier):
+    """Multi-rank decision tree classifier (one rank per GPU, rows sharded).
+
+    Run the same script on every rank (``torchrun --nproc-per-node N``).  All
+    ranks end ``fit`` holding the identical tree, as in the reference.
+
+    Parameters (in addition to :class:`DecisionTreeClassifier`)
+    ----------
+    data_layout : {"replicated", "sharded"}, default="replicated"
+        ``replicated``: every rank passes the full ``(X, y)`` like the reference
+        (``:356-361``) and a row shard is taken internally.  ``sharded``: every
+        rank passes only its own rows.
+    handoff_rows : int, optional
+        Global row count below which a subtree is handed to a single owner rank
+        (``None`` = automatic, ``0`` = never).
+    comm : communicator, optional
+        Defaults to the world group at ``fit`` time.
+    """
+
+    WORLD_COMM = _WorldAttr("comm")
+    WORLD_RANK = _WorldAttr("rank")
+    WORLD_SIZE = _WorldAttr("size")
+
+    def __init__(
+        self,
+        *,
+        max_depth: Optional[int] = None,
+        min_samples_split: int = 2,
+        criterion: str = "entropy",
+        max_bins: int = 256,
+        device: str = "auto",
+        data_layout: str = "replicated",
+        handoff_rows: Optional[int] = None,
+        comm=None,
+    ):
+        super().__init__(
+            max_depth=max_depth,
+            min_samples_split=min_samples_split,
+            criterion=criterion,
+            max_bins=max_bins,
+            device=device,
+        )
+        self.data_layout = data_layout
+        self.handoff_rows = handoff_rows
+        self.comm = comm
+
+    def _communicator(self):
+        return self.comm if self.comm is not None else _comm.world()
+
+    def _get_cyclic_dist(self, comm=None, *, n_blocks: int = 1):
+        """Round-robin communicator split (reference ``:319-338``): colour = ``rank % n_blocks``."""
+        comm = comm if comm is not None else self._communicator()
+        key, color = divmod(comm.rank, n_blocks)
+        return comm.split(color, key)
+
+    def _shard(self, X, y, comm):
+        if self.data_layout not in ("replicated", "sharded"):
+            raise ValueError("data_layout must be 'replicated' or 'sharded'")
+        if self.data_layout == "sharded" or comm is None or comm.size <= 1:
+            return X, y
+        n = X.shape[0]
+        lo = (n * comm.rank) // comm.size
+        hi = (n * (comm.rank + 1)) // comm.size
+        return X[lo:hi], y[lo:hi]
+
+    def fit(self, X, y):
+        """Train on all ranks; see :class:`ParallelDecisionTreeClassifier` for data layouts."""
+        comm = self._communicator()
+        if self.data_layout == "sharded" and comm.size > 1 and not _is_torch_tensor(X):
+            # classes must be agreed on globally before encoding labels
+            X, y = check_X_y(X, y, dtype=None, ensure_all_finite=True)
+            y = _validate_labels(y)
+            parts = comm.allgather_object(np.unique(y))
+            self.n_features_ = X.shape[1]
+            self.n_features_in_ = X.shape[1]
+            self.classes_ = np.unique(np.concatenate(parts))
+            self.flat_tree_ = self._fit_flat(X, y, comm=comm)
+            self.tree_ = self.flat_tree_.to_nodes()
+            return self
+        return super().fit(X, y)
+
+    def _make_tree(self, X, y, *, parent=None, depth=0, comm=None):
+        """Subtree for ``(X, y)`` built cooperatively over ``comm`` (reference ``:364-479``)."""
+        comm = comm if comm is not None else self._communicator()
+        Xs, ys = self._shard(np.asarray(X), np.asarray(y), comm)
+        flat = self._fit_flat(Xs, ys, depth_offset=depth, comm=comm, local=True)
+        root = flat.to_nodes()
+        if parent is not None or depth:
+            _reparent(root, parent, depth)
+        return root
+
+    def __getstate__(self):
+        state = super().__getstate__()
+        state = dict(state)
+        state["comm"] = None  # communicators are process-local
+        return state

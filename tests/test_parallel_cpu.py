@@ -1,0 +1,140 @@
+"""Multi-rank host logic on CPU: thread-ranks and real gloo processes (world_size 2..5)."""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+from mpitree_b200.parallel.comm import ThreadComm, run_threaded
+from mpitree_b200.parallel.handoff import Graft, assign_owners, halving_groups, stitch_subtrees
+from mpitree_b200.tree import DecisionTreeClassifier, ParallelDecisionTreeClassifier
+
+from .goldens import IRIS2_DEPTH3
+
+
+def _fit_rank(comm, X, y, kw):
+    clf = ParallelDecisionTreeClassifier(comm=comm, device="cpu", **kw).fit(X, y)
+    return clf.export_text(), clf.predict(X).tolist()
+
+
+@pytest.mark.parametrize("world", [1, 2, 3, 4, 5, 8])
+def test_parallel_equals_serial_replicated(iris, world):
+    X, y = iris.data, iris.target
+    want = DecisionTreeClassifier(max_depth=3, device="cpu").fit(X, y)
+    out = run_threaded(world, _fit_rank, X, y, dict(max_depth=3, handoff_rows=0))
+    for text, pred in out:
+        assert text == want.export_text()
+        assert pred == want.predict(X).tolist()
+
+
+def test_parallel_golden_four_ranks(iris):
+    # the notebook's 4-rank run (experiments.ipynb:58-70)
+    X, y = iris.data[:, :2], iris.target
+
+    def run(comm):
+        clf = ParallelDecisionTreeClassifier(max_depth=3, comm=comm, device="cpu").fit(X, y)
+        return clf.export_text(feature_names=iris.feature_names, class_names=iris.target_names)
+
+    assert run_threaded(4, run) == [IRIS2_DEPTH3] * 4
+
+
+@pytest.mark.parametrize("world", [2, 3, 4])
+@pytest.mark.parametrize("handoff", [10, 60, 1000])
+def test_handoff_gives_identical_tree(iris, world, handoff):
+    X, y = iris.data, iris.target
+    want = DecisionTreeClassifier(device="cpu").fit(X, y).export_text()
+    out = run_threaded(world, _fit_rank, X, y, dict(handoff_rows=handoff))
+    assert [t for t, _ in out] == [want] * world
+
+
+def test_sharded_layout_with_disjoint_values():
+    rng = np.random.default_rng(3)
+    X = rng.integers(0, 50, size=(400, 5)).astype(float)
+    y = (X[:, 0] + X[:, 3] > 50).astype(int)
+    want = DecisionTreeClassifier(max_depth=5, device="cpu").fit(X, y).export_text()
+
+    def run(comm):
+        lo, hi = 400 * comm.rank // comm.size, 400 * (comm.rank + 1) // comm.size
+        clf = ParallelDecisionTreeClassifier(max_depth=5, comm=comm, device="cpu", data_layout="sharded")
+        return clf.fit(X[lo:hi], y[lo:hi]).export_text()
+
+    assert run_threaded(3, run) == [want] * 3
+
+
+def test_rank_failure_propagates_instead_of_deadlocking():
+    def run(comm):
+        if comm.rank == 1:
+            raise RuntimeError("boom")
+        comm.barrier()
+
+    with pytest.raises(RuntimeError, match="boom"):
+        run_threaded(3, run)
+
+
+def test_comm_split_parity():
+    def run(comm):
+        sub = comm.split(comm.rank % 2, comm.rank // 2)
+        return sub.rank, sub.size, sub.allgather_object(comm.rank)
+
+    out = run_threaded(5, run)
+    assert out[0] == (0, 3, [0, 2, 4]) and out[3] == (1, 2, [1, 3]) and out[4] == (2, 3, [0, 2, 4])
+    assert halving_groups([0, 1, 2, 3, 4]) == ([0, 2, 4], [1, 3])
+
+
+def test_assign_owners_is_balanced_and_deterministic():
+    rows = [100, 90, 50, 40, 30, 5]
+    owners = assign_owners(rows, 3)
+    assert owners == assign_owners(rows, 3)
+    load = [sum(r for r, o in zip(rows, owners) if o == k) for k in range(3)]
+    assert max(load) - min(load) <= 30  # LPT bound: within the largest small item
+
+
+def test_stitch_renumbers_breadth_first(iris):
+    X, y = iris.data, iris.target
+    full = DecisionTreeClassifier(device="cpu").fit(X, y).flat_tree_
+    trunk = DecisionTreeClassifier(max_depth=1, device="cpu").fit(X, y).flat_tree_
+    right_rows = X[:, int(trunk.feature[0])] > trunk.thresholds[0]
+    sub = DecisionTreeClassifier(device="cpu").fit(X[right_rows], y[right_rows]).flat_tree_
+    # subtree saw only classes {1,2}: widen counts to the trunk's class space
+    wide = np.zeros((sub.n_nodes, 3), dtype=np.int64)
+    wide[:, 1:] = sub.counts
+    sub.counts = wide
+    merged = stitch_subtrees(trunk, [Graft(int(trunk.right[0]), sub)])
+    assert merged.structurally_equal(full)
+
+
+_WORKER = r"""
+import os, sys
+sys.path.insert(0, os.environ["REPO"])
+import numpy as np, torch.distributed as dist
+from sklearn.datasets import load_iris
+from mpitree_b200.parallel.comm import init_process_group_from_env
+from mpitree_b200.tree import ParallelDecisionTreeClassifier, DecisionTreeClassifier
+assert init_process_group_from_env("gloo")
+iris = load_iris()
+clf = ParallelDecisionTreeClassifier(max_depth=3, device="cpu").fit(iris.data, iris.target)
+assert clf.WORLD_SIZE == 2 and clf.WORLD_RANK == dist.get_rank()
+want = DecisionTreeClassifier(max_depth=3, device="cpu").fit(iris.data, iris.target).export_text()
+assert clf.export_text() == want, clf.export_text()
+deep = ParallelDecisionTreeClassifier(device="cpu", handoff_rows=60).fit(iris.data, iris.target)
+assert deep.export_text() == DecisionTreeClassifier(device="cpu").fit(iris.data, iris.target).export_text()
+sub = clf._get_cyclic_dist(clf.WORLD_COMM, n_blocks=2)
+assert sub.size == 1
+if dist.get_rank() == 0:
+    print("GLOO_OK", clf.score(iris.data, iris.target))
+dist.destroy_process_group()
+"""
+
+
+def test_two_process_gloo_torchrun(tmp_path):
+    """The BASELINE.json plumbing config: iris, entropy, max_depth=3, 2 ranks on CPU."""
+    import subprocess
+
+    script = tmp_path / "worker.py"
+    script.write_text(_WORKER)
+    env = dict(os.environ, REPO=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+           "--master-addr", "127.0.0.1", "--master-port", "29613", str(script)]
+    res = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=300)
+    assert res.returncode == 0, res.stdout + res.stderr
+    assert "GLOO_OK 0.97" in res.stdout
