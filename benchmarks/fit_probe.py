@@ -1,0 +1,58 @@
+"""Time one device-resident fit with a per-level breakdown (development probe, 1 GPU)."""
+import argparse
+import json
+import time
+
+import numpy as np
+import torch
+
+from mpitree_b200.ops import cuda_engine
+from mpitree_b200.ops.binning import BinMapper
+from mpitree_b200.ops.cpu_engine import SplitParams
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--rows", type=int, default=10_000_000)
+    ap.add_argument("--features", type=int, default=64)
+    ap.add_argument("--classes", type=int, default=10)
+    ap.add_argument("--depth", type=int, default=10)
+    ap.add_argument("--reps", type=int, default=3)
+    ap.add_argument("--unfused", action="store_true")
+    ap.add_argument("--informative", type=int, default=8)
+    a = ap.parse_args()
+    dev = torch.device("cuda")
+    g = torch.Generator(device=dev).manual_seed(0)
+    X = torch.randint(0, 256, (a.rows, a.features), dtype=torch.uint8, device=dev, generator=g)
+    w = torch.randn(a.informative, device=dev, generator=g)
+    score = (X[:, : a.informative].float() - 127.5) @ w + 40 * torch.randn(a.rows, device=dev, generator=g)
+    qs = torch.quantile(score[:1_000_000], torch.linspace(0, 1, a.classes + 1, device=dev)[1:-1])
+    y = torch.bucketize(score, qs).to(torch.uint8)
+    del score
+    params = SplitParams(max_depth=a.depth)
+    data = cuda_engine.DeviceDataset.allocate(a.rows, a.features, a.classes, dev)
+    out = []
+    for rep in range(a.reps):
+        data.cur = 0
+        data.encode_u8(X)
+        data.set_labels(y)
+        torch.cuda.synchronize()
+        b = cuda_engine.TreeBuilder(data, 256, params, fused=not a.unfused, profile=True)
+        t0 = time.perf_counter()
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record()
+        flat = b.build()
+        e.record()
+        torch.cuda.synchronize()
+        ms = s.elapsed_time(e)
+        out.append(ms)
+        print(f"rep {rep}: {ms:.2f} ms ({a.rows / ms / 1e3:.1f} M rows/s) nodes={flat.n_nodes} wall={time.perf_counter() - t0:.3f}s")
+    st = b.stats
+    print(json.dumps({"FT": st.FT, "stages": st.stages, "smem": st.smem_bytes, "m_cap": st.m_cap,
+                      "hist_MB": st.hist_bytes / 2**20, "launches": st.launches}))
+    for lv, d in enumerate(st.level_ms):
+        print(f"  level {lv:2d} slots={d['slots']:5d} search={d['search_ms']:8.3f} ms partition={d['partition_ms']:8.3f} ms")
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,149 @@
+/*
+ * mpitree_b200 native library — C ABI (libmpitree_b200.so, sm_100a only).
+ *
+ * Every entry point is `extern "C"`, takes raw device pointers and a CUDA stream
+ * (as void*), launches asynchronously on that stream and returns 0 on success or
+ * a negative error code (text via mtb_last_error()).  Nothing here allocates device
+ * memory unless its comment says so: buffers are owned by the caller (the Python
+ * layer allocates them as torch tensors).
+ *
+ * Reference hot paths these kernels replace (paths relative to the reference repo):
+ *   K1 encode      np.unique candidate discovery      mpitree/tree/decision_tree.py:73
+ *   K2 split search feature loop :133-138, threshold loop :76-86, entropy :49-51,
+ *                   argmin/argmax :88-91 / :140-141
+ *   K3 partition    boolean-mask copies               :150-164
+ *   K4 predict      walk + apply_along_axis + argmax  :208-227, :248
+ *   K5 all-reduce   (no counterpart; replaces the role of mpi4py collectives, :456)
+ *   K6 hand-off     parity split + subtree allgather  :447-466
+ */
+#ifndef MPITREE_B200_H
+#define MPITREE_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MTB_GROUP 16        /* features per 128-bit code chunk              */
+#define MTB_MAX_BINS 256    /* bin codes are one byte                       */
+#define MTB_MAX_CLASSES 128 /* CUDA engine limit (smem tile = B*C*4 bytes)  */
+#define MTB_MAX_WORLD 16
+
+/* slot modes */
+#define MTB_MODE_NONE 0
+#define MTB_MODE_BUILD 1
+#define MTB_MODE_DERIVE 2
+
+/*
+ * Build context.  Plain struct of 64-bit fields so that ctypes / any FFI can fill
+ * it without worrying about padding.  Pointers are device pointers unless noted.
+ */
+typedef struct MtbCtx {
+  /* ---- problem shape ---- */
+  int64_t n_cap;    /* rows per feature-group plane (allocation stride)        */
+  int64_t n_local;  /* rows of this rank's shard                               */
+  int64_t F;        /* real features                                           */
+  int64_t G;        /* feature groups = ceil(F/16)                             */
+  int64_t B;        /* bin stride (multiple of 32, <= 256)                     */
+  int64_t C;        /* classes                                                 */
+  int64_t FT;       /* features per shared-memory histogram tile (1,2,4,8,16)  */
+  int64_t max_depth;          /* -1 = unlimited                                */
+  int64_t min_samples_split;
+  int64_t criterion;          /* 0 entropy, 1 gini                             */
+  int64_t dot_mode;           /* host np.dot rounding model, see cpu_engine    */
+  int64_t world, rank;
+  int64_t m_cap;              /* frontier slot capacity                        */
+  int64_t node_cap;           /* tree node capacity                            */
+  /* ---- row data, ping-pong: [G][n_cap][16] codes, [n_cap] labels ---- */
+  int64_t codes[2];
+  int64_t labels[2];
+  int64_t cur;                /* which ping-pong side holds the current level  */
+  /* ---- histograms, ping-pong by level: [m_cap][G*16][B][C] u32 ---- */
+  int64_t hist[2];
+  int64_t hcur;               /* side holding the current level's histograms   */
+  /* ---- frontier (current level, SoA length m_cap) ---- */
+  int64_t slot_node, slot_begin, slot_end, slot_mode, slot_parent, slot_sibling;
+  /* ---- frontier being produced for the next level ---- */
+  int64_t nslot_node, nslot_begin, nslot_end, nslot_mode, nslot_parent, nslot_sibling;
+  int64_t nslot_src;          /* i32: parent slot * 2 + side (0 left, 1 right)   */
+  int64_t n_slots_host;       /* host's copy of the current slot count (launch sizing) */
+  /* ---- per (slot, feature) results of the gain phase ---- */
+  int64_t fb_cost;   /* f64 [m_cap][F]   min cost (inf if no candidate)        */
+  int64_t fb_bin;    /* i32 [m_cap][F]                                         */
+  int64_t fb_left;   /* u32 [m_cap][F][C] left class counts at the best bin    */
+  int64_t node_cnt;  /* u32 [m_cap][C]   class counts of the slot's node       */
+  /* ---- per slot decisions ---- */
+  int64_t rec_feature, rec_bin;  /* i32 [m_cap]                                 */
+  int64_t part_flags;            /* i32 [m_cap] bit0: keep left, bit1: keep right */
+  int64_t cursors;               /* u32 [m_cap][2] rows written left / right    */
+  /* ---- tree (SoA length node_cap) ---- */
+  int64_t t_feature, t_bin, t_left, t_parent, t_depth; /* i32 */
+  int64_t t_gain;                /* f64 */
+  int64_t t_counts;              /* u32 [node_cap][C] */
+  /* ---- device scalars: i32[8] = {n_slots, n_next, n_nodes, units_hist, units_part, overflow, 0, 0} ---- */
+  int64_t scalars;
+  int64_t unit_prefix;           /* i32 [m_cap+1] scratch for work decomposition */
+  int64_t depth;                 /* depth of the current level                  */
+  /* ---- multi-GPU (filled by the comm runtime; zero when world == 1) ---- */
+  int64_t peer_hist[MTB_MAX_WORLD];   /* peers' staging buffers (mapped)        */
+  int64_t peer_rec[MTB_MAX_WORLD];    /* peers' record mailboxes (mapped)       */
+  int64_t peer_flags[MTB_MAX_WORLD];  /* peers' barrier flags (mapped)          */
+  int64_t epoch;                      /* barrier epoch, advanced by the host    */
+  int64_t reserved[8];
+} MtbCtx;
+
+const char* mtb_last_error(void);
+int mtb_version(void);
+int mtb_sm_count(int device);
+/* Make `device` current for this library's (statically linked) CUDA runtime. */
+int mtb_set_device(int device);
+
+/* ---- K1: encode raw rows into tiled bin codes ------------------------------------ */
+/* X: [n][ldx] row-major (device or mapped pinned host); edges: f64 [F][256] padded with
+ * +inf; writes codes[g][row0 + i][k] and (optionally) counts values that match no edge
+ * exactly into *mismatch (u64, may be NULL).  dtype: 0 = f32, 1 = f64.                */
+int mtb_encode_float(const void* X, int dtype, int64_t n, int64_t F, int64_t ldx, const double* edges,
+                     const int32_t* n_bins, uint8_t* codes, int64_t n_cap, int64_t row0,
+                     unsigned long long* mismatch, void* stream);
+/* uint8 input; lut: u8 [F][256] value->code, or NULL for identity.                    */
+int mtb_encode_u8(const uint8_t* X, int64_t n, int64_t F, int64_t ldx, const uint8_t* lut, uint8_t* codes,
+                  int64_t n_cap, int64_t row0, void* stream);
+
+/* ---- K2/K3: level-wise tree build (separate phases) ------------------------------- */
+int mtb_level_plan(const MtbCtx* ctx, void* stream);      /* work decomposition + zero cursors       */
+int mtb_level_hist(const MtbCtx* ctx, void* stream);      /* TMA-fed shared-memory histograms        */
+int mtb_level_gain(const MtbCtx* ctx, void* stream);      /* derive siblings, prefix, gain, arg-min  */
+int mtb_level_finalize(const MtbCtx* ctx, void* stream);  /* arg-max, children, next frontier        */
+int mtb_level_partition(const MtbCtx* ctx, void* stream); /* stream compaction into the other side   */
+int mtb_level_commit(const MtbCtx* ctx, void* stream);    /* next frontier's row segments            */
+/* One cooperative launch doing plan + hist + (peer reduction) + gain + finalize.      */
+int mtb_level_fused(const MtbCtx* ctx, void* stream);
+/* Shared memory / launch geometry the hist phase will use for this ctx (for reports). */
+int mtb_hist_config(const MtbCtx* ctx, int* threads, int* smem_bytes, int* stages, int* rows_per_stage);
+
+/* ---- K4: batched predict ----------------------------------------------------------- */
+/* Pack {feature, left child, leaf label} into 16-byte node records (packed_out: n_nodes*16 B). */
+int mtb_pack_nodes(const int32_t* feature, const int32_t* left, const int32_t* leaf_label, int64_t n_nodes,
+                   void* packed_out, void* stream);
+/* dtype: 0 f32 X / f32 thresholds, 1 u8 X / i32 bin thresholds, 2 f64 X / f64 thresholds.
+ * X [n][ldx]; out_leaf / out_label are i32 [n] and either may be NULL.                  */
+int mtb_predict(const void* X, int dtype, int64_t n, int64_t F, int64_t ldx, const void* packed_nodes,
+                const void* threshold, int64_t n_nodes, int32_t* out_leaf, int32_t* out_label, void* stream);
+
+/* ---- K5 / comm runtime -------------------------------------------------------------- */
+int mtb_ipc_handle_size(void);
+int mtb_ipc_get_handle(void* dev_ptr, void* handle_out);          /* cudaIpcGetMemHandle   */
+int mtb_ipc_open_handle(const void* handle, void** dev_ptr_out);  /* cudaIpcOpenMemHandle  */
+int mtb_ipc_close(void* dev_ptr);
+int mtb_enable_peer_access(int peer_device);
+/* u32 sum all-reduce over peer-mapped buffers.  bufs[r] = rank r's symmetric buffer
+ * (count u32 in, count u32 scratch after it), flags[r] = rank r's flag words.
+ * algo: 0 one-shot, 1 two-shot.  All ranks must call with the same epoch.              */
+int mtb_allreduce_u32(int algo, int rank, int world, void* const* bufs, void* const* flags, int64_t count,
+                      uint32_t epoch, uint32_t* out, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MPITREE_B200_H */

@@ -1,0 +1,807 @@
+// K2 (split search) + K3 (row partition) — level-wise tree construction on sm_100a.
+//
+// Replaces the reference's per-node Python loops (mpitree/tree/decision_tree.py):
+// feature loop :133-138, threshold loop :76-86, entropy :49-51, arg-min/arg-max
+// :88-91 / :140-141, node counts :146, mask-and-copy partition :150-164.
+//
+// Data layout (chosen for 128-bit loads and TMA bulk tiles):
+//   codes  [G][n_cap][16] u8   feature-group planes, rows of a node are contiguous
+//   labels [n_cap] u8
+//   hist   [slot][G*16][B][C] u32, one slab per frontier slot, ping-pong by level
+//
+// Phases of one level (each also callable on its own; mtb_level_fused runs
+// plan+hist+gain+finalize in a single cooperative launch):
+//   plan      work decomposition (prefix over slots), cursor reset
+//   hist      persistent CTAs; a producer warp streams 1024-row x 16-byte tiles with
+//             cp.async.bulk (TMA) through an mbarrier ring; 16 consumer warps do
+//             shared-memory atomic increments into an [FT][B][C] tile; tiles are
+//             flushed with red.global.add (to the owner GPU's slab when world > 1)
+//   gain      one warp per (slot, feature): sibling = parent - built child,
+//             prefix over bins, float64 entropy cost with the reference's rounding,
+//             first arg-min
+//   finalize  per slot first arg-max over features, stop rules, child creation with
+//             deterministic breadth-first ids, next frontier
+//   partition unstable two-sided stream compaction of a node's rows into the other
+//             ping-pong side (left rows grow up from the segment start, right rows
+//             grow down from its end)
+//   commit    row segments of the next frontier from the partition cursors
+#include <cooperative_groups.h>
+
+#include "common.cuh"
+#include "impurity.cuh"
+
+namespace cg = cooperative_groups;
+using namespace mtb;
+
+namespace {
+
+constexpr int kRows = 1024;            // rows per TMA stage
+constexpr int kStageBytes = kRows * 16;
+constexpr int kConsumerWarps = 16;
+constexpr int kConsumers = kConsumerWarps * 32;
+constexpr int kHistThreads = kConsumers + 32;  // + producer warp
+constexpr int kMaxStages = 8;
+constexpr int kSmemBudget = 225 * 1024;
+constexpr int kPartRows = 1024;
+constexpr int kPartThreads = 256;
+constexpr int kGainWarps = 8;
+
+struct HistGeom {
+  int tile_words;  // FT*B*C
+  int stages;
+  int smem_bytes;
+};
+
+__host__ __device__ inline HistGeom hist_geom(int FT, int B, int C) {
+  HistGeom g;
+  g.tile_words = FT * B * C;
+  int tile_bytes = g.tile_words * 4;
+  int left = kSmemBudget - tile_bytes - 256;
+  int st = left / kStageBytes;
+  if (st > kMaxStages) st = kMaxStages;
+  g.stages = st;
+  g.smem_bytes = tile_bytes + st * kStageBytes + 256;
+  return g;
+}
+
+// ------------------------------------------------------------------ device view
+struct View {
+  const MtbCtx& c;
+  __device__ explicit View(const MtbCtx& ctx) : c(ctx) {}
+  __device__ int* scalars() const { return ptr_of<int>(c.scalars); }
+  __device__ int n_slots() const { return scalars()[0]; }
+  __device__ const uint8_t* codes_cur() const { return ptr_of<const uint8_t>(c.codes[c.cur]); }
+  __device__ uint8_t* codes_nxt() const { return ptr_of<uint8_t>(c.codes[c.cur ^ 1]); }
+  __device__ const uint8_t* labels_cur() const { return ptr_of<const uint8_t>(c.labels[c.cur]); }
+  __device__ uint8_t* labels_nxt() const { return ptr_of<uint8_t>(c.labels[c.cur ^ 1]); }
+  __device__ uint32_t* hist_cur() const { return ptr_of<uint32_t>(c.hist[c.hcur]); }
+  __device__ const uint32_t* hist_prev() const { return ptr_of<const uint32_t>(c.hist[c.hcur ^ 1]); }
+  __device__ int64_t slab_words() const { return c.G * 16 * c.B * c.C; }
+};
+
+__device__ __forceinline__ int find_slot(const int* prefix, int n, int u) {
+  // largest s with prefix[s] <= u
+  int lo = 0, hi = n;
+  while (hi - lo > 1) {
+    int mid = (lo + hi) >> 1;
+    if (prefix[mid] <= u) lo = mid; else hi = mid;
+  }
+  return lo;
+}
+
+// block-wide exclusive scan of one int per thread (blockDim multiple of 32, <= 1024)
+__device__ int block_excl_scan(int v, int* smem_warp /*[33]*/, int& total) {
+  uint32_t inc = warp_incl_scan((uint32_t)v);
+  int lane = lane_id(), w = warp_id();
+  int nw = blockDim.x >> 5;
+  __syncthreads();
+  if (lane == 31) smem_warp[w] = (int)inc;
+  __syncthreads();
+  if (w == 0) {
+    int x = lane < nw ? smem_warp[lane] : 0;
+    uint32_t s = warp_incl_scan((uint32_t)x);
+    smem_warp[lane] = (int)s - x;
+    if (lane == 31) smem_warp[32] = (int)s;
+  }
+  __syncthreads();
+  total = smem_warp[32];
+  return (int)inc - v + smem_warp[w];
+}
+
+// ------------------------------------------------------------------------ plan
+__device__ void plan_phase(const MtbCtx& ctx, int* smem_warp) {
+  View v(ctx);
+  const int n = v.n_slots();
+  const int* mode = ptr_of<const int>(ctx.slot_mode);
+  const int* sb = ptr_of<const int>(ctx.slot_begin);
+  const int* se = ptr_of<const int>(ctx.slot_end);
+  int* prefix = ptr_of<int>(ctx.unit_prefix);
+  uint32_t* cursors = ptr_of<uint32_t>(ctx.cursors);
+  const int GS = (int)(ctx.G * (16 / ctx.FT));
+  int carry = 0;
+  for (int base = 0; base < n; base += blockDim.x) {
+    int s = base + threadIdx.x;
+    int units = 0;
+    if (s < n) {
+      if (mode[s] == MTB_MODE_BUILD) units = ((se[s] - sb[s] + kRows - 1) / kRows) * GS;
+      cursors[2 * s] = 0;
+      cursors[2 * s + 1] = 0;
+    }
+    int total;
+    int ex = block_excl_scan(units, smem_warp, total);
+    if (s < n) prefix[s] = carry + ex;
+    carry += total;
+  }
+  if (threadIdx.x == 0) {
+    prefix[n] = carry;
+    v.scalars()[3] = carry;
+  }
+}
+
+__global__ void k_plan(const __grid_constant__ MtbCtx ctx) {
+  __shared__ int smem_warp[33];
+  plan_phase(ctx, smem_warp);
+}
+
+// ------------------------------------------------------------------------ hist
+struct UnitInfo {
+  int slot, gs, chunk, row0, nrows;
+};
+
+__device__ __forceinline__ UnitInfo decode_unit(const MtbCtx& ctx, const int* prefix, int n_slots, int u) {
+  UnitInfo r;
+  r.slot = find_slot(prefix, n_slots, u);
+  int local = u - prefix[r.slot];
+  int b = ptr_of<const int>(ctx.slot_begin)[r.slot];
+  int e = ptr_of<const int>(ctx.slot_end)[r.slot];
+  int chunks = (e - b + kRows - 1) / kRows;
+  r.gs = local / chunks;
+  r.chunk = local - r.gs * chunks;
+  r.row0 = b + r.chunk * kRows;
+  r.nrows = min(kRows, e - r.row0);
+  return r;
+}
+
+// destination slab of (slot, gs): local hist, or the owning peer's staging slab
+template <int FT>
+__device__ void flush_tile(const MtbCtx& ctx, uint32_t* tile, int slot, int gs, int tid) {
+  View v(ctx);
+  const int S = 16 / FT;
+  const int g = gs / S, s = gs - g * S;
+  const int64_t f0 = (int64_t)g * 16 + (int64_t)s * FT;
+  const int words = FT * (int)ctx.B * (int)ctx.C;
+  uint32_t* dst = v.hist_cur() + (int64_t)slot * v.slab_words() + f0 * ctx.B * ctx.C;
+  for (int i = tid; i < words; i += kConsumers) {
+    uint32_t x = tile[i];
+    if (x) {
+      red_add_u32(dst + i, x);
+      tile[i] = 0;
+    }
+  }
+}
+
+template <int FT>
+__device__ void hist_phase(const MtbCtx& ctx, uint8_t* smem) {
+  View v(ctx);
+  const int B = (int)ctx.B, C = (int)ctx.C;
+  const HistGeom geom = hist_geom(FT, B, C);
+  uint32_t* tile = reinterpret_cast<uint32_t*>(smem);
+  uint8_t* stage_base = smem + (size_t)geom.tile_words * 4;
+  uint64_t* full = reinterpret_cast<uint64_t*>(stage_base + (size_t)geom.stages * kStageBytes);
+  uint64_t* empty = full + kMaxStages;
+  const int stages = geom.stages;
+
+  const int total_units = v.scalars()[3];
+  const int n_slots = v.n_slots();
+  const int* prefix = ptr_of<const int>(ctx.unit_prefix);
+  const int u0 = (int)((int64_t)total_units * blockIdx.x / gridDim.x);
+  const int u1 = (int)((int64_t)total_units * (blockIdx.x + 1) / gridDim.x);
+
+  const int tid = threadIdx.x;
+  if (tid == 0) {
+    for (int i = 0; i < stages; ++i) {
+      mbar_init(&full[i], 1);
+      mbar_init(&empty[i], kConsumerWarps);
+    }
+    fence_barrier_init();
+  }
+  for (int i = tid; i < geom.tile_words; i += blockDim.x) tile[i] = 0;
+  __syncthreads();
+
+  const uint8_t* codes = v.codes_cur();
+  const int S = 16 / FT;
+
+  if (tid >= kConsumers) {
+    // ===== producer warp: one elected lane issues the bulk copies =====
+    if (tid == kConsumers) {
+      int st = 0;
+      uint32_t ph = 0;
+      for (int u = u0; u < u1; ++u) {
+        UnitInfo ui = decode_unit(ctx, prefix, n_slots, u);
+        const int g = ui.gs / S;
+        mbar_wait(&empty[st], ph ^ 1);
+        const uint32_t bytes = (uint32_t)ui.nrows * 16u;
+        mbar_arrive_expect_tx(&full[st], bytes);
+        tma_load_1d(stage_base + (size_t)st * kStageBytes, codes + ((int64_t)g * ctx.n_cap + ui.row0) * 16, bytes,
+                    &full[st]);
+        if (++st == stages) { st = 0; ph ^= 1; }
+      }
+    }
+  } else {
+    // ===== consumer warps =====
+    const uint8_t* labels = v.labels_cur();
+    int st = 0;
+    uint32_t ph = 0;
+    int cur_slot = -1, cur_gs = -1;
+    for (int u = u0; u < u1; ++u) {
+      UnitInfo ui = decode_unit(ctx, prefix, n_slots, u);
+      if (ui.slot != cur_slot || ui.gs != cur_gs) {
+        if (cur_slot >= 0) {
+          named_bar_sync(1, kConsumers);
+          flush_tile<FT>(ctx, tile, cur_slot, cur_gs, tid);
+          named_bar_sync(1, kConsumers);
+        }
+        cur_slot = ui.slot;
+        cur_gs = ui.gs;
+      }
+      const int sub = (ui.gs % S) * FT;
+      // labels first (global), then wait for the tile
+      const int r_a = tid, r_b = tid + kConsumers;
+      uint32_t lab_a = 0, lab_b = 0;
+      if (r_a < ui.nrows) lab_a = labels[ui.row0 + r_a];
+      if (r_b < ui.nrows) lab_b = labels[ui.row0 + r_b];
+      mbar_wait(&full[st], ph);
+      const uint4* rows = reinterpret_cast<const uint4*>(stage_base + (size_t)st * kStageBytes);
+      uint4 va = make_uint4(0, 0, 0, 0), vb = va;
+      if (r_a < ui.nrows) va = rows[r_a];
+      if (r_b < ui.nrows) vb = rows[r_b];
+      __syncwarp();
+      if (lane_id() == 0) mbar_arrive(&empty[st]);  // tile is in registers: release the stage
+      if (r_a < ui.nrows) {
+#pragma unroll
+        for (int k = 0; k < FT; ++k) atomicAdd(&tile[(k * B + (int)code_byte(va, sub + k)) * C + (int)lab_a], 1u);
+      }
+      if (r_b < ui.nrows) {
+#pragma unroll
+        for (int k = 0; k < FT; ++k) atomicAdd(&tile[(k * B + (int)code_byte(vb, sub + k)) * C + (int)lab_b], 1u);
+      }
+      if (++st == stages) { st = 0; ph ^= 1; }
+    }
+    if (cur_slot >= 0) {
+      named_bar_sync(1, kConsumers);
+      flush_tile<FT>(ctx, tile, cur_slot, cur_gs, tid);
+    }
+  }
+}
+
+template <int FT>
+__global__ void __launch_bounds__(kHistThreads, 1) k_hist(const __grid_constant__ MtbCtx ctx) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  hist_phase<FT>(ctx, smem);
+}
+
+// ------------------------------------------------------------------------ gain
+// One warp per (slot, feature).  `slab` is this warp's padded shared-memory copy of
+// the feature's [B][C] counts: lane L owns bins [L*BPL, (L+1)*BPL) at offset
+// L*(BPL*C+1) so that lane-sequential walks are bank-conflict free.
+__device__ void gain_pair(const MtbCtx& ctx, uint32_t* slab, int slot, int f) {
+  View v(ctx);
+  const int B = (int)ctx.B, C = (int)ctx.C, F = (int)ctx.F;
+  const int BPL = B / 32;
+  const int lane_stride = BPL * C + 1;
+  const int lane = lane_id();
+  const int mode = ptr_of<const int>(ctx.slot_mode)[slot];
+  double* fb_cost = ptr_of<double>(ctx.fb_cost);
+  int* fb_bin = ptr_of<int>(ctx.fb_bin);
+  if (mode == MTB_MODE_NONE) {
+    if (lane == 0) {
+      fb_cost[(int64_t)slot * F + f] = INFINITY;
+      fb_bin[(int64_t)slot * F + f] = -1;
+    }
+    return;
+  }
+  uint32_t* mine = v.hist_cur() + (int64_t)slot * v.slab_words() + (int64_t)f * B * C;
+  const int words = B * C;
+  if (mode == MTB_MODE_DERIVE) {
+    const int par = ptr_of<const int>(ctx.slot_parent)[slot];
+    const int sib = ptr_of<const int>(ctx.slot_sibling)[slot];
+    const uint32_t* hp = v.hist_prev() + (int64_t)par * v.slab_words() + (int64_t)f * B * C;
+    const uint32_t* hs = v.hist_cur() + (int64_t)sib * v.slab_words() + (int64_t)f * B * C;
+    for (int w = lane; w < words; w += 32) {
+      uint32_t x = hp[w] - hs[w];
+      mine[w] = x;
+      int b = w / C, c = w - b * C;
+      slab[(b / BPL) * lane_stride + (b % BPL) * C + c] = x;
+    }
+  } else {
+    for (int w = lane; w < words; w += 32) {
+      uint32_t x = mine[w];
+      int b = w / C, c = w - b * C;
+      slab[(b / BPL) * lane_stride + (b % BPL) * C + c] = x;
+    }
+  }
+  __syncwarp();
+
+  uint32_t* my = slab + lane * lane_stride;
+  // per-bin row counts before the scan -> which bins are candidates
+  uint32_t present = 0;
+  for (int j = 0; j < BPL; ++j) {
+    uint32_t s = 0;
+    for (int c = 0; c < C; ++c) s += my[j * C + c];
+    if (s) present |= 1u << j;
+  }
+  // lane-local inclusive scan along bins, then cross-lane offsets per class
+  for (int j = 1; j < BPL; ++j)
+    for (int c = 0; c < C; ++c) my[j * C + c] += my[(j - 1) * C + c];
+  for (int c = 0; c < C; ++c) {
+    uint32_t tot = my[(BPL - 1) * C + c];
+    uint32_t inc = warp_incl_scan(tot);
+    uint32_t off = inc - tot;
+    if (off)
+      for (int j = 0; j < BPL; ++j) my[j * C + c] += off;
+  }
+  __syncwarp();
+  const uint32_t* last = slab + 31 * lane_stride + (BPL - 1) * C;  // totals per class
+  uint32_t n = 0;
+  for (int c = 0; c < C; ++c) n += last[c];
+
+  if (f == 0) {
+    uint32_t* node_cnt = ptr_of<uint32_t>(ctx.node_cnt) + (int64_t)slot * C;
+    for (int c = lane; c < C; c += 32) node_cnt[c] = last[c];
+  }
+
+  double best = INFINITY;
+  int best_bin = 0x7fffffff;
+  const int crit = (int)ctx.criterion, dm = (int)ctx.dot_mode;
+  for (int j = 0; j < BPL; ++j) {
+    if (!(present >> j & 1u)) continue;
+    const uint32_t* L = my + j * C;
+    uint32_t nl = 0;
+    for (int c = 0; c < C; ++c) nl += L[c];
+    const uint32_t nr = n - nl;
+    if (nr == 0) continue;  // right side empty: not a usable split
+    double hl = impurity(C, [&](int c) { return L[c]; }, nl, crit);
+    double hr = impurity(C, [&](int c) { return last[c] - L[c]; }, nr, crit);
+    double cost = split_cost(nl, nr, hl, hr, dm);
+    if (cost < best) {  // strict: first (lowest) bin wins ties inside the lane
+      best = cost;
+      best_bin = lane * BPL + j;
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    double oc = __shfl_xor_sync(0xffffffffu, best, o);
+    int ob = __shfl_xor_sync(0xffffffffu, best_bin, o);
+    if (oc < best || (oc == best && ob < best_bin)) {
+      best = oc;
+      best_bin = ob;
+    }
+  }
+  const bool ok = best_bin != 0x7fffffff;
+  if (lane == 0) {
+    fb_cost[(int64_t)slot * F + f] = ok ? best : INFINITY;
+    fb_bin[(int64_t)slot * F + f] = ok ? best_bin : -1;
+  }
+  if (ok) {
+    uint32_t* fl = ptr_of<uint32_t>(ctx.fb_left) + ((int64_t)slot * F + f) * C;
+    const uint32_t* L = slab + (best_bin / BPL) * lane_stride + (best_bin % BPL) * C;
+    for (int c = lane; c < C; c += 32) fl[c] = L[c];
+  }
+  __syncwarp();
+}
+
+__device__ void gain_phase(const MtbCtx& ctx, uint8_t* smem, int warps_per_block) {
+  View v(ctx);
+  const int F = (int)ctx.F;
+  const int n_pairs = v.n_slots() * F;
+  const int slab_words = (int)ctx.B * (int)ctx.C + 32;
+  const int w = warp_id();
+  if (w >= warps_per_block) return;
+  uint32_t* slab = reinterpret_cast<uint32_t*>(smem) + (size_t)w * slab_words;
+  // derive reads a sibling built in this level: pairs are independent otherwise
+  for (int p = blockIdx.x * warps_per_block + w; p < n_pairs; p += gridDim.x * warps_per_block) {
+    gain_pair(ctx, slab, p / F, p % F);
+  }
+}
+
+__global__ void __launch_bounds__(kGainWarps * 32) k_gain(const __grid_constant__ MtbCtx ctx) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  gain_phase(ctx, smem, kGainWarps);
+}
+
+// -------------------------------------------------------------------- finalize
+template <typename Cnt>
+__device__ __forceinline__ bool is_terminal(Cnt cnt, int C, int depth, const MtbCtx& ctx, uint32_t& n) {
+  int present = 0;
+  n = 0;
+  for (int c = 0; c < C; ++c) {
+    const uint32_t x = cnt(c);
+    n += x;
+    present += x != 0u;
+  }
+  return present <= 1 || (ctx.max_depth >= 0 && depth >= ctx.max_depth) || (int64_t)n < ctx.min_samples_split;
+}
+
+__device__ void finalize_phase(const MtbCtx& ctx, int* smem_warp) {
+  View v(ctx);
+  const int n = v.n_slots();
+  const int F = (int)ctx.F, C = (int)ctx.C;
+  const int depth = (int)ctx.depth;
+  int* scal = v.scalars();
+  const int nodes0 = scal[2];
+
+  const int* slot_node = ptr_of<const int>(ctx.slot_node);
+  const int* slot_mode = ptr_of<const int>(ctx.slot_mode);
+  const int* sb = ptr_of<const int>(ctx.slot_begin);
+  const int* se = ptr_of<const int>(ctx.slot_end);
+  const double* fb_cost = ptr_of<const double>(ctx.fb_cost);
+  const int* fb_bin = ptr_of<const int>(ctx.fb_bin);
+  const uint32_t* fb_left = ptr_of<const uint32_t>(ctx.fb_left);
+  const uint32_t* node_cnt = ptr_of<const uint32_t>(ctx.node_cnt);
+  int* rec_feature = ptr_of<int>(ctx.rec_feature);
+  int* rec_bin = ptr_of<int>(ctx.rec_bin);
+  int* part_flags = ptr_of<int>(ctx.part_flags);
+  int* t_feature = ptr_of<int>(ctx.t_feature);
+  int* t_bin = ptr_of<int>(ctx.t_bin);
+  int* t_left = ptr_of<int>(ctx.t_left);
+  int* t_parent = ptr_of<int>(ctx.t_parent);
+  int* t_depth = ptr_of<int>(ctx.t_depth);
+  double* t_gain = ptr_of<double>(ctx.t_gain);
+  uint32_t* t_counts = ptr_of<uint32_t>(ctx.t_counts);
+  int* ns_node = ptr_of<int>(ctx.nslot_node);
+  int* ns_mode = ptr_of<int>(ctx.nslot_mode);
+  int* ns_parent = ptr_of<int>(ctx.nslot_parent);
+  int* ns_sibling = ptr_of<int>(ctx.nslot_sibling);
+  int* ns_src = ptr_of<int>(ctx.nslot_src);
+  int* pprefix = ptr_of<int>(ctx.unit_prefix) + (ctx.m_cap + 1);
+
+  int carry_split = 0, carry_pair = 0, carry_units = 0;
+  for (int base = 0; base < n; base += blockDim.x) {
+    const int s = base + threadIdx.x;
+    int split = 0, pair = 0, units = 0;
+    int bf = -1, bb = -1;
+    double bgain = 0.0;
+    bool tl = true, tr = true;
+    uint32_t nl = 0, nr = 0;
+    if (s < n && slot_mode[s] != MTB_MODE_NONE) {
+      const uint32_t* cnt = node_cnt + (int64_t)s * C;
+      const int node = slot_node[s];
+      for (int c = 0; c < C; ++c) t_counts[(int64_t)node * C + c] = cnt[c];
+      uint32_t ntot;
+      if (!is_terminal([&](int c) { return cnt[c]; }, C, depth, ctx, ntot)) {
+        const double hp = impurity(C, [&](int c) { return cnt[c]; }, ntot, (int)ctx.criterion);
+        bool have = false;
+        for (int f = 0; f < F; ++f) {
+          const double cost = fb_cost[(int64_t)s * F + f];
+          if (!(cost < INFINITY)) continue;
+          const double g = __dsub_rn(hp, cost);
+          if (!have || g > bgain) {  // strict: first (lowest) feature wins ties
+            have = true;
+            bgain = g;
+            bf = f;
+            bb = fb_bin[(int64_t)s * F + f];
+          }
+        }
+        if (have) {
+          split = 1;
+          const uint32_t* L = fb_left + ((int64_t)s * F + bf) * C;
+          tl = is_terminal([&](int c) { return L[c]; }, C, depth + 1, ctx, nl);
+          tr = is_terminal([&](int c) { return cnt[c] - L[c]; }, C, depth + 1, ctx, nr);
+          pair = !(tl && tr);
+          if (pair) units = (se[s] - sb[s] + kPartRows - 1) / kPartRows;
+        }
+      }
+      rec_feature[s] = bf;
+      rec_bin[s] = bb;
+      t_feature[node] = bf;
+      t_bin[node] = bb;
+      t_gain[node] = split ? bgain : NAN;
+      part_flags[s] = pair ? ((tl ? 0 : 1) | (tr ? 0 : 2)) : 0;
+    } else if (s < n) {
+      rec_feature[s] = -1;
+      rec_bin[s] = -1;
+      part_flags[s] = 0;
+    }
+    int tot_split, tot_pair, tot_units;
+    const int ex_split = block_excl_scan(split, smem_warp, tot_split);
+    const int ex_pair = block_excl_scan(pair, smem_warp, tot_pair);
+    const int ex_units = block_excl_scan(units, smem_warp, tot_units);
+    if (s < n) pprefix[s] = carry_units + ex_units;
+    if (split) {
+      const int node = slot_node[s];
+      const int lid = nodes0 + 2 * (carry_split + ex_split), rid = lid + 1;
+      t_left[node] = lid;
+      const uint32_t* cnt = node_cnt + (int64_t)s * C;
+      const uint32_t* L = fb_left + ((int64_t)s * F + bf) * C;
+      for (int c = 0; c < C; ++c) {
+        t_counts[(int64_t)lid * C + c] = L[c];
+        t_counts[(int64_t)rid * C + c] = cnt[c] - L[c];
+      }
+      t_parent[lid] = node; t_parent[rid] = node;
+      t_depth[lid] = depth + 1; t_depth[rid] = depth + 1;
+      t_feature[lid] = -1; t_feature[rid] = -1;
+      t_bin[lid] = -1; t_bin[rid] = -1;
+      t_left[lid] = -1; t_left[rid] = -1;
+      t_gain[lid] = NAN; t_gain[rid] = NAN;
+      if (pair) {
+        const int a = 2 * (carry_pair + ex_pair), b = a + 1;
+        ns_node[a] = lid; ns_node[b] = rid;
+        ns_parent[a] = s; ns_parent[b] = s;
+        ns_sibling[a] = b; ns_sibling[b] = a;
+        ns_src[a] = 2 * s; ns_src[b] = 2 * s + 1;
+        int ma, mb;
+        if (!tl && !tr) {
+          // both children continue: build the smaller (global count, ties -> left), derive the other
+          const bool left_small = nl <= nr;
+          ma = left_small ? MTB_MODE_BUILD : MTB_MODE_DERIVE;
+          mb = left_small ? MTB_MODE_DERIVE : MTB_MODE_BUILD;
+        } else {
+          ma = tl ? MTB_MODE_NONE : MTB_MODE_BUILD;
+          mb = tr ? MTB_MODE_NONE : MTB_MODE_BUILD;
+        }
+        ns_mode[a] = ma; ns_mode[b] = mb;
+      }
+    }
+    carry_split += tot_split;
+    carry_pair += tot_pair;
+    carry_units += tot_units;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    pprefix[n] = carry_units;
+    scal[1] = 2 * carry_pair;
+    scal[2] = nodes0 + 2 * carry_split;
+    scal[4] = carry_units;
+  }
+}
+
+__global__ void __launch_bounds__(1024) k_finalize(const __grid_constant__ MtbCtx ctx) {
+  __shared__ int smem_warp[33];
+  finalize_phase(ctx, smem_warp);
+}
+
+// ------------------------------------------------------------------- partition
+__global__ void __launch_bounds__(kPartThreads) k_partition(const __grid_constant__ MtbCtx ctx) {
+  View v(ctx);
+  __shared__ uint32_t wl[4][kPartThreads / 32], wr[4][kPartThreads / 32];
+  __shared__ uint32_t base_l, base_r;
+  const int n_slots = v.n_slots();
+  const int total = v.scalars()[4];
+  const int* pprefix = ptr_of<const int>(ctx.unit_prefix) + (ctx.m_cap + 1);
+  const int* sb = ptr_of<const int>(ctx.slot_begin);
+  const int* se = ptr_of<const int>(ctx.slot_end);
+  const int* rec_feature = ptr_of<const int>(ctx.rec_feature);
+  const int* rec_bin = ptr_of<const int>(ctx.rec_bin);
+  const int* part_flags = ptr_of<const int>(ctx.part_flags);
+  uint32_t* cursors = ptr_of<uint32_t>(ctx.cursors);
+  const uint4* src = reinterpret_cast<const uint4*>(v.codes_cur());
+  uint4* dst = reinterpret_cast<uint4*>(v.codes_nxt());
+  const uint8_t* lsrc = v.labels_cur();
+  uint8_t* ldst = v.labels_nxt();
+  const int G = (int)ctx.G;
+  const int64_t plane = ctx.n_cap;
+  const int tid = threadIdx.x, lane = lane_id(), w = warp_id();
+
+  const int u0 = (int)((int64_t)total * blockIdx.x / gridDim.x);
+  const int u1 = (int)((int64_t)total * (blockIdx.x + 1) / gridDim.x);
+  for (int u = u0; u < u1; ++u) {
+    const int slot = find_slot(pprefix, n_slots, u);
+    const int chunk = u - pprefix[slot];
+    const int b = sb[slot], e = se[slot];
+    const int r0 = b + chunk * kPartRows;
+    const int r1 = min(e, r0 + kPartRows);
+    const int f = rec_feature[slot], bin = rec_bin[slot], flags = part_flags[slot];
+    const int g = f >> 4, k = f & 15;
+
+    bool valid[4], left[4];
+    uint32_t rank[4];
+#pragma unroll
+    for (int it = 0; it < 4; ++it) {
+      const int row = r0 + it * kPartThreads + tid;
+      valid[it] = row < r1;
+      uint32_t code = 0;
+      if (valid[it]) code = reinterpret_cast<const uint8_t*>(src + (int64_t)g * plane + row)[k];
+      left[it] = valid[it] && (int)code <= bin;
+      const uint32_t ml = __ballot_sync(0xffffffffu, left[it]);
+      const uint32_t mr = __ballot_sync(0xffffffffu, valid[it] && !left[it]);
+      const uint32_t below = (1u << lane) - 1u;
+      rank[it] = left[it] ? __popc(ml & below) : __popc(mr & below);
+      if (lane == 0) {
+        wl[it][w] = __popc(ml);
+        wr[it][w] = __popc(mr);
+      }
+    }
+    __syncthreads();
+    if (w == 0) {
+      // exclusive scan over the 4*NW (iteration, warp) cells, in row order
+      const int cell = lane;  // 4*NW == 32
+      uint32_t cl = (&wl[0][0])[cell], cr = (&wr[0][0])[cell];
+      uint32_t il = warp_incl_scan(cl), ir = warp_incl_scan(cr);
+      (&wl[0][0])[cell] = il - cl;
+      (&wr[0][0])[cell] = ir - cr;
+      if (lane == 31) {
+        base_l = atomicAdd(&cursors[2 * slot], il);
+        base_r = atomicAdd(&cursors[2 * slot + 1], ir);
+      }
+    }
+    __syncthreads();
+    const bool keep_l = flags & 1, keep_r = flags & 2;
+#pragma unroll
+    for (int it = 0; it < 4; ++it) {
+      if (!valid[it]) continue;
+      const int row = r0 + it * kPartThreads + tid;
+      int64_t d;
+      if (left[it]) {
+        if (!keep_l) continue;
+        d = (int64_t)b + base_l + wl[it][w] + rank[it];
+      } else {
+        if (!keep_r) continue;
+        d = (int64_t)e - 1 - (base_r + wr[it][w] + rank[it]);
+      }
+      for (int gg = 0; gg < G; ++gg) st_na_u4(dst + (int64_t)gg * plane + d, ld_nc_u4(src + (int64_t)gg * plane + row));
+      ldst[d] = lsrc[row];
+    }
+    __syncthreads();
+  }
+}
+static_assert(4 * (kPartThreads / 32) == 32, "partition scan assumes 32 cells");
+
+__global__ void k_commit(const __grid_constant__ MtbCtx ctx) {
+  View v(ctx);
+  const int n_next = v.scalars()[1];
+  const int* ns_src = ptr_of<const int>(ctx.nslot_src);
+  const int* ns_mode = ptr_of<const int>(ctx.nslot_mode);
+  const int* sb = ptr_of<const int>(ctx.slot_begin);
+  const int* se = ptr_of<const int>(ctx.slot_end);
+  const uint32_t* cursors = ptr_of<const uint32_t>(ctx.cursors);
+  int* nb = ptr_of<int>(ctx.nslot_begin);
+  int* ne = ptr_of<int>(ctx.nslot_end);
+  for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < n_next; j += gridDim.x * blockDim.x) {
+    const int p = ns_src[j] >> 1, side = ns_src[j] & 1;
+    int b = 0, e = 0;
+    if (ns_mode[j] != MTB_MODE_NONE) {
+      if (side == 0) {
+        b = sb[p];
+        e = b + (int)cursors[2 * p];
+      } else {
+        e = se[p];
+        b = e - (int)cursors[2 * p + 1];
+      }
+    }
+    nb[j] = b;
+    ne[j] = e;
+  }
+  // the next level's slot count becomes current (nothing in this kernel reads scalars[0])
+  if (blockIdx.x == 0 && threadIdx.x == 0) v.scalars()[0] = n_next;
+}
+
+// ----------------------------------------------------------------- fused level
+template <int FT>
+__global__ void __launch_bounds__(kHistThreads, 1) k_level_fused(const __grid_constant__ MtbCtx ctx) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  __shared__ int smem_warp[33];
+  cg::grid_group grid = cg::this_grid();
+  if (blockIdx.x == 0) plan_phase(ctx, smem_warp);
+  grid.sync();
+  hist_phase<FT>(ctx, smem);
+  grid.sync();
+  gain_phase(ctx, smem, kGainWarps);
+  grid.sync();
+  if (blockIdx.x == 0) finalize_phase(ctx, smem_warp);
+}
+
+int g_sm_count = 0;
+int sm_count() {
+  if (!g_sm_count) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&g_sm_count, cudaDevAttrMultiProcessorCount, dev);
+  }
+  return g_sm_count;
+}
+
+template <typename K>
+int set_smem(K kernel, int bytes) {
+  MTB_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+  return 0;
+}
+
+int gain_smem(const MtbCtx* ctx) { return kGainWarps * ((int)ctx->B * (int)ctx->C + 32) * 4; }
+
+}  // namespace
+
+template <int FT>
+static int launch_hist(const MtbCtx* ctx, const HistGeom& g, cudaStream_t stream) {
+  if (set_smem(k_hist<FT>, g.smem_bytes)) return -1;
+  k_hist<FT><<<sm_count(), kHistThreads, g.smem_bytes, stream>>>(*ctx);
+  MTB_CHECK(cudaGetLastError());
+  return 0;
+}
+
+template <int FT>
+static int launch_fused(const MtbCtx* ctx, int smem, cudaStream_t stream) {
+  if (set_smem(k_level_fused<FT>, smem)) return -1;
+  MtbCtx local = *ctx;
+  void* args[] = {&local};
+  MTB_CHECK(cudaLaunchCooperativeKernel((void*)k_level_fused<FT>, dim3(sm_count()), dim3(kHistThreads), args, smem,
+                                        stream));
+  return 0;
+}
+
+#define FT_SWITCH(ft, FN, ...)                                                                         \
+  switch (ft) {                                                                                        \
+    case 16: return FN<16>(__VA_ARGS__);                                                               \
+    case 8: return FN<8>(__VA_ARGS__);                                                                 \
+    case 4: return FN<4>(__VA_ARGS__);                                                                 \
+    case 2: return FN<2>(__VA_ARGS__);                                                                 \
+    case 1: return FN<1>(__VA_ARGS__);                                                                 \
+    default:                                                                                           \
+      mtb_set_error("FT", "features per tile must be 1, 2, 4, 8 or 16", __FILE__, __LINE__);           \
+      return -2;                                                                                       \
+  }
+
+extern "C" int mtb_hist_config(const MtbCtx* ctx, int* threads, int* smem_bytes, int* stages, int* rows_per_stage) {
+  HistGeom g = hist_geom((int)ctx->FT, (int)ctx->B, (int)ctx->C);
+  if (threads) *threads = kHistThreads;
+  if (smem_bytes) *smem_bytes = g.smem_bytes;
+  if (stages) *stages = g.stages;
+  if (rows_per_stage) *rows_per_stage = kRows;
+  return g.stages >= 2 ? 0 : -2;
+}
+
+extern "C" int mtb_level_plan(const MtbCtx* ctx, void* stream) {
+  k_plan<<<1, 1024, 0, (cudaStream_t)stream>>>(*ctx);
+  MTB_CHECK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int mtb_level_hist(const MtbCtx* ctx, void* stream) {
+  HistGeom g = hist_geom((int)ctx->FT, (int)ctx->B, (int)ctx->C);
+  if (g.stages < 2) {
+    mtb_set_error("hist", "histogram tile does not fit in shared memory", __FILE__, __LINE__);
+    return -2;
+  }
+  FT_SWITCH((int)ctx->FT, launch_hist, ctx, g, (cudaStream_t)stream);
+}
+
+extern "C" int mtb_level_gain(const MtbCtx* ctx, void* stream) {
+  const int smem = gain_smem(ctx);
+  if (set_smem(k_gain, smem)) return -1;
+  int64_t pairs = ctx->n_slots_host * ctx->F;
+  int blocks = (int)((pairs + kGainWarps - 1) / kGainWarps);
+  int maxb = sm_count() * 2;
+  if (blocks > maxb) blocks = maxb;
+  if (blocks < 1) blocks = 1;
+  k_gain<<<blocks, kGainWarps * 32, smem, (cudaStream_t)stream>>>(*ctx);
+  MTB_CHECK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int mtb_level_finalize(const MtbCtx* ctx, void* stream) {
+  k_finalize<<<1, 1024, 0, (cudaStream_t)stream>>>(*ctx);
+  MTB_CHECK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int mtb_level_partition(const MtbCtx* ctx, void* stream) {
+  k_partition<<<sm_count() * 4, kPartThreads, 0, (cudaStream_t)stream>>>(*ctx);
+  MTB_CHECK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int mtb_level_commit(const MtbCtx* ctx, void* stream) {
+  k_commit<<<64, 256, 0, (cudaStream_t)stream>>>(*ctx);
+  MTB_CHECK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int mtb_level_fused(const MtbCtx* ctx, void* stream) {
+  HistGeom g = hist_geom((int)ctx->FT, (int)ctx->B, (int)ctx->C);
+  if (g.stages < 2) {
+    mtb_set_error("hist", "histogram tile does not fit in shared memory", __FILE__, __LINE__);
+    return -2;
+  }
+  int smem = g.smem_bytes;
+  if (gain_smem(ctx) > smem) smem = gain_smem(ctx);
+  FT_SWITCH((int)ctx->FT, launch_fused, ctx, smem, (cudaStream_t)stream);
+}

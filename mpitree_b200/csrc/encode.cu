@@ -1,0 +1,127 @@
+// K1 — encode raw feature rows into tiled one-byte bin codes.
+//
+// The reference discovers candidate thresholds with np.unique at every node
+// (mpitree/tree/decision_tree.py:73).  Here each feature gets an ascending edge
+// table once per fit and every value is replaced by the index of the first edge
+// >= value, so `x <= threshold` on raw values equals `code <= bin` on codes.
+// Output layout: codes[g][row][k] for feature f = 16*g + k (one 128-bit word per
+// row per feature group), the layout the histogram kernel streams with TMA.
+#include "common.cuh"
+
+namespace {
+
+constexpr int kThreads = 256;
+
+template <typename T>
+__global__ void __launch_bounds__(kThreads) k_encode_float(const T* __restrict__ X, int64_t n, int F, int64_t ldx,
+                                                           const double* __restrict__ edges,
+                                                           const int* __restrict__ n_bins, uint4* __restrict__ codes,
+                                                           int64_t n_cap, int64_t row0,
+                                                           unsigned long long* mismatch) {
+  __shared__ double s_edges[16][MTB_MAX_BINS];
+  __shared__ int s_nb[16];
+  const int g = blockIdx.y;
+  for (int i = threadIdx.x; i < 16 * MTB_MAX_BINS; i += kThreads) {
+    const int k = i / MTB_MAX_BINS, b = i % MTB_MAX_BINS;
+    const int f = g * 16 + k;
+    s_edges[k][b] = f < F ? edges[(int64_t)f * MTB_MAX_BINS + b] : INFINITY;
+  }
+  if (threadIdx.x < 16) {
+    const int f = g * 16 + threadIdx.x;
+    s_nb[threadIdx.x] = f < F ? n_bins[f] : 1;
+  }
+  __syncthreads();
+  unsigned int bad = 0;
+  for (int64_t row = (int64_t)blockIdx.x * kThreads + threadIdx.x; row < n; row += (int64_t)gridDim.x * kThreads) {
+    uint32_t w[4] = {0, 0, 0, 0};
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+      const int f = g * 16 + k;
+      if (f >= F) break;
+      const double x = (double)X[row * ldx + f];
+      // first edge >= x (edges beyond n_bins are +inf)
+      int lo = 0, hi = s_nb[k] - 1;
+      while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (s_edges[k][mid] >= x) hi = mid; else lo = mid + 1;
+      }
+      bad += s_edges[k][lo] != x;
+      w[k >> 2] |= (uint32_t)lo << ((k & 3) * 8);
+    }
+    codes[(int64_t)g * n_cap + row0 + row] = make_uint4(w[0], w[1], w[2], w[3]);
+  }
+  if (mismatch) {
+    for (int o = 16; o > 0; o >>= 1) bad += __shfl_xor_sync(0xffffffffu, bad, o);
+    if ((threadIdx.x & 31) == 0 && bad) atomicAdd(mismatch, (unsigned long long)bad);
+  }
+}
+
+__global__ void __launch_bounds__(kThreads) k_encode_u8(const uint8_t* __restrict__ X, int64_t n, int F, int64_t ldx,
+                                                        const uint8_t* __restrict__ lut, uint4* __restrict__ codes,
+                                                        int64_t n_cap, int64_t row0, int vec_ok) {
+  __shared__ uint8_t s_lut[16][256];
+  const int g = blockIdx.y;
+  if (lut) {
+    for (int i = threadIdx.x; i < 16 * 256; i += kThreads) {
+      const int k = i >> 8, f = g * 16 + k;
+      s_lut[k][i & 255] = f < F ? lut[(int64_t)f * 256 + (i & 255)] : 0;
+    }
+    __syncthreads();
+  }
+  const int kmax = min(16, F - g * 16);
+  for (int64_t row = (int64_t)blockIdx.x * kThreads + threadIdx.x; row < n; row += (int64_t)gridDim.x * kThreads) {
+    const uint8_t* src = X + row * ldx + g * 16;
+    uint4 v = make_uint4(0, 0, 0, 0);
+    if (vec_ok && kmax == 16) {
+      v = mtb::ld_nc_u4(src);
+    } else {
+      uint32_t w[4] = {0, 0, 0, 0};
+      for (int k = 0; k < kmax; ++k) w[k >> 2] |= (uint32_t)src[k] << ((k & 3) * 8);
+      v = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+    if (lut) {
+      uint32_t w[4] = {v.x, v.y, v.z, v.w};
+      uint32_t o[4] = {0, 0, 0, 0};
+#pragma unroll
+      for (int k = 0; k < 16; ++k) {
+        const uint32_t c = (w[k >> 2] >> ((k & 3) * 8)) & 0xffu;
+        o[k >> 2] |= (uint32_t)(k < kmax ? s_lut[k][c] : 0) << ((k & 3) * 8);
+      }
+      v = make_uint4(o[0], o[1], o[2], o[3]);
+    }
+    codes[(int64_t)g * n_cap + row0 + row] = v;
+  }
+}
+
+}  // namespace
+
+extern "C" int mtb_encode_float(const void* X, int dtype, int64_t n, int64_t F, int64_t ldx, const double* edges,
+                                const int32_t* n_bins, uint8_t* codes, int64_t n_cap, int64_t row0,
+                                unsigned long long* mismatch, void* stream) {
+  if (n <= 0) return 0;
+  const int G = (int)((F + 15) / 16);
+  int64_t bx = (n + kThreads - 1) / kThreads;
+  if (bx > 148 * 16) bx = 148 * 16;
+  dim3 grid((unsigned)bx, (unsigned)G);
+  if (dtype == 0)
+    k_encode_float<float><<<grid, kThreads, 0, (cudaStream_t)stream>>>((const float*)X, n, (int)F, ldx, edges, n_bins,
+                                                                       (uint4*)codes, n_cap, row0, mismatch);
+  else
+    k_encode_float<double><<<grid, kThreads, 0, (cudaStream_t)stream>>>((const double*)X, n, (int)F, ldx, edges,
+                                                                        n_bins, (uint4*)codes, n_cap, row0, mismatch);
+  MTB_CHECK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int mtb_encode_u8(const uint8_t* X, int64_t n, int64_t F, int64_t ldx, const uint8_t* lut, uint8_t* codes,
+                             int64_t n_cap, int64_t row0, void* stream) {
+  if (n <= 0) return 0;
+  const int G = (int)((F + 15) / 16);
+  int64_t bx = (n + kThreads - 1) / kThreads;
+  if (bx > 148 * 16) bx = 148 * 16;
+  dim3 grid((unsigned)bx, (unsigned)G);
+  const int vec_ok = (ldx % 16 == 0) && ((uintptr_t)X % 16 == 0);
+  k_encode_u8<<<grid, kThreads, 0, (cudaStream_t)stream>>>(X, n, (int)F, ldx, lut, (uint4*)codes, n_cap, row0, vec_ok);
+  MTB_CHECK(cudaGetLastError());
+  return 0;
+}

@@ -1,0 +1,73 @@
+// Impurity / split-cost arithmetic with the reference's float64 rounding.
+//
+// The reference evaluates (mpitree/tree/decision_tree.py:49-51, :79-91)
+//     H(x)  = -np.sum(p * np.log2(p)),  p = counts_present / n
+//     cost  = np.dot([nL/n, nR/n], [H(yL), H(yR)])
+//     gain  = H(y) - min(cost)
+// To make first-arg-min / first-arg-max ties resolve the same way on the GPU,
+// every operation below is a separately rounded IEEE double operation
+// (__dmul_rn / __dadd_rn stop nvcc from contracting into FMAs), the sum follows
+// numpy's pairwise order (plain loop below 8 terms, 8 running accumulators
+// otherwise) and the 2-term dot follows the host BLAS's rounding, probed at
+// start-up (dot_mode: 0 plain, 1 fma(b,d,a*c), 2 fma(a,c,b*d)).
+#pragma once
+
+#include <math.h>
+#include <stdint.h>
+
+namespace mtb {
+
+// Sums `terms` produced on the fly in numpy.add.reduce order for a contiguous
+// float64 vector of length k (k <= 128).  `next()` yields the terms in order.
+template <typename Next>
+__device__ __forceinline__ double numpy_sum(int k, Next next) {
+  if (k < 8) {
+    double res = 0.0;
+    for (int i = 0; i < k; ++i) res = __dadd_rn(res, next());
+    return res;
+  }
+  double r[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) r[j] = next();
+  int body = k - (k % 8);
+  for (int i = 8; i < body; i += 8) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) r[j] = __dadd_rn(r[j], next());
+  }
+  double res = __dadd_rn(__dadd_rn(__dadd_rn(r[0], r[1]), __dadd_rn(r[2], r[3])),
+                         __dadd_rn(__dadd_rn(r[4], r[5]), __dadd_rn(r[6], r[7])));
+  for (int i = body; i < k; ++i) res = __dadd_rn(res, next());
+  return res;
+}
+
+// Impurity of a class-count vector read through `cnt(c)`, total n > 0.
+// criterion 0: entropy (base 2), 1: gini.
+template <typename Cnt>
+__device__ __forceinline__ double impurity(int C, Cnt cnt, uint32_t n, int criterion) {
+  int k = 0;
+  for (int c = 0; c < C; ++c) k += (cnt(c) != 0u);
+  const double dn = (double)n;
+  int c = 0;
+  auto next = [&]() -> double {
+    uint32_t v;
+    do {
+      v = cnt(c++);
+    } while (v == 0u);
+    double p = __ddiv_rn((double)v, dn);
+    return criterion == 0 ? __dmul_rn(p, log2(p)) : __dmul_rn(p, p);
+  };
+  double s = numpy_sum(k, next);
+  return criterion == 0 ? -s : __dsub_rn(1.0, s);
+}
+
+__device__ __forceinline__ double split_cost(uint32_t n_left, uint32_t n_right, double h_left, double h_right,
+                                             int dot_mode) {
+  const double n = (double)(n_left + n_right);
+  const double wl = __ddiv_rn((double)n_left, n);
+  const double wr = __ddiv_rn((double)n_right, n);
+  if (dot_mode == 1) return __fma_rn(wr, h_right, __dmul_rn(wl, h_left));
+  if (dot_mode == 2) return __fma_rn(wl, h_left, __dmul_rn(wr, h_right));
+  return __dadd_rn(__dmul_rn(wl, h_left), __dmul_rn(wr, h_right));
+}
+
+}  // namespace mtb

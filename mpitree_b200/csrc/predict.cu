@@ -1,0 +1,106 @@
+// K4 — batched prediction: every row walks the flattened node array.
+//
+// Replaces the reference's per-row recursive Python walk driven by
+// np.apply_along_axis and the arg-max over leaf counts
+// (mpitree/tree/decision_tree.py:208-227, :248).  Nodes are packed into 16-byte
+// records {feature, threshold, left child, leaf label}; children are numbered
+// consecutively (right = left + 1), so one shared-memory load per level decides the
+// step.  Trees up to kSmemNodes nodes are staged in shared memory, larger ones are
+// read through L1/L2.
+#include "common.cuh"
+
+namespace {
+
+constexpr int kThreads = 256;
+constexpr int kSmemNodes = 8192;  // 128 KB of records
+
+template <typename T>
+struct Rec {
+  int feature;
+  int left;
+  int label;
+  int pad;
+};
+
+template <typename T, typename TH, bool kSmem>
+__global__ void __launch_bounds__(kThreads) k_predict(const T* __restrict__ X, int64_t n, int64_t ldx,
+                                                      const int4* __restrict__ nodes,
+                                                      const TH* __restrict__ thr, int n_nodes,
+                                                      int* __restrict__ out_leaf, int* __restrict__ out_label) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  int4* s_nodes = reinterpret_cast<int4*>(smem);
+  TH* s_thr = reinterpret_cast<TH*>(smem + (size_t)(kSmem ? n_nodes : 0) * sizeof(int4));
+  if (kSmem) {
+    for (int i = threadIdx.x; i < n_nodes; i += kThreads) {
+      s_nodes[i] = nodes[i];
+      s_thr[i] = thr[i];
+    }
+    __syncthreads();
+  }
+  const int4* N = kSmem ? s_nodes : nodes;
+  const TH* TT = kSmem ? s_thr : thr;
+  for (int64_t row = (int64_t)blockIdx.x * kThreads + threadIdx.x; row < n; row += (int64_t)gridDim.x * kThreads) {
+    const T* x = X + row * ldx;
+    int node = 0;
+    int4 r = N[0];
+    while (r.x >= 0) {
+      const TH v = (TH)x[r.x];
+      node = r.y + (v <= TT[node] ? 0 : 1);
+      r = N[node];
+    }
+    if (out_leaf) out_leaf[row] = node;
+    if (out_label) out_label[row] = r.z;
+  }
+}
+
+__global__ void k_pack_nodes(const int* feature, const int* left, const int* label, int n, int4* out) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = make_int4(feature[i], left[i], label ? label[i] : 0, 0);
+}
+
+template <typename T, typename TH>
+int launch(const void* X, int64_t n, int64_t ldx, const int4* nodes, const void* thr, int n_nodes, int* out_leaf,
+           int* out_label, cudaStream_t stream) {
+  int64_t blocks = (n + kThreads - 1) / kThreads;
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  if (n_nodes <= kSmemNodes) {
+    const int smem = n_nodes * (int)(sizeof(int4) + sizeof(TH));
+    auto kern = k_predict<T, TH, true>;
+    MTB_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem > 48 * 1024 ? smem : 48 * 1024));
+    kern<<<(unsigned)blocks, kThreads, smem, stream>>>((const T*)X, n, ldx, nodes, (const TH*)thr, n_nodes, out_leaf,
+                                                       out_label);
+  } else {
+    k_predict<T, TH, false><<<(unsigned)blocks, kThreads, 0, stream>>>((const T*)X, n, ldx, nodes, (const TH*)thr,
+                                                                       n_nodes, out_leaf, out_label);
+  }
+  MTB_CHECK(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace
+
+// packs {feature, left, label} into 16-byte node records (scratch: int4[n_nodes])
+extern "C" int mtb_pack_nodes(const int32_t* feature, const int32_t* left, const int32_t* leaf_label, int64_t n_nodes,
+                              void* packed_out, void* stream) {
+  k_pack_nodes<<<(unsigned)((n_nodes + 255) / 256), 256, 0, (cudaStream_t)stream>>>(feature, left, leaf_label,
+                                                                                    (int)n_nodes, (int4*)packed_out);
+  MTB_CHECK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int mtb_predict(const void* X, int dtype, int64_t n, int64_t F, int64_t ldx, const void* packed_nodes,
+                           const void* threshold, int64_t n_nodes, int32_t* out_leaf, int32_t* out_label,
+                           void* stream) {
+  (void)F;
+  if (n <= 0) return 0;
+  const int4* nodes = (const int4*)packed_nodes;
+  cudaStream_t s = (cudaStream_t)stream;
+  switch (dtype) {
+    case 0: return launch<float, float>(X, n, ldx, nodes, threshold, (int)n_nodes, out_leaf, out_label, s);
+    case 1: return launch<uint8_t, int>(X, n, ldx, nodes, threshold, (int)n_nodes, out_leaf, out_label, s);
+    case 2: return launch<double, double>(X, n, ldx, nodes, threshold, (int)n_nodes, out_leaf, out_label, s);
+    default:
+      mtb_set_error("predict", "dtype must be 0 (f32), 1 (u8) or 2 (f64)", __FILE__, __LINE__);
+      return -2;
+  }
+}
