@@ -1,0 +1,328 @@
+#!/usr/bin/env python
+"""Headline benchmark: depth-10 tree fit on synthetic 100M x 64 (256 bins, 10 classes).
+
+Contract (see BASELINE.json): ``python bench.py --gpus N --steps K --warmup W`` prints ONE
+JSON line on rank 0.  A *step* is one complete ``fit`` (one training pass over the fixed
+synthetic matrix).  ``value`` is whole-job rows/s (total rows / max-over-ranks device time
+per fit); strong scaling: the 100M rows are split across the N ranks.
+
+* device-timed arm (``value``): public API ``ParallelDecisionTreeClassifier.fit`` on
+  device-resident tensors, CUDA events around K fits, max over ranks.
+* ``e2e``: the same API call on *pinned host* tensors — every step copies the step's inputs
+  host->device and reads the fitted tree back device->host.
+* ``--impl reference``: the unmodified reference (baseline/_ref) over the mpi4py shim; it
+  cannot run the named shape, so it is measured at the largest row count that fits a time
+  budget and says so in ``config``.
+"""
+
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+BASELINE_PUBLISHED = None  # BASELINE.json "published": {} -> no number to divide by
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--rows", type=int, default=100_000_000, help="total rows (all ranks)")
+    ap.add_argument("--features", type=int, default=64)
+    ap.add_argument("--classes", type=int, default=10)
+    ap.add_argument("--depth", type=int, default=10)
+    ap.add_argument("--reduce", default=os.environ.get("MTB_REDUCE", "auto"), choices=["auto", "p2p", "nccl"])
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--ref-budget-s", type=float, default=float(os.environ.get("MTB_REF_BUDGET_S", "150")))
+    return ap.parse_args()
+
+
+# ----------------------------------------------------------------------------- clocks
+class ClockSampler:
+    QUERY = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+             "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int = 0):
+        self.proc = None
+        self.gpu = gpu_index
+        self.path = f"/tmp/mtb_clocks_{os.getpid()}.csv"
+
+    def start(self):
+        try:
+            self.fh = open(self.path, "w")
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.QUERY}", "--format=csv,noheader,nounits", "-lms", "100",
+                 "-i", str(self.gpu)], stdout=self.fh, stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        self.fh.close()
+        sm, mx, reasons = [], [], set()
+        for line in open(self.path):
+            p = [x.strip() for x in line.split(",")]
+            if len(p) < 9:
+                continue
+            try:
+                sm.append(float(p[1]))
+                mx.append(float(p[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), p[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        try:
+            os.remove(self.path)
+        except OSError:
+            pass
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------ ours
+def synth_shard(torch, dev, rows, features, classes, seed):
+    """Seeded synthetic shard on the device: uint8 bin codes + labels with real structure."""
+    g = torch.Generator(device=dev).manual_seed(seed)
+    X = torch.randint(0, 256, (rows, features), dtype=torch.uint8, device=dev, generator=g)
+    k = min(8, features)
+    w = torch.tensor([1.0, -0.8, 0.6, 0.5, -0.4, 0.3, 0.25, -0.2][:k], device=dev)
+    score = torch.zeros(rows, device=dev)
+    for j in range(k):  # column-wise to bound temporary memory
+        score += (X[:, j].float() - 127.5) * w[j]
+    score += 40.0 * torch.randn(rows, device=dev, generator=g)
+    # fixed class boundaries (identical on every rank): quantiles of the analytic score distribution
+    sd = float((w.pow(2).sum() * (256 ** 2 - 1) / 12.0 + 1600.0).sqrt())
+    qs = torch.distributions.Normal(0.0, sd).icdf(torch.linspace(0, 1, classes + 1, device=dev)[1:-1])
+    y = torch.bucketize(score, qs).to(torch.uint8)
+    return X, y
+
+
+def run_ours(a):
+    import torch
+    import torch.distributed as dist
+
+    from mpitree_b200.ops import cuda_engine
+    from mpitree_b200.parallel.comm import init_process_group_from_env
+    from mpitree_b200.tree import ParallelDecisionTreeClassifier
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != a.gpus:
+        if world == 1 and a.gpus > 1:
+            # convenience: re-launch ourselves under torchrun
+            cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={a.gpus}",
+                   "--master-addr", "127.0.0.1", "--master-port", os.environ.get("MASTER_PORT", "29541"),
+                   os.path.abspath(__file__)] + sys.argv[1:]
+            sys.exit(subprocess.call(cmd))
+        raise SystemExit(f"--gpus {a.gpus} but WORLD_SIZE={world}")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        init_process_group_from_env("nccl")
+
+    lo, hi = a.rows * rank // world, a.rows * (rank + 1) // world
+    X, y = synth_shard(torch, dev, hi - lo, a.features, a.classes, seed=1234 + rank)
+    reduce = a.reduce
+    clf = ParallelDecisionTreeClassifier(max_depth=a.depth, data_layout="sharded", device="cuda")
+    if reduce != "auto":
+        clf.builder_kwargs = {"reduce": reduce}
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fit_fn, steps, warmup, sample_clocks):
+        for _ in range(warmup):
+            fit_fn()
+        barrier()
+        sampler = ClockSampler(local) if (sample_clocks and rank == 0) else None
+        if sampler:
+            sampler.start()
+        l0 = cuda_engine.KERNEL_LAUNCHES["count"]
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record()
+        for _ in range(steps):
+            fit_fn()
+        e.record()
+        barrier()
+        ms = s.elapsed_time(e)
+        launches = cuda_engine.KERNEL_LAUNCHES["count"] - l0
+        clocks = sampler.stop() if sampler else None
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item()), launches, clocks
+
+    # ---- device-timed arm
+    ms_total, launches, clocks = timed(lambda: clf.fit(X, y), a.steps, a.warmup, True)
+    ms_step = ms_total / a.steps
+    value = a.rows / (ms_step / 1e3)
+    n_nodes = clf.flat_tree_.n_nodes
+    acc_rows = min(1_000_000, X.shape[0])
+    acc = float((clf.predict(X[:acc_rows]) == y[:acc_rows].to(torch.int64)).float().mean().item())
+
+    # ---- end-to-end arm: pinned host inputs, tree read back
+    e2e = None
+    if not a.no_e2e:
+        Xh = torch.empty(X.shape, dtype=X.dtype).pin_memory()
+        yh = torch.empty(y.shape, dtype=y.dtype).pin_memory()
+        Xh.copy_(X)
+        yh.copy_(y)
+        torch.cuda.synchronize()
+        del X, y
+        torch.cuda.empty_cache()
+        e_steps = max(1, min(a.steps, 3))
+        ms_e2e, _, _ = timed(lambda: clf.fit(Xh, yh), e_steps, 1, False)
+        ft = clf.flat_tree_
+        d2h = sum(int(getattr(ft, k).nbytes) for k in ("feature", "bin", "left", "parent", "depth", "gain", "counts"))
+        e2e = {
+            "value": a.rows / (ms_e2e / e_steps / 1e3),
+            "unit": "rows/s",
+            "ms_per_step": ms_e2e / e_steps,
+            "h2d_bytes_per_step": int(Xh.numel() * Xh.element_size() + yh.numel() * yh.element_size()) * world,
+            "d2h_bytes_per_step": d2h * world,
+            "steps": e_steps,
+        }
+
+    if rank == 0:
+        stats = getattr(cuda_engine.fit_from_torch, "last_stats", None)
+        out = {
+            "metric": "fit_rows_per_s_depth10_100Mx64",
+            "value": value,
+            "unit": "rows/s",
+            "n_gpus": world,
+            "steps": a.steps,
+            "warmup": a.warmup,
+            "ms_per_step": ms_step,
+            "fit_seconds": ms_step / 1e3,
+            "higher_is_better": True,
+            "scaling": "strong",
+            "vs_baseline": None,
+            "dtype": "u8 bin codes / u32 counts / fp64 gain",
+            "data": "synthetic (seeded, generated on device; random-init, no files)",
+            "impl": "ours",
+            "config": {
+                "model": "entropy decision tree, level-wise fused split search",
+                "rows": a.rows, "features": a.features, "bins": 256, "classes": a.classes, "max_depth": a.depth,
+                "global_batch": a.rows, "seq_len": a.features,
+                "parallelism": f"row-sharded dp{world}" + ("" if world == 1 else f" ({getattr(stats, 'reduce', reduce)} histogram reduction)"),
+                "l2_policy": "inputs (>= 6.4 GB per fit) are far larger than the 126 MB L2; no explicit flush",
+                "tree_nodes": n_nodes, "train_acc_first_1M": acc,
+            },
+            "clocks": clocks,
+            "e2e": e2e,
+            "gpu_launches": launches,
+        }
+        print(json.dumps(out))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+# ------------------------------------------------------------------------- reference
+def run_reference(a):
+    import numpy as np
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    try:
+        from baseline.oracle import load_reference
+
+        ref = load_reference()
+        if ref is None:
+            raise RuntimeError("baseline/_ref is missing (python baseline/install_ref.py)")
+    except Exception as exc:  # noqa: BLE001
+        if rank == 0:
+            print(json.dumps({"impl": "reference", "unavailable": str(exc).splitlines()[0][:200]}))
+        return
+
+    def data(n):
+        rng = np.random.default_rng(1234)
+        X = rng.integers(0, 256, size=(n, a.features)).astype(np.float64)
+        w = np.array([1.0, -0.8, 0.6, 0.5, -0.4, 0.3, 0.25, -0.2][: min(8, a.features)])
+        score = (X[:, : len(w)] - 127.5) @ w + 40.0 * rng.normal(size=n)
+        qs = np.quantile(score, np.linspace(0, 1, a.classes + 1)[1:-1])
+        return X, np.digitize(score, qs)
+
+    cls = ref.ParallelDecisionTreeClassifier if world > 1 else ref.DecisionTreeClassifier
+
+    def fit_time(n):
+        X, y = data(n)
+        if world > 1:
+            ref.ParallelDecisionTreeClassifier.WORLD_COMM.allgather(0)  # align ranks
+        t0 = time.perf_counter()
+        cls(max_depth=a.depth).fit(X, y)
+        return time.perf_counter() - t0
+
+    # calibrate on a small problem, then take the largest size that fits the time budget
+    t_small = fit_time(250)
+    fits = a.steps + a.warmup
+    n = 250
+    for cand in (8000, 4000, 2000, 1000, 500):
+        est = t_small * (cand / 250) ** 1.7
+        if est * fits <= a.ref_budget_s:
+            n = cand
+            break
+    if world > 1:  # all ranks must agree on n
+        n = min(ref.ParallelDecisionTreeClassifier.WORLD_COMM.allgather(n))
+    for _ in range(a.warmup):
+        fit_time(n)
+    times = [fit_time(n) for _ in range(a.steps)]
+    if world > 1:
+        times = [max(t) for t in zip(*ref.ParallelDecisionTreeClassifier.WORLD_COMM.allgather(times))]
+    sec = sum(times) / len(times)
+    if rank == 0:
+        print(json.dumps({
+            "impl": "reference",
+            "metric": "fit_rows_per_s_depth10_100Mx64",
+            "value": n / sec,
+            "unit": "rows/s",
+            "n_gpus": world,
+            "steps": a.steps,
+            "warmup": a.warmup,
+            "ms_per_step": sec * 1e3,
+            "higher_is_better": True,
+            "scaling": "strong",
+            "vs_baseline": None,
+            "dtype": "float64 (python objects)",
+            "data": "synthetic (seeded numpy), pre-quantised to 256 distinct values per feature",
+            "config": {
+                "model": "reference mpitree DecisionTreeClassifier (CPU, unmodified, mpi4py shim transport)",
+                "rows": n, "features": a.features, "bins": 256, "classes": a.classes, "max_depth": a.depth,
+                "parallelism": f"{world} CPU rank(s), replicated data",
+                "note": "the reference cannot run the named 100M x 64 shape (exact search is O(U*n*F) per feature "
+                        "per node on object arrays, data replicated per rank); measured at the largest row count "
+                        "whose (steps+warmup) fits fit the time budget, rows/s is for that size",
+            },
+            "gpu_launches": 0,
+        }))
+
+
+if __name__ == "__main__":
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)

@@ -90,7 +90,12 @@ typedef struct MtbCtx {
   int64_t peer_rec[MTB_MAX_WORLD];    /* peers' record mailboxes (mapped)       */
   int64_t peer_flags[MTB_MAX_WORLD];  /* peers' barrier flags (mapped)          */
   int64_t epoch;                      /* barrier epoch, advanced by the host    */
-  int64_t reserved[8];
+  /* ---- host-computed (k/n)*log2(k/n) table for n <= plogp_n: entry (n-1)*n/2 + (k-1), f64.
+   * Small nodes are where rounding-level ties happen; using the host's own log2 values there
+   * makes the device arithmetic bit-identical to numpy's.  0 = no table. ---- */
+  int64_t plogp;
+  int64_t plogp_n;
+  int64_t reserved[6];
 } MtbCtx;
 
 const char* mtb_last_error(void);

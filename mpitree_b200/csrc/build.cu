@@ -353,6 +353,8 @@ __device__ void gain_pair(const MtbCtx& ctx, uint32_t* slab, int slot, int f) {
   double best = INFINITY;
   int best_bin = 0x7fffffff;
   const int crit = (int)ctx.criterion, dm = (int)ctx.dot_mode;
+  const double* plogp = ptr_of<const double>(ctx.plogp);
+  const uint32_t plogp_n = (uint32_t)ctx.plogp_n;
   for (int j = 0; j < BPL; ++j) {
     if (!(present >> j & 1u)) continue;
     const uint32_t* L = my + j * C;
@@ -360,8 +362,8 @@ __device__ void gain_pair(const MtbCtx& ctx, uint32_t* slab, int slot, int f) {
     for (int c = 0; c < C; ++c) nl += L[c];
     const uint32_t nr = n - nl;
     if (nr == 0) continue;  // right side empty: not a usable split
-    double hl = impurity(C, [&](int c) { return L[c]; }, nl, crit);
-    double hr = impurity(C, [&](int c) { return last[c] - L[c]; }, nr, crit);
+    double hl = impurity(C, [&](int c) { return L[c]; }, nl, crit, plogp, plogp_n);
+    double hr = impurity(C, [&](int c) { return last[c] - L[c]; }, nr, crit, plogp, plogp_n);
     double cost = split_cost(nl, nr, hl, hr, dm);
     if (cost < best) {  // strict: first (lowest) bin wins ties inside the lane
       best = cost;
@@ -469,7 +471,8 @@ __device__ void finalize_phase(const MtbCtx& ctx, int* smem_warp) {
       for (int c = 0; c < C; ++c) t_counts[(int64_t)node * C + c] = cnt[c];
       uint32_t ntot;
       if (!is_terminal([&](int c) { return cnt[c]; }, C, depth, ctx, ntot)) {
-        const double hp = impurity(C, [&](int c) { return cnt[c]; }, ntot, (int)ctx.criterion);
+        const double hp = impurity(C, [&](int c) { return cnt[c]; }, ntot, (int)ctx.criterion,
+                                   ptr_of<const double>(ctx.plogp), (uint32_t)ctx.plogp_n);
         bool have = false;
         for (int f = 0; f < F; ++f) {
           const double cost = fb_cost[(int64_t)s * F + f];

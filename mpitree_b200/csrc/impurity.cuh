@@ -42,17 +42,23 @@ __device__ __forceinline__ double numpy_sum(int k, Next next) {
 
 // Impurity of a class-count vector read through `cnt(c)`, total n > 0.
 // criterion 0: entropy (base 2), 1: gini.
+// `plogp` (may be null) is the host's table of (k/n)*log2(k/n) for n <= plogp_n.
 template <typename Cnt>
-__device__ __forceinline__ double impurity(int C, Cnt cnt, uint32_t n, int criterion) {
+__device__ __forceinline__ double impurity(int C, Cnt cnt, uint32_t n, int criterion, const double* plogp = nullptr,
+                                           uint32_t plogp_n = 0) {
   int k = 0;
   for (int c = 0; c < C; ++c) k += (cnt(c) != 0u);
   const double dn = (double)n;
+  const double* row = (criterion == 0 && plogp != nullptr && n <= plogp_n)
+                          ? plogp + ((size_t)(n - 1) * n) / 2 - 1
+                          : nullptr;
   int c = 0;
   auto next = [&]() -> double {
     uint32_t v;
     do {
       v = cnt(c++);
     } while (v == 0u);
+    if (row) return row[v];
     double p = __ddiv_rn((double)v, dn);
     return criterion == 0 ? __dmul_rn(p, log2(p)) : __dmul_rn(p, p);
   };

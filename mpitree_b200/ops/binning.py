@@ -149,9 +149,9 @@ class BinMapper:
         v = self.edges[feature][bin_code]
         return v.item() if isinstance(v, np.generic) else v
 
-    def edges_matrix(self, dtype=np.float32) -> np.ndarray:
-        """(n_features, max_bins) array of edges padded with +inf (device encode table)."""
-        out = np.full((self.n_features, self.max_bins), np.inf, dtype=dtype)
+    def edges_matrix(self, dtype=np.float64) -> np.ndarray:
+        """(n_features, 256) array of edges padded with +inf (device encode table)."""
+        out = np.full((self.n_features, 256), np.inf, dtype=dtype)
         for f, e in enumerate(self.edges):
             if e.dtype == object:
                 raise TypeError("object/string features are encoded on the host")

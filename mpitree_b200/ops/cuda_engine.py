@@ -85,6 +85,30 @@ def _p(t) -> int:
     return int(t.data_ptr())
 
 
+PLOGP_N = 1024
+_PLOGP_CACHE: dict = {}
+
+
+def plogp_table(device):
+    """Device table of ``(k/n) * log2(k/n)`` for ``1 <= k <= n <= PLOGP_N`` computed by numpy.
+
+    Rounding-level ties between mathematically equal split costs occur in small
+    nodes; evaluating those with the host's own ``np.log2`` values makes the device
+    arithmetic bit-identical to the reference's numpy arithmetic there
+    (``mpitree/tree/decision_tree.py:49-51``).
+    """
+    import torch
+
+    key = str(device)
+    if key not in _PLOGP_CACHE:
+        rows = []
+        for n in range(1, PLOGP_N + 1):
+            p = np.arange(1, n + 1) / n
+            rows.append(p * np.log2(p))
+        _PLOGP_CACHE[key] = torch.from_numpy(np.concatenate(rows)).to(device)
+    return _PLOGP_CACHE[key]
+
+
 # ---------------------------------------------------------------------------
 # device data set: tiled codes + labels
 # ---------------------------------------------------------------------------
@@ -248,6 +272,8 @@ class TreeBuilder:
         ctx.min_samples_split = int(params.min_samples_split)
         ctx.criterion = 0 if params.criterion == "entropy" else 1
         ctx.dot_mode = probe_dot_mode()
+        self._plogp = plogp_table(dev)
+        ctx.plogp, ctx.plogp_n = _p(self._plogp), PLOGP_N
         ctx.world, ctx.rank = self.world, self.rank
 
         # features per shared-memory tile: the largest that leaves >= 2 TMA stages
@@ -538,7 +564,17 @@ def fit_from_torch(X, y, params: SplitParams, *, max_bins: int = 256, comm=None,
     y_dev = y.to(dev, non_blocking=True)
     if y_dev.dtype.is_floating_point or y_dev.dtype == torch.bool:
         raise TypeError("class labels must be non-negative integers")
-    classes_t = torch.unique(y_dev)
+    if y_dev.numel() == 0:
+        raise ValueError("Found array with 0 sample(s)")
+    y_min, y_max = int(y_dev.min()), int(y_dev.max())
+    if y_min < 0:
+        raise ValueError("class labels must be non-negative integers")
+    if y_max < (1 << 16):  # small label range: one counting pass instead of a sort
+        present = torch.bincount(y_dev.view(-1).to(torch.int64) if y_dev.dtype != torch.uint8 else y_dev.view(-1).int(),
+                                 minlength=y_max + 1)
+        classes_t = torch.nonzero(present, as_tuple=False).view(-1)
+    else:
+        classes_t = torch.unique(y_dev)
     classes = classes_t.cpu().numpy().astype(np.int64)
     if comm is not None and comm.size > 1:
         classes = np.unique(np.concatenate(comm.allgather_object(classes)))
@@ -547,7 +583,10 @@ def fit_from_torch(X, y, params: SplitParams, *, max_bins: int = 256, comm=None,
         raise ValueError("class labels must be non-negative integers")
     if len(classes) > MAX_CLASSES:
         raise ValueError(f"the CUDA engine supports at most {MAX_CLASSES} classes")
-    y_codes = torch.bucketize(y_dev, classes_t.to(y_dev.dtype))
+    if np.array_equal(classes, np.arange(len(classes))):
+        y_codes = y_dev  # labels already are 0..C-1
+    else:
+        y_codes = torch.bucketize(y_dev.to(torch.int64), classes_t.to(torch.int64))
 
     if X.dtype == torch.uint8:
         mapper = BinMapper(edges=[np.arange(256, dtype=np.uint8) for _ in range(F)], lossless=np.ones(F, bool), max_bins=256)

@@ -192,7 +192,8 @@ class DecisionTreeClassifier(ClassifierMixin, BaseEstimator):
             from ..ops import cuda_engine
 
             flat, mapper = cuda_engine.fit_from_host(
-                X, y_codes, len(classes), params, max_bins=self.max_bins, comm=comm
+                X, y_codes, len(classes), params, max_bins=self.max_bins, comm=comm,
+                builder_kwargs=getattr(self, "builder_kwargs", None),
             )
         else:
             summaries = None
@@ -250,6 +251,7 @@ class DecisionTreeClassifier(ClassifierMixin, BaseEstimator):
         flat, mapper, classes = cuda_engine.fit_from_torch(
             X, y, self._params(), max_bins=self.max_bins, comm=comm,
             replicated=getattr(self, "data_layout", "sharded") == "replicated",
+            builder_kwargs=getattr(self, "builder_kwargs", None),
         )
         self.n_features_ = int(X.shape[1])
         self.n_features_in_ = int(X.shape[1])
