@@ -136,6 +136,18 @@ int mtb_pack_nodes(const int32_t* feature, const int32_t* left, const int32_t* l
 int mtb_predict(const void* X, int dtype, int64_t n, int64_t F, int64_t ldx, const void* packed_nodes,
                 const void* threshold, int64_t n_nodes, int32_t* out_leaf, int32_t* out_label, void* stream);
 
+/* Prediction for callers that cannot allocate device memory (a server that pre-partitioned the
+ * GPU and forbids later cudaMalloc; a plugin running inside another application's allocator).
+ * Same result as mtb_pack_nodes + mtb_predict, but the node-record scratch is a fixed 1 MiB array
+ * inside the library (held by every GPU that loads it), so n_nodes must be <= 65536 or the call
+ * fails with an error.  Takes the raw tree arrays (feature/left/leaf_label i32 [n_nodes], threshold
+ * typed as for mtb_predict).  Allocates nothing.  The first call on a device resolves the array's
+ * address: make it before any stream capture.  Calls share the array: overlapping calls race.
+ * This entry point has no counterpart in the reference.                                          */
+int mtb_predict_noalloc(const void* X, int dtype, int64_t n, int64_t F, int64_t ldx, const int32_t* feature,
+                        const void* threshold, const int32_t* left, const int32_t* leaf_label, int64_t n_nodes,
+                        int32_t* out_leaf, int32_t* out_label, void* stream);
+
 /* ---- K5 / comm runtime -------------------------------------------------------------- */
 int mtb_ipc_handle_size(void);
 int mtb_ipc_get_handle(void* dev_ptr, void* handle_out);          /* cudaIpcGetMemHandle   */

@@ -7,6 +7,8 @@
 // consecutively (right = left + 1), so one shared-memory load per level decides the
 // step.  Trees up to kSmemNodes nodes are staged in shared memory, larger ones are
 // read through L1/L2.
+#include <stdio.h>
+
 #include "common.cuh"
 
 namespace {
@@ -103,4 +105,83 @@ extern "C" int mtb_predict(const void* X, int dtype, int64_t n, int64_t F, int64
       mtb_set_error("predict", "dtype must be 0 (f32), 1 (u8) or 2 (f64)", __FILE__, __LINE__);
       return -2;
   }
+}
+
+// ---------------------------------------------------------------------------------------
+// mtb_predict_noalloc — prediction for callers that cannot obtain device memory.
+//
+// Who needs this.  mtb_predict() wants a 16-byte-per-node scratch buffer that the caller
+// has to allocate.  Some callers have no way to do that: a serving process that carved up
+// the whole GPU at start-up and forbids any later cudaMalloc (an allocation may fail because
+// the pool already owns every byte, and cudaMalloc/cudaFree synchronise the device, which
+// stalls the other streams of a latency-bound server); or a C plugin invoked from inside a
+// host application's operator, where every device byte belongs to that application's
+// allocator and this library is only handed input and output pointers.
+//
+// What it does instead.  The node-record scratch lives in the fixed array below, which is
+// part of the library image: every GPU that loads the library holds these
+// MTB_NOALLOC_MAX_NODES * 16 bytes (1 MiB) until the process exits.  Trees with more nodes
+// are rejected with an error; nothing is truncated.
+//
+// Rules for callers.
+//  * Inputs (X, feature, threshold, left, leaf_label) and outputs (out_leaf, out_label) are
+//    still the caller's buffers; the device that owns them must be current.
+//  * The first call on each device looks up the array's device address (one
+//    cudaGetSymbolAddress, no allocation).  Make that first call before starting any stream
+//    capture on that device.
+//  * All calls on one device share the one array, and it keeps whatever the previous call
+//    packed into it.  Each call rewrites records [0, n_nodes) before reading them and never
+//    reads past n_nodes, so nothing needs clearing between calls.  Two calls whose GPU work
+//    overlaps (different streams, or different host threads) race on the array: serialise
+//    them, e.g. by using one stream.
+//  * No cudaMalloc, cudaFree or other allocating routine is reached from this entry point.
+// ---------------------------------------------------------------------------------------
+#include <mutex>
+
+#define MTB_NOALLOC_MAX_NODES 65536
+#define MTB_NOALLOC_MAX_DEVICES 64
+
+static __device__ __align__(256) unsigned char g_noalloc_nodes[(size_t)MTB_NOALLOC_MAX_NODES * 16];
+
+static std::mutex g_noalloc_mutex;
+static void* g_noalloc_addr[MTB_NOALLOC_MAX_DEVICES] = {nullptr};
+
+// Device address of g_noalloc_nodes on the current device.  In host code the symbol's name is
+// only a handle, never a pointer a kernel may use, so the address is resolved once per device.
+static int noalloc_scratch(void** out) {
+  int dev = -1;
+  MTB_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= MTB_NOALLOC_MAX_DEVICES) {
+    mtb_set_error("mtb_predict_noalloc", "device ordinal out of range (0..63)", __FILE__, __LINE__);
+    return -2;
+  }
+  std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+  if (g_noalloc_addr[dev] == nullptr) {
+    void* ptr = nullptr;
+    MTB_CHECK(cudaGetSymbolAddress((void**)&ptr, g_noalloc_nodes));
+    g_noalloc_addr[dev] = ptr;
+  }
+  *out = g_noalloc_addr[dev];
+  return 0;
+}
+
+extern "C" int mtb_predict_noalloc(const void* X, int dtype, int64_t n, int64_t F, int64_t ldx,
+                                   const int32_t* feature, const void* threshold, const int32_t* left,
+                                   const int32_t* leaf_label, int64_t n_nodes, int32_t* out_leaf,
+                                   int32_t* out_label, void* stream) {
+  if (n_nodes < 1 || n_nodes > MTB_NOALLOC_MAX_NODES) {
+    char why[160];
+    snprintf(why, sizeof(why), "tree has %lld nodes; this entry point holds at most %d (use mtb_predict with your own scratch)",
+             (long long)n_nodes, MTB_NOALLOC_MAX_NODES);
+    mtb_set_error("mtb_predict_noalloc", why, __FILE__, __LINE__);
+    return -3;
+  }
+  if (n <= 0) return 0;
+  void* scratch = nullptr;
+  int rc = noalloc_scratch(&scratch);
+  if (rc != 0) return rc;
+  k_pack_nodes<<<(unsigned)((n_nodes + 255) / 256), 256, 0, (cudaStream_t)stream>>>(feature, left, leaf_label,
+                                                                                    (int)n_nodes, (int4*)scratch);
+  MTB_CHECK(cudaGetLastError());
+  return mtb_predict(X, dtype, n, F, ldx, scratch, threshold, n_nodes, out_leaf, out_label, stream);
 }
