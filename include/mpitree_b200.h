@@ -86,16 +86,22 @@ typedef struct MtbCtx {
   int64_t unit_prefix;           /* i32 [m_cap+1] scratch for work decomposition */
   int64_t depth;                 /* depth of the current level                  */
   /* ---- multi-GPU (filled by the comm runtime; zero when world == 1) ---- */
-  int64_t peer_hist[MTB_MAX_WORLD];   /* peers' staging buffers (mapped)        */
+  /* Feature f is owned by rank f / fpo.  Rank o's staging area is u32 [world][h_cap][fpo*B*C]:
+   * source rank p pushes its partial counts of o's features for slot s to [p][s][...].
+   * Rank q's record mailbox holds fb_cost | fb_bin | fb_left | node_cnt back to back (the local
+   * fb_* / node_cnt pointers above point into the own mailbox), written by the owners.        */
+  int64_t peer_hist[MTB_MAX_WORLD];   /* peers' staging areas (mapped)          */
   int64_t peer_rec[MTB_MAX_WORLD];    /* peers' record mailboxes (mapped)       */
-  int64_t peer_flags[MTB_MAX_WORLD];  /* peers' barrier flags (mapped)          */
-  int64_t epoch;                      /* barrier epoch, advanced by the host    */
+  int64_t peer_flags[MTB_MAX_WORLD];  /* peers' barrier flags u32[world] (mapped) */
+  int64_t epoch;                      /* barrier epoch base for this level (host advances by 2) */
   /* ---- host-computed (k/n)*log2(k/n) table for n <= plogp_n: entry (n-1)*n/2 + (k-1), f64.
    * Small nodes are where rounding-level ties happen; using the host's own log2 values there
    * makes the device arithmetic bit-identical to numpy's.  0 = no table. ---- */
   int64_t plogp;
   int64_t plogp_n;
-  int64_t reserved[6];
+  int64_t h_cap;                      /* histogram slabs per side == staging slots per source */
+  int64_t fpo;                        /* features per owner rank (F when world == 1)          */
+  int64_t reserved[4];
 } MtbCtx;
 
 const char* mtb_last_error(void);
@@ -122,7 +128,8 @@ int mtb_level_gain(const MtbCtx* ctx, void* stream);      /* derive siblings, pr
 int mtb_level_finalize(const MtbCtx* ctx, void* stream);  /* arg-max, children, next frontier        */
 int mtb_level_partition(const MtbCtx* ctx, void* stream); /* stream compaction into the other side   */
 int mtb_level_commit(const MtbCtx* ctx, void* stream);    /* next frontier's row segments            */
-/* One cooperative launch doing plan + hist + (peer reduction) + gain + finalize.      */
+int mtb_level_push(const MtbCtx* ctx, void* stream);      /* world > 1: push partial slabs to their owners */
+/* One cooperative launch doing plan + hist + (peer push + barriers) + gain + finalize. */
 int mtb_level_fused(const MtbCtx* ctx, void* stream);
 /* Shared memory / launch geometry the hist phase will use for this ctx (for reports). */
 int mtb_hist_config(const MtbCtx* ctx, int* threads, int* smem_bytes, int* stages, int* rows_per_stage);
@@ -154,6 +161,11 @@ int mtb_ipc_get_handle(void* dev_ptr, void* handle_out);          /* cudaIpcGetM
 int mtb_ipc_open_handle(const void* handle, void** dev_ptr_out);  /* cudaIpcOpenMemHandle  */
 int mtb_ipc_close(void* dev_ptr);
 int mtb_enable_peer_access(int peer_device);
+int mtb_can_access_peer(int device, int peer);
+/* The only allocating entry points: raw cudaMalloc/cudaFree for peer-visible (IPC) regions. */
+int mtb_device_malloc(int64_t bytes, void** out);
+int mtb_device_free(void* ptr);
+int mtb_memset_async(void* ptr, int value, int64_t bytes, void* stream);
 /* u32 sum all-reduce over peer-mapped buffers.  bufs[r] = rank r's symmetric buffer
  * (count u32 in, count u32 scratch after it), flags[r] = rank r's flag words.
  * algo: 0 one-shot, 1 two-shot.  All ranks must call with the same epoch.              */

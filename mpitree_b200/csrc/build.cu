@@ -281,22 +281,89 @@ __global__ void __launch_bounds__(kHistThreads, 1) k_hist(const __grid_constant_
 }
 
 // ------------------------------------------------------------------------ gain
-// One warp per (slot, feature).  `slab` is this warp's padded shared-memory copy of
+// ------------------------------------------------------------- peer helpers
+// Record mailbox layout (identical on every rank): fb_cost | fb_bin | fb_left | node_cnt.
+struct Mailbox {
+  double* cost;
+  int* bin;
+  uint32_t* left;
+  uint32_t* node_cnt;
+};
+__device__ __forceinline__ Mailbox mailbox_at(const MtbCtx& ctx, int64_t base) {
+  Mailbox m;
+  uint8_t* p = ptr_of<uint8_t>(base);
+  const int64_t MF = ctx.m_cap * ctx.F;
+  m.cost = reinterpret_cast<double*>(p);
+  m.bin = reinterpret_cast<int*>(p + MF * 8);
+  m.left = reinterpret_cast<uint32_t*>(p + MF * 12);
+  m.node_cnt = reinterpret_cast<uint32_t*>(p + MF * 12 + MF * ctx.C * 4);
+  return m;
+}
+
+// Cross-GPU barrier inside a cooperative kernel.  Every CTA calls it.  Data written to
+// peers before the call is visible to them after it: grid.sync orders the CTAs' writes
+// before thread 0's system-scope fence and release store of the flag.
+__device__ void peer_barrier(const MtbCtx& ctx, cg::grid_group& grid, uint32_t epoch) {
+  grid.sync();
+  if (blockIdx.x == 0 && threadIdx.x < (unsigned)ctx.world) {
+    __threadfence_system();
+    uint32_t* remote = ptr_of<uint32_t>(ctx.peer_flags[threadIdx.x]) + ctx.rank;
+    st_release_sys_u32(remote, epoch);
+    const uint32_t* mine = ptr_of<const uint32_t>(ctx.peer_flags[ctx.rank]) + threadIdx.x;
+    while ((int32_t)(ld_acquire_sys_u32(mine) - epoch) < 0) {
+    }
+    __threadfence_system();
+  }
+  grid.sync();
+}
+
+// world > 1: copy this rank's partial counts of every BUILD slot to the owners' staging
+// areas with 128-bit stores over NVLink (the own features stay in the local slab).
+__device__ void push_phase(const MtbCtx& ctx) {
+  View v(ctx);
+  const int P = (int)ctx.world, r = (int)ctx.rank;
+  if (P <= 1) return;
+  const int n_slots = v.n_slots();
+  const int F = (int)ctx.F, fpo = (int)ctx.fpo;
+  const int64_t BC = ctx.B * ctx.C;
+  const int64_t region = (int64_t)fpo * BC;  // words per (source, slot) staging cell
+  const int* mode = ptr_of<const int>(ctx.slot_mode);
+  const int64_t items = (int64_t)n_slots * (P - 1);
+  // one (slot, owner) region per CTA iteration
+  for (int64_t it = blockIdx.x; it < items; it += gridDim.x) {
+    const int slot = (int)(it / (P - 1));
+    int o = (int)(it % (P - 1));
+    if (o >= r) ++o;
+    if (mode[slot] != MTB_MODE_BUILD) continue;
+    const int f0 = o * fpo;
+    if (f0 >= F) continue;
+    const int nf = min(fpo, F - f0);
+    const uint4* src = reinterpret_cast<const uint4*>(v.hist_cur() + (int64_t)slot * v.slab_words() + (int64_t)f0 * BC);
+    uint4* dst = reinterpret_cast<uint4*>(ptr_of<uint32_t>(ctx.peer_hist[o]) + ((int64_t)r * ctx.h_cap + slot) * region);
+    const int64_t n16 = (int64_t)nf * BC / 4;
+    for (int64_t i = threadIdx.x; i < n16; i += blockDim.x) st_na_u4(dst + i, ld_nc_u4(src + i));
+  }
+}
+
+__global__ void __launch_bounds__(512) k_push(const __grid_constant__ MtbCtx ctx) { push_phase(ctx); }
+
+// One warp per (slot, owned feature).  `slab` is this warp's padded shared-memory copy of
 // the feature's [B][C] counts: lane L owns bins [L*BPL, (L+1)*BPL) at offset
 // L*(BPL*C+1) so that lane-sequential walks are bank-conflict free.
 __device__ void gain_pair(const MtbCtx& ctx, uint32_t* slab, int slot, int f) {
   View v(ctx);
   const int B = (int)ctx.B, C = (int)ctx.C, F = (int)ctx.F;
+  const int P = (int)ctx.world, r = (int)ctx.rank;
   const int BPL = B / 32;
   const int lane_stride = BPL * C + 1;
   const int lane = lane_id();
   const int mode = ptr_of<const int>(ctx.slot_mode)[slot];
-  double* fb_cost = ptr_of<double>(ctx.fb_cost);
-  int* fb_bin = ptr_of<int>(ctx.fb_bin);
+  const int64_t rec = (int64_t)slot * F + f;
   if (mode == MTB_MODE_NONE) {
-    if (lane == 0) {
-      fb_cost[(int64_t)slot * F + f] = INFINITY;
-      fb_bin[(int64_t)slot * F + f] = -1;
+    if (lane < P) {
+      Mailbox m = mailbox_at(ctx, P > 1 ? ctx.peer_rec[lane] : ctx.fb_cost);
+      m.cost[rec] = INFINITY;
+      m.bin[rec] = -1;
     }
     return;
   }
@@ -309,6 +376,18 @@ __device__ void gain_pair(const MtbCtx& ctx, uint32_t* slab, int slot, int f) {
     const uint32_t* hs = v.hist_cur() + (int64_t)sib * v.slab_words() + (int64_t)f * B * C;
     for (int w = lane; w < words; w += 32) {
       uint32_t x = hp[w] - hs[w];
+      mine[w] = x;
+      int b = w / C, c = w - b * C;
+      slab[(b / BPL) * lane_stride + (b % BPL) * C + c] = x;
+    }
+  } else if (P > 1) {
+    // BUILD on the owner: own partial + the partials the peers pushed into the staging area
+    const int64_t region = ctx.fpo * ctx.B * ctx.C;
+    const uint32_t* stage = ptr_of<const uint32_t>(ctx.peer_hist[r]) + (int64_t)(f - r * (int)ctx.fpo) * B * C;
+    for (int w = lane; w < words; w += 32) {
+      uint32_t x = mine[w];
+      for (int p = 0; p < P; ++p)
+        if (p != r) x += stage[((int64_t)p * ctx.h_cap + slot) * region + w];
       mine[w] = x;
       int b = w / C, c = w - b * C;
       slab[(b / BPL) * lane_stride + (b % BPL) * C + c] = x;
@@ -345,11 +424,6 @@ __device__ void gain_pair(const MtbCtx& ctx, uint32_t* slab, int slot, int f) {
   uint32_t n = 0;
   for (int c = 0; c < C; ++c) n += last[c];
 
-  if (f == 0) {
-    uint32_t* node_cnt = ptr_of<uint32_t>(ctx.node_cnt) + (int64_t)slot * C;
-    for (int c = lane; c < C; c += 32) node_cnt[c] = last[c];
-  }
-
   double best = INFINITY;
   int best_bin = 0x7fffffff;
   const int crit = (int)ctx.criterion, dm = (int)ctx.dot_mode;
@@ -380,35 +454,48 @@ __device__ void gain_pair(const MtbCtx& ctx, uint32_t* slab, int slot, int f) {
     }
   }
   const bool ok = best_bin != 0x7fffffff;
-  if (lane == 0) {
-    fb_cost[(int64_t)slot * F + f] = ok ? best : INFINITY;
-    fb_bin[(int64_t)slot * F + f] = ok ? best_bin : -1;
-  }
-  if (ok) {
-    uint32_t* fl = ptr_of<uint32_t>(ctx.fb_left) + ((int64_t)slot * F + f) * C;
-    const uint32_t* L = slab + (best_bin / BPL) * lane_stride + (best_bin % BPL) * C;
-    for (int c = lane; c < C; c += 32) fl[c] = L[c];
+  const uint32_t* Lb = ok ? slab + (best_bin / BPL) * lane_stride + (best_bin % BPL) * C : last;
+  // publish the record to every rank's mailbox (the own one when world == 1)
+  for (int q = 0; q < P; ++q) {
+    Mailbox m = mailbox_at(ctx, P > 1 ? ctx.peer_rec[q] : ctx.fb_cost);
+    if (lane == 0) {
+      m.cost[rec] = ok ? best : INFINITY;
+      m.bin[rec] = ok ? best_bin : -1;
+    }
+    if (ok)
+      for (int c = lane; c < C; c += 32) m.left[rec * C + c] = Lb[c];
+    if (f == 0)
+      for (int c = lane; c < C; c += 32) m.node_cnt[(int64_t)slot * C + c] = last[c];
   }
   __syncwarp();
 }
 
-__device__ void gain_phase(const MtbCtx& ctx, uint8_t* smem, int warps_per_block) {
+// pass -1: every pair; 0: BUILD/NONE slots only; 1: DERIVE slots only.  With world > 1 a BUILD
+// pair reduces its slab in place, so DERIVE pairs (which read their sibling's reduced slab)
+// must run after a grid-wide sync.
+__device__ void gain_phase(const MtbCtx& ctx, uint8_t* smem, int warps_per_block, int pass) {
   View v(ctx);
   const int F = (int)ctx.F;
-  const int n_pairs = v.n_slots() * F;
+  const int f_lo = (int)(ctx.rank * ctx.fpo);
+  const int f_hi = min(F, f_lo + (int)ctx.fpo);
+  const int n_own = max(0, f_hi - f_lo);
+  const int n_pairs = v.n_slots() * n_own;
   const int slab_words = (int)ctx.B * (int)ctx.C + 32;
   const int w = warp_id();
   if (w >= warps_per_block) return;
   uint32_t* slab = reinterpret_cast<uint32_t*>(smem) + (size_t)w * slab_words;
-  // derive reads a sibling built in this level: pairs are independent otherwise
+  // a DERIVE pair reads a sibling slab completed in the hist phase: pairs are independent
+  const int* mode = ptr_of<const int>(ctx.slot_mode);
   for (int p = blockIdx.x * warps_per_block + w; p < n_pairs; p += gridDim.x * warps_per_block) {
-    gain_pair(ctx, slab, p / F, p % F);
+    const int slot = p / n_own;
+    if (pass >= 0 && (mode[slot] == MTB_MODE_DERIVE) != (pass == 1)) continue;
+    gain_pair(ctx, slab, slot, f_lo + p % n_own);
   }
 }
 
-__global__ void __launch_bounds__(kGainWarps * 32) k_gain(const __grid_constant__ MtbCtx ctx) {
+__global__ void __launch_bounds__(kGainWarps * 32) k_gain(const __grid_constant__ MtbCtx ctx, int pass) {
   extern __shared__ __align__(128) uint8_t smem[];
-  gain_phase(ctx, smem, kGainWarps);
+  gain_phase(ctx, smem, kGainWarps, pass);
 }
 
 // -------------------------------------------------------------------- finalize
@@ -679,6 +766,9 @@ __global__ void k_commit(const __grid_constant__ MtbCtx ctx) {
 }
 
 // ----------------------------------------------------------------- fused level
+// plan -> hist -> [push partial slabs to owners -> peer barrier] -> gain on owned features
+// (records go to every rank's mailbox) -> [peer barrier] -> finalize.  One cooperative
+// launch; with world > 1 no NCCL call and no separate reduction or gain kernel runs.
 template <int FT>
 __global__ void __launch_bounds__(kHistThreads, 1) k_level_fused(const __grid_constant__ MtbCtx ctx) {
   extern __shared__ __align__(128) uint8_t smem[];
@@ -687,9 +777,22 @@ __global__ void __launch_bounds__(kHistThreads, 1) k_level_fused(const __grid_co
   if (blockIdx.x == 0) plan_phase(ctx, smem_warp);
   grid.sync();
   hist_phase<FT>(ctx, smem);
-  grid.sync();
-  gain_phase(ctx, smem, kGainWarps);
-  grid.sync();
+  if (ctx.world > 1) {
+    grid.sync();
+    push_phase(ctx);
+    peer_barrier(ctx, grid, (uint32_t)ctx.epoch + 1u);
+  } else {
+    grid.sync();
+  }
+  if (ctx.world > 1) {
+    gain_phase(ctx, smem, kGainWarps, 0);
+    grid.sync();
+    gain_phase(ctx, smem, kGainWarps, 1);
+    peer_barrier(ctx, grid, (uint32_t)ctx.epoch + 2u);
+  } else {
+    gain_phase(ctx, smem, kGainWarps, -1);
+    grid.sync();
+  }
   if (blockIdx.x == 0) finalize_phase(ctx, smem_warp);
 }
 
@@ -770,12 +873,24 @@ extern "C" int mtb_level_hist(const MtbCtx* ctx, void* stream) {
 extern "C" int mtb_level_gain(const MtbCtx* ctx, void* stream) {
   const int smem = gain_smem(ctx);
   if (set_smem(k_gain, smem)) return -1;
-  int64_t pairs = ctx->n_slots_host * ctx->F;
+  int64_t pairs = ctx->n_slots_host * (ctx->world > 1 ? ctx->fpo : ctx->F);
   int blocks = (int)((pairs + kGainWarps - 1) / kGainWarps);
   int maxb = sm_count() * 2;
   if (blocks > maxb) blocks = maxb;
   if (blocks < 1) blocks = 1;
-  k_gain<<<blocks, kGainWarps * 32, smem, (cudaStream_t)stream>>>(*ctx);
+  if (ctx->world > 1) {
+    k_gain<<<blocks, kGainWarps * 32, smem, (cudaStream_t)stream>>>(*ctx, 0);
+    k_gain<<<blocks, kGainWarps * 32, smem, (cudaStream_t)stream>>>(*ctx, 1);
+  } else {
+    k_gain<<<blocks, kGainWarps * 32, smem, (cudaStream_t)stream>>>(*ctx, -1);
+  }
+  MTB_CHECK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int mtb_level_push(const MtbCtx* ctx, void* stream) {
+  if (ctx->world <= 1) return 0;
+  k_push<<<sm_count() * 2, 512, 0, (cudaStream_t)stream>>>(*ctx);
   MTB_CHECK(cudaGetLastError());
   return 0;
 }

@@ -57,3 +57,28 @@ extern "C" int mtb_enable_peer_access(int peer_device) {
   MTB_CHECK(e);
   return 0;
 }
+
+// ---- raw device allocations for symmetric (peer-mapped) regions -------------------------
+// cudaIpcGetMemHandle needs the base of a cudaMalloc allocation, which a sub-allocating pool
+// (torch's caching allocator) does not give; these two calls are the only allocating entry
+// points of the library and are used once per builder for the peer-visible region.
+extern "C" int mtb_device_malloc(int64_t bytes, void** out) {
+  MTB_CHECK(cudaMalloc(out, (size_t)bytes));
+  return 0;
+}
+
+extern "C" int mtb_device_free(void* ptr) {
+  MTB_CHECK(cudaFree(ptr));
+  return 0;
+}
+
+extern "C" int mtb_memset_async(void* ptr, int value, int64_t bytes, void* stream) {
+  MTB_CHECK(cudaMemsetAsync(ptr, value, (size_t)bytes, (cudaStream_t)stream));
+  return 0;
+}
+
+extern "C" int mtb_can_access_peer(int device, int peer) {
+  int ok = 0;
+  if (cudaDeviceCanAccessPeer(&ok, device, peer) != cudaSuccess) return -1;
+  return ok;
+}

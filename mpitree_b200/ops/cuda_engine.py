@@ -210,15 +210,26 @@ class BuildStats:
     FT: int = 0
     stages: int = 0
     smem_bytes: int = 0
+    reduce: str = "none"
+    world: int = 1
+
+
+_EPOCH = {"next": 0}  # barrier epochs are monotonic for the life of the process
 
 
 class TreeBuilder:
-    """Level-wise builder bound to one :class:`DeviceDataset`.
+    """Level-wise builder bound to one :class:`DeviceDataset` (one rank).
 
-    ``reduce`` selects the cross-rank histogram reduction when ``world > 1``:
-    ``"p2p"`` (fused peer pushes inside the split-search kernel, the product path)
-    or ``"nccl"`` (local histogram kernel -> ``ncclAllReduce`` -> gain kernel, the
-    in-house baseline).
+    Cross-rank histogram reduction when ``world > 1``:
+
+    * ``reduce="p2p"`` — the product path: one cooperative launch per level pushes
+      partial slabs into the owners' staging areas over NVLink, synchronises with
+      in-kernel flags, evaluates gains feature-parallel on the owners and broadcasts
+      16-byte-class best-split records to every rank's mailbox.  No NCCL call.
+    * ``reduce="nccl"`` — in-house baseline: local-hist kernel -> ``ncclAllReduce`` ->
+      gain kernel (every rank evaluates every feature).
+    * ``peers=<LocalRegion view>`` — several virtual ranks in one process, driven in
+      lock-step by :func:`build_lockstep` (same kernels, phases launched separately).
     """
 
     def __init__(
@@ -229,10 +240,12 @@ class TreeBuilder:
         *,
         n_global: Optional[int] = None,
         fused: bool = True,
-        reduce: str = "nccl",
-        group=None,
+        reduce: str = "auto",
+        comm=None,
+        peers=None,
         profile: bool = False,
         hist_budget_bytes: Optional[int] = None,
+        h_cap: Optional[int] = None,
     ):
         import torch
 
@@ -244,17 +257,21 @@ class TreeBuilder:
         self.data = data
         self.params = params
         self.fused = fused
-        self.reduce = reduce
-        self.group = group
         self.profile = profile
-        self.world = 1
-        self.rank = 0
-        if group is not None or (torch.distributed.is_available() and torch.distributed.is_initialized()):
-            import torch.distributed as dist
-
-            if dist.is_initialized() and dist.get_world_size(group) > 1:
-                self.world = dist.get_world_size(group)
-                self.rank = dist.get_rank(group)
+        self.comm = comm
+        self.world = 1 if comm is None else comm.size
+        self.rank = 0 if comm is None else comm.rank
+        self.region = None
+        if peers is not None:  # virtual ranks in one process
+            self.world, self.rank = peers.world, peers.rank
+            reduce = "lockstep"
+        elif self.world == 1:
+            reduce = "none"
+        elif reduce == "auto":
+            reduce = "p2p"
+        if reduce not in ("none", "p2p", "nccl", "lockstep"):
+            raise ValueError("reduce must be 'auto', 'p2p' or 'nccl'")
+        self.reduce = reduce
         dev = data.device
         F, C, G = data.n_features, data.n_classes, data.G
         if C > MAX_CLASSES:
@@ -265,6 +282,9 @@ class TreeBuilder:
         self.F, self.C, self.G, self.B = F, C, G, B
         n_global = int(n_global if n_global is not None else data.n_local)
         self.n_global = n_global
+        P = self.world
+        peer_mode = reduce in ("p2p", "lockstep")
+        self.fpo = (F + P - 1) // P if peer_mode else F
 
         ctx = L.MtbCtx()
         ctx.n_cap, ctx.n_local, ctx.F, ctx.G, ctx.B, ctx.C = data.n_cap, data.n_local, F, G, B, C
@@ -274,10 +294,11 @@ class TreeBuilder:
         ctx.dot_mode = probe_dot_mode()
         self._plogp = plogp_table(dev)
         ctx.plogp, ctx.plogp_n = _p(self._plogp), PLOGP_N
-        ctx.world, ctx.rank = self.world, self.rank
+        ctx.world, ctx.rank = (P, self.rank) if peer_mode else (1, 0)
+        ctx.fpo = self.fpo
 
         # features per shared-memory tile: the largest that leaves >= 2 TMA stages
-        self.stats = BuildStats()
+        self.stats = BuildStats(reduce=reduce, world=P)
         for ft in (16, 8, 4, 2, 1):
             ctx.FT = ft
             th, sm, st, rp = ctypes.c_int(), ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
@@ -289,39 +310,78 @@ class TreeBuilder:
 
         slab_words = G * 16 * B * C
         self.slab_words = slab_words
-        if hist_budget_bytes is None:
-            free, _total = torch.cuda.mem_get_info(dev)
-            hist_budget_bytes = int(free * 0.35)
-        depth_cap = 1 << 30 if params.max_depth is None else 1 << max(int(params.max_depth) - 1, 0)
-        rows_cap = max(2, n_global // max(int(params.min_samples_split), 2) + 1)
-        h_cap = min(depth_cap, rows_cap, max(2, hist_budget_bytes // (2 * slab_words * 4)))
-        h_cap = max(2, h_cap + (h_cap & 1))
-        self.h_cap = h_cap  # histogram slabs per ping-pong side
-        m_cap = 2 * h_cap + 2  # slot-array capacity: a level may emit two children per slot
+        if h_cap is None:
+            if hist_budget_bytes is None:
+                free, _total = torch.cuda.mem_get_info(dev)
+                hist_budget_bytes = int(free * 0.35)
+            depth_cap = 1 << 30 if params.max_depth is None else 1 << max(int(params.max_depth) - 1, 0)
+            rows_cap = max(2, n_global // max(int(params.min_samples_split), 2) + 1)
+            per_slot = slab_words * 4 * (3 if peer_mode else 2)  # two sides (+ staging)
+            h_cap = min(depth_cap, rows_cap, max(2, hist_budget_bytes // per_slot))
+            h_cap = max(2, h_cap + (h_cap & 1))
+            if comm is not None and comm.size > 1:
+                h_cap = min(comm.allgather_object(h_cap))  # every rank must use the same layout
+        self.h_cap = int(h_cap)  # histogram slabs per ping-pong side
+        m_cap = 2 * self.h_cap + 2  # slot-array capacity: a level may emit two children per slot
         self.m_cap = m_cap
-        self.stats.m_cap = h_cap
-        self.stats.hist_bytes = 2 * h_cap * slab_words * 4
+        self.stats.m_cap = self.h_cap
+        self.stats.hist_bytes = 2 * self.h_cap * slab_words * 4
         node_cap = 2 * n_global + 1 if params.max_depth is None else min((1 << (int(params.max_depth) + 1)) - 1, 2 * n_global + 1)
         self.node_cap = max(3, min(node_cap, 1 << 16))
-        self._node_cap_limit = max(3, node_cap)
 
-        i32, f64 = torch.int32, torch.float64
+        i32 = torch.int32
         z = lambda n, dt=i32: torch.zeros(max(int(n), 1), dtype=dt, device=dev)  # noqa: E731
-        self.hist = [z(h_cap * slab_words), z(h_cap * slab_words)]
+        self.hist = [z(self.h_cap * slab_words), z(self.h_cap * slab_words)]
         self.slots = [{k: z(m_cap) for k in ("node", "begin", "end", "mode", "parent", "sibling")} for _ in range(2)]
         self.nslot_src = z(m_cap)
-        self.fb_cost = z(m_cap * F, f64)
-        self.fb_bin = z(m_cap * F)
-        self.fb_left = z(m_cap * F * C)
-        self.node_cnt = z(m_cap * C)
         self.rec_feature, self.rec_bin, self.part_flags = z(m_cap), z(m_cap), z(m_cap)
         self.cursors = z(2 * m_cap)
         self.scalars = z(8)
         self.unit_prefix = z(2 * (m_cap + 1))
         self._alloc_tree(self.node_cap)
+
+        # record mailbox: fb_cost | fb_bin | fb_left | node_cnt (layout shared with the kernels)
+        MF = m_cap * F
+        self._rec_off = (0, MF * 8, MF * 12, MF * 12 + MF * C * 4)
+        rec_bytes = _round_up(self._rec_off[3] + m_cap * C * 4, 256)
+        stage_bytes = _round_up(P * self.h_cap * self.fpo * B * C * 4, 256) if peer_mode else 0
+        self._layout = (0, stage_bytes, stage_bytes + rec_bytes)  # stage | mailbox | flags
+        total = stage_bytes + rec_bytes + 256
+        if reduce == "p2p":
+            ptrs = _shared_region(total, comm).ptrs
+        elif reduce == "lockstep":
+            if peers.nbytes < total:
+                raise ValueError(f"LocalRegion too small: need {total} bytes")
+            ptrs = peers.ptrs
+        else:
+            self._mailbox = torch.zeros(total, dtype=torch.uint8, device=dev)
+            ptrs = [_p(self._mailbox)]
+        me = self.rank if peer_mode else 0
+        self._mailbox_ptr = ptrs[me] + self._layout[1]
+        if peer_mode:
+            for q in range(P):
+                ctx.peer_hist[q] = ptrs[q] + self._layout[0]
+                ctx.peer_rec[q] = ptrs[q] + self._layout[1]
+                ctx.peer_flags[q] = ptrs[q] + self._layout[2]
+        ctx.h_cap = self.h_cap
         self.ctx = ctx
         self.side = 0  # which slot set is "current"
         self.hcur = 0
+        self.n_slots, self.n_nodes, self.depth = 1, 1, 0
+
+    @staticmethod
+    def region_bytes(world: int, F: int, B: int, C: int, h_cap: int) -> int:
+        """Bytes each rank's symmetric region needs (for :class:`LocalRegion` sizing)."""
+        m_cap = 2 * h_cap + 2
+        MF = m_cap * F
+        rec = _round_up(MF * 12 + MF * C * 4 + m_cap * C * 4, 256)
+        fpo = (F + world - 1) // world
+        return _round_up(world * h_cap * fpo * B * C * 4, 256) + rec + 256
+
+    def close(self) -> None:
+        if self.region is not None:
+            self.region.close()
+            self.region = None
 
     # ------------------------------------------------------------------ tree
     def _alloc_tree(self, cap: int, old=None) -> None:
@@ -354,7 +414,8 @@ class TreeBuilder:
         c.nslot_node, c.nslot_begin, c.nslot_end = _p(nxt["node"]), _p(nxt["begin"]), _p(nxt["end"])
         c.nslot_mode, c.nslot_parent, c.nslot_sibling = _p(nxt["mode"]), _p(nxt["parent"]), _p(nxt["sibling"])
         c.nslot_src = _p(self.nslot_src)
-        c.fb_cost, c.fb_bin, c.fb_left, c.node_cnt = _p(self.fb_cost), _p(self.fb_bin), _p(self.fb_left), _p(self.node_cnt)
+        mb = self._mailbox_ptr
+        c.fb_cost, c.fb_bin, c.fb_left, c.node_cnt = (mb + o for o in self._rec_off)
         c.rec_feature, c.rec_bin, c.part_flags, c.cursors = (
             _p(self.rec_feature), _p(self.rec_bin), _p(self.part_flags), _p(self.cursors),
         )
@@ -370,75 +431,97 @@ class TreeBuilder:
         _call(name, ctypes.byref(self.ctx), _stream_ptr())
         self.stats.launches += 1
 
+    # ------------------------------------------------------------ level steps
+    def start(self) -> None:
+        torch = self.torch
+        cur = self.slots[self.side]
+        init = [0, 0, self.data.n_local, 1, -1, -1]
+        for k, v in zip(("node", "begin", "end", "mode", "parent", "sibling"), init):
+            cur[k][0] = v
+        self.scalars.copy_(torch.tensor([1, 0, 1, 0, 0, 0, 0, 0], dtype=torch.int32))
+        self.n_slots, self.n_nodes, self.depth = 1, 1, 0
+        self._host_scal = torch.empty(8, dtype=torch.int32).pin_memory()
+
+    def prepare_level(self) -> None:
+        n_slots, n_nodes = self.n_slots, self.n_nodes
+        if n_slots > self.h_cap:
+            raise RuntimeError(
+                f"frontier of {n_slots} nodes exceeds the histogram slot capacity {self.h_cap}; "
+                "raise hist_budget_bytes, lower max_depth or raise min_samples_split"
+            )
+        if n_nodes + 2 * n_slots > self.node_cap:
+            self._alloc_tree(max(2 * self.node_cap, n_nodes + 2 * n_slots), self.tree)
+        self.ctx.depth = self.depth
+        self.ctx.n_slots_host = n_slots
+        self._bind()
+        # slabs of BUILD slots must start at zero (DERIVE slots are overwritten)
+        self.hist[self.hcur][: n_slots * self.slab_words].zero_()
+
+    def search_level(self) -> None:
+        """plan + histogram + reduction + gain + finalize for the current level."""
+        if self.reduce == "p2p":
+            self.ctx.epoch = _EPOCH["next"]
+            _EPOCH["next"] += 2
+            self._launch("mtb_level_fused")
+        elif self.reduce == "none" and self.fused:
+            self._launch("mtb_level_fused")
+        else:
+            self._launch("mtb_level_plan")
+            self._launch("mtb_level_hist")
+            if self.reduce == "nccl":
+                import torch.distributed as dist
+
+                dist.all_reduce(self.hist[self.hcur][: self.n_slots * self.slab_words])
+            self._launch("mtb_level_gain")
+            self._launch("mtb_level_finalize")
+
+    def read_level(self) -> int:
+        self._host_scal.copy_(self.scalars, non_blocking=True)
+        self.torch.cuda.current_stream().synchronize()
+        self.n_next, self.n_nodes = int(self._host_scal[1]), int(self._host_scal[2])
+        return self.n_next
+
+    def advance_level(self) -> None:
+        if self.n_next > 0:
+            self._launch("mtb_level_partition")
+            self._launch("mtb_level_commit")
+            self.data.cur ^= 1
+            self.side ^= 1
+            self.hcur ^= 1
+        self.n_slots = self.n_next
+        self.depth += 1
+        self.stats.levels += 1
+
     # ----------------------------------------------------------------- build
     def build(self) -> FlatTree:
         torch = self.torch
-        d = self.data
-        cur = self.slots[self.side]
-        # root slot
-        init = torch.tensor([0, 0, d.n_local, 1, -1, -1], dtype=torch.int32)
-        for k, v in zip(("node", "begin", "end", "mode", "parent", "sibling"), init.tolist()):
-            cur[k][0] = v
-        self.scalars.copy_(torch.tensor([1, 0, 1, 0, 0, 0, 0, 0], dtype=torch.int32))
-        n_slots, n_nodes, depth = 1, 1, 0
-        use_fused = self.fused and (self.world == 1 or self.reduce == "p2p")
-        host_scal = torch.empty(8, dtype=torch.int32).pin_memory()
+        if self.reduce == "lockstep":
+            raise RuntimeError("virtual ranks are driven by build_lockstep()")
+        self.start()
         events = []
-        while n_slots > 0:
-            if n_slots > self.h_cap:
-                raise RuntimeError(
-                    f"frontier of {n_slots} nodes exceeds the histogram slot capacity {self.h_cap}; "
-                    "raise hist_budget_bytes, lower max_depth or raise min_samples_split"
-                )
-            if n_nodes + 2 * n_slots > self.node_cap:
-                if n_nodes + 2 * n_slots > max(self._node_cap_limit, 3):
-                    pass  # cannot happen: every split consumes rows / depth
-                self._alloc_tree(max(2 * self.node_cap, n_nodes + 2 * n_slots), self.tree)
-            self.ctx.depth = depth
-            self.ctx.n_slots_host = n_slots
-            self._bind()
-            # slabs of BUILD slots must start at zero (DERIVE slots are overwritten)
-            self.hist[self.hcur][: n_slots * self.slab_words].zero_()
+        while self.n_slots > 0:
+            self.prepare_level()
             ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)] if self.profile else None
             if ev:
                 ev[0].record()
-            if use_fused:
-                self._launch("mtb_level_fused")
-            else:
-                self._launch("mtb_level_plan")
-                self._launch("mtb_level_hist")
-                if self.world > 1:
-                    import torch.distributed as dist
-
-                    dist.all_reduce(self.hist[self.hcur][: n_slots * self.slab_words], group=self.group)
-                self._launch("mtb_level_gain")
-                self._launch("mtb_level_finalize")
+            self.search_level()
             if ev:
                 ev[1].record()
-            host_scal.copy_(self.scalars, non_blocking=True)
-            torch.cuda.current_stream().synchronize()
-            n_next, n_nodes = int(host_scal[1]), int(host_scal[2])
+            self.read_level()
             if ev:
                 ev[2].record()
-            if n_next > 0:
-                self._launch("mtb_level_partition")
-                self._launch("mtb_level_commit")
-                d.cur ^= 1
-                self.side ^= 1
-                self.hcur ^= 1
+            n_slots = self.n_slots
+            self.advance_level()
             if ev:
                 ev[3].record()
                 events.append((n_slots, ev))
-            n_slots = n_next
-            depth += 1
-            self.stats.levels += 1
         if events:
             torch.cuda.synchronize()
             for ns, ev in events:
                 self.stats.level_ms.append(
                     {"slots": ns, "search_ms": ev[0].elapsed_time(ev[1]), "partition_ms": ev[2].elapsed_time(ev[3])}
                 )
-        return self._download(n_nodes)
+        return self._download(self.n_nodes)
 
     def _download(self, n_nodes: int) -> FlatTree:
         t = {k: v[: n_nodes * (self.C if k == "counts" else 1)].cpu().numpy() for k, v in self.tree.items()}
@@ -456,6 +539,74 @@ class TreeBuilder:
             gain=t["gain"].astype(np.float64),
             thresholds=[None] * n_nodes,
         )
+
+
+_REGIONS: dict = {}
+
+
+def _shared_region(nbytes: int, comm):
+    """Peer-mapped region reused across fits (mapping costs milliseconds; epochs keep flags valid)."""
+    from ..parallel.symm import IpcRegion
+
+    key = (comm.size, comm.rank)
+    reg = _REGIONS.get(key)
+    need = max(comm.allgather_object(int(nbytes)))
+    if reg is None or reg.nbytes < need:
+        if reg is not None:
+            reg.close()
+        reg = IpcRegion(need, comm)
+        _REGIONS[key] = reg
+    return reg
+
+
+def fit_virtual_ranks(shards, n_classes: int, n_bins: int, params: SplitParams, *, h_cap: int = 64):
+    """Fit one tree from several row shards held by *virtual ranks* on this GPU.
+
+    ``shards``: list of ``(X_uint8_cuda, y_uint8_cuda)``.  Returns the per-rank trees
+    (they must be identical).  See :func:`build_lockstep`.
+    """
+    from ..parallel.symm import LocalRegion
+
+    P = len(shards)
+    F = int(shards[0][0].shape[1])
+    B = max(32, ((int(n_bins) + 31) // 32) * 32)
+    region = LocalRegion(TreeBuilder.region_bytes(P, F, B, n_classes, h_cap), P)
+    n_global = sum(int(x.shape[0]) for x, _ in shards)
+    builders = []
+    for r, (X, y) in enumerate(shards):
+        data = DeviceDataset.allocate(int(X.shape[0]), F, n_classes, X.device)
+        data.encode_u8(X)
+        data.set_labels(y)
+        builders.append(TreeBuilder(data, n_bins, params, n_global=n_global, peers=region.view(r), h_cap=h_cap))
+    return build_lockstep(builders)
+
+
+def _round_up(x: int, m: int) -> int:
+    return ((int(x) + m - 1) // m) * m
+
+
+def build_lockstep(builders: List[TreeBuilder]) -> List[FlatTree]:
+    """Drive several virtual ranks (one process, one stream) through the multi-rank data path.
+
+    The same kernels as the ``p2p`` path run, but as separate launches in phase order
+    (all ranks' histograms, then all pushes, then all gains, ...), so no kernel ever
+    waits on another: this is how the peer push / owner reduction / record broadcast
+    logic is exercised with fewer GPUs than ranks.
+    """
+    for b in builders:
+        b.start()
+    while builders[0].n_slots > 0:
+        for b in builders:
+            b.prepare_level()
+        for name in ("mtb_level_plan", "mtb_level_hist", "mtb_level_push", "mtb_level_gain", "mtb_level_finalize"):
+            for b in builders:
+                b._launch(name)
+        nexts = {b.read_level() for b in builders}
+        if len(nexts) != 1:
+            raise RuntimeError(f"virtual ranks disagree on the next frontier: {sorted(nexts)}")
+        for b in builders:
+            b.advance_level()
+    return [b._download(b.n_nodes) for b in builders]
 
 
 # ---------------------------------------------------------------------------
@@ -535,9 +686,13 @@ def fit_from_host(X: np.ndarray, y_codes: np.ndarray, n_classes: int, params: Sp
     n_global = n
     if comm is not None and comm.size > 1:
         n_global = int(sum(comm.allgather_object(n)))
-    builder = TreeBuilder(data, int(mapper.n_bins.max()), params, n_global=n_global, group=_dist_group(comm),
+    _dist_group(comm)
+    builder = TreeBuilder(data, int(mapper.n_bins.max()), params, n_global=n_global, comm=comm,
                           **(builder_kwargs or {}))
-    flat = builder.build()
+    try:
+        flat = builder.build()
+    finally:
+        builder.close()
     fit_from_host.last_stats = builder.stats
     return flat, mapper
 
@@ -620,9 +775,13 @@ def fit_from_torch(X, y, params: SplitParams, *, max_bins: int = 256, comm=None,
     n_global = n
     if comm is not None and comm.size > 1:
         n_global = int(sum(comm.allgather_object(n)))
-    builder = TreeBuilder(data, int(mapper.n_bins.max()), params, n_global=n_global, group=_dist_group(comm),
+    _dist_group(comm)
+    builder = TreeBuilder(data, int(mapper.n_bins.max()), params, n_global=n_global, comm=comm,
                           **(builder_kwargs or {}))
-    flat = builder.build()
+    try:
+        flat = builder.build()
+    finally:
+        builder.close()
     fit_from_torch.last_stats = builder.stats
     return flat, mapper, classes
 
