@@ -20,13 +20,25 @@ def main():
     ap.add_argument("--reps", type=int, default=3)
     ap.add_argument("--unfused", action="store_true")
     ap.add_argument("--informative", type=int, default=8)
+    ap.add_argument("--reduce", default="auto")
     a = ap.parse_args()
-    dev = torch.device("cuda")
-    g = torch.Generator(device=dev).manual_seed(0)
+    import os
+    world, rank = int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("RANK", "0"))
+    comm = None
+    if world > 1:
+        from mpitree_b200.parallel.comm import TorchComm, init_process_group_from_env
+
+        init_process_group_from_env("nccl")
+        comm = TorchComm()
+        total = a.rows
+        a.rows = total * (rank + 1) // world - total * rank // world
+    dev = torch.device("cuda", torch.cuda.current_device())
+    g = torch.Generator(device=dev).manual_seed(rank)
     X = torch.randint(0, 256, (a.rows, a.features), dtype=torch.uint8, device=dev, generator=g)
     w = torch.randn(a.informative, device=dev, generator=g)
     score = (X[:, : a.informative].float() - 127.5) @ w + 40 * torch.randn(a.rows, device=dev, generator=g)
-    qs = torch.quantile(score[:1_000_000], torch.linspace(0, 1, a.classes + 1, device=dev)[1:-1])
+    sd = float((w.pow(2).sum() * (256 ** 2 - 1) / 12.0 + 1600.0).sqrt())
+    qs = torch.distributions.Normal(0.0, sd).icdf(torch.linspace(0, 1, a.classes + 1, device=dev)[1:-1])
     y = torch.bucketize(score, qs).to(torch.uint8)
     del score
     params = SplitParams(max_depth=a.depth)
@@ -37,7 +49,8 @@ def main():
         data.encode_u8(X)
         data.set_labels(y)
         torch.cuda.synchronize()
-        b = cuda_engine.TreeBuilder(data, 256, params, fused=not a.unfused, profile=True)
+        b = cuda_engine.TreeBuilder(data, 256, params, fused=not a.unfused, profile=True, comm=comm,
+                                    n_global=a.rows * world, reduce=a.reduce)
         t0 = time.perf_counter()
         s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         s.record()
@@ -46,12 +59,16 @@ def main():
         torch.cuda.synchronize()
         ms = s.elapsed_time(e)
         out.append(ms)
-        print(f"rep {rep}: {ms:.2f} ms ({a.rows / ms / 1e3:.1f} M rows/s) nodes={flat.n_nodes} wall={time.perf_counter() - t0:.3f}s")
+        if rank == 0:
+          print(f"rep {rep}: {ms:.2f} ms ({a.rows / ms / 1e3:.1f} M rows/s) nodes={flat.n_nodes} wall={time.perf_counter() - t0:.3f}s")
     st = b.stats
+    if rank != 0:
+        return
     print(json.dumps({"FT": st.FT, "stages": st.stages, "smem": st.smem_bytes, "m_cap": st.m_cap,
                       "hist_MB": st.hist_bytes / 2**20, "launches": st.launches}))
     for lv, d in enumerate(st.level_ms):
-        print(f"  level {lv:2d} slots={d['slots']:5d} search={d['search_ms']:8.3f} ms partition={d['partition_ms']:8.3f} ms")
+        extra = " ".join(f"{k[:-3]}={v:.3f}" for k, v in d.items() if k.endswith("_ms") and k not in ("search_ms", "partition_ms"))
+        print(f"  level {lv:2d} slots={d['slots']:5d} search={d['search_ms']:8.3f} ms partition={d['partition_ms']:8.3f} ms | {extra}")
 
 
 if __name__ == "__main__":

@@ -101,7 +101,13 @@ typedef struct MtbCtx {
   int64_t plogp_n;
   int64_t h_cap;                      /* histogram slabs per side == staging slots per source */
   int64_t fpo;                        /* features per owner rank (F when world == 1)          */
-  int64_t reserved[4];
+  int64_t timers;                     /* u64[16] phase timestamps (%globaltimer) or 0         */
+  /* Nodes with more than plogp_n rows use a cheaper, still deterministic evaluation:
+   * cost = (g(nL) + g(nR) - sum_c g(kL_c) - sum_c g(kR_c)) / n with g(k) = k*log2(k);
+   * klogk is the host's table of g(k) for k < klogk_n (0 = compute on device).            */
+  int64_t klogk;
+  int64_t klogk_n;
+  int64_t reserved[1];
 } MtbCtx;
 
 const char* mtb_last_error(void);

@@ -45,6 +45,7 @@ constexpr int kSmemBudget = 225 * 1024;
 constexpr int kPartRows = 1024;
 constexpr int kPartThreads = 256;
 constexpr int kGainWarps = 8;
+constexpr int kFusedGainWarps = 16;  // the fused kernel's consumer warps all evaluate gains
 
 struct HistGeom {
   int tile_words;  // FT*B*C
@@ -135,6 +136,8 @@ __device__ void plan_phase(const MtbCtx& ctx, int* smem_warp) {
   if (threadIdx.x == 0) {
     prefix[n] = carry;
     v.scalars()[3] = carry;
+    v.scalars()[6] = 0;  // gain-phase work counters (pass 0 / -1, pass 1)
+    v.scalars()[7] = 0;
   }
 }
 
@@ -144,38 +147,74 @@ __global__ void k_plan(const __grid_constant__ MtbCtx ctx) {
 }
 
 // ------------------------------------------------------------------------ hist
-struct UnitInfo {
-  int slot, gs, chunk, row0, nrows;
+// Walks the CTA's contiguous range of work units (1024-row chunks ordered by slot, then
+// feature tile `gs`, then chunk) without a search per unit: the slot lookup is redone only
+// when the range crosses into the next slot.
+struct UnitCursor {
+  const int* prefix;
+  const int* sb;
+  const int* se;
+  int n_slots, GS;
+  int slot, slot_u0, slot_u1, chunks, begin, end;
+  int gs, chunk, row0, nrows;
+
+  __device__ void init(const MtbCtx& ctx, const int* prefix_, int n_slots_) {
+    prefix = prefix_;
+    sb = ptr_of<const int>(ctx.slot_begin);
+    se = ptr_of<const int>(ctx.slot_end);
+    n_slots = n_slots_;
+    GS = (int)(ctx.G * (16 / ctx.FT));
+    slot = -1;
+    slot_u0 = slot_u1 = 0;
+  }
+  __device__ __forceinline__ void seek(int u) {
+    if (u >= slot_u1 || slot < 0) {
+      slot = find_slot(prefix, n_slots, u);
+      slot_u0 = prefix[slot];
+      slot_u1 = prefix[slot + 1];
+      begin = sb[slot];
+      end = se[slot];
+      chunks = (end - begin + kRows - 1) / kRows;
+    }
+    const int local = u - slot_u0;
+    gs = local / chunks;
+    chunk = local - gs * chunks;
+    row0 = begin + chunk * kRows;
+    nrows = min(kRows, end - row0);
+  }
+  // true when units [u0, u1) contain every chunk of the current (slot, gs) tile
+  __device__ __forceinline__ bool owns_whole_tile(int u0, int u1) const {
+    const int t0 = slot_u0 + gs * chunks;
+    return u0 <= t0 && t0 + chunks <= u1;
+  }
 };
 
-__device__ __forceinline__ UnitInfo decode_unit(const MtbCtx& ctx, const int* prefix, int n_slots, int u) {
-  UnitInfo r;
-  r.slot = find_slot(prefix, n_slots, u);
-  int local = u - prefix[r.slot];
-  int b = ptr_of<const int>(ctx.slot_begin)[r.slot];
-  int e = ptr_of<const int>(ctx.slot_end)[r.slot];
-  int chunks = (e - b + kRows - 1) / kRows;
-  r.gs = local / chunks;
-  r.chunk = local - r.gs * chunks;
-  r.row0 = b + r.chunk * kRows;
-  r.nrows = min(kRows, e - r.row0);
-  return r;
-}
-
-// destination slab of (slot, gs): local hist, or the owning peer's staging slab
+// Flush a finished [FT][B][C] tile into the slot's slab.  When this CTA processed every
+// row of the tile it simply stores it (128-bit, no atomics, no zero-skipping); otherwise
+// several CTAs share the tile and merge with red.global.add.
 template <int FT>
-__device__ void flush_tile(const MtbCtx& ctx, uint32_t* tile, int slot, int gs, int tid) {
+__device__ void flush_tile(const MtbCtx& ctx, uint32_t* tile, int slot, int gs, int tid, bool exclusive) {
   View v(ctx);
   const int S = 16 / FT;
   const int g = gs / S, s = gs - g * S;
   const int64_t f0 = (int64_t)g * 16 + (int64_t)s * FT;
   const int words = FT * (int)ctx.B * (int)ctx.C;
   uint32_t* dst = v.hist_cur() + (int64_t)slot * v.slab_words() + f0 * ctx.B * ctx.C;
-  for (int i = tid; i < words; i += kConsumers) {
-    uint32_t x = tile[i];
-    if (x) {
-      red_add_u32(dst + i, x);
-      tile[i] = 0;
+  if (exclusive) {
+    uint4* d4 = reinterpret_cast<uint4*>(dst);
+    uint4* t4 = reinterpret_cast<uint4*>(tile);
+    const uint4 zero = make_uint4(0, 0, 0, 0);
+    for (int i = tid; i < words / 4; i += kConsumers) {
+      d4[i] = t4[i];
+      t4[i] = zero;
+    }
+  } else {
+    for (int i = tid; i < words; i += kConsumers) {
+      uint32_t x = tile[i];
+      if (x) {
+        red_add_u32(dst + i, x);
+        tile[i] = 0;
+      }
     }
   }
 }
@@ -210,6 +249,8 @@ __device__ void hist_phase(const MtbCtx& ctx, uint8_t* smem) {
 
   const uint8_t* codes = v.codes_cur();
   const int S = 16 / FT;
+  UnitCursor cur;
+  cur.init(ctx, prefix, n_slots);
 
   if (tid >= kConsumers) {
     // ===== producer warp: one elected lane issues the bulk copies =====
@@ -217,12 +258,12 @@ __device__ void hist_phase(const MtbCtx& ctx, uint8_t* smem) {
       int st = 0;
       uint32_t ph = 0;
       for (int u = u0; u < u1; ++u) {
-        UnitInfo ui = decode_unit(ctx, prefix, n_slots, u);
-        const int g = ui.gs / S;
+        cur.seek(u);
+        const int g = cur.gs / S;
         mbar_wait(&empty[st], ph ^ 1);
-        const uint32_t bytes = (uint32_t)ui.nrows * 16u;
+        const uint32_t bytes = (uint32_t)cur.nrows * 16u;
         mbar_arrive_expect_tx(&full[st], bytes);
-        tma_load_1d(stage_base + (size_t)st * kStageBytes, codes + ((int64_t)g * ctx.n_cap + ui.row0) * 16, bytes,
+        tma_load_1d(stage_base + (size_t)st * kStageBytes, codes + ((int64_t)g * ctx.n_cap + cur.row0) * 16, bytes,
                     &full[st]);
         if (++st == stages) { st = 0; ph ^= 1; }
       }
@@ -233,35 +274,38 @@ __device__ void hist_phase(const MtbCtx& ctx, uint8_t* smem) {
     int st = 0;
     uint32_t ph = 0;
     int cur_slot = -1, cur_gs = -1;
+    bool cur_excl = false;
     for (int u = u0; u < u1; ++u) {
-      UnitInfo ui = decode_unit(ctx, prefix, n_slots, u);
-      if (ui.slot != cur_slot || ui.gs != cur_gs) {
+      cur.seek(u);
+      if (cur.slot != cur_slot || cur.gs != cur_gs) {
         if (cur_slot >= 0) {
           named_bar_sync(1, kConsumers);
-          flush_tile<FT>(ctx, tile, cur_slot, cur_gs, tid);
+          flush_tile<FT>(ctx, tile, cur_slot, cur_gs, tid, cur_excl);
           named_bar_sync(1, kConsumers);
         }
-        cur_slot = ui.slot;
-        cur_gs = ui.gs;
+        cur_slot = cur.slot;
+        cur_gs = cur.gs;
+        cur_excl = cur.owns_whole_tile(u0, u1);
       }
-      const int sub = (ui.gs % S) * FT;
+      const int sub = (cur.gs % S) * FT;
       // labels first (global), then wait for the tile
       const int r_a = tid, r_b = tid + kConsumers;
+      const int nrows = cur.nrows;
       uint32_t lab_a = 0, lab_b = 0;
-      if (r_a < ui.nrows) lab_a = labels[ui.row0 + r_a];
-      if (r_b < ui.nrows) lab_b = labels[ui.row0 + r_b];
+      if (r_a < nrows) lab_a = labels[cur.row0 + r_a];
+      if (r_b < nrows) lab_b = labels[cur.row0 + r_b];
       mbar_wait(&full[st], ph);
       const uint4* rows = reinterpret_cast<const uint4*>(stage_base + (size_t)st * kStageBytes);
       uint4 va = make_uint4(0, 0, 0, 0), vb = va;
-      if (r_a < ui.nrows) va = rows[r_a];
-      if (r_b < ui.nrows) vb = rows[r_b];
+      if (r_a < nrows) va = rows[r_a];
+      if (r_b < nrows) vb = rows[r_b];
       __syncwarp();
       if (lane_id() == 0) mbar_arrive(&empty[st]);  // tile is in registers: release the stage
-      if (r_a < ui.nrows) {
+      if (r_a < nrows) {
 #pragma unroll
         for (int k = 0; k < FT; ++k) atomicAdd(&tile[(k * B + (int)code_byte(va, sub + k)) * C + (int)lab_a], 1u);
       }
-      if (r_b < ui.nrows) {
+      if (r_b < nrows) {
 #pragma unroll
         for (int k = 0; k < FT; ++k) atomicAdd(&tile[(k * B + (int)code_byte(vb, sub + k)) * C + (int)lab_b], 1u);
       }
@@ -269,7 +313,7 @@ __device__ void hist_phase(const MtbCtx& ctx, uint8_t* smem) {
     }
     if (cur_slot >= 0) {
       named_bar_sync(1, kConsumers);
-      flush_tile<FT>(ctx, tile, cur_slot, cur_gs, tid);
+      flush_tile<FT>(ctx, tile, cur_slot, cur_gs, tid, cur_excl);
     }
   }
 }
@@ -359,6 +403,7 @@ __device__ void gain_pair(const MtbCtx& ctx, uint32_t* slab, int slot, int f) {
   const int lane = lane_id();
   const int mode = ptr_of<const int>(ctx.slot_mode)[slot];
   const int64_t rec = (int64_t)slot * F + f;
+  const unsigned divC = ((1u << 24) + (unsigned)C - 1u) / (unsigned)C;  // w / C == (w * divC) >> 24 for w < B*C
   if (mode == MTB_MODE_NONE) {
     if (lane < P) {
       Mailbox m = mailbox_at(ctx, P > 1 ? ctx.peer_rec[lane] : ctx.fb_cost);
@@ -369,35 +414,50 @@ __device__ void gain_pair(const MtbCtx& ctx, uint32_t* slab, int slot, int f) {
   }
   uint32_t* mine = v.hist_cur() + (int64_t)slot * v.slab_words() + (int64_t)f * B * C;
   const int words = B * C;
+  // scatter 4 consecutive histogram words into the padded per-lane slab layout
+  auto put4 = [&](const uint4& x, int w) {
+    int b = (int)(((unsigned)w * divC) >> 24), c = w - b * C;
+    const uint32_t xs[4] = {x.x, x.y, x.z, x.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      slab[(b / BPL) * lane_stride + (b % BPL) * C + c] = xs[i];
+      if (++c == C) { c = 0; ++b; }
+    }
+  };
   if (mode == MTB_MODE_DERIVE) {
     const int par = ptr_of<const int>(ctx.slot_parent)[slot];
     const int sib = ptr_of<const int>(ctx.slot_sibling)[slot];
     const uint32_t* hp = v.hist_prev() + (int64_t)par * v.slab_words() + (int64_t)f * B * C;
     const uint32_t* hs = v.hist_cur() + (int64_t)sib * v.slab_words() + (int64_t)f * B * C;
-    for (int w = lane; w < words; w += 32) {
-      uint32_t x = hp[w] - hs[w];
-      mine[w] = x;
-      int b = w / C, c = w - b * C;
-      slab[(b / BPL) * lane_stride + (b % BPL) * C + c] = x;
+    const uint4* hp4 = reinterpret_cast<const uint4*>(hp);
+    const uint4* hs4 = reinterpret_cast<const uint4*>(hs);
+    uint4* mine4 = reinterpret_cast<uint4*>(mine);
+#pragma unroll 4
+    for (int q = lane; q < words / 4; q += 32) {
+      const uint4 a = hp4[q], d = hs4[q];
+      const uint4 x = make_uint4(a.x - d.x, a.y - d.y, a.z - d.z, a.w - d.w);
+      mine4[q] = x;
+      put4(x, q * 4);
     }
   } else if (P > 1) {
     // BUILD on the owner: own partial + the partials the peers pushed into the staging area
     const int64_t region = ctx.fpo * ctx.B * ctx.C;
     const uint32_t* stage = ptr_of<const uint32_t>(ctx.peer_hist[r]) + (int64_t)(f - r * (int)ctx.fpo) * B * C;
-    for (int w = lane; w < words; w += 32) {
-      uint32_t x = mine[w];
+    uint4* mine4 = reinterpret_cast<uint4*>(mine);
+    for (int q = lane; q < words / 4; q += 32) {
+      uint4 x = mine4[q];
       for (int p = 0; p < P; ++p)
-        if (p != r) x += stage[((int64_t)p * ctx.h_cap + slot) * region + w];
-      mine[w] = x;
-      int b = w / C, c = w - b * C;
-      slab[(b / BPL) * lane_stride + (b % BPL) * C + c] = x;
+        if (p != r) {
+          const uint4 y = *reinterpret_cast<const uint4*>(stage + ((int64_t)p * ctx.h_cap + slot) * region + q * 4);
+          x.x += y.x; x.y += y.y; x.z += y.z; x.w += y.w;
+        }
+      mine4[q] = x;
+      put4(x, q * 4);
     }
   } else {
-    for (int w = lane; w < words; w += 32) {
-      uint32_t x = mine[w];
-      int b = w / C, c = w - b * C;
-      slab[(b / BPL) * lane_stride + (b % BPL) * C + c] = x;
-    }
+    const uint4* mine4 = reinterpret_cast<const uint4*>(mine);
+#pragma unroll 4
+    for (int q = lane; q < words / 4; q += 32) put4(mine4[q], q * 4);
   }
   __syncwarp();
 
@@ -429,6 +489,9 @@ __device__ void gain_pair(const MtbCtx& ctx, uint32_t* slab, int slot, int f) {
   const int crit = (int)ctx.criterion, dm = (int)ctx.dot_mode;
   const double* plogp = ptr_of<const double>(ctx.plogp);
   const uint32_t plogp_n = (uint32_t)ctx.plogp_n;
+  // small nodes: the reference's exact float64 operation order; large nodes: the cheap form
+  const bool exact = plogp == nullptr || n <= plogp_n;
+  const KlogK klogk{ptr_of<const double>(ctx.klogk), (uint32_t)ctx.klogk_n};
   for (int j = 0; j < BPL; ++j) {
     if (!(present >> j & 1u)) continue;
     const uint32_t* L = my + j * C;
@@ -436,9 +499,14 @@ __device__ void gain_pair(const MtbCtx& ctx, uint32_t* slab, int slot, int f) {
     for (int c = 0; c < C; ++c) nl += L[c];
     const uint32_t nr = n - nl;
     if (nr == 0) continue;  // right side empty: not a usable split
-    double hl = impurity(C, [&](int c) { return L[c]; }, nl, crit, plogp, plogp_n);
-    double hr = impurity(C, [&](int c) { return last[c] - L[c]; }, nr, crit, plogp, plogp_n);
-    double cost = split_cost(nl, nr, hl, hr, dm);
+    double cost;
+    if (exact) {
+      double hl = impurity(C, [&](int c) { return L[c]; }, nl, crit, plogp, plogp_n);
+      double hr = impurity(C, [&](int c) { return last[c] - L[c]; }, nr, crit, plogp, plogp_n);
+      cost = split_cost(nl, nr, hl, hr, dm);
+    } else {
+      cost = fast_split_cost(C, [&](int c) { return L[c]; }, [&](int c) { return last[c] - L[c]; }, nl, nr, crit, klogk);
+    }
     if (cost < best) {  // strict: first (lowest) bin wins ties inside the lane
       best = cost;
       best_bin = lane * BPL + j;
@@ -486,7 +554,13 @@ __device__ void gain_phase(const MtbCtx& ctx, uint8_t* smem, int warps_per_block
   uint32_t* slab = reinterpret_cast<uint32_t*>(smem) + (size_t)w * slab_words;
   // a DERIVE pair reads a sibling slab completed in the hist phase: pairs are independent
   const int* mode = ptr_of<const int>(ctx.slot_mode);
-  for (int p = blockIdx.x * warps_per_block + w; p < n_pairs; p += gridDim.x * warps_per_block) {
+  // dynamic scheduling: pairs differ a lot in cost (NONE slots are free, DERIVE reads two slabs)
+  int* counter = v.scalars() + (pass == 1 ? 7 : 6);
+  for (;;) {
+    int p = 0;
+    if (lane_id() == 0) p = atomicAdd(counter, 1);
+    p = __shfl_sync(0xffffffffu, p, 0);
+    if (p >= n_pairs) break;
     const int slot = p / n_own;
     if (pass >= 0 && (mode[slot] == MTB_MODE_DERIVE) != (pass == 1)) continue;
     gain_pair(ctx, slab, slot, f_lo + p % n_own);
@@ -558,8 +632,11 @@ __device__ void finalize_phase(const MtbCtx& ctx, int* smem_warp) {
       for (int c = 0; c < C; ++c) t_counts[(int64_t)node * C + c] = cnt[c];
       uint32_t ntot;
       if (!is_terminal([&](int c) { return cnt[c]; }, C, depth, ctx, ntot)) {
-        const double hp = impurity(C, [&](int c) { return cnt[c]; }, ntot, (int)ctx.criterion,
-                                   ptr_of<const double>(ctx.plogp), (uint32_t)ctx.plogp_n);
+        const bool exact = ctx.plogp == 0 || ntot <= (uint32_t)ctx.plogp_n;
+        const KlogK klogk{ptr_of<const double>(ctx.klogk), (uint32_t)ctx.klogk_n};
+        const double hp = exact ? impurity(C, [&](int c) { return cnt[c]; }, ntot, (int)ctx.criterion,
+                                           ptr_of<const double>(ctx.plogp), (uint32_t)ctx.plogp_n)
+                                : fast_impurity(C, [&](int c) { return cnt[c]; }, ntot, (int)ctx.criterion, klogk);
         bool have = false;
         for (int f = 0; f < F; ++f) {
           const double cost = fb_cost[(int64_t)s * F + f];
@@ -769,31 +846,48 @@ __global__ void k_commit(const __grid_constant__ MtbCtx ctx) {
 // plan -> hist -> [push partial slabs to owners -> peer barrier] -> gain on owned features
 // (records go to every rank's mailbox) -> [peer barrier] -> finalize.  One cooperative
 // launch; with world > 1 no NCCL call and no separate reduction or gain kernel runs.
+__device__ __forceinline__ void stamp(const MtbCtx& ctx, int i) {
+  // optional phase timestamps (ns, %globaltimer) for profiling: ctx.timers = u64[16] or 0
+  if (ctx.timers && blockIdx.x == 0 && threadIdx.x == 0) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    ptr_of<unsigned long long>(ctx.timers)[i] = t;
+  }
+}
+
 template <int FT>
 __global__ void __launch_bounds__(kHistThreads, 1) k_level_fused(const __grid_constant__ MtbCtx ctx) {
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ int smem_warp[33];
   cg::grid_group grid = cg::this_grid();
+  stamp(ctx, 0);
   if (blockIdx.x == 0) plan_phase(ctx, smem_warp);
   grid.sync();
+  stamp(ctx, 1);
   hist_phase<FT>(ctx, smem);
   if (ctx.world > 1) {
     grid.sync();
+    stamp(ctx, 2);
     push_phase(ctx);
     peer_barrier(ctx, grid, (uint32_t)ctx.epoch + 1u);
-  } else {
+    stamp(ctx, 3);
+    gain_phase(ctx, smem, kFusedGainWarps, 0);
     grid.sync();
-  }
-  if (ctx.world > 1) {
-    gain_phase(ctx, smem, kGainWarps, 0);
-    grid.sync();
-    gain_phase(ctx, smem, kGainWarps, 1);
+    stamp(ctx, 4);
+    gain_phase(ctx, smem, kFusedGainWarps, 1);
     peer_barrier(ctx, grid, (uint32_t)ctx.epoch + 2u);
+    stamp(ctx, 5);
   } else {
-    gain_phase(ctx, smem, kGainWarps, -1);
     grid.sync();
+    stamp(ctx, 2);
+    stamp(ctx, 3);
+    gain_phase(ctx, smem, kFusedGainWarps, -1);
+    grid.sync();
+    stamp(ctx, 4);
+    stamp(ctx, 5);
   }
   if (blockIdx.x == 0) finalize_phase(ctx, smem_warp);
+  stamp(ctx, 6);
 }
 
 int g_sm_count = 0;
@@ -920,6 +1014,11 @@ extern "C" int mtb_level_fused(const MtbCtx* ctx, void* stream) {
     return -2;
   }
   int smem = g.smem_bytes;
-  if (gain_smem(ctx) > smem) smem = gain_smem(ctx);
+  const int gsm = kFusedGainWarps * ((int)ctx->B * (int)ctx->C + 32) * 4;
+  if (gsm > smem) smem = gsm;
+  if (smem > 227 * 1024) {
+    mtb_set_error("fused", "gain slabs do not fit in shared memory", __FILE__, __LINE__);
+    return -2;
+  }
   FT_SWITCH((int)ctx->FT, launch_fused, ctx, smem, (cudaStream_t)stream);
 }

@@ -93,6 +93,18 @@ __global__ void __launch_bounds__(kThreads) k_encode_u8(const uint8_t* __restric
   }
 }
 
+// identity codes, F a multiple of 16, 16-byte aligned rows: consecutive threads read consecutive
+// 16-byte chunks of a row (fully coalesced) and write them to their feature-group planes
+__global__ void __launch_bounds__(kThreads) k_retile_u8(const uint4* __restrict__ X, int64_t n, int G, int64_t ldx16,
+                                                        uint4* __restrict__ codes, int64_t n_cap, int64_t row0) {
+  const int64_t total = n * G;
+  for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < total; i += (int64_t)gridDim.x * kThreads) {
+    const int64_t row = i / G;
+    const int g = (int)(i - row * G);
+    codes[(int64_t)g * n_cap + row0 + row] = mtb::ld_nc_u4(X + row * ldx16 + g);
+  }
+}
+
 }  // namespace
 
 extern "C" int mtb_encode_float(const void* X, int dtype, int64_t n, int64_t F, int64_t ldx, const double* edges,
@@ -121,6 +133,14 @@ extern "C" int mtb_encode_u8(const uint8_t* X, int64_t n, int64_t F, int64_t ldx
   if (bx > 148 * 16) bx = 148 * 16;
   dim3 grid((unsigned)bx, (unsigned)G);
   const int vec_ok = (ldx % 16 == 0) && ((uintptr_t)X % 16 == 0);
+  if (vec_ok && lut == nullptr && F % 16 == 0) {
+    int64_t blocks = (n * G + kThreads - 1) / kThreads;
+    if (blocks > 148 * 32) blocks = 148 * 32;
+    k_retile_u8<<<(unsigned)blocks, kThreads, 0, (cudaStream_t)stream>>>((const uint4*)X, n, G, ldx / 16, (uint4*)codes,
+                                                                        n_cap, row0);
+    MTB_CHECK(cudaGetLastError());
+    return 0;
+  }
   k_encode_u8<<<grid, kThreads, 0, (cudaStream_t)stream>>>(X, n, (int)F, ldx, lut, (uint4*)codes, n_cap, row0, vec_ok);
   MTB_CHECK(cudaGetLastError());
   return 0;

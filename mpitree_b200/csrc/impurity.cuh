@@ -76,4 +76,62 @@ __device__ __forceinline__ double split_cost(uint32_t n_left, uint32_t n_right, 
   return __dadd_rn(__dmul_rn(wl, h_left), __dmul_rn(wr, h_right));
 }
 
+// ---------------------------------------------------------------------------------------
+// Large nodes (n > plogp_n).  Rounding-level ties between *different* count configurations
+// do not occur in practice there, so the evaluation only has to be a deterministic function
+// of the counts (identical configurations still tie exactly and resolve by position).  The
+// algebraically equal form below needs one table lookup and one add per class instead of a
+// division, a log2 and a multiply:
+//     (nL/n) H(L) + (nR/n) H(R) = ( g(nL) + g(nR) - sum_c g(kL_c) - sum_c g(kR_c) ) / n
+// with g(k) = k log2 k, g(0) = 0.
+struct KlogK {
+  const double* tab;
+  uint32_t n;
+  __device__ __forceinline__ double operator()(uint32_t k) const {
+    if (k < n) return tab[k];
+    const double d = (double)k;
+    return d * log2(d);
+  }
+};
+
+template <typename L, typename R>
+__device__ __forceinline__ double fast_split_cost(int C, L left, R right, uint32_t nl, uint32_t nr, int criterion,
+                                                  const KlogK& g) {
+  const double n = (double)nl + (double)nr;
+  if (criterion == 0) {
+    double s = g(nl) + g(nr);
+    int c = 0;
+    for (; c + 4 <= C; c += 4) {  // issue the eight table loads together, then accumulate
+      const double a0 = g(left(c)), a1 = g(left(c + 1)), a2 = g(left(c + 2)), a3 = g(left(c + 3));
+      const double b0 = g(right(c)), b1 = g(right(c + 1)), b2 = g(right(c + 2)), b3 = g(right(c + 3));
+      s -= ((a0 + b0) + (a1 + b1)) + ((a2 + b2) + (a3 + b3));
+    }
+    for (; c < C; ++c) s -= g(left(c)) + g(right(c));
+    return s / n;
+  }
+  double sl = 0.0, sr = 0.0;
+  for (int c = 0; c < C; ++c) {
+    const double a = (double)left(c), b = (double)right(c);
+    sl += a * a;
+    sr += b * b;
+  }
+  return (((double)nl - sl / (double)nl) + ((double)nr - sr / (double)nr)) / n;
+}
+
+template <typename Cnt>
+__device__ __forceinline__ double fast_impurity(int C, Cnt cnt, uint32_t n, int criterion, const KlogK& g) {
+  const double dn = (double)n;
+  if (criterion == 0) {
+    double s = g(n);
+    for (int c = 0; c < C; ++c) s -= g(cnt(c));
+    return s / dn;
+  }
+  double sq = 0.0;
+  for (int c = 0; c < C; ++c) {
+    const double a = (double)cnt(c);
+    sq += a * a;
+  }
+  return 1.0 - sq / (dn * dn);
+}
+
 }  // namespace mtb

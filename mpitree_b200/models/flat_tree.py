@@ -55,6 +55,11 @@ class FlatTree:
     thresholds: List[Any] = field(default_factory=list)
     class_labels: Optional[np.ndarray] = None
 
+    def __getstate__(self):
+        state = dict(self.__dict__)
+        state.pop("_packed", None)  # device-side cache of the predict kernel, rebuilt on demand
+        return state
+
     # ------------------------------------------------------------------ basic
     @property
     def n_nodes(self) -> int:

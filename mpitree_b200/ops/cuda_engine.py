@@ -109,9 +109,28 @@ def plogp_table(device):
     return _PLOGP_CACHE[key]
 
 
+KLOGK_N = 1 << 16
+
+
+def klogk_table(device):
+    """Device table of ``k * log2(k)`` for ``k < KLOGK_N`` (``0`` at ``k = 0``), used for large nodes."""
+    import torch
+
+    key = ("klogk", str(device))
+    if key not in _PLOGP_CACHE:
+        k = np.arange(KLOGK_N, dtype=np.float64)
+        with np.errstate(divide="ignore", invalid="ignore"):
+            t = np.where(k > 0, k * np.log2(np.where(k > 0, k, 1.0)), 0.0)
+        _PLOGP_CACHE[key] = torch.from_numpy(t).to(device)
+    return _PLOGP_CACHE[key]
+
+
 # ---------------------------------------------------------------------------
 # device data set: tiled codes + labels
 # ---------------------------------------------------------------------------
+_WORKSPACE: dict = {}
+
+
 @dataclass
 class DeviceDataset:
     """Bin codes ``[G][n_cap][16]`` (two ping-pong sides) and labels on one GPU."""
@@ -132,9 +151,24 @@ class DeviceDataset:
 
         G = (n_features + 15) // 16
         n_cap = ((max(n_local, 1) + 1023) // 1024) * 1024
-        codes = [torch.empty(G * n_cap * 16 + 256, dtype=torch.uint8, device=device) for _ in range(2)]
-        labels = [torch.empty(n_cap + 256, dtype=torch.uint8, device=device) for _ in range(2)]
+        # the two ping-pong sides are the largest allocations of a fit: keep the last set around
+        # (repeated fits of the same shape then skip cudaMalloc/cudaFree entirely)
+        key = (str(device), G * n_cap * 16 + 256, n_cap + 256)
+        cached = _WORKSPACE.pop("buffers", None)
+        if cached is not None and cached[0] == key:
+            codes, labels = cached[1], cached[2]
+        else:
+            del cached
+            codes = [torch.empty(key[1], dtype=torch.uint8, device=device) for _ in range(2)]
+            labels = [torch.empty(key[2], dtype=torch.uint8, device=device) for _ in range(2)]
         return cls(n_local, n_features, n_classes, n_cap, G, codes, labels, device)
+
+    def release(self) -> None:
+        """Hand the big buffers back to the one-entry workspace cache (call when the fit is done)."""
+        if self.codes is not None:
+            key = (str(self.device), self.G * self.n_cap * 16 + 256, self.n_cap + 256)
+            _WORKSPACE["buffers"] = (key, self.codes, self.labels)
+            self.codes = self.labels = None
 
     # -- encode ---------------------------------------------------------------
     def encode_float(self, X, mapper: BinMapper, row0: int = 0, mismatch=None) -> None:
@@ -294,6 +328,8 @@ class TreeBuilder:
         ctx.dot_mode = probe_dot_mode()
         self._plogp = plogp_table(dev)
         ctx.plogp, ctx.plogp_n = _p(self._plogp), PLOGP_N
+        self._klogk = klogk_table(dev)
+        ctx.klogk, ctx.klogk_n = _p(self._klogk), KLOGK_N
         ctx.world, ctx.rank = (P, self.rank) if peer_mode else (1, 0)
         ctx.fpo = self.fpo
 
@@ -368,6 +404,10 @@ class TreeBuilder:
         self.side = 0  # which slot set is "current"
         self.hcur = 0
         self.n_slots, self.n_nodes, self.depth = 1, 1, 0
+        self._timers = None
+        if profile:
+            self._timers = torch.zeros(16, dtype=torch.int64, device=dev)
+            ctx.timers = _p(self._timers)
 
     @staticmethod
     def region_bytes(world: int, F: int, B: int, C: int, h_cap: int) -> int:
@@ -441,6 +481,7 @@ class TreeBuilder:
         self.scalars.copy_(torch.tensor([1, 0, 1, 0, 0, 0, 0, 0], dtype=torch.int32))
         self.n_slots, self.n_nodes, self.depth = 1, 1, 0
         self._host_scal = torch.empty(8, dtype=torch.int32).pin_memory()
+        self._phase_ns = []
 
     def prepare_level(self) -> None:
         n_slots, n_nodes = self.n_slots, self.n_nodes
@@ -478,6 +519,10 @@ class TreeBuilder:
     def read_level(self) -> int:
         self._host_scal.copy_(self.scalars, non_blocking=True)
         self.torch.cuda.current_stream().synchronize()
+        if self._timers is not None:
+            t = self._timers.cpu().numpy().astype(np.float64) / 1e6
+            names = ("plan", "hist", "push+bar", "gainB", "gainD+bar", "finalize")
+            self._phase_ns.append({n + "_ms": float(t[i + 1] - t[i]) for i, n in enumerate(names)})
         self.n_next, self.n_nodes = int(self._host_scal[1]), int(self._host_scal[2])
         return self.n_next
 
@@ -517,10 +562,11 @@ class TreeBuilder:
                 events.append((n_slots, ev))
         if events:
             torch.cuda.synchronize()
-            for ns, ev in events:
-                self.stats.level_ms.append(
-                    {"slots": ns, "search_ms": ev[0].elapsed_time(ev[1]), "partition_ms": ev[2].elapsed_time(ev[3])}
-                )
+            for i, (ns, ev) in enumerate(events):
+                d = {"slots": ns, "search_ms": ev[0].elapsed_time(ev[1]), "partition_ms": ev[2].elapsed_time(ev[3])}
+                if i < len(self._phase_ns):
+                    d.update(self._phase_ns[i])
+                self.stats.level_ms.append(d)
         return self._download(self.n_nodes)
 
     def _download(self, n_nodes: int) -> FlatTree:
@@ -693,6 +739,7 @@ def fit_from_host(X: np.ndarray, y_codes: np.ndarray, n_classes: int, params: Sp
         flat = builder.build()
     finally:
         builder.close()
+        data.release()
     fit_from_host.last_stats = builder.stats
     return flat, mapper
 
@@ -724,23 +771,27 @@ def fit_from_torch(X, y, params: SplitParams, *, max_bins: int = 256, comm=None,
     y_min, y_max = int(y_dev.min()), int(y_dev.max())
     if y_min < 0:
         raise ValueError("class labels must be non-negative integers")
-    if y_max < (1 << 16):  # small label range: one counting pass instead of a sort
-        present = torch.bincount(y_dev.view(-1).to(torch.int64) if y_dev.dtype != torch.uint8 else y_dev.view(-1).int(),
-                                 minlength=y_max + 1)
-        classes_t = torch.nonzero(present, as_tuple=False).view(-1)
-    else:
-        classes_t = torch.unique(y_dev)
-    classes = classes_t.cpu().numpy().astype(np.int64)
+    lazy_classes = False
     if comm is not None and comm.size > 1:
-        classes = np.unique(np.concatenate(comm.allgather_object(classes)))
-        classes_t = torch.from_numpy(classes).to(dev)
-    if classes.size and classes.min() < 0:
-        raise ValueError("class labels must be non-negative integers")
-    if len(classes) > MAX_CLASSES:
-        raise ValueError(f"the CUDA engine supports at most {MAX_CLASSES} classes")
-    if np.array_equal(classes, np.arange(len(classes))):
-        y_codes = y_dev  # labels already are 0..C-1
+        y_max = max(comm.allgather_object(y_max))
+    if y_max < MAX_CLASSES:
+        # label values are used as class codes; the labels that actually occur are read off the
+        # root histogram afterwards (saves a counting pass over y)
+        lazy_classes = True
+        classes = np.arange(y_max + 1, dtype=np.int64)
+        y_codes = y_dev
     else:
+        if y_max < (1 << 16):  # small label range: one counting pass instead of a sort
+            present = torch.bincount(y_dev.view(-1).to(torch.int64), minlength=y_max + 1)
+            classes_t = torch.nonzero(present, as_tuple=False).view(-1)
+        else:
+            classes_t = torch.unique(y_dev)
+        classes = classes_t.cpu().numpy().astype(np.int64)
+        if comm is not None and comm.size > 1:
+            classes = np.unique(np.concatenate(comm.allgather_object(classes)))
+            classes_t = torch.from_numpy(classes).to(dev)
+        if len(classes) > MAX_CLASSES:
+            raise ValueError(f"the CUDA engine supports at most {MAX_CLASSES} classes")
         y_codes = torch.bucketize(y_dev.to(torch.int64), classes_t.to(torch.int64))
 
     if X.dtype == torch.uint8:
@@ -782,7 +833,13 @@ def fit_from_torch(X, y, params: SplitParams, *, max_bins: int = 256, comm=None,
         flat = builder.build()
     finally:
         builder.close()
+        data.release()
     fit_from_torch.last_stats = builder.stats
+    if lazy_classes:
+        # classes_ = labels that occur: read them off the root's class counts
+        seen = np.flatnonzero(flat.counts[0] > 0)
+        classes = seen.astype(np.int64)
+        flat.counts = np.ascontiguousarray(flat.counts[:, seen])
     return flat, mapper, classes
 
 

@@ -122,6 +122,18 @@ class DecisionTreeClassifier(ClassifierMixin, BaseEstimator):
         self.max_bins = max_bins
         self.device = device
 
+    # ``tree_`` (the reference's Node graph, ``:189``) is materialised from the flat arrays the
+    # first time it is read: fitting a 2000-node tree should not pay for 2000 Python objects
+    # unless somebody looks at them.
+    def __getattr__(self, name):
+        if name == "tree_":
+            flat = self.__dict__.get("flat_tree_")
+            if flat is not None:
+                root = flat.to_nodes()
+                self.__dict__["tree_"] = root
+                return root
+        raise AttributeError(f"{type(self).__name__!r} object has no attribute {name!r}")
+
     # ------------------------------------------------------------------ util
     def _params(self, depth_offset: int = 0) -> SplitParams:
         if self.criterion not in ("entropy", "gini"):
@@ -232,8 +244,8 @@ class DecisionTreeClassifier(ClassifierMixin, BaseEstimator):
         self.n_features_in_ = X.shape[1]
         self.classes_ = np.unique(y)
         X, y = self._shard(X, y, comm)
+        self.__dict__.pop("tree_", None)
         self.flat_tree_ = self._fit_flat(X, y, comm=comm)
-        self.tree_ = self.flat_tree_.to_nodes()
         return self
 
     def _fit_torch(self, X, y, comm):
@@ -263,8 +275,8 @@ class DecisionTreeClassifier(ClassifierMixin, BaseEstimator):
         ]
         self.bin_mapper_ = mapper
         self.engine_ = "cuda"
+        self.__dict__.pop("tree_", None)
         self.flat_tree_ = flat
-        self.tree_ = flat.to_nodes()
         return self
 
     # --------------------------------------------------------------- predict
@@ -283,8 +295,8 @@ class DecisionTreeClassifier(ClassifierMixin, BaseEstimator):
         return flat.apply_raw(X)
 
     def _flat(self) -> FlatTree:
-        check_is_fitted(self, "tree_")
-        flat = getattr(self, "flat_tree_", None)
+        check_is_fitted(self)
+        flat = self.__dict__.get("flat_tree_")
         if flat is None:  # e.g. tree_ assigned by hand or unpickled from an older object
             flat = FlatTree.from_nodes(self.tree_)
             self.flat_tree_ = flat
@@ -438,8 +450,8 @@ class ParallelDecisionTreeClassifier(DecisionTreeClassifier):
             self.n_features_ = X.shape[1]
             self.n_features_in_ = X.shape[1]
             self.classes_ = np.unique(np.concatenate(parts))
+            self.__dict__.pop("tree_", None)
             self.flat_tree_ = self._fit_flat(X, y, comm=comm)
-            self.tree_ = self.flat_tree_.to_nodes()
             return self
         return super().fit(X, y)
 
