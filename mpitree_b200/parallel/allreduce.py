@@ -1,0 +1,68 @@
+"""K5 front end: peer-memory u32 sum all-reduce (one-shot / two-shot) vs ``ncclAllReduce``.
+
+There is no counterpart in the reference (its only collective is the pickled subtree
+``allgather``, ``mpitree/tree/decision_tree.py:456-466``).  Histograms are integer counts, so
+the peer reduction is bit-deterministic regardless of arrival order.
+"""
+
+from __future__ import annotations
+
+import ctypes
+
+__all__ = ["PeerAllReduce"]
+
+
+class PeerAllReduce:
+    """Symmetric buffers + flags for repeated all-reduces of up to ``max_count`` u32 values.
+
+    Producers can write straight into :meth:`input_view` (zero-copy); :meth:`all_reduce`
+    copies from an ordinary tensor first.
+    """
+
+    def __init__(self, comm, max_count: int):
+        import torch
+
+        from ..ops import _lib as L
+        from .symm import IpcRegion
+
+        self.L, self.lib = L, L.load()
+        self.comm = comm
+        self.world, self.rank = comm.size, comm.rank
+        self.cap = ((int(max_count) + 3) // 4) * 4
+        self.region = IpcRegion(2 * self.cap * 4 + 256, comm)
+        self._bufs = (ctypes.c_void_p * 16)(*[p for p in self.region.ptrs])
+        self._flags = (ctypes.c_void_p * 16)(*[p + 2 * self.cap * 4 for p in self.region.ptrs])
+        self._mem = self.region.buf.as_tensor()
+        self.epoch = 0
+        self.torch = torch
+
+    def input_view(self, count: int):
+        return self._mem[: count * 4].view(self.torch.int32)
+
+    def result_view(self, count: int):
+        return self._mem[self.cap * 4 : (self.cap + count) * 4].view(self.torch.int32)
+
+    def launch(self, count: int, algo: int = 1, out=None) -> None:
+        """Reduce what is in :meth:`input_view`; result in ``out`` or :meth:`result_view`."""
+        torch = self.torch
+        dst = out.data_ptr() if out is not None else self.region.ptrs[self.rank] + self.cap * 4
+        rc = self.lib.mtb_allreduce_u32(
+            ctypes.c_int(algo), ctypes.c_int(self.rank), ctypes.c_int(self.world), self._bufs, self._flags,
+            ctypes.c_int64(count), ctypes.c_int64(self.cap), ctypes.c_uint32(self.epoch), ctypes.c_void_p(dst),
+            ctypes.c_void_p(torch.cuda.current_stream().cuda_stream),
+        )
+        self.epoch = (self.epoch + 2) & 0x7FFFFFFF
+        self.L.check(rc, "mtb_allreduce_u32")
+
+    def all_reduce(self, tensor, algo: int = 1):
+        """Sum ``tensor`` (int32/uint32, 1-D, CUDA) across ranks; returns a new tensor."""
+        count = tensor.numel()
+        if count > self.cap:
+            raise ValueError(f"{count} elements exceed the symmetric buffer capacity {self.cap}")
+        self.input_view(count).copy_(tensor.view(self.torch.int32).reshape(-1))
+        out = self.torch.empty(count, dtype=self.torch.int32, device=tensor.device)
+        self.launch(count, algo, out)
+        return out.view(tensor.dtype)
+
+    def close(self) -> None:
+        self.region.close()

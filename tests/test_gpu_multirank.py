@@ -69,6 +69,17 @@ for reduce in ("p2p", "nccl"):
 Xt, yt = torch.from_numpy(X[lo:hi]).cuda(), torch.from_numpy(y[lo:hi]).cuda()
 clf = ParallelDecisionTreeClassifier(max_depth=7, data_layout="sharded").fit(Xt, yt)
 assert clf.export_text() == want.export_text()
+# K5: peer all-reduce kernels vs torch
+from mpitree_b200.parallel.allreduce import PeerAllReduce
+from mpitree_b200.parallel.comm import TorchComm
+ar = PeerAllReduce(TorchComm(), 1 << 20)
+for count in (1, 5, 1024, 100_003, 1 << 20):
+    x = torch.randint(0, 1 << 20, (count,), dtype=torch.int32, device="cuda")
+    want = x.clone(); dist.all_reduce(want)
+    for algo in (0, 1):
+        got = ar.all_reduce(x, algo)
+        assert torch.equal(got, want), (count, algo)
+ar.close()
 dist.barrier()
 if rank == 0:
     print("MULTIGPU_OK", world)
