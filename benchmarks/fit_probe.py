@@ -60,7 +60,7 @@ def main():
         ms = s.elapsed_time(e)
         out.append(ms)
         if rank == 0:
-          print(f"rep {rep}: {ms:.2f} ms ({a.rows / ms / 1e3:.1f} M rows/s) nodes={flat.n_nodes} wall={time.perf_counter() - t0:.3f}s")
+          print(f"rep {rep}: {ms:.2f} ms ({a.rows * world / ms / 1e3:.1f} M rows/s total) nodes={flat.n_nodes} wall={time.perf_counter() - t0:.3f}s")
     st = b.stats
     if rank != 0:
         return

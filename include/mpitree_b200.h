@@ -107,6 +107,11 @@ typedef struct MtbCtx {
    * klogk is the host's table of g(k) for k < klogk_n (0 = compute on device).            */
   int64_t klogk;
   int64_t klogk_n;
+  /* world > 1: the owner's reduced slabs for its own features, ping-pong by level:
+   * u32 [h_cap][fpo*B*C] each.  BUILD pairs write (own partial + staged partials) here and
+   * DERIVE pairs write (parent - sibling) here, so neither touches the local partial slabs and
+   * both kinds of pair can run in one pass.                                                  */
+  int64_t rstore[2];
   int64_t reserved[1];
 } MtbCtx;
 

@@ -143,6 +143,13 @@ __device__ void plan_phase(const MtbCtx& ctx, int* smem_warp) {
 
 __global__ void k_plan(const __grid_constant__ MtbCtx ctx) {
   __shared__ int smem_warp[33];
+  if (ptr_of<const int>(ctx.scalars)[0] == 0) {  // empty frontier: leave a consistent "nothing to do"
+    if (threadIdx.x == 0) {
+      int* sc = ptr_of<int>(ctx.scalars);
+      sc[1] = 0; sc[3] = 0; sc[4] = 0; sc[6] = 0; sc[7] = 0;
+    }
+    return;
+  }
   plan_phase(ctx, smem_warp);
 }
 
@@ -424,7 +431,43 @@ __device__ void gain_pair(const MtbCtx& ctx, uint32_t* slab, int slot, int f) {
       if (++c == C) { c = 0; ++b; }
     }
   };
-  if (mode == MTB_MODE_DERIVE) {
+  if (P > 1) {
+    // Multi-rank owner path.  Reduced slabs of the own features live in rstore (ping-pong by
+    // level); the local partial slabs are never modified, so BUILD and DERIVE pairs are
+    // independent of each other and run in one pass.
+    const int fl = f - r * (int)ctx.fpo;
+    const int64_t region = ctx.fpo * ctx.B * ctx.C;
+    const uint32_t* stage = ptr_of<const uint32_t>(ctx.peer_hist[r]) + (int64_t)fl * B * C;
+    uint4* out4 = reinterpret_cast<uint4*>(ptr_of<uint32_t>(ctx.rstore[ctx.hcur]) + (int64_t)slot * region + (int64_t)fl * B * C);
+    // reduced counts of `s`: own partial + what the peers pushed
+    auto reduced4 = [&](int s, int q) -> uint4 {
+      uint4 x = reinterpret_cast<const uint4*>(v.hist_cur() + (int64_t)s * v.slab_words() + (int64_t)f * B * C)[q];
+      for (int p = 0; p < P; ++p)
+        if (p != r) {
+          const uint4 y = *reinterpret_cast<const uint4*>(stage + ((int64_t)p * ctx.h_cap + s) * region + q * 4);
+          x.x += y.x; x.y += y.y; x.z += y.z; x.w += y.w;
+        }
+      return x;
+    };
+    if (mode == MTB_MODE_DERIVE) {
+      const int par = ptr_of<const int>(ctx.slot_parent)[slot];
+      const int sib = ptr_of<const int>(ctx.slot_sibling)[slot];
+      const uint4* hp4 = reinterpret_cast<const uint4*>(ptr_of<const uint32_t>(ctx.rstore[ctx.hcur ^ 1]) +
+                                                        (int64_t)par * region + (int64_t)fl * B * C);
+      for (int q = lane; q < words / 4; q += 32) {
+        const uint4 a = hp4[q], d = reduced4(sib, q);
+        const uint4 x = make_uint4(a.x - d.x, a.y - d.y, a.z - d.z, a.w - d.w);
+        out4[q] = x;
+        put4(x, q * 4);
+      }
+    } else {
+      for (int q = lane; q < words / 4; q += 32) {
+        const uint4 x = reduced4(slot, q);
+        out4[q] = x;
+        put4(x, q * 4);
+      }
+    }
+  } else if (mode == MTB_MODE_DERIVE) {
     const int par = ptr_of<const int>(ctx.slot_parent)[slot];
     const int sib = ptr_of<const int>(ctx.slot_sibling)[slot];
     const uint32_t* hp = v.hist_prev() + (int64_t)par * v.slab_words() + (int64_t)f * B * C;
@@ -436,21 +479,6 @@ __device__ void gain_pair(const MtbCtx& ctx, uint32_t* slab, int slot, int f) {
     for (int q = lane; q < words / 4; q += 32) {
       const uint4 a = hp4[q], d = hs4[q];
       const uint4 x = make_uint4(a.x - d.x, a.y - d.y, a.z - d.z, a.w - d.w);
-      mine4[q] = x;
-      put4(x, q * 4);
-    }
-  } else if (P > 1) {
-    // BUILD on the owner: own partial + the partials the peers pushed into the staging area
-    const int64_t region = ctx.fpo * ctx.B * ctx.C;
-    const uint32_t* stage = ptr_of<const uint32_t>(ctx.peer_hist[r]) + (int64_t)(f - r * (int)ctx.fpo) * B * C;
-    uint4* mine4 = reinterpret_cast<uint4*>(mine);
-    for (int q = lane; q < words / 4; q += 32) {
-      uint4 x = mine4[q];
-      for (int p = 0; p < P; ++p)
-        if (p != r) {
-          const uint4 y = *reinterpret_cast<const uint4*>(stage + ((int64_t)p * ctx.h_cap + slot) * region + q * 4);
-          x.x += y.x; x.y += y.y; x.z += y.z; x.w += y.w;
-        }
       mine4[q] = x;
       put4(x, q * 4);
     }
@@ -538,9 +566,8 @@ __device__ void gain_pair(const MtbCtx& ctx, uint32_t* slab, int slot, int f) {
   __syncwarp();
 }
 
-// pass -1: every pair; 0: BUILD/NONE slots only; 1: DERIVE slots only.  With world > 1 a BUILD
-// pair reduces its slab in place, so DERIVE pairs (which read their sibling's reduced slab)
-// must run after a grid-wide sync.
+// pass -1: every pair (the normal case); 0 / 1: BUILD+NONE / DERIVE slots only (kept for
+// experiments: pairs never depend on one another, see gain_pair).
 __device__ void gain_phase(const MtbCtx& ctx, uint8_t* smem, int warps_per_block, int pass) {
   View v(ctx);
   const int F = (int)ctx.F;
@@ -724,6 +751,7 @@ __device__ void finalize_phase(const MtbCtx& ctx, int* smem_warp) {
 
 __global__ void __launch_bounds__(1024) k_finalize(const __grid_constant__ MtbCtx ctx) {
   __shared__ int smem_warp[33];
+  if (ptr_of<const int>(ctx.scalars)[0] == 0) return;
   finalize_phase(ctx, smem_warp);
 }
 
@@ -860,6 +888,9 @@ __global__ void __launch_bounds__(kHistThreads, 1) k_level_fused(const __grid_co
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ int smem_warp[33];
   cg::grid_group grid = cg::this_grid();
+  // empty frontier (the tree finished at an earlier level): uniform early exit on every CTA of
+  // every rank, before any grid or peer barrier
+  if (ptr_of<const int>(ctx.scalars)[0] == 0) return;
   stamp(ctx, 0);
   if (blockIdx.x == 0) plan_phase(ctx, smem_warp);
   grid.sync();
@@ -871,10 +902,8 @@ __global__ void __launch_bounds__(kHistThreads, 1) k_level_fused(const __grid_co
     push_phase(ctx);
     peer_barrier(ctx, grid, (uint32_t)ctx.epoch + 1u);
     stamp(ctx, 3);
-    gain_phase(ctx, smem, kFusedGainWarps, 0);
-    grid.sync();
+    gain_phase(ctx, smem, kFusedGainWarps, -1);
     stamp(ctx, 4);
-    gain_phase(ctx, smem, kFusedGainWarps, 1);
     peer_barrier(ctx, grid, (uint32_t)ctx.epoch + 2u);
     stamp(ctx, 5);
   } else {
@@ -972,12 +1001,7 @@ extern "C" int mtb_level_gain(const MtbCtx* ctx, void* stream) {
   int maxb = sm_count() * 2;
   if (blocks > maxb) blocks = maxb;
   if (blocks < 1) blocks = 1;
-  if (ctx->world > 1) {
-    k_gain<<<blocks, kGainWarps * 32, smem, (cudaStream_t)stream>>>(*ctx, 0);
-    k_gain<<<blocks, kGainWarps * 32, smem, (cudaStream_t)stream>>>(*ctx, 1);
-  } else {
-    k_gain<<<blocks, kGainWarps * 32, smem, (cudaStream_t)stream>>>(*ctx, -1);
-  }
+  k_gain<<<blocks, kGainWarps * 32, smem, (cudaStream_t)stream>>>(*ctx, -1);
   MTB_CHECK(cudaGetLastError());
   return 0;
 }

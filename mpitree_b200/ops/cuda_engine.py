@@ -280,6 +280,8 @@ class TreeBuilder:
         profile: bool = False,
         hist_budget_bytes: Optional[int] = None,
         h_cap: Optional[int] = None,
+        min_free_bytes: Optional[int] = None,
+        async_levels: bool = True,
     ):
         import torch
 
@@ -347,15 +349,16 @@ class TreeBuilder:
         slab_words = G * 16 * B * C
         self.slab_words = slab_words
         if h_cap is None:
+            agreed = min_free_bytes is not None or hist_budget_bytes is not None
             if hist_budget_bytes is None:
-                free, _total = torch.cuda.mem_get_info(dev)
+                free = min_free_bytes if min_free_bytes is not None else torch.cuda.mem_get_info(dev)[0]
                 hist_budget_bytes = int(free * 0.35)
             depth_cap = 1 << 30 if params.max_depth is None else 1 << max(int(params.max_depth) - 1, 0)
             rows_cap = max(2, n_global // max(int(params.min_samples_split), 2) + 1)
             per_slot = slab_words * 4 * (3 if peer_mode else 2)  # two sides (+ staging)
             h_cap = min(depth_cap, rows_cap, max(2, hist_budget_bytes // per_slot))
             h_cap = max(2, h_cap + (h_cap & 1))
-            if comm is not None and comm.size > 1:
+            if comm is not None and comm.size > 1 and not agreed:
                 h_cap = min(comm.allgather_object(h_cap))  # every rank must use the same layout
         self.h_cap = int(h_cap)  # histogram slabs per ping-pong side
         m_cap = 2 * self.h_cap + 2  # slot-array capacity: a level may emit two children per slot
@@ -364,6 +367,16 @@ class TreeBuilder:
         self.stats.hist_bytes = 2 * self.h_cap * slab_words * 4
         node_cap = 2 * n_global + 1 if params.max_depth is None else min((1 << (int(params.max_depth) + 1)) - 1, 2 * n_global + 1)
         self.node_cap = max(3, min(node_cap, 1 << 16))
+        # With a bounded depth whose worst-case frontier and node count fit, the whole fit is
+        # enqueued without reading anything back between levels (kernels of levels that turn
+        # out to be empty return immediately).
+        worst_frontier = None if params.max_depth is None else 1 << max(int(params.max_depth) - 1, 0)
+        self.async_levels = bool(
+            async_levels and not profile and params.max_depth is not None and int(params.max_depth) >= 1
+            and worst_frontier <= self.h_cap and node_cap <= (1 << 22) and reduce != "lockstep"
+        )
+        if self.async_levels:
+            self.node_cap = max(3, node_cap)
 
         i32 = torch.int32
         z = lambda n, dt=i32: torch.zeros(max(int(n), 1), dtype=dt, device=dev)  # noqa: E731
@@ -400,6 +413,10 @@ class TreeBuilder:
                 ctx.peer_rec[q] = ptrs[q] + self._layout[1]
                 ctx.peer_flags[q] = ptrs[q] + self._layout[2]
         ctx.h_cap = self.h_cap
+        if peer_mode:
+            rs_words = self.h_cap * self.fpo * B * C
+            self.rstore = [z(rs_words), z(rs_words)]
+            ctx.rstore[0], ctx.rstore[1] = _p(self.rstore[0]), _p(self.rstore[1])
         self.ctx = ctx
         self.side = 0  # which slot set is "current"
         self.hcur = 0
@@ -521,7 +538,7 @@ class TreeBuilder:
         self.torch.cuda.current_stream().synchronize()
         if self._timers is not None:
             t = self._timers.cpu().numpy().astype(np.float64) / 1e6
-            names = ("plan", "hist", "push+bar", "gainB", "gainD+bar", "finalize")
+            names = ("plan", "hist", "push+bar", "gain", "bar", "finalize")
             self._phase_ns.append({n + "_ms": float(t[i + 1] - t[i]) for i, n in enumerate(names)})
         self.n_next, self.n_nodes = int(self._host_scal[1]), int(self._host_scal[2])
         return self.n_next
@@ -543,6 +560,8 @@ class TreeBuilder:
         if self.reduce == "lockstep":
             raise RuntimeError("virtual ranks are driven by build_lockstep()")
         self.start()
+        if self.async_levels:
+            return self._build_async()
         events = []
         while self.n_slots > 0:
             self.prepare_level()
@@ -567,6 +586,27 @@ class TreeBuilder:
                 if i < len(self._phase_ns):
                     d.update(self._phase_ns[i])
                 self.stats.level_ms.append(d)
+        return self._download(self.n_nodes)
+
+    def _build_async(self) -> FlatTree:
+        """All levels enqueued back to back; one read-back at the end."""
+        for depth in range(int(self.params.max_depth)):
+            self.depth = depth
+            self.n_slots = min(1 << depth, self.h_cap)  # upper bound: sizes the zeroing and launches
+            self.ctx.depth = depth
+            self.ctx.n_slots_host = self.n_slots
+            self._bind()
+            self.hist[self.hcur][: self.n_slots * self.slab_words].zero_()
+            self.search_level()
+            self._launch("mtb_level_partition")
+            self._launch("mtb_level_commit")
+            self.data.cur ^= 1
+            self.side ^= 1
+            self.hcur ^= 1
+            self.stats.levels += 1
+        self._host_scal.copy_(self.scalars, non_blocking=True)
+        self.torch.cuda.current_stream().synchronize()
+        self.n_nodes = int(self._host_scal[2])
         return self._download(self.n_nodes)
 
     def _download(self, n_nodes: int) -> FlatTree:
@@ -596,7 +636,7 @@ def _shared_region(nbytes: int, comm):
 
     key = (comm.size, comm.rank)
     reg = _REGIONS.get(key)
-    need = max(comm.allgather_object(int(nbytes)))
+    need = int(nbytes)  # a pure function of (h_cap, shapes): identical on every rank by construction
     if reg is None or reg.nbytes < need:
         if reg is not None:
             reg.close()
@@ -658,6 +698,31 @@ def build_lockstep(builders: List[TreeBuilder]) -> List[FlatTree]:
 # ---------------------------------------------------------------------------
 # front ends
 # ---------------------------------------------------------------------------
+class _Stages:
+    """Optional wall-clock stage timer for ``fit`` (``MTB_TIMING=1``): syncs the device at each mark."""
+
+    def __init__(self):
+        import os
+
+        self.on = os.environ.get("MTB_TIMING") == "1"
+        self.t = time.perf_counter()
+        self.rows = []
+
+    def mark(self, name: str) -> None:
+        if not self.on:
+            return
+        import torch
+
+        torch.cuda.synchronize()
+        now = time.perf_counter()
+        self.rows.append((name, (now - self.t) * 1e3))
+        self.t = now
+
+    def report(self) -> None:
+        if self.on:
+            print("[mtb timing] " + "  ".join(f"{n}={ms:.2f}ms" for n, ms in self.rows), flush=True)
+
+
 def _sample_rows(n: int, cap: int = SAMPLE_ROWS) -> Optional[np.ndarray]:
     if n <= cap:
         return None
@@ -729,12 +794,13 @@ def fit_from_host(X: np.ndarray, y_codes: np.ndarray, n_classes: int, params: Sp
         else:
             data.encode_float(chunk, mapper, r0)
     data.set_labels(torch.from_numpy(np.asarray(y_codes)).to(dev))
-    n_global = n
+    n_global, min_free = n, None
     if comm is not None and comm.size > 1:
-        n_global = int(sum(comm.allgather_object(n)))
+        meta = comm.allgather_object((n, int(torch.cuda.mem_get_info(dev)[0])))
+        n_global, min_free = int(sum(m[0] for m in meta)), min(m[1] for m in meta)
     _dist_group(comm)
     builder = TreeBuilder(data, int(mapper.n_bins.max()), params, n_global=n_global, comm=comm,
-                          **(builder_kwargs or {}))
+                          min_free_bytes=min_free, **(builder_kwargs or {}))
     try:
         flat = builder.build()
     finally:
@@ -754,6 +820,7 @@ def fit_from_torch(X, y, params: SplitParams, *, max_bins: int = 256, comm=None,
     import torch
 
     dev = _device()
+    st = _Stages()
     if replicated and comm is not None and comm.size > 1:
         n = X.shape[0]
         lo, hi = (n * comm.rank) // comm.size, (n * (comm.rank + 1)) // comm.size
@@ -771,9 +838,14 @@ def fit_from_torch(X, y, params: SplitParams, *, max_bins: int = 256, comm=None,
     y_min, y_max = int(y_dev.min()), int(y_dev.max())
     if y_min < 0:
         raise ValueError("class labels must be non-negative integers")
+    st.mark("labels")
     lazy_classes = False
+    n_global, min_free = n, None
     if comm is not None and comm.size > 1:
-        y_max = max(comm.allgather_object(y_max))
+        # the one host-side exchange of a fit: label range, shard sizes, free memory
+        meta = comm.allgather_object((y_max, n, int(torch.cuda.mem_get_info(dev)[0])))
+        y_max = max(m[0] for m in meta)
+        n_global, min_free = int(sum(m[1] for m in meta)), min(m[2] for m in meta)
     if y_max < MAX_CLASSES:
         # label values are used as class codes; the labels that actually occur are read off the
         # root histogram afterwards (saves a counting pass over y)
@@ -815,7 +887,9 @@ def fit_from_torch(X, y, params: SplitParams, *, max_bins: int = 256, comm=None,
                         e[-1] = col_max[f]
                     mapper.lossless[f] = False
 
+    st.mark("meta+mapper")
     data = DeviceDataset.allocate(n, F, len(classes), dev)
+    st.mark("alloc")
     if X.is_cuda:
         (data.encode_u8(X, None, 0) if X.dtype == torch.uint8 else data.encode_float(X, mapper, 0))
     else:
@@ -823,17 +897,18 @@ def fit_from_torch(X, y, params: SplitParams, *, max_bins: int = 256, comm=None,
             chunk = X[r0 : r0 + ENCODE_CHUNK_ROWS].to(dev, non_blocking=True)
             (data.encode_u8(chunk, None, r0) if X.dtype == torch.uint8 else data.encode_float(chunk, mapper, r0))
     data.set_labels(y_codes)
-    n_global = n
-    if comm is not None and comm.size > 1:
-        n_global = int(sum(comm.allgather_object(n)))
+    st.mark("encode")
     _dist_group(comm)
     builder = TreeBuilder(data, int(mapper.n_bins.max()), params, n_global=n_global, comm=comm,
-                          **(builder_kwargs or {}))
+                          min_free_bytes=min_free, **(builder_kwargs or {}))
+    st.mark("builder_init")
     try:
         flat = builder.build()
     finally:
         builder.close()
         data.release()
+    st.mark("build")
+    st.report()
     fit_from_torch.last_stats = builder.stats
     if lazy_classes:
         # classes_ = labels that occur: read them off the root's class counts
