@@ -34,6 +34,7 @@ extern "C" {
 #define MTB_MODE_NONE 0
 #define MTB_MODE_BUILD 1
 #define MTB_MODE_DERIVE 2
+#define MTB_MODE_HANDOFF 3 /* rows are kept and listed for the subtree phase; no histogram */
 
 /*
  * Build context.  Plain struct of 64-bit fields so that ctypes / any FFI can fill
@@ -112,6 +113,12 @@ typedef struct MtbCtx {
    * DERIVE pairs write (parent - sibling) here, so neither touches the local partial slabs and
    * both kinds of pair can run in one pass.                                                  */
   int64_t rstore[2];
+  /* ---- hand-off (phase 2): a non-terminal child with <= small_rows global rows leaves the
+   * level-wise build; after its rows are partitioned into place the commit phase appends
+   * (node id, row segment, ping-pong side) to this list; scalars[5] counts the entries. ---- */
+  int64_t small_rows;                 /* 0 = never hand off                                   */
+  int64_t ho_cap;
+  int64_t ho_node, ho_begin, ho_end, ho_side; /* i32 [ho_cap]                                 */
   int64_t reserved[1];
 } MtbCtx;
 
@@ -144,6 +151,19 @@ int mtb_level_push(const MtbCtx* ctx, void* stream);      /* world > 1: push par
 int mtb_level_fused(const MtbCtx* ctx, void* stream);
 /* Shared memory / launch geometry the hist phase will use for this ctx (for reports). */
 int mtb_hist_config(const MtbCtx* ctx, int* threads, int* smem_bytes, int* stages, int* rows_per_stage);
+
+/* ---- K6: finish small subtrees, one CTA each (struct MtbSubtreeArgs is defined in
+ * mpitree_b200/csrc/subtree.cu and mirrored in mpitree_b200/ops/_lib.py) ------------------------ */
+struct MtbSubtreeArgs;
+int mtb_subtree_config(int64_t B, int64_t C); /* features per tile, 0 = does not fit */
+int mtb_subtree_build(const struct MtbSubtreeArgs* args, int grid, void* stream);
+/* Copy row segments (all feature-group planes + labels) into another (possibly peer-mapped)
+ * data set: item i copies rows [src_begin[i], src_end[i]) of side src_side[i] to
+ * dst_begin[i].. of the destination planes (K6 gather half).                                 */
+int mtb_gather_rows(const void* src_codes0, const void* src_codes1, const void* src_labels0, const void* src_labels1,
+                    int64_t src_n_cap, int64_t G, const int32_t* src_side, const int32_t* src_begin,
+                    const int32_t* src_end, const int64_t* dst_codes, const int64_t* dst_labels,
+                    const int64_t* dst_n_cap, const int32_t* dst_begin, int64_t n_items, void* stream);
 
 /* ---- K4: batched predict ----------------------------------------------------------- */
 /* Pack {feature, left child, leaf label} into 16-byte node records (packed_out: n_nodes*16 B). */

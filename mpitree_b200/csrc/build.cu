@@ -174,6 +174,8 @@ struct UnitCursor {
     slot = -1;
     slot_u0 = slot_u1 = 0;
   }
+  // position on unit u: a full search/divide only when entering a new slot, otherwise the
+  // (gs, chunk) pair of the previous unit is stepped by one
   __device__ __forceinline__ void seek(int u) {
     if (u >= slot_u1 || slot < 0) {
       slot = find_slot(prefix, n_slots, u);
@@ -182,10 +184,13 @@ struct UnitCursor {
       begin = sb[slot];
       end = se[slot];
       chunks = (end - begin + kRows - 1) / kRows;
+      const int local = u - slot_u0;
+      gs = local / chunks;
+      chunk = local - gs * chunks;
+    } else if (++chunk == chunks) {
+      chunk = 0;
+      ++gs;
     }
-    const int local = u - slot_u0;
-    gs = local / chunks;
-    chunk = local - gs * chunks;
     row0 = begin + chunk * kRows;
     nrows = min(kRows, end - row0);
   }
@@ -411,7 +416,7 @@ __device__ void gain_pair(const MtbCtx& ctx, uint32_t* slab, int slot, int f) {
   const int mode = ptr_of<const int>(ctx.slot_mode)[slot];
   const int64_t rec = (int64_t)slot * F + f;
   const unsigned divC = ((1u << 24) + (unsigned)C - 1u) / (unsigned)C;  // w / C == (w * divC) >> 24 for w < B*C
-  if (mode == MTB_MODE_NONE) {
+  if (mode == MTB_MODE_NONE || mode == MTB_MODE_HANDOFF) {
     if (lane < P) {
       Mailbox m = mailbox_at(ctx, P > 1 ? ctx.peer_rec[lane] : ctx.fb_cost);
       m.cost[rec] = INFINITY;
@@ -651,9 +656,10 @@ __device__ void finalize_phase(const MtbCtx& ctx, int* smem_warp) {
     int split = 0, pair = 0, units = 0;
     int bf = -1, bb = -1;
     double bgain = 0.0;
-    bool tl = true, tr = true;
+    bool tl = true, tr = true;   // child is a leaf by the stop rules
+    bool hl = false, hr = false; // child leaves the level-wise build (handed to the subtree phase)
     uint32_t nl = 0, nr = 0;
-    if (s < n && slot_mode[s] != MTB_MODE_NONE) {
+    if (s < n && (slot_mode[s] == MTB_MODE_BUILD || slot_mode[s] == MTB_MODE_DERIVE)) {
       const uint32_t* cnt = node_cnt + (int64_t)s * C;
       const int node = slot_node[s];
       for (int c = 0; c < C; ++c) t_counts[(int64_t)node * C + c] = cnt[c];
@@ -681,6 +687,8 @@ __device__ void finalize_phase(const MtbCtx& ctx, int* smem_warp) {
           const uint32_t* L = fb_left + ((int64_t)s * F + bf) * C;
           tl = is_terminal([&](int c) { return L[c]; }, C, depth + 1, ctx, nl);
           tr = is_terminal([&](int c) { return cnt[c] - L[c]; }, C, depth + 1, ctx, nr);
+          hl = !tl && (int64_t)nl <= ctx.small_rows;
+          hr = !tr && (int64_t)nr <= ctx.small_rows;
           pair = !(tl && tr);
           if (pair) units = (se[s] - sb[s] + kPartRows - 1) / kPartRows;
         }
@@ -724,7 +732,11 @@ __device__ void finalize_phase(const MtbCtx& ctx, int* smem_warp) {
         ns_sibling[a] = b; ns_sibling[b] = a;
         ns_src[a] = 2 * s; ns_src[b] = 2 * s + 1;
         int ma, mb;
-        if (!tl && !tr) {
+        if (hl || hr) {
+          // a handed-off child has no histogram, so its sibling (if it continues) is built directly
+          ma = tl ? MTB_MODE_NONE : (hl ? MTB_MODE_HANDOFF : MTB_MODE_BUILD);
+          mb = tr ? MTB_MODE_NONE : (hr ? MTB_MODE_HANDOFF : MTB_MODE_BUILD);
+        } else if (!tl && !tr) {
           // both children continue: build the smaller (global count, ties -> left), derive the other
           const bool left_small = nl <= nr;
           ma = left_small ? MTB_MODE_BUILD : MTB_MODE_DERIVE;
@@ -865,6 +877,17 @@ __global__ void k_commit(const __grid_constant__ MtbCtx ctx) {
     }
     nb[j] = b;
     ne[j] = e;
+    if (ns_mode[j] == MTB_MODE_HANDOFF) {
+      // rows are in place (side cur^1): list the node for the subtree phase.  Order of the
+      // entries is arbitrary; the host sorts them by node id.
+      const int k = atomicAdd(v.scalars() + 5, 1);
+      if (k < (int)ctx.ho_cap) {
+        ptr_of<int>(ctx.ho_node)[k] = ptr_of<const int>(ctx.nslot_node)[j];
+        ptr_of<int>(ctx.ho_begin)[k] = b;
+        ptr_of<int>(ctx.ho_end)[k] = e;
+        ptr_of<int>(ctx.ho_side)[k] = (int)(ctx.cur ^ 1);
+      }
+    }
   }
   // the next level's slot count becomes current (nothing in this kernel reads scalars[0])
   if (blockIdx.x == 0 && threadIdx.x == 0) v.scalars()[0] = n_next;

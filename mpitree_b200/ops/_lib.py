@@ -49,8 +49,19 @@ class MtbCtx(ctypes.Structure):
     _fields_ = (
         [(n, ctypes.c_int64) for n in _names]
         + [("peer_hist", ctypes.c_int64 * 16), ("peer_rec", ctypes.c_int64 * 16), ("peer_flags", ctypes.c_int64 * 16)]
-        + [("epoch", ctypes.c_int64), ("plogp", ctypes.c_int64), ("plogp_n", ctypes.c_int64), ("h_cap", ctypes.c_int64), ("fpo", ctypes.c_int64), ("timers", ctypes.c_int64), ("klogk", ctypes.c_int64), ("klogk_n", ctypes.c_int64), ("rstore", ctypes.c_int64 * 2), ("reserved", ctypes.c_int64 * 1)]
+        + [("epoch", ctypes.c_int64), ("plogp", ctypes.c_int64), ("plogp_n", ctypes.c_int64), ("h_cap", ctypes.c_int64), ("fpo", ctypes.c_int64), ("timers", ctypes.c_int64), ("klogk", ctypes.c_int64), ("klogk_n", ctypes.c_int64), ("rstore", ctypes.c_int64 * 2), ("small_rows", ctypes.c_int64), ("ho_cap", ctypes.c_int64), ("ho_node", ctypes.c_int64), ("ho_begin", ctypes.c_int64), ("ho_end", ctypes.c_int64), ("ho_side", ctypes.c_int64), ("reserved", ctypes.c_int64 * 1)]
     )
+
+
+class MtbSubtreeArgs(ctypes.Structure):
+    """Mirror of ``struct MtbSubtreeArgs`` (mpitree_b200/csrc/subtree.cu): all fields are int64."""
+
+    _names = (
+        "codes0 codes1 labels0 labels1 n_cap F G B C FT T max_depth min_samples_split criterion dot_mode "
+        "plogp plogp_n klogk klogk_n n_items it_side it_begin it_end it_depth it_off it_counts "
+        "o_feature o_bin o_left o_depth o_gain o_counts o_nn stack counter"
+    ).split()
+    _fields_ = [(n, ctypes.c_int64) for n in _names]
 
 
 def sources():

@@ -35,6 +35,8 @@ __all__ = [
 ]
 
 MAX_CLASSES = 128
+SMALL_ROWS_DEFAULT = 2048  # hand a node to the subtree kernel at or below this many rows
+SMALL_ROWS_MAX = 8192      # row indices live in shared memory as uint16 next to the histogram tile
 SAMPLE_ROWS = 1 << 18
 ENCODE_CHUNK_ROWS = 1 << 22
 
@@ -246,6 +248,7 @@ class BuildStats:
     smem_bytes: int = 0
     reduce: str = "none"
     world: int = 1
+    handed_off: int = 0
 
 
 _EPOCH = {"next": 0}  # barrier epochs are monotonic for the life of the process
@@ -282,6 +285,7 @@ class TreeBuilder:
         h_cap: Optional[int] = None,
         min_free_bytes: Optional[int] = None,
         async_levels: bool = True,
+        small_rows: Optional[int] = None,
     ):
         import torch
 
@@ -375,6 +379,22 @@ class TreeBuilder:
             async_levels and not profile and params.max_depth is not None and int(params.max_depth) >= 1
             and worst_frontier <= self.h_cap and node_cap <= (1 << 22) and reduce != "lockstep"
         )
+        # phase 2 (hand-off): nodes with <= small_rows global rows are finished by the subtree kernel.
+        # Default: only when the level-wise frontier could outgrow the histogram slot capacity.
+        if small_rows is None:
+            small_rows = 0 if (worst_frontier is not None and worst_frontier <= self.h_cap) else SMALL_ROWS_DEFAULT
+        if small_rows and reduce in ("lockstep", "nccl"):
+            small_rows = 0
+        if small_rows and self.lib.mtb_subtree_config(ctypes.c_int64(B), ctypes.c_int64(C)) == 0:
+            small_rows = 0
+        self.small_rows = int(min(small_rows, SMALL_ROWS_MAX))
+        ctx.small_rows = self.small_rows
+        if self.small_rows:
+            self.async_levels = False
+            self.ho_cap = int(min(max(n_global // 2 + 1, 16), 1 << 22))
+            self.ho = {k: torch.zeros(self.ho_cap, dtype=torch.int32, device=dev) for k in ("node", "begin", "end", "side")}
+            ctx.ho_cap = self.ho_cap
+            ctx.ho_node, ctx.ho_begin, ctx.ho_end, ctx.ho_side = (_p(self.ho[k]) for k in ("node", "begin", "end", "side"))
         if self.async_levels:
             self.node_cap = max(3, node_cap)
 
@@ -586,7 +606,12 @@ class TreeBuilder:
                 if i < len(self._phase_ns):
                     d.update(self._phase_ns[i])
                 self.stats.level_ms.append(d)
-        return self._download(self.n_nodes)
+        trunk = self._download(self.n_nodes)
+        if self.small_rows:
+            from .subtree_phase import finish_subtrees
+
+            trunk = finish_subtrees(self, trunk)
+        return trunk
 
     def _build_async(self) -> FlatTree:
         """All levels enqueued back to back; one read-back at the end."""

@@ -1,0 +1,262 @@
+"""Phase 2 on GPUs: finish handed-off subtrees (K6) and stitch them into the trunk.
+
+Host driver for ``mtb_subtree_build`` / ``mtb_gather_rows`` (``csrc/subtree.cu``).  The
+reference gives each half of a communicator one child subtree and gathers the pickled
+results (``mpitree/tree/decision_tree.py:447-477``); here
+
+1. the level-wise builder lists every non-terminal node whose global row count dropped to
+   ``small_rows`` (its rows are already contiguous on every rank),
+2. owners are chosen by sized bin-packing (:func:`mpitree_b200.parallel.handoff.assign_owners`),
+3. every rank writes its rows of a node straight into the owner's peer-mapped receive planes,
+4. each owner finishes its subtrees, one CTA per subtree, with no further communication,
+5. the flat node records are exchanged and every rank stitches the identical tree.
+"""
+
+from __future__ import annotations
+
+import ctypes
+from typing import List, Optional
+
+import numpy as np
+
+from ..models.flat_tree import FlatTree
+
+__all__ = ["finish_subtrees", "stitch_arrays"]
+
+
+def _p(t) -> int:
+    return int(t.data_ptr())
+
+
+def stitch_arrays(trunk: FlatTree, roots: np.ndarray, offs: np.ndarray, nn: np.ndarray, sub: dict) -> FlatTree:
+    """Attach finished subtrees (flat arrays) to the trunk and renumber breadth-first.
+
+    ``roots[i]`` is the trunk node replaced by subtree ``i``; its records live at
+    ``sub[...][offs[i] : offs[i] + nn[i]]`` with child ids relative to ``offs[i]``.
+    Vectorised per tree level, so millions of nodes are fine.
+    """
+    Nt, C = trunk.n_nodes, trunk.counts.shape[1]
+    if len(roots) == 0:
+        return trunk
+    total_sub = int(sub["feature"].shape[0])
+    # combined table: trunk ids, then every subtree record at Nt + index
+    feature = np.concatenate([trunk.feature, sub["feature"]]).astype(np.int32)
+    bin_ = np.concatenate([trunk.bin, sub["bin"]]).astype(np.int32)
+    gain = np.concatenate([trunk.gain, sub["gain"]])
+    counts = np.concatenate([trunk.counts, sub["counts"].astype(np.int64)])
+    # absolute child ids of subtree records
+    offs = np.asarray(offs, np.int64)
+    nn = np.asarray(nn, np.int64)
+    base_of = np.repeat(offs, nn)  # per record of the *used* ranges
+    starts = np.concatenate([[0], np.cumsum(nn)[:-1]])
+    used = base_of + (np.arange(int(nn.sum())) - np.repeat(starts, nn))
+    sub_left_abs = np.full(total_sub, -1, np.int64)
+    rel_left = sub["left"][used].astype(np.int64)
+    sub_left_abs[used] = np.where(rel_left >= 0, Nt + base_of + rel_left, -1)
+    left = np.concatenate([trunk.left.astype(np.int64), sub_left_abs])
+    right = np.where(left >= 0, left + 1, -1)
+    right[:Nt] = trunk.right
+    # the trunk leaf that was handed off takes over its subtree root's record
+    r_abs = Nt + offs
+    feature[roots] = feature[r_abs]
+    bin_[roots] = bin_[r_abs]
+    gain[roots] = gain[r_abs]
+    left[roots] = left[r_abs]
+    right[roots] = right[r_abs]
+
+    # breadth-first renumbering, one vectorised step per level
+    order = [np.zeros(1, np.int64)]
+    parents = [np.full(1, -1, np.int64)]
+    frontier = order[0]
+    count = 1
+    while True:
+        inner = frontier[feature[frontier] >= 0]
+        if inner.size == 0:
+            break
+        pos = np.flatnonzero(feature[frontier] >= 0) + (count - frontier.size)  # new ids of the parents
+        kids = np.empty(inner.size * 2, np.int64)
+        kids[0::2], kids[1::2] = left[inner], right[inner]
+        order.append(kids)
+        parents.append(np.repeat(pos, 2))
+        count += kids.size
+        frontier = kids
+    order_a = np.concatenate(order)
+    parent_new = np.concatenate(parents)
+    m = order_a.size
+    new_id = np.full(left.size, -1, np.int64)
+    new_id[order_a] = np.arange(m)
+    f_new = feature[order_a]
+    l_new = np.where(f_new >= 0, new_id[np.maximum(left[order_a], 0)], -1)
+    depth = np.zeros(m, np.int64)
+    start = 0
+    for lvl, ids in enumerate(order):
+        depth[start : start + ids.size] = lvl
+        start += ids.size
+    return FlatTree(
+        feature=f_new.astype(np.int32),
+        bin=bin_[order_a].astype(np.int32),
+        left=l_new.astype(np.int32),
+        right=np.where(l_new >= 0, l_new + 1, -1).astype(np.int32),
+        parent=parent_new.astype(np.int32),
+        depth=depth.astype(np.int32),
+        counts=counts[order_a],
+        gain=gain[order_a],
+        thresholds=[None] * m,
+        class_labels=trunk.class_labels,
+    )
+
+
+def finish_subtrees(builder, trunk: FlatTree) -> FlatTree:
+    """Run phase 2 for ``builder`` (a :class:`TreeBuilder` whose level loop has ended)."""
+    import torch
+
+    from . import _lib as L
+    from .cuda_engine import KERNEL_LAUNCHES, _stream_ptr
+
+    lib = L.load()
+    n_ho = int(builder._host_scal[5])
+    if n_ho == 0:
+        return trunk
+    builder.stats.handed_off = n_ho
+    if n_ho > builder.ho_cap:
+        raise RuntimeError(f"{n_ho} handed-off nodes exceed the list capacity {builder.ho_cap}")
+    dev = builder.data.device
+    comm = builder.comm
+    P = 1 if comm is None else comm.size
+    rank = 0 if comm is None else comm.rank
+    node = builder.ho["node"][:n_ho].cpu().numpy()
+    order = np.argsort(node, kind="stable")
+    node = node[order]
+    begin = builder.ho["begin"][:n_ho].cpu().numpy()[order]
+    end = builder.ho["end"][:n_ho].cpu().numpy()[order]
+    side = builder.ho["side"][:n_ho].cpu().numpy()[order]
+    depth = trunk.depth[node].astype(np.int32)
+    root_counts = trunk.counts[node].astype(np.uint32)
+    rows_global = trunk.counts[node].sum(axis=1).astype(np.int64)
+    d = builder.data
+    G, C = d.G, builder.C
+
+    if P > 1:
+        from ..parallel.handoff import assign_owners
+        from ..parallel.symm import IpcRegion
+
+        local_n = (end - begin).astype(np.int64)
+        all_n = np.stack(comm.allgather_object(local_n))  # [P][n_ho]
+        owners = np.asarray(assign_owners(rows_global.tolist(), P), dtype=np.int64)
+        # receive planes: capacity = the largest per-owner row total, identical on all ranks
+        owner_rows = np.bincount(owners, weights=rows_global, minlength=P).astype(np.int64)
+        cap = int(((owner_rows.max() + 1023) // 1024) * 1024) + 1024
+        recv = IpcRegion(G * cap * 16 + cap + 512, comm)
+        # destination offset of item i on its owner, and of this rank's part inside it
+        item_base = np.zeros(n_ho, np.int64)
+        for o in range(P):
+            mine_o = np.flatnonzero(owners == o)
+            item_base[mine_o] = np.concatenate([[0], np.cumsum(rows_global[mine_o])[:-1]]) if mine_o.size else 0
+        before = all_n[:rank].sum(axis=0) if rank else np.zeros(n_ho, np.int64)
+        dst_begin = (item_base + before).astype(np.int32)
+        dst_codes = np.asarray([recv.ptrs[o] for o in owners], dtype=np.int64)
+        dst_labels = dst_codes + G * cap * 16
+        t = lambda a, dt: torch.from_numpy(np.ascontiguousarray(a.astype(dt))).to(dev)  # noqa: E731
+        args = [t(side, np.int32), t(begin, np.int32), t(end, np.int32), t(dst_codes, np.int64), t(dst_labels, np.int64),
+                t(np.full(n_ho, cap, np.int64), np.int64), t(dst_begin, np.int32)]
+        rc = lib.mtb_gather_rows(
+            ctypes.c_void_p(_p(d.codes[0])), ctypes.c_void_p(_p(d.codes[1])), ctypes.c_void_p(_p(d.labels[0])),
+            ctypes.c_void_p(_p(d.labels[1])), ctypes.c_int64(d.n_cap), ctypes.c_int64(G),
+            *[ctypes.c_void_p(_p(a)) for a in args], ctypes.c_int64(n_ho), _stream_ptr(),
+        )
+        KERNEL_LAUNCHES["count"] += 1
+        L.check(rc, "mtb_gather_rows")
+        torch.cuda.synchronize()
+        comm.barrier()  # every rank's rows have landed at their owners
+        mine = np.flatnonzero(owners == rank)
+        it_side = np.zeros(mine.size, np.int32)
+        it_begin = item_base[mine].astype(np.int32)
+        it_end = (item_base[mine] + rows_global[mine]).astype(np.int32)
+        codes_ptrs = (recv.ptrs[rank], recv.ptrs[rank])
+        labels_ptrs = (recv.ptrs[rank] + G * cap * 16,) * 2
+        n_cap = cap
+    else:
+        recv = None
+        mine = np.arange(n_ho)
+        it_side, it_begin, it_end = side.astype(np.int32), begin.astype(np.int32), end.astype(np.int32)
+        codes_ptrs = (_p(d.codes[0]), _p(d.codes[1]))
+        labels_ptrs = (_p(d.labels[0]), _p(d.labels[1]))
+        n_cap = d.n_cap
+
+    out = _run_subtrees(builder, lib, L, dev, mine, it_side, it_begin, it_end, depth[mine], root_counts[mine],
+                        codes_ptrs, labels_ptrs, n_cap)
+    if P > 1:
+        everyone = comm.allgather_object((node[mine], out))
+        comm.barrier()
+        recv.close()
+        roots = np.concatenate([e[0] for e in everyone])
+        shift, parts = 0, {k: [] for k in ("feature", "bin", "left", "gain", "counts")}
+        offs, nns = [], []
+        for _nodes, o in everyone:
+            offs.append(o["offs"] + shift)
+            nns.append(o["nn"])
+            for k in parts:
+                parts[k].append(o[k])
+            shift += o["feature"].shape[0]
+        sub = {k: np.concatenate(v) for k, v in parts.items()}
+        offs, nns = np.concatenate(offs), np.concatenate(nns)
+        srt = np.argsort(roots, kind="stable")
+        return stitch_arrays(trunk, roots[srt], offs[srt], nns[srt], sub)
+    return stitch_arrays(trunk, node[mine], out["offs"], out["nn"], out)
+
+
+def _run_subtrees(builder, lib, L, dev, mine, it_side, it_begin, it_end, depth, root_counts, codes_ptrs, labels_ptrs,
+                  n_cap) -> dict:
+    import torch
+
+    from .cuda_engine import KERNEL_LAUNCHES, _stream_ptr
+
+    C = builder.C
+    n_items = int(mine.size)
+    rows = (it_end - it_begin).astype(np.int64)
+    offs = np.concatenate([[0], np.cumsum(2 * rows - 1)[:-1]]).astype(np.int64) if n_items else np.zeros(0, np.int64)
+    total = int((2 * rows - 1).sum()) if n_items else 0
+    empty = {"offs": offs, "nn": np.zeros(n_items, np.int64), "feature": np.zeros(0, np.int32), "bin": np.zeros(0, np.int32),
+             "left": np.zeros(0, np.int32), "gain": np.zeros(0), "counts": np.zeros((0, C), np.uint32)}
+    if n_items == 0:
+        return empty
+    if total >= 2**31:
+        raise RuntimeError("too many subtree nodes for 32-bit offsets")
+    t = lambda a, dt: torch.from_numpy(np.ascontiguousarray(np.asarray(a).astype(dt))).to(dev)  # noqa: E731
+    a = L.MtbSubtreeArgs()
+    ctx = builder.ctx
+    a.codes0, a.codes1, a.labels0, a.labels1 = codes_ptrs[0], codes_ptrs[1], labels_ptrs[0], labels_ptrs[1]
+    a.n_cap, a.F, a.G, a.B, a.C = n_cap, builder.F, builder.G, builder.B, C
+    a.FT = lib.mtb_subtree_config(ctypes.c_int64(builder.B), ctypes.c_int64(C))
+    a.T = int(builder.small_rows)
+    a.max_depth, a.min_samples_split, a.criterion, a.dot_mode = ctx.max_depth, ctx.min_samples_split, ctx.criterion, ctx.dot_mode
+    a.plogp, a.plogp_n, a.klogk, a.klogk_n = ctx.plogp, ctx.plogp_n, ctx.klogk, ctx.klogk_n
+    a.n_items = n_items
+    keep = [t(it_side, np.int32), t(it_begin, np.int32), t(it_end, np.int32), t(depth, np.int32), t(offs, np.int32),
+            t(root_counts, np.uint32)]
+    a.it_side, a.it_begin, a.it_end, a.it_depth, a.it_off, a.it_counts = (_p(x) for x in keep)
+    o_feature = torch.full((total,), -1, dtype=torch.int32, device=dev)
+    o_bin = torch.full((total,), -1, dtype=torch.int32, device=dev)
+    o_left = torch.full((total,), -1, dtype=torch.int32, device=dev)
+    o_depth = torch.zeros(total, dtype=torch.int32, device=dev)
+    o_gain = torch.full((total,), float("nan"), dtype=torch.float64, device=dev)
+    o_counts = torch.zeros(total * C, dtype=torch.int32, device=dev)
+    o_nn = torch.zeros(n_items, dtype=torch.int32, device=dev)
+    grid = min(lib.mtb_sm_count(torch.cuda.current_device()), n_items)
+    stack = torch.zeros(grid * int(a.T) * 3, dtype=torch.int32, device=dev)
+    counter = torch.zeros(1, dtype=torch.int32, device=dev)
+    a.o_feature, a.o_bin, a.o_left, a.o_depth = _p(o_feature), _p(o_bin), _p(o_left), _p(o_depth)
+    a.o_gain, a.o_counts, a.o_nn, a.stack, a.counter = _p(o_gain), _p(o_counts), _p(o_nn), _p(stack), _p(counter)
+    rc = lib.mtb_subtree_build(ctypes.byref(a), ctypes.c_int(grid), _stream_ptr())
+    KERNEL_LAUNCHES["count"] += 1
+    L.check(rc, "mtb_subtree_build")
+    torch.cuda.synchronize()
+    return {
+        "offs": offs,
+        "nn": o_nn.cpu().numpy().astype(np.int64),
+        "feature": o_feature.cpu().numpy(),
+        "bin": o_bin.cpu().numpy(),
+        "left": o_left.cpu().numpy(),
+        "gain": o_gain.cpu().numpy(),
+        "counts": o_counts.cpu().numpy().view(np.uint32).reshape(total, C),
+    }

@@ -151,6 +151,14 @@ class DecisionTreeClassifier(ClassifierMixin, BaseEstimator):
     def _shard(self, X, y, comm):
         return X, y
 
+    def _builder_kwargs(self):
+        """Extra arguments for the CUDA ``TreeBuilder`` (``builder_kwargs`` attribute, hand-off size)."""
+        kw = dict(getattr(self, "builder_kwargs", None) or {})
+        handoff = getattr(self, "handoff_rows", None)
+        if handoff is not None:
+            kw.setdefault("small_rows", int(handoff))
+        return kw
+
     # --------------------------------------------------- reference internals
     def _compute_entropy(self, x):
         """Shannon entropy (base 2) of a label array (reference ``:37-51``)."""
@@ -205,7 +213,7 @@ class DecisionTreeClassifier(ClassifierMixin, BaseEstimator):
 
             flat, mapper = cuda_engine.fit_from_host(
                 X, y_codes, len(classes), params, max_bins=self.max_bins, comm=comm,
-                builder_kwargs=getattr(self, "builder_kwargs", None),
+                builder_kwargs=self._builder_kwargs(),
             )
         else:
             summaries = None
@@ -263,7 +271,7 @@ class DecisionTreeClassifier(ClassifierMixin, BaseEstimator):
         flat, mapper, classes = cuda_engine.fit_from_torch(
             X, y, self._params(), max_bins=self.max_bins, comm=comm,
             replicated=getattr(self, "data_layout", "sharded") == "replicated",
-            builder_kwargs=getattr(self, "builder_kwargs", None),
+            builder_kwargs=self._builder_kwargs(),
         )
         self.n_features_ = int(X.shape[1])
         self.n_features_in_ = int(X.shape[1])

@@ -191,3 +191,42 @@ def test_large_single_node_counts():
         if flat.feature[node] >= 0:
             l, r = flat.left[node], flat.right[node]
             assert np.array_equal(flat.counts[l] + flat.counts[r], flat.counts[node])
+
+
+@pytest.mark.parametrize("small_rows", [16, 300, 4096])
+@pytest.mark.parametrize("shape", [(5000, 7, 3, 5, None, 2), (20000, 40, 64, 10, 9, 2), (3000, 130, 256, 4, None, 20)])
+def test_subtree_phase_equals_level_wise(shape, small_rows):
+    """Phase 2: nodes handed to the one-CTA-per-subtree kernel give the same tree as the level-wise build."""
+    from mpitree_b200.ops import cuda_engine
+    from mpitree_b200.parallel.scheduler import fit_flat_tree_host
+
+    n, F, vals, k, depth, mss = shape
+    rng = np.random.default_rng(F * 7 + small_rows)
+    X = rng.integers(0, vals, size=(n, F)).astype(np.float32)
+    w = rng.normal(size=F)
+    s = X @ w + rng.normal(scale=vals, size=n)
+    y = np.digitize(s, np.quantile(s, np.linspace(0, 1, k + 1)[1:-1]))
+    y[:k] = np.arange(k)
+    params = SplitParams(max_depth=depth, min_samples_split=mss)
+    got, mapper = cuda_engine.fit_from_host(X, y, k, params, builder_kwargs=dict(small_rows=small_rows))
+    if small_rows >= mss:  # smaller nodes are leaves by min_samples_split and are never handed off
+        assert cuda_engine.fit_from_host.last_stats.handed_off > 0
+    want = fit_flat_tree_host(mapper.transform(X), y, mapper.n_bins, k, params)
+    assert got.n_nodes == want.n_nodes
+    assert np.array_equal(got.feature, want.feature) and np.array_equal(got.bin, want.bin)
+    assert np.array_equal(got.counts, want.counts) and np.array_equal(got.left, want.left)
+    assert np.array_equal(got.depth, want.depth) and np.array_equal(got.parent, want.parent)
+
+
+def test_unbounded_depth_many_small_nodes():
+    """Fully grown tree on noisy data: tens of thousands of nodes, far beyond the slab capacity."""
+    rng = np.random.default_rng(9)
+    n = 60000
+    X = rng.integers(0, 256, size=(n, 24), dtype=np.uint8)
+    y = rng.integers(0, 3, size=n)
+    clf = DecisionTreeClassifier(device="cuda").fit(X, y)
+    flat = clf.flat_tree_
+    assert flat.n_nodes > 20000
+    assert clf.score(X, y) == 1.0  # distinct rows: a fully grown tree memorises the data
+    leaves = flat.feature < 0
+    assert int(flat.counts[leaves].sum()) == n

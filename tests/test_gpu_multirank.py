@@ -65,6 +65,12 @@ for reduce in ("p2p", "nccl"):
             clf.fit(Xs, ys)
             assert clf.export_text() == want.export_text(), (reduce, layout, rank)
             assert np.array_equal(clf.flat_tree_.counts, want.flat_tree_.counts)
+# phase 2: hand-off of small subtrees to owner ranks (row gather over NVLink + subtree kernel)
+deep = DecisionTreeClassifier(max_depth=14, device="cuda").fit(X[:30000], y[:30000])
+lo2, hi2 = 30000 * rank // world, 30000 * (rank + 1) // world
+clf = ParallelDecisionTreeClassifier(max_depth=14, device="cuda", data_layout="sharded", handoff_rows=700)
+clf.fit(X[lo2:hi2], y[lo2:hi2])
+assert clf.flat_tree_.structurally_equal(deep.flat_tree_), ("handoff", rank)
 # torch tensor API, sharded
 Xt, yt = torch.from_numpy(X[lo:hi]).cuda(), torch.from_numpy(y[lo:hi]).cuda()
 clf = ParallelDecisionTreeClassifier(max_depth=7, data_layout="sharded").fit(Xt, yt)
