@@ -55,16 +55,103 @@ __global__ void __launch_bounds__(kThreads) k_predict(const T* __restrict__ X, i
   }
 }
 
+// Staged variant: each warp copies 32 whole rows into shared memory with coalesced 128-bit
+// loads (every input byte is read exactly once at full-line efficiency), then each lane walks
+// the tree on its own row.  Rows are padded to an odd number of words so that lanes reading the
+// same feature hit different banks.  Needs contiguous rows whose size is a multiple of 16 bytes.
+template <typename T>
+__device__ __forceinline__ T staged_elem(const uint32_t* row, int f);
+template <>
+__device__ __forceinline__ float staged_elem<float>(const uint32_t* row, int f) { return __uint_as_float(row[f]); }
+template <>
+__device__ __forceinline__ uint8_t staged_elem<uint8_t>(const uint32_t* row, int f) {
+  return (uint8_t)((row[f >> 2] >> ((f & 3) * 8)) & 0xffu);
+}
+template <>
+__device__ __forceinline__ double staged_elem<double>(const uint32_t* row, int f) {
+  return __hiloint2double((int)row[2 * f + 1], (int)row[2 * f]);
+}
+
+template <typename T, typename TH>
+__global__ void __launch_bounds__(kThreads) k_predict_staged(const T* __restrict__ X, int64_t n, int F,
+                                                             const int4* __restrict__ nodes,
+                                                             const TH* __restrict__ thr, int n_nodes, int stage_nodes,
+                                                             int* __restrict__ out_leaf, int* __restrict__ out_label) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  const int rowbytes = F * (int)sizeof(T);
+  const int cpr = rowbytes / 16;             // 16-byte chunks per row
+  const int stride = (rowbytes / 4) | 1;     // words per staged row (odd)
+  int4* s_nodes = reinterpret_cast<int4*>(smem);
+  TH* s_thr = reinterpret_cast<TH*>(smem + (size_t)(stage_nodes ? n_nodes : 0) * sizeof(int4));
+  uint32_t* s_rows = reinterpret_cast<uint32_t*>(
+      smem + (((size_t)(stage_nodes ? n_nodes : 0) * (sizeof(int4) + sizeof(TH)) + 15) & ~(size_t)15));
+  if (stage_nodes) {
+    for (int i = threadIdx.x; i < n_nodes; i += kThreads) {
+      s_nodes[i] = nodes[i];
+      s_thr[i] = thr[i];
+    }
+    __syncthreads();
+  }
+  const int4* N = stage_nodes ? s_nodes : nodes;
+  const TH* TT = stage_nodes ? s_thr : thr;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  uint32_t* mine = s_rows + (size_t)w * 32 * stride;
+  const int64_t tiles = (n + 31) / 32;
+  const int64_t wstride = (int64_t)gridDim.x * (kThreads / 32);
+  for (int64_t tile = (int64_t)blockIdx.x * (kThreads / 32) + w; tile < tiles; tile += wstride) {
+    const int64_t row0 = tile * 32;
+    const int rows = (int)min((int64_t)32, n - row0);
+    const uint4* src = reinterpret_cast<const uint4*>(reinterpret_cast<const uint8_t*>(X) + row0 * rowbytes);
+    const int chunks = rows * cpr;
+    for (int q = lane; q < chunks; q += 32) {
+      const uint4 v = mtb::ld_nc_u4(src + q);
+      const int r = q / cpr, c = q - r * cpr;
+      uint32_t* d = mine + r * stride + c * 4;
+      d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
+    }
+    __syncwarp();
+    if (lane < rows) {
+      const uint32_t* x = mine + lane * stride;
+      int node = 0;
+      int4 r = N[0];
+      while (r.x >= 0) {
+        const TH v = (TH)staged_elem<T>(x, r.x);
+        node = r.y + (v <= TT[node] ? 0 : 1);
+        r = N[node];
+      }
+      if (out_leaf) out_leaf[row0 + lane] = node;
+      if (out_label) out_label[row0 + lane] = r.z;
+    }
+    __syncwarp();
+  }
+}
+
 __global__ void k_pack_nodes(const int* feature, const int* left, const int* label, int n, int4* out) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) out[i] = make_int4(feature[i], left[i], label ? label[i] : 0, 0);
 }
 
 template <typename T, typename TH>
-int launch(const void* X, int64_t n, int64_t ldx, const int4* nodes, const void* thr, int n_nodes, int* out_leaf,
-           int* out_label, cudaStream_t stream) {
+int launch(const void* X, int64_t n, int64_t F, int64_t ldx, const int4* nodes, const void* thr, int n_nodes,
+           int* out_leaf, int* out_label, cudaStream_t stream) {
   int64_t blocks = (n + kThreads - 1) / kThreads;
   if (blocks > 148 * 8) blocks = 148 * 8;
+  const int64_t rowbytes = F * (int64_t)sizeof(T);
+  if (ldx == F && rowbytes % 16 == 0 && rowbytes <= 1024 && ((uintptr_t)X % 16) == 0) {
+    const int stride = (int)(rowbytes / 4) | 1;
+    const int rows_smem = (kThreads / 32) * 32 * stride * 4;
+    const int node_smem = (n_nodes * (int)(sizeof(int4) + sizeof(TH)) + 15) & ~15;
+    const int stage_nodes = (n_nodes <= kSmemNodes && node_smem + rows_smem <= 200 * 1024) ? 1 : 0;
+    const int smem = (stage_nodes ? node_smem : 0) + rows_smem + 16;
+    auto kern = k_predict_staged<T, TH>;
+    MTB_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem > 48 * 1024 ? smem : 48 * 1024));
+    int64_t sblocks = ((n + 31) / 32 + (kThreads / 32) - 1) / (kThreads / 32);
+    if (sblocks > 148 * 4) sblocks = 148 * 4;
+    kern<<<(unsigned)sblocks, kThreads, smem, stream>>>((const T*)X, n, (int)F, nodes, (const TH*)thr, n_nodes,
+                                                        stage_nodes, out_leaf, out_label);
+    MTB_CHECK(cudaGetLastError());
+    return 0;
+  }
   if (n_nodes <= kSmemNodes) {
     const int smem = n_nodes * (int)(sizeof(int4) + sizeof(TH));
     auto kern = k_predict<T, TH, true>;
@@ -93,14 +180,13 @@ extern "C" int mtb_pack_nodes(const int32_t* feature, const int32_t* left, const
 extern "C" int mtb_predict(const void* X, int dtype, int64_t n, int64_t F, int64_t ldx, const void* packed_nodes,
                            const void* threshold, int64_t n_nodes, int32_t* out_leaf, int32_t* out_label,
                            void* stream) {
-  (void)F;
   if (n <= 0) return 0;
   const int4* nodes = (const int4*)packed_nodes;
   cudaStream_t s = (cudaStream_t)stream;
   switch (dtype) {
-    case 0: return launch<float, float>(X, n, ldx, nodes, threshold, (int)n_nodes, out_leaf, out_label, s);
-    case 1: return launch<uint8_t, int>(X, n, ldx, nodes, threshold, (int)n_nodes, out_leaf, out_label, s);
-    case 2: return launch<double, double>(X, n, ldx, nodes, threshold, (int)n_nodes, out_leaf, out_label, s);
+    case 0: return launch<float, float>(X, n, F, ldx, nodes, threshold, (int)n_nodes, out_leaf, out_label, s);
+    case 1: return launch<uint8_t, int>(X, n, F, ldx, nodes, threshold, (int)n_nodes, out_leaf, out_label, s);
+    case 2: return launch<double, double>(X, n, F, ldx, nodes, threshold, (int)n_nodes, out_leaf, out_label, s);
     default:
       mtb_set_error("predict", "dtype must be 0 (f32), 1 (u8) or 2 (f64)", __FILE__, __LINE__);
       return -2;

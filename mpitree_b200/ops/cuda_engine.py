@@ -777,6 +777,69 @@ def _fit_mapper_numpy(X: np.ndarray, max_bins: int, comm=None) -> BinMapper:
     return mapper
 
 
+def _fit_mapper_device(sample, max_bins: int, comm=None, col_max=None) -> BinMapper:
+    """Bin edges from a device-resident sample: one sort, then order statistics (K1, edge discovery).
+
+    Per feature: all distinct values when there are at most ``max_bins`` (lossless), otherwise
+    ``max_bins`` order statistics ("higher" quantiles, so every edge is a data value).  With
+    several ranks each contributes its candidates and the merged set is reduced the same way on
+    every rank (the cross-rank edge agreement of K1).  ``col_max`` (full-data maxima) extends the
+    last edge when the sample missed the maximum.
+    """
+    import torch
+
+    K, F = int(sample.shape[0]), int(sample.shape[1])
+    if not bool(torch.isfinite(sample).all()):
+        raise ValueError("Input X contains NaN or infinity.")
+    srt = sample.sort(dim=0).values
+    new = torch.ones((K, F), dtype=torch.bool, device=sample.device)
+    if K > 1:
+        new[1:] = srt[1:] != srt[:-1]
+    distinct = new.sum(dim=0)
+    # distinct values (first 256 of them) per feature, scattered into a dense [F, 256] table
+    rank = torch.cumsum(new, dim=0) - 1
+    keep = new & (rank < 256)
+    uniq = torch.full((F, 256), float("inf"), dtype=srt.dtype, device=sample.device)
+    cols = torch.arange(F, device=sample.device).expand(K, F)
+    uniq[cols[keep], rank[keep]] = srt[keep]
+    # order statistics for the quantile-binned features
+    q = torch.linspace(0.0, 1.0, max_bins + 1, device=sample.device, dtype=torch.float64)[1:]
+    qidx = torch.ceil(q * (K - 1)).to(torch.int64).clamp_(0, K - 1)
+    cand = srt[qidx]  # [max_bins, F]
+    distinct_h = distinct.cpu().numpy()
+    uniq_h = uniq.cpu().numpy()
+    cand_h = cand.cpu().numpy()
+    np_dtype = uniq_h.dtype
+
+    if comm is not None and comm.size > 1:
+        parts = comm.allgather_object((distinct_h, uniq_h, cand_h))
+    else:
+        parts = [(distinct_h, uniq_h, cand_h)]
+    edges, lossless = [], np.zeros(F, dtype=bool)
+    for f in range(F):
+        all_small = all(int(p[0][f]) <= 256 for p in parts)
+        if all_small:
+            vals = np.unique(np.concatenate([p[1][f][: int(p[0][f])] for p in parts]))
+            if len(vals) <= max_bins:
+                edges.append(vals.astype(np_dtype))
+                lossless[f] = len(parts) == 1 and col_max is None
+                continue
+        merged = np.sort(np.concatenate([p[2][:, f] for p in parts]))
+        if len(parts) > 1 or len(merged) > max_bins:
+            pick = np.ceil(np.linspace(0.0, 1.0, max_bins + 1)[1:] * (len(merged) - 1)).astype(np.int64)
+            merged = merged[pick]
+        edges.append(np.unique(merged).astype(np_dtype))
+    mapper = BinMapper(edges=edges, lossless=lossless, max_bins=max_bins)
+    if col_max is not None:
+        for f, e in enumerate(mapper.edges):
+            if len(e) and col_max[f] > e[-1]:
+                if len(e) < max_bins:
+                    mapper.edges[f] = np.append(e, col_max[f]).astype(e.dtype)
+                else:
+                    e[-1] = col_max[f]
+    return mapper
+
+
 def _device():
     import torch
 
@@ -896,21 +959,12 @@ def fit_from_torch(X, y, params: SplitParams, *, max_bins: int = 256, comm=None,
     else:
         idx = _sample_rows(n)
         sample = X if idx is None else X[torch.from_numpy(idx).to(X.device)]
-        sample_np = sample.cpu().numpy()
-        if not np.isfinite(sample_np).all():
-            raise ValueError("Input X contains NaN or infinity.")
-        mapper = _fit_mapper_numpy(sample_np, max_bins, comm)
+        col_max = None
         if idx is not None:
-            col_max = (X.max(dim=0).values if X.is_cuda else X.max(dim=0).values).cpu().numpy()
+            col_max = X.max(dim=0).values.cpu().numpy()
             if comm is not None and comm.size > 1:
                 col_max = np.max(np.stack(comm.allgather_object(col_max)), axis=0)
-            for f, e in enumerate(mapper.edges):
-                if len(e) and col_max[f] > e[-1]:
-                    if len(e) < max_bins:
-                        mapper.edges[f] = np.append(e, col_max[f]).astype(e.dtype)
-                    else:
-                        e[-1] = col_max[f]
-                    mapper.lossless[f] = False
+        mapper = _fit_mapper_device(sample.to(dev, non_blocking=True), max_bins, comm, col_max)
 
     st.mark("meta+mapper")
     data = DeviceDataset.allocate(n, F, len(classes), dev)

@@ -330,12 +330,12 @@ class DecisionTreeClassifier(ClassifierMixin, BaseEstimator):
 
     def predict(self, X):
         """Predicted class label per row (arg-max of the leaf counts, ties -> lowest label)."""
+        if _is_torch_tensor(X):
+            from ..ops import cuda_engine
+
+            return cuda_engine.predict_leaf_ids(self._flat(), X, want="label")  # label looked up in-kernel
         ids = self._leaf_ids(X)
         labels = self._flat().expanded_counts().argmax(axis=1)
-        if _is_torch_tensor(ids):
-            import torch
-
-            return torch.as_tensor(labels, device=ids.device)[ids]
         return labels[ids]
 
     # ---------------------------------------------------------------- export
