@@ -72,8 +72,10 @@ __device__ __forceinline__ double staged_elem<double>(const uint32_t* row, int f
   return __hiloint2double((int)row[2 * f + 1], (int)row[2 * f]);
 }
 
+constexpr int kStagedThreads = 1024;  // the walk is latency bound: many warps per SM
+
 template <typename T, typename TH>
-__global__ void __launch_bounds__(kThreads) k_predict_staged(const T* __restrict__ X, int64_t n, int F,
+__global__ void __launch_bounds__(kStagedThreads) k_predict_staged(const T* __restrict__ X, int64_t n, int F,
                                                              const int4* __restrict__ nodes,
                                                              const TH* __restrict__ thr, int n_nodes, int stage_nodes,
                                                              int* __restrict__ out_leaf, int* __restrict__ out_label) {
@@ -81,24 +83,33 @@ __global__ void __launch_bounds__(kThreads) k_predict_staged(const T* __restrict
   const int rowbytes = F * (int)sizeof(T);
   const int cpr = rowbytes / 16;             // 16-byte chunks per row
   const int stride = (rowbytes / 4) | 1;     // words per staged row (odd)
+  // node records staged in shared memory carry the threshold in .w when it is a 4-byte type
+  constexpr bool kPacked = sizeof(TH) == 4;
   int4* s_nodes = reinterpret_cast<int4*>(smem);
+  const size_t node_bytes = stage_nodes ? (size_t)n_nodes * (sizeof(int4) + (kPacked ? 0 : sizeof(TH))) : 0;
   TH* s_thr = reinterpret_cast<TH*>(smem + (size_t)(stage_nodes ? n_nodes : 0) * sizeof(int4));
-  uint32_t* s_rows = reinterpret_cast<uint32_t*>(
-      smem + (((size_t)(stage_nodes ? n_nodes : 0) * (sizeof(int4) + sizeof(TH)) + 15) & ~(size_t)15));
+  uint32_t* s_rows = reinterpret_cast<uint32_t*>(smem + ((node_bytes + 15) & ~(size_t)15));
   if (stage_nodes) {
-    for (int i = threadIdx.x; i < n_nodes; i += kThreads) {
-      s_nodes[i] = nodes[i];
-      s_thr[i] = thr[i];
+    for (int i = threadIdx.x; i < n_nodes; i += kStagedThreads) {
+      int4 r = nodes[i];
+      if (kPacked) {
+        const TH t = thr[i];
+        r.w = *reinterpret_cast<const int*>(&t);
+      } else {
+        s_thr[i] = thr[i];
+      }
+      s_nodes[i] = r;
     }
     __syncthreads();
   }
   const int4* N = stage_nodes ? s_nodes : nodes;
   const TH* TT = stage_nodes ? s_thr : thr;
+  const bool packed = kPacked && stage_nodes;
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   uint32_t* mine = s_rows + (size_t)w * 32 * stride;
   const int64_t tiles = (n + 31) / 32;
-  const int64_t wstride = (int64_t)gridDim.x * (kThreads / 32);
-  for (int64_t tile = (int64_t)blockIdx.x * (kThreads / 32) + w; tile < tiles; tile += wstride) {
+  const int64_t wstride = (int64_t)gridDim.x * (kStagedThreads / 32);
+  for (int64_t tile = (int64_t)blockIdx.x * (kStagedThreads / 32) + w; tile < tiles; tile += wstride) {
     const int64_t row0 = tile * 32;
     const int rows = (int)min((int64_t)32, n - row0);
     const uint4* src = reinterpret_cast<const uint4*>(reinterpret_cast<const uint8_t*>(X) + row0 * rowbytes);
@@ -116,7 +127,9 @@ __global__ void __launch_bounds__(kThreads) k_predict_staged(const T* __restrict
       int4 r = N[0];
       while (r.x >= 0) {
         const TH v = (TH)staged_elem<T>(x, r.x);
-        node = r.y + (v <= TT[node] ? 0 : 1);
+        TH t;
+        if (packed) t = *reinterpret_cast<const TH*>(&r.w); else t = TT[node];
+        node = r.y + (v <= t ? 0 : 1);
         r = N[node];
       }
       if (out_leaf) out_leaf[row0 + lane] = node;
@@ -139,18 +152,21 @@ int launch(const void* X, int64_t n, int64_t F, int64_t ldx, const int4* nodes, 
   const int64_t rowbytes = F * (int64_t)sizeof(T);
   if (ldx == F && rowbytes % 16 == 0 && rowbytes <= 1024 && ((uintptr_t)X % 16) == 0) {
     const int stride = (int)(rowbytes / 4) | 1;
-    const int rows_smem = (kThreads / 32) * 32 * stride * 4;
-    const int node_smem = (n_nodes * (int)(sizeof(int4) + sizeof(TH)) + 15) & ~15;
-    const int stage_nodes = (n_nodes <= kSmemNodes && node_smem + rows_smem <= 200 * 1024) ? 1 : 0;
+    const int rows_smem = (kStagedThreads / 32) * 32 * stride * 4;
+    const int per_node = (int)sizeof(int4) + (sizeof(TH) == 4 ? 0 : (int)sizeof(TH));
+    const int node_smem = (n_nodes * per_node + 15) & ~15;
+    const int stage_nodes = (node_smem + rows_smem <= 220 * 1024) ? 1 : 0;
     const int smem = (stage_nodes ? node_smem : 0) + rows_smem + 16;
-    auto kern = k_predict_staged<T, TH>;
-    MTB_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem > 48 * 1024 ? smem : 48 * 1024));
-    int64_t sblocks = ((n + 31) / 32 + (kThreads / 32) - 1) / (kThreads / 32);
-    if (sblocks > 148 * 4) sblocks = 148 * 4;
-    kern<<<(unsigned)sblocks, kThreads, smem, stream>>>((const T*)X, n, (int)F, nodes, (const TH*)thr, n_nodes,
-                                                        stage_nodes, out_leaf, out_label);
-    MTB_CHECK(cudaGetLastError());
-    return 0;
+    if (smem <= 220 * 1024) {
+      auto kern = k_predict_staged<T, TH>;
+      MTB_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem > 48 * 1024 ? smem : 48 * 1024));
+      int64_t sblocks = ((n + 31) / 32 + (kStagedThreads / 32) - 1) / (kStagedThreads / 32);
+      if (sblocks > 148 * 2) sblocks = 148 * 2;
+      kern<<<(unsigned)sblocks, kStagedThreads, smem, stream>>>((const T*)X, n, (int)F, nodes, (const TH*)thr, n_nodes,
+                                                                stage_nodes, out_leaf, out_label);
+      MTB_CHECK(cudaGetLastError());
+      return 0;
+    }
   }
   if (n_nodes <= kSmemNodes) {
     const int smem = n_nodes * (int)(sizeof(int4) + sizeof(TH));

@@ -789,27 +789,22 @@ def _fit_mapper_device(sample, max_bins: int, comm=None, col_max=None) -> BinMap
     import torch
 
     K, F = int(sample.shape[0]), int(sample.shape[1])
-    if not bool(torch.isfinite(sample).all()):
+    srt = sample.t().contiguous().sort(dim=1).values  # [F, K], rows sorted
+    # sorted rows end in +inf / nan when the input has them: one check on the extremes
+    if not bool(torch.isfinite(srt[:, [0, -1]]).all()):
         raise ValueError("Input X contains NaN or infinity.")
-    srt = sample.sort(dim=0).values
-    new = torch.ones((K, F), dtype=torch.bool, device=sample.device)
-    if K > 1:
-        new[1:] = srt[1:] != srt[:-1]
-    distinct = new.sum(dim=0)
-    # distinct values (first 256 of them) per feature, scattered into a dense [F, 256] table
-    rank = torch.cumsum(new, dim=0) - 1
-    keep = new & (rank < 256)
-    uniq = torch.full((F, 256), float("inf"), dtype=srt.dtype, device=sample.device)
-    cols = torch.arange(F, device=sample.device).expand(K, F)
-    uniq[cols[keep], rank[keep]] = srt[keep]
-    # order statistics for the quantile-binned features
-    q = torch.linspace(0.0, 1.0, max_bins + 1, device=sample.device, dtype=torch.float64)[1:]
-    qidx = torch.ceil(q * (K - 1)).to(torch.int64).clamp_(0, K - 1)
-    cand = srt[qidx]  # [max_bins, F]
+    distinct = (srt[:, 1:] != srt[:, :-1]).sum(dim=1) + 1 if K > 1 else torch.ones(F, dtype=torch.int64, device=sample.device)
+    # order statistics ("higher" quantiles): every edge is a data value
+    q = np.linspace(0.0, 1.0, max_bins + 1)[1:]
+    qidx = torch.from_numpy(np.ceil(q * (K - 1)).astype(np.int64).clip(0, K - 1)).to(sample.device)
+    cand_h = srt[:, qidx].t().cpu().numpy()  # [max_bins, F]
     distinct_h = distinct.cpu().numpy()
-    uniq_h = uniq.cpu().numpy()
-    cand_h = cand.cpu().numpy()
-    np_dtype = uniq_h.dtype
+    np_dtype = cand_h.dtype
+    # features with few distinct values keep all of them (lossless bins)
+    uniq_h = np.full((F, 256), np.inf, dtype=np_dtype)
+    for f in np.flatnonzero(distinct_h <= 256):
+        u = torch.unique_consecutive(srt[f]).cpu().numpy()
+        uniq_h[f, : len(u)] = u
 
     if comm is not None and comm.size > 1:
         parts = comm.allgather_object((distinct_h, uniq_h, cand_h))
