@@ -1,0 +1,79 @@
+"""Utilities: checkpoint format, synthetic data, device mapper (CPU tensors), stitch_arrays."""
+import io
+
+import numpy as np
+
+from mpitree_b200.tree import DecisionTreeClassifier
+from mpitree_b200.utils.checkpoint import load_model, save_model
+from mpitree_b200.utils.data import notebook_workload, synthetic_codes, synthetic_continuous, synthetic_mixed
+
+
+def test_checkpoint_roundtrip(iris, tmp_path):
+    clf = DecisionTreeClassifier(max_depth=4, device="cpu").fit(iris.data, iris.target)
+    p = tmp_path / "model.npz"
+    save_model(clf, str(p))
+    again = load_model(str(p))
+    assert again.export_text() == clf.export_text()
+    assert np.array_equal(again.predict(iris.data), clf.predict(iris.data))
+    assert again.get_params()["max_depth"] == 4
+    buf = io.BytesIO()
+    save_model(clf, buf)
+    buf.seek(0)
+    assert load_model(buf).score(iris.data, iris.target) == clf.score(iris.data, iris.target)
+
+
+def test_synthetic_generators_are_seeded():
+    X1, y1 = synthetic_codes(2000, 16, 4, seed=3)
+    X2, y2 = synthetic_codes(2000, 16, 4, seed=3)
+    assert X1.dtype == np.uint8 and np.array_equal(X1, X2) and np.array_equal(y1, y2)
+    assert set(np.unique(y1)) == {0, 1, 2, 3}
+    Xc, yc = synthetic_continuous(1000, 8)
+    assert Xc.dtype == np.float32 and set(np.unique(yc)) == {0, 1}
+    Xm, ym = synthetic_mixed(1000, 4, 40)
+    assert Xm.shape == (1000, 44) and ym.max() <= 4
+    clf = DecisionTreeClassifier(max_depth=6, device="cpu").fit(X1, y1)
+    assert clf.score(X1, y1) > 0.4  # structure, not noise
+    Xn, yn = notebook_workload(11)
+    assert DecisionTreeClassifier(device="cpu").fit(Xn, yn).score(Xn, yn) == 1.0
+
+
+def test_device_mapper_matches_host_mapper_on_cpu_tensors():
+    import torch
+
+    from mpitree_b200.ops.binning import BinMapper
+    from mpitree_b200.ops.cuda_engine import _fit_mapper_device
+
+    rng = np.random.default_rng(0)
+    X = rng.normal(size=(4000, 5)).astype(np.float32)
+    X[:, 1] = rng.integers(0, 9, 4000)
+    X[:, 2] = np.round(X[:, 2], 1)
+    for bins in (16, 64, 256):
+        got = _fit_mapper_device(torch.from_numpy(X), bins)
+        want = BinMapper.fit(X, bins)
+        assert all(np.array_equal(a, b) for a, b in zip(got.edges, want.edges))
+
+
+def test_stitch_arrays_equals_full_tree(iris):
+    from mpitree_b200.ops.subtree_phase import stitch_arrays
+
+    X, y = iris.data, iris.target
+    full = DecisionTreeClassifier(device="cpu").fit(X, y).flat_tree_
+    trunk = DecisionTreeClassifier(max_depth=2, device="cpu").fit(X, y).flat_tree_
+    leaf_ids = trunk.apply_raw(X)
+    roots, offs, nn, parts = [], [], [], {k: [] for k in ("feature", "bin", "left", "gain", "counts")}
+    off = 0
+    for leaf in np.unique(leaf_ids):
+        if trunk.depth[leaf] < 2 or (trunk.counts[leaf] > 0).sum() <= 1:
+            continue
+        rows = leaf_ids == leaf
+        sub_clf = DecisionTreeClassifier(device="cpu")
+        sub_clf.classes_ = np.arange(3)
+        sub = sub_clf._fit_flat(X[rows], y[rows], local=True)
+        roots.append(leaf); offs.append(off); nn.append(sub.n_nodes)
+        for k in parts:
+            parts[k].append(getattr(sub, k))
+        off += sub.n_nodes
+    merged = stitch_arrays(trunk, np.array(roots), np.array(offs), np.array(nn), {k: np.concatenate(v) for k, v in parts.items()})
+    assert merged.n_nodes == full.n_nodes
+    for k in ("feature", "counts", "left", "right", "depth", "parent"):
+        assert np.array_equal(getattr(merged, k), getattr(full, k)), k
