@@ -119,6 +119,11 @@ typedef struct MtbCtx {
   int64_t small_rows;                 /* 0 = never hand off                                   */
   int64_t ho_cap;
   int64_t ho_node, ho_begin, ho_end, ho_side; /* i32 [ho_cap]                                 */
+  /* ---- fused partition + next-level histogram (mtb_level_fused2) ----
+   * part_child: i32 [m_cap] first child slot of a split slot that keeps rows, else -1
+   * mask_words: u32 [max_units][32] "row goes left" bits of every 1024-row partition unit
+   * unit_base : u32 [max_units][2]  rows already placed left / right before the unit          */
+  int64_t part_child, mask_words, unit_base;
   int64_t reserved[1];
 } MtbCtx;
 
@@ -147,6 +152,11 @@ int mtb_level_finalize(const MtbCtx* ctx, void* stream);  /* arg-max, children, 
 int mtb_level_partition(const MtbCtx* ctx, void* stream); /* stream compaction into the other side   */
 int mtb_level_commit(const MtbCtx* ctx, void* stream);    /* next frontier's row segments            */
 int mtb_level_push(const MtbCtx* ctx, void* stream);      /* world > 1: push partial slabs to their owners */
+/* Levels >= 1 in one cooperative launch: partition the parents' rows (view P, the finished
+ * previous level) into the children's segments while building the children's histograms
+ * (view C, same buffers with the two slot sets / ping-pong sides swapped), then commit, plan,
+ * peer push + barriers, gain and finalize for the children.                                  */
+int mtb_level_fused2(const MtbCtx* parents, const MtbCtx* children, void* stream);
 /* One cooperative launch doing plan + hist + (peer push + barriers) + gain + finalize. */
 int mtb_level_fused(const MtbCtx* ctx, void* stream);
 /* Shared memory / launch geometry the hist phase will use for this ctx (for reports). */

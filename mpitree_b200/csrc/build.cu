@@ -699,10 +699,12 @@ __device__ void finalize_phase(const MtbCtx& ctx, int* smem_warp) {
       t_bin[node] = bb;
       t_gain[node] = split ? bgain : NAN;
       part_flags[s] = pair ? ((tl ? 0 : 1) | (tr ? 0 : 2)) : 0;
+      if (ctx.part_child) ptr_of<int>(ctx.part_child)[s] = -1;
     } else if (s < n) {
       rec_feature[s] = -1;
       rec_bin[s] = -1;
       part_flags[s] = 0;
+      if (ctx.part_child) ptr_of<int>(ctx.part_child)[s] = -1;
     }
     int tot_split, tot_pair, tot_units;
     const int ex_split = block_excl_scan(split, smem_warp, tot_split);
@@ -727,6 +729,7 @@ __device__ void finalize_phase(const MtbCtx& ctx, int* smem_warp) {
       t_gain[lid] = NAN; t_gain[rid] = NAN;
       if (pair) {
         const int a = 2 * (carry_pair + ex_pair), b = a + 1;
+        if (ctx.part_child) ptr_of<int>(ctx.part_child)[s] = a;
         ns_node[a] = lid; ns_node[b] = rid;
         ns_parent[a] = s; ns_parent[b] = s;
         ns_sibling[a] = b; ns_sibling[b] = a;
@@ -853,7 +856,7 @@ __global__ void __launch_bounds__(kPartThreads) k_partition(const __grid_constan
 }
 static_assert(4 * (kPartThreads / 32) == 32, "partition scan assumes 32 cells");
 
-__global__ void k_commit(const __grid_constant__ MtbCtx ctx) {
+__device__ void commit_phase(const MtbCtx& ctx) {
   View v(ctx);
   const int n_next = v.scalars()[1];
   const int* ns_src = ptr_of<const int>(ctx.nslot_src);
@@ -889,8 +892,286 @@ __global__ void k_commit(const __grid_constant__ MtbCtx ctx) {
       }
     }
   }
+}
+
+__global__ void k_commit(const __grid_constant__ MtbCtx ctx) {
+  commit_phase(ctx);
   // the next level's slot count becomes current (nothing in this kernel reads scalars[0])
-  if (blockIdx.x == 0 && threadIdx.x == 0) v.scalars()[0] = n_next;
+  if (blockIdx.x == 0 && threadIdx.x == 0) ptr_of<int>(ctx.scalars)[0] = ptr_of<int>(ctx.scalars)[1];
+}
+
+// ------------------------------------------------ partition fused with the next level's histograms
+// Levels >= 1.  P is the finished parent level, C the same buffers seen from the children's
+// level.  Three grid-wide steps replace the separate partition kernel and the histogram phase:
+//
+//   prepass  one pass over the split feature's plane only: "goes left" bits of every 1024-row
+//            unit and the unit's destination bases (atomic cursors per parent slot);
+//   move     every (parent slot, feature tile, unit): stream the plane tile with TMA, rank rows
+//            from the unit's bit words, write them to their child's segment, and - for rows of
+//            the child that is built directly - increment the child's shared-memory histogram
+//            tile.  Memory traffic and shared-memory atomics overlap instead of adding up;
+//   commit   children's row segments (+ hand-off list).
+struct PartUnit {
+  int slot, chunk, r0, r1;
+};
+
+constexpr int kMetaWords = 36;  // per partition unit: 32 "goes left" words, base_l, base_r, 2 pad (144 B)
+
+// One warp per 1024-row unit, no block-wide syncs: lane i ends up holding bit word i, the unit's
+// destination bases are reserved with one atomic pair, and the 144-byte unit record is written
+// in one go (it is later fetched by TMA next to the unit's rows).
+__device__ void prepass_phase(const MtbCtx& P) {
+  View v(P);
+  const int n_slots = v.n_slots();
+  const int total = v.scalars()[4];
+  const int* pprefix = ptr_of<const int>(P.unit_prefix) + (P.m_cap + 1);
+  const int* sb = ptr_of<const int>(P.slot_begin);
+  const int* se = ptr_of<const int>(P.slot_end);
+  const int* rec_feature = ptr_of<const int>(P.rec_feature);
+  const int* rec_bin = ptr_of<const int>(P.rec_bin);
+  uint32_t* cursors = ptr_of<uint32_t>(P.cursors);
+  uint32_t* meta = ptr_of<uint32_t>(P.mask_words);
+  const uint4* src = reinterpret_cast<const uint4*>(v.codes_cur());
+  const int64_t plane = P.n_cap;
+  const int lane = lane_id();
+  const int warps = blockDim.x >> 5;
+  for (int u = blockIdx.x * warps + warp_id(); u < total; u += gridDim.x * warps) {
+    const int slot = find_slot(pprefix, n_slots, u);
+    const int chunk = u - pprefix[slot];
+    const int e = se[slot];
+    const int r0 = sb[slot] + chunk * kPartRows;
+    const int f = rec_feature[slot], bin = rec_bin[slot];
+    const uint8_t* col = reinterpret_cast<const uint8_t*>(src + (int64_t)(f >> 4) * plane) + (f & 15);
+    uint32_t mine = 0, nl = 0, nv = 0;
+#pragma unroll 8
+    for (int i = 0; i < 32; ++i) {
+      const int row = r0 + i * 32 + lane;
+      const bool valid = row < e;
+      uint32_t code = 0;
+      if (valid) code = col[(int64_t)row * 16];
+      const uint32_t ml = __ballot_sync(0xffffffffu, valid && (int)code <= bin);
+      const uint32_t mv = __ballot_sync(0xffffffffu, valid);
+      if (lane == i) mine = ml;
+      nl += __popc(ml);
+      nv += __popc(mv);
+    }
+    uint32_t* rec = meta + (int64_t)u * kMetaWords;
+    rec[lane] = mine;
+    if (lane == 0) {
+      rec[32] = atomicAdd(&cursors[2 * slot], nl);
+      rec[33] = atomicAdd(&cursors[2 * slot + 1], nv - nl);
+    }
+  }
+}
+
+// cursor over (parent slot, feature tile gs, 1024-row unit) triples, slot-major
+struct MoveCursor {
+  const int* pprefix;
+  const int* sb;
+  const int* se;
+  int n_slots, GS;
+  int slot, slot_u0, slot_u1, chunks, begin, end;
+  int gs, chunk, row0, nrows;
+  __device__ __forceinline__ int find(int u) const {
+    int lo = 0, hi = n_slots;
+    while (hi - lo > 1) {
+      const int mid = (lo + hi) >> 1;
+      if (pprefix[mid] * GS <= u) lo = mid; else hi = mid;
+    }
+    return lo;
+  }
+  __device__ void init(const MtbCtx& P, int n_slots_) {
+    pprefix = ptr_of<const int>(P.unit_prefix) + (P.m_cap + 1);
+    sb = ptr_of<const int>(P.slot_begin);
+    se = ptr_of<const int>(P.slot_end);
+    n_slots = n_slots_;
+    GS = (int)(P.G * (16 / P.FT));
+    slot = -1;
+    slot_u0 = slot_u1 = 0;
+  }
+  __device__ __forceinline__ void seek(int u) {
+    if (u >= slot_u1 || slot < 0) {
+      slot = find(u);
+      slot_u0 = pprefix[slot] * GS;
+      slot_u1 = pprefix[slot + 1] * GS;
+      begin = sb[slot];
+      end = se[slot];
+      chunks = pprefix[slot + 1] - pprefix[slot];
+      const int local = u - slot_u0;
+      gs = local / chunks;
+      chunk = local - gs * chunks;
+    } else if (++chunk == chunks) {
+      chunk = 0;
+      ++gs;
+    }
+    row0 = begin + chunk * kPartRows;
+    nrows = min(kPartRows, end - row0);
+  }
+  __device__ __forceinline__ int unit_index() const { return pprefix[slot] + chunk; }
+  __device__ __forceinline__ bool owns_whole_tile(int u0, int u1) const {
+    const int t0 = slot_u0 + gs * chunks;
+    return u0 <= t0 && t0 + chunks <= u1;
+  }
+};
+
+constexpr int kLabelStage = 1056;                               // 1024 labels + alignment slack
+constexpr int kStage2Bytes = kStageBytes + kLabelStage + 160;   // + 144-byte unit record, 16-byte multiple
+
+__host__ __device__ inline HistGeom move_geom(int FT, int B, int C) {
+  HistGeom g;
+  g.tile_words = FT * B * C;
+  int tile_bytes = g.tile_words * 4;
+  int st = (kSmemBudget - tile_bytes - 256) / kStage2Bytes;
+  if (st > kMaxStages) st = kMaxStages;
+  g.stages = st;
+  g.smem_bytes = tile_bytes + st * kStage2Bytes + 256;
+  return g;
+}
+
+template <int FT>
+__device__ void move_hist_phase(const MtbCtx& P, const MtbCtx& C, uint8_t* smem) {
+  View vp(P);
+  const int B = (int)P.B, Cn = (int)P.C;
+  const HistGeom geom = move_geom(FT, B, Cn);
+  uint32_t* tile = reinterpret_cast<uint32_t*>(smem);
+  uint8_t* stage_base = smem + (size_t)geom.tile_words * 4;
+  uint64_t* full = reinterpret_cast<uint64_t*>(stage_base + (size_t)geom.stages * kStage2Bytes);
+  uint64_t* empty = full + kMaxStages;
+  const int stages = geom.stages;
+  const int n_slots = vp.n_slots();
+  const int S = 16 / FT;
+  const int GS = (int)(P.G * S);
+  const int total_units = vp.scalars()[4] * GS;
+  const int u0 = (int)((int64_t)total_units * blockIdx.x / gridDim.x);
+  const int u1 = (int)((int64_t)total_units * (blockIdx.x + 1) / gridDim.x);
+  const int tid = threadIdx.x;
+  if (tid == 0) {
+    for (int i = 0; i < stages; ++i) {
+      mbar_init(&full[i], 1);
+      mbar_init(&empty[i], kConsumerWarps);
+    }
+    fence_barrier_init();
+  }
+  for (int i = tid; i < geom.tile_words; i += blockDim.x) tile[i] = 0;
+  __syncthreads();
+
+  const uint8_t* codes = vp.codes_cur();
+  const uint8_t* lsrc = vp.labels_cur();
+  const uint32_t* meta = ptr_of<const uint32_t>(P.mask_words);
+  MoveCursor cur;
+  cur.init(P, n_slots);
+
+  if (tid >= kConsumers) {
+    // ===== producer: rows of one plane, their labels and the unit record, all by TMA =====
+    if (tid == kConsumers) {
+      int st = 0;
+      uint32_t ph = 0;
+      for (int u = u0; u < u1; ++u) {
+        cur.seek(u);
+        const int g = cur.gs / S;
+        mbar_wait(&empty[st], ph ^ 1);
+        uint8_t* sbuf = stage_base + (size_t)st * kStage2Bytes;
+        const uint32_t cbytes = (uint32_t)cur.nrows * 16u;
+        const uint32_t loff = (uint32_t)cur.row0 & 15u;
+        const uint32_t lbytes = (loff + (uint32_t)cur.nrows + 15u) & ~15u;
+        mbar_arrive_expect_tx(&full[st], cbytes + lbytes + kMetaWords * 4);
+        tma_load_1d(sbuf, codes + ((int64_t)g * P.n_cap + cur.row0) * 16, cbytes, &full[st]);
+        tma_load_1d(sbuf + kStageBytes, lsrc + (cur.row0 - (int)loff), lbytes, &full[st]);
+        tma_load_1d(sbuf + kStageBytes + kLabelStage, meta + (int64_t)cur.unit_index() * kMetaWords, kMetaWords * 4,
+                    &full[st]);
+        if (++st == stages) { st = 0; ph ^= 1; }
+      }
+    }
+    return;
+  }
+  // ===== consumer warps: warp w owns rows [64 w, 64 w + 64) of every unit =====
+  const int lane = lane_id(), w = warp_id();
+  uint8_t* ldst = vp.labels_nxt();
+  uint4* dst = reinterpret_cast<uint4*>(vp.codes_nxt());
+  const int* part_flags = ptr_of<const int>(P.part_flags);
+  const int* part_child = ptr_of<const int>(P.part_child);
+  const int* cmode = ptr_of<const int>(C.slot_mode);
+  const int64_t plane = P.n_cap;
+  int st = 0;
+  uint32_t ph = 0;
+  int cur_slot = -1, cur_gs = -1, build_child = -1, build_side = -1, flags = 0;
+  bool cur_excl = false;
+  for (int u = u0; u < u1; ++u) {
+    cur.seek(u);
+    if (cur.slot != cur_slot || cur.gs != cur_gs) {
+      if (build_child >= 0) {
+        named_bar_sync(1, kConsumers);
+        flush_tile<FT>(C, tile, build_child, cur_gs, tid, cur_excl);
+        named_bar_sync(1, kConsumers);
+      }
+      cur_slot = cur.slot;
+      cur_gs = cur.gs;
+      cur_excl = cur.owns_whole_tile(u0, u1);
+      flags = part_flags[cur_slot];
+      const int a = part_child[cur_slot];
+      build_child = -1;
+      build_side = -1;
+      if (a >= 0) {
+        if (cmode[a] == MTB_MODE_BUILD) { build_child = a; build_side = 0; }
+        else if (cmode[a + 1] == MTB_MODE_BUILD) { build_child = a + 1; build_side = 1; }
+      }
+    }
+    const int g = cur.gs / S, sub = (cur.gs % S) * FT;
+    const bool mover = (cur.gs % S) == 0;  // one feature tile per plane moves the plane's bytes
+    const int ra = w * 64 + lane, rb = ra + 32;
+    const bool va_ok = ra < cur.nrows, vb_ok = rb < cur.nrows;
+    mbar_wait(&full[st], ph);
+    const uint8_t* sbuf = stage_base + (size_t)st * kStage2Bytes;
+    const uint4* rows = reinterpret_cast<const uint4*>(sbuf);
+    const uint8_t* slab = sbuf + kStageBytes + ((uint32_t)cur.row0 & 15u);
+    const uint32_t* rec = reinterpret_cast<const uint32_t*>(sbuf + kStageBytes + kLabelStage);
+    // rank rows from the unit's "goes left" bits
+    const uint32_t word = rec[lane];
+    const uint32_t base_l = rec[32], base_r = rec[33];
+    uint4 xa = make_uint4(0, 0, 0, 0), xb = xa;
+    uint32_t lab_a = 0, lab_b = 0;
+    if (va_ok) { xa = rows[ra]; lab_a = slab[ra]; }
+    if (vb_ok) { xb = rows[rb]; lab_b = slab[rb]; }
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&empty[st]);
+    const uint32_t inc = warp_incl_scan(__popc(word));
+    const uint32_t w0 = __shfl_sync(0xffffffffu, word, 2 * w), w1 = __shfl_sync(0xffffffffu, word, 2 * w + 1);
+    const uint32_t before0 = __shfl_sync(0xffffffffu, inc, 2 * w) - __popc(w0);  // lefts before word 2w
+    const uint32_t below = (1u << lane) - 1u;
+    const bool la = (w0 >> lane) & 1u, lb = (w1 >> lane) & 1u;
+    const uint32_t lefts_a = before0 + __popc(w0 & below);
+    const uint32_t lefts_b = before0 + __popc(w0) + __popc(w1 & below);
+    if (mover) {
+      const bool keep_l = flags & 1, keep_r = flags & 2;
+      if (va_ok && (la ? keep_l : keep_r)) {
+        const int64_t d = la ? (int64_t)cur.begin + base_l + lefts_a
+                             : (int64_t)cur.end - 1 - (base_r + ((uint32_t)ra - lefts_a));
+        st_na_u4(dst + (int64_t)g * plane + d, xa);
+        if (g == 0) ldst[d] = (uint8_t)lab_a;
+      }
+      if (vb_ok && (lb ? keep_l : keep_r)) {
+        const int64_t d = lb ? (int64_t)cur.begin + base_l + lefts_b
+                             : (int64_t)cur.end - 1 - (base_r + ((uint32_t)rb - lefts_b));
+        st_na_u4(dst + (int64_t)g * plane + d, xb);
+        if (g == 0) ldst[d] = (uint8_t)lab_b;
+      }
+    }
+    if (build_child >= 0) {
+      if (va_ok && (int)(!la) == build_side) {
+#pragma unroll
+        for (int k = 0; k < FT; ++k) atomicAdd(&tile[(k * B + (int)code_byte(xa, sub + k)) * Cn + (int)lab_a], 1u);
+      }
+      if (vb_ok && (int)(!lb) == build_side) {
+#pragma unroll
+        for (int k = 0; k < FT; ++k) atomicAdd(&tile[(k * B + (int)code_byte(xb, sub + k)) * Cn + (int)lab_b], 1u);
+      }
+    }
+    if (++st == stages) { st = 0; ph ^= 1; }
+  }
+  if (build_child >= 0) {
+    named_bar_sync(1, kConsumers);
+    flush_tile<FT>(C, tile, build_child, cur_gs, tid, cur_excl);
+  }
 }
 
 // ----------------------------------------------------------------- fused level
@@ -942,6 +1223,51 @@ __global__ void __launch_bounds__(kHistThreads, 1) k_level_fused(const __grid_co
   stamp(ctx, 6);
 }
 
+template <int FT>
+__global__ void __launch_bounds__(kHistThreads, 1) k_level_fused2(const __grid_constant__ MtbCtx P,
+                                                                  const __grid_constant__ MtbCtx C) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  __shared__ int smem_warp[33];
+  cg::grid_group grid = cg::this_grid();
+  // nothing to partition and nothing to search: the tree finished at an earlier level
+  if (ptr_of<const int>(P.scalars)[1] == 0) {
+    if (blockIdx.x == 0 && threadIdx.x == 0) ptr_of<int>(P.scalars)[0] = 0;
+    return;
+  }
+  stamp(C, 0);
+  prepass_phase(P);
+  grid.sync();
+  stamp(C, 8);
+  move_hist_phase<FT>(P, C, smem);
+  grid.sync();
+  commit_phase(P);
+  if (blockIdx.x == 0 && threadIdx.x == 0) ptr_of<int>(P.scalars)[0] = ptr_of<int>(P.scalars)[1];
+  grid.sync();
+  stamp(C, 1);
+  if (blockIdx.x == 0) plan_phase(C, smem_warp);  // resets cursors and the gain work counters
+  if (C.world > 1) {
+    grid.sync();
+    stamp(C, 2);
+    push_phase(C);
+    peer_barrier(C, grid, (uint32_t)C.epoch + 1u);
+    stamp(C, 3);
+    gain_phase(C, smem, kFusedGainWarps, -1);
+    stamp(C, 4);
+    peer_barrier(C, grid, (uint32_t)C.epoch + 2u);
+    stamp(C, 5);
+  } else {
+    grid.sync();
+    stamp(C, 2);
+    stamp(C, 3);
+    gain_phase(C, smem, kFusedGainWarps, -1);
+    grid.sync();
+    stamp(C, 4);
+    stamp(C, 5);
+  }
+  if (blockIdx.x == 0) finalize_phase(C, smem_warp);
+  stamp(C, 6);
+}
+
 int g_sm_count = 0;
 int sm_count() {
   if (!g_sm_count) {
@@ -976,6 +1302,16 @@ static int launch_fused(const MtbCtx* ctx, int smem, cudaStream_t stream) {
   MtbCtx local = *ctx;
   void* args[] = {&local};
   MTB_CHECK(cudaLaunchCooperativeKernel((void*)k_level_fused<FT>, dim3(sm_count()), dim3(kHistThreads), args, smem,
+                                        stream));
+  return 0;
+}
+
+template <int FT>
+static int launch_fused2(const MtbCtx* P, const MtbCtx* C, int smem, cudaStream_t stream) {
+  if (set_smem(k_level_fused2<FT>, smem)) return -1;
+  MtbCtx p = *P, c = *C;
+  void* args[] = {&p, &c};
+  MTB_CHECK(cudaLaunchCooperativeKernel((void*)k_level_fused2<FT>, dim3(sm_count()), dim3(kHistThreads), args, smem,
                                         stream));
   return 0;
 }
@@ -1068,4 +1404,25 @@ extern "C" int mtb_level_fused(const MtbCtx* ctx, void* stream) {
     return -2;
   }
   FT_SWITCH((int)ctx->FT, launch_fused, ctx, smem, (cudaStream_t)stream);
+}
+
+extern "C" int mtb_level_fused2(const MtbCtx* parents, const MtbCtx* children, void* stream) {
+  HistGeom g = hist_geom((int)parents->FT, (int)parents->B, (int)parents->C);
+  if (g.stages < 2) {
+    mtb_set_error("hist", "histogram tile does not fit in shared memory", __FILE__, __LINE__);
+    return -2;
+  }
+  HistGeom mg = move_geom((int)parents->FT, (int)parents->B, (int)parents->C);
+  if (mg.stages < 2) {
+    mtb_set_error("fused2", "histogram tile leaves no room for two row stages", __FILE__, __LINE__);
+    return -3;
+  }
+  int smem = mg.smem_bytes > g.smem_bytes ? mg.smem_bytes : g.smem_bytes;
+  const int gsm = kFusedGainWarps * ((int)parents->B * (int)parents->C + 32) * 4;
+  if (gsm > smem) smem = gsm;
+  if (smem > 227 * 1024) {
+    mtb_set_error("fused", "gain slabs do not fit in shared memory", __FILE__, __LINE__);
+    return -2;
+  }
+  FT_SWITCH((int)parents->FT, launch_fused2, parents, children, smem, (cudaStream_t)stream);
 }

@@ -286,6 +286,7 @@ class TreeBuilder:
         min_free_bytes: Optional[int] = None,
         async_levels: bool = True,
         small_rows: Optional[int] = None,
+        fuse_partition: bool = True,
     ):
         import torch
 
@@ -407,6 +408,14 @@ class TreeBuilder:
         self.cursors = z(2 * m_cap)
         self.scalars = z(8)
         self.unit_prefix = z(2 * (m_cap + 1))
+        # fused partition + next-level histogram (levels >= 1 of the fused paths)
+        self.fuse_partition = bool(fuse_partition and fused and reduce in ("none", "p2p"))
+        if self.fuse_partition:
+            max_units = data.n_cap // 1024 + m_cap + 2
+            self.part_child = z(m_cap)
+            self.mask_words = z(max_units * 36)  # 144-byte unit records (32 bit words + 2 bases + pad)
+            self.unit_base = z(2)
+        self._ctx_prev = None
         self._alloc_tree(self.node_cap)
 
         # record mailbox: fb_cost | fb_bin | fb_left | node_cnt (layout shared with the kernels)
@@ -503,6 +512,8 @@ class TreeBuilder:
         c.t_gain, c.t_counts = _p(t["gain"]), _p(t["counts"])
         c.scalars, c.unit_prefix = _p(self.scalars), _p(self.unit_prefix)
         c.m_cap, c.node_cap = self.m_cap, self.node_cap
+        if self.fuse_partition:
+            c.part_child, c.mask_words, c.unit_base = _p(self.part_child), _p(self.mask_words), _p(self.unit_base)
 
     def _launch(self, name: str) -> None:
         _call(name, ctypes.byref(self.ctx), _stream_ptr())
@@ -519,6 +530,7 @@ class TreeBuilder:
         self.n_slots, self.n_nodes, self.depth = 1, 1, 0
         self._host_scal = torch.empty(8, dtype=torch.int32).pin_memory()
         self._phase_ns = []
+        self._ctx_prev = None
 
     def prepare_level(self) -> None:
         n_slots, n_nodes = self.n_slots, self.n_nodes
@@ -537,12 +549,16 @@ class TreeBuilder:
 
     def search_level(self) -> None:
         """plan + histogram + reduction + gain + finalize for the current level."""
-        if self.reduce == "p2p":
-            self.ctx.epoch = _EPOCH["next"]
-            _EPOCH["next"] += 2
-            self._launch("mtb_level_fused")
-        elif self.reduce == "none" and self.fused:
-            self._launch("mtb_level_fused")
+        if self.reduce == "p2p" or (self.reduce == "none" and self.fused):
+            if self.reduce == "p2p":
+                self.ctx.epoch = _EPOCH["next"]
+                _EPOCH["next"] += 2
+            if self.fuse_partition and self._ctx_prev is not None:
+                # partition of the previous level's rows + this level's histograms + search, one launch
+                _call("mtb_level_fused2", ctypes.byref(self._ctx_prev), ctypes.byref(self.ctx), _stream_ptr())
+                self.stats.launches += 1
+            else:
+                self._launch("mtb_level_fused")
         else:
             self._launch("mtb_level_plan")
             self._launch("mtb_level_hist")
@@ -558,18 +574,28 @@ class TreeBuilder:
         self.torch.cuda.current_stream().synchronize()
         if self._timers is not None:
             t = self._timers.cpu().numpy().astype(np.float64) / 1e6
-            names = ("plan", "hist", "push+bar", "gain", "bar", "finalize")
-            self._phase_ns.append({n + "_ms": float(t[i + 1] - t[i]) for i, n in enumerate(names)})
+            names = ("plan|part+hist", "hist|plan", "push+bar", "gain", "bar", "finalize")
+            row = {n + "_ms": float(t[i + 1] - t[i]) for i, n in enumerate(names)}
+            if t[8] > t[0]:
+                row["prepass_ms"] = float(t[8] - t[0])
+            self._phase_ns.append(row)
         self.n_next, self.n_nodes = int(self._host_scal[1]), int(self._host_scal[2])
         return self.n_next
 
-    def advance_level(self) -> None:
-        if self.n_next > 0:
+    def _swap_sides(self) -> None:
+        if self.fuse_partition:
+            # the partition of this level's rows runs at the start of the next level's launch
+            self._ctx_prev = type(self.ctx).from_buffer_copy(self.ctx)
+        else:
             self._launch("mtb_level_partition")
             self._launch("mtb_level_commit")
-            self.data.cur ^= 1
-            self.side ^= 1
-            self.hcur ^= 1
+        self.data.cur ^= 1
+        self.side ^= 1
+        self.hcur ^= 1
+
+    def advance_level(self) -> None:
+        if self.n_next > 0:
+            self._swap_sides()
         self.n_slots = self.n_next
         self.depth += 1
         self.stats.levels += 1
@@ -623,11 +649,7 @@ class TreeBuilder:
             self._bind()
             self.hist[self.hcur][: self.n_slots * self.slab_words].zero_()
             self.search_level()
-            self._launch("mtb_level_partition")
-            self._launch("mtb_level_commit")
-            self.data.cur ^= 1
-            self.side ^= 1
-            self.hcur ^= 1
+            self._swap_sides()
             self.stats.levels += 1
         self._host_scal.copy_(self.scalars, non_blocking=True)
         self.torch.cuda.current_stream().synchronize()
