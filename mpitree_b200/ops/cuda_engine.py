@@ -357,11 +357,12 @@ class TreeBuilder:
             agreed = min_free_bytes is not None or hist_budget_bytes is not None
             if hist_budget_bytes is None:
                 free = min_free_bytes if min_free_bytes is not None else torch.cuda.mem_get_info(dev)[0]
-                hist_budget_bytes = int(free * 0.35)
+                hist_budget_bytes = int(free * 0.5)
             depth_cap = 1 << 30 if params.max_depth is None else 1 << max(int(params.max_depth) - 1, 0)
             rows_cap = max(2, n_global // max(int(params.min_samples_split), 2) + 1)
-            per_slot = slab_words * 4 * (3 if peer_mode else 2)  # two sides (+ staging)
-            h_cap = min(depth_cap, rows_cap, max(2, hist_budget_bytes // per_slot))
+            # single rank: two ping-pong sides; peers: one side of local partials + staging + 2/P reduced
+            per_slot = slab_words * 4 * (2.0 + 2.0 / P if peer_mode else 2.0)
+            h_cap = min(depth_cap, rows_cap, max(2, int(hist_budget_bytes // per_slot)))
             h_cap = max(2, h_cap + (h_cap & 1))
             if comm is not None and comm.size > 1 and not agreed:
                 h_cap = min(comm.allgather_object(h_cap))  # every rank must use the same layout
@@ -376,6 +377,10 @@ class TreeBuilder:
         # enqueued without reading anything back between levels (kernels of levels that turn
         # out to be empty return immediately).
         worst_frontier = None if params.max_depth is None else 1 << max(int(params.max_depth) - 1, 0)
+        import os as _os
+
+        if _os.environ.get("MTB_ASYNC") == "0":
+            async_levels = False
         self.async_levels = bool(
             async_levels and not profile and params.max_depth is not None and int(params.max_depth) >= 1
             and worst_frontier <= self.h_cap and node_cap <= (1 << 22) and reduce != "lockstep"
@@ -401,7 +406,12 @@ class TreeBuilder:
 
         i32 = torch.int32
         z = lambda n, dt=i32: torch.zeros(max(int(n), 1), dtype=dt, device=dev)  # noqa: E731
-        self.hist = [z(self.h_cap * slab_words), z(self.h_cap * slab_words)]
+        if reduce == "p2p":
+            # peers never read the previous level's local partials (reduced slabs live in rstore)
+            one = z(self.h_cap * slab_words)
+            self.hist = [one, one]
+        else:
+            self.hist = [z(self.h_cap * slab_words), z(self.h_cap * slab_words)]
         self.slots = [{k: z(m_cap) for k in ("node", "begin", "end", "mode", "parent", "sibling")} for _ in range(2)]
         self.nslot_src = z(m_cap)
         self.rec_feature, self.rec_bin, self.part_flags = z(m_cap), z(m_cap), z(m_cap)
@@ -901,8 +911,8 @@ def fit_from_host(X: np.ndarray, y_codes: np.ndarray, n_classes: int, params: Sp
     data.set_labels(torch.from_numpy(np.asarray(y_codes)).to(dev))
     n_global, min_free = n, None
     if comm is not None and comm.size > 1:
-        meta = comm.allgather_object((n, int(torch.cuda.mem_get_info(dev)[0])))
-        n_global, min_free = int(sum(m[0] for m in meta)), min(m[1] for m in meta)
+        meta = comm.allgather_ints((n, int(torch.cuda.mem_get_info(dev)[0])))
+        n_global, min_free = int(meta[:, 0].sum()), int(meta[:, 1].min())
     _dist_group(comm)
     builder = TreeBuilder(data, int(mapper.n_bins.max()), params, n_global=n_global, comm=comm,
                           min_free_bytes=min_free, **(builder_kwargs or {}))
@@ -948,9 +958,9 @@ def fit_from_torch(X, y, params: SplitParams, *, max_bins: int = 256, comm=None,
     n_global, min_free = n, None
     if comm is not None and comm.size > 1:
         # the one host-side exchange of a fit: label range, shard sizes, free memory
-        meta = comm.allgather_object((y_max, n, int(torch.cuda.mem_get_info(dev)[0])))
-        y_max = max(m[0] for m in meta)
-        n_global, min_free = int(sum(m[1] for m in meta)), min(m[2] for m in meta)
+        meta = comm.allgather_ints((y_max, n, int(torch.cuda.mem_get_info(dev)[0])))
+        y_max = int(meta[:, 0].max())
+        n_global, min_free = int(meta[:, 1].sum()), int(meta[:, 2].min())
     if y_max < MAX_CLASSES:
         # label values are used as class codes; the labels that actually occur are read off the
         # root histogram afterwards (saves a counting pass over y)

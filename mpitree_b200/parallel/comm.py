@@ -42,6 +42,9 @@ class SelfComm:
     def allgather_object(self, obj: Any) -> List[Any]:
         return [obj]
 
+    def allgather_ints(self, values) -> "np.ndarray":
+        return np.asarray([[int(v) for v in values]], dtype=np.int64)
+
     def broadcast_object(self, obj: Any, src: int = 0) -> Any:
         return obj
 
@@ -92,6 +95,23 @@ class TorchComm:
         out = [None] * self.size
         self._dist.all_gather_object(out, obj, group=self._group)
         return out
+
+    def allgather_ints(self, values) -> "np.ndarray":
+        """Gather a few integers from every rank -> ``(size, k)`` int64 array.
+
+        On a NCCL world this is one tiny device all-gather (tens of microseconds) instead of
+        the pickled gloo exchange, which costs milliseconds at 8 ranks.
+        """
+        import torch
+
+        vals = [int(v) for v in values]
+        world_is_default = self._ranks == list(range(self._dist.get_world_size()))
+        if world_is_default and self._dist.get_backend() == "nccl" and torch.cuda.is_available():
+            t = torch.tensor(vals, dtype=torch.int64, device="cuda")
+            out = torch.empty(self.size * len(vals), dtype=torch.int64, device="cuda")
+            self._dist.all_gather_into_tensor(out, t)
+            return out.cpu().numpy().reshape(self.size, len(vals))
+        return np.asarray(self.allgather_object(vals), dtype=np.int64)
 
     def broadcast_object(self, obj: Any, src: int = 0) -> Any:
         box = [obj]
@@ -224,6 +244,9 @@ class ThreadComm:
 
     def allgather_object(self, obj: Any) -> List[Any]:
         return self._exchange(obj)
+
+    def allgather_ints(self, values) -> "np.ndarray":
+        return np.asarray(self._exchange([int(v) for v in values]), dtype=np.int64)
 
     def broadcast_object(self, obj: Any, src: int = 0) -> Any:
         return self._exchange(obj)[src]
