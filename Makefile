@@ -1,0 +1,26 @@
+# mpitree_b200 developer targets (the reference's Makefile only creates a conda env: Makefile:1-8)
+PY ?= python
+
+build:            ## compile the sm_100a native library in-tree
+	$(PY) -c "import __graft_entry__ as g; g.build()"
+
+test:             ## CPU test-suite (oracle parity, multi-process gloo, host engine)
+	$(PY) -m pytest tests -x -q -m "not gpu"
+
+test-gpu:         ## GPU test-suite (needs a B200)
+	$(PY) -m pytest tests -x -q -m gpu
+
+bench:            ## headline benchmark on one GPU
+	$(PY) bench.py --steps 3 --warmup 3
+
+reference:        ## install the unmodified reference for the oracle / reference arm
+	$(PY) baseline/install_ref.py
+
+lint:
+	ruff check mpitree_b200 tests bench.py
+
+clean:
+	rm -rf mpitree_b200/lib build *.egg-info .pytest_cache .ruff_cache .hypothesis
+	find . -name __pycache__ -type d -prune -exec rm -rf {} +
+
+.PHONY: build test test-gpu bench reference lint clean

@@ -72,6 +72,17 @@ def fit_flat_tree_host(
     if world <= 1 or handoff_rows <= 0:
         return build_tree_cpu(codes, y, n_bins, n_classes, params, comm)
 
+    # the whole problem is below the hand-off size: one owner builds it, everyone receives the tree
+    n_global = int(comm.allreduce_sum(np.array([codes.shape[0]], dtype=np.int64))[0])
+    if n_global <= handoff_rows:
+        shards = comm.allgather_object((codes, y))
+        blob = None
+        if comm.rank == 0:
+            all_codes = np.concatenate([s[0] for s in shards])
+            all_y = np.concatenate([s[1] for s in shards])
+            blob = build_tree_cpu(all_codes, all_y, n_bins, n_classes, params, None).to_bytes()
+        return FlatTree.from_bytes(comm.broadcast_object(blob, src=0))
+
     pending: dict = {}
     trunk = build_tree_cpu(
         codes, y, n_bins, n_classes, params, comm, handoff_rows=handoff_rows, pending_out=pending
