@@ -444,14 +444,25 @@ __device__ void gain_pair(const MtbCtx& ctx, uint32_t* slab, int slot, int f) {
     const int64_t region = ctx.fpo * ctx.B * ctx.C;
     const uint32_t* stage = ptr_of<const uint32_t>(ctx.peer_hist[r]) + (int64_t)fl * B * C;
     uint4* out4 = reinterpret_cast<uint4*>(ptr_of<uint32_t>(ctx.rstore[ctx.hcur]) + (int64_t)slot * region + (int64_t)fl * B * C);
-    // reduced counts of `s`: own partial + what the peers pushed
+    // reduced counts of `s`: own partial + what the peers pushed.  The staged loads are issued
+    // four at a time (fixed unroll over the maximum world size) so their latencies overlap.
     auto reduced4 = [&](int s, int q) -> uint4 {
       uint4 x = reinterpret_cast<const uint4*>(v.hist_cur() + (int64_t)s * v.slab_words() + (int64_t)f * B * C)[q];
-      for (int p = 0; p < P; ++p)
-        if (p != r) {
-          const uint4 y = *reinterpret_cast<const uint4*>(stage + ((int64_t)p * ctx.h_cap + s) * region + q * 4);
-          x.x += y.x; x.y += y.y; x.z += y.z; x.w += y.w;
+      const uint32_t* cell = stage + (int64_t)s * region + q * 4;
+      const int64_t src_stride = ctx.h_cap * region;
+#pragma unroll
+      for (int p0 = 0; p0 < MTB_MAX_WORLD; p0 += 4) {
+        if (p0 < P) {
+          uint4 y[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const int p = p0 + j;
+            y[j] = (p < P && p != r) ? ld_nc_u4(cell + (int64_t)p * src_stride) : make_uint4(0, 0, 0, 0);
+          }
+#pragma unroll
+          for (int j = 0; j < 4; ++j) { x.x += y[j].x; x.y += y[j].y; x.z += y[j].z; x.w += y[j].w; }
         }
+      }
       return x;
     };
     if (mode == MTB_MODE_DERIVE) {

@@ -131,3 +131,31 @@ class _LocalView:
 
     def close(self) -> None:
         return None
+
+
+def multicast_supported(device: int = 0) -> bool:
+    """Does the driver expose NVLS multicast objects (``cuMulticastCreate``) on ``device``?
+
+    Round 1 ships the always-available peer (P2P load/store) data plane; the probe is what a
+    ``multimem.red`` / ``multimem.ld_reduce`` fast path would key on.  Returns False whenever
+    the attribute cannot be queried (no driver, no cuda-python, CPU box).
+    """
+    try:
+        try:
+            from cuda.bindings import driver as drv  # cuda-python >= 12.8
+        except ImportError:
+            from cuda import cuda as drv
+
+        (err,) = drv.cuInit(0)
+        if int(err) != 0:
+            return False
+        attr = getattr(drv.CUdevice_attribute, "CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED", None)
+        if attr is None:
+            return False
+        err, dev = drv.cuDeviceGet(device)
+        if int(err) != 0:
+            return False
+        err, val = drv.cuDeviceGetAttribute(attr, dev)
+        return int(err) == 0 and int(val) == 1
+    except Exception:  # noqa: BLE001
+        return False
