@@ -208,11 +208,12 @@ int mtb_device_malloc(int64_t bytes, void** out);
 int mtb_device_free(void* ptr);
 int mtb_memset_async(void* ptr, int value, int64_t bytes, void* stream);
 /* u32 sum all-reduce over peer-mapped buffers (K5).  bufs[q] = rank q's symmetric area as mapped
- * in this process: [in: cap u32][res: cap u32]; flags[q] = rank q's flag words u32[world].  Every
+ * in this process: [in: cap u32][res: cap u32]; flags[q] = rank q's flag words u32[512][16].  Every
  * rank writes its `count` inputs at the start of its own area, then all ranks call this with the
  * same arguments and a common `epoch` (advance by 2 per call).  algo: 0 one-shot (pull + sum),
- * 1 two-shot (reduce-scatter + push).  The result lands in `out` (device pointer; may be the own
- * result area bufs[rank] + cap).  Spins on peers: one rank per GPU.                              */
+ * 1 two-shot (reduce-scatter + push; result in the own result area bufs[rank] + cap and, when `out`
+ * is non-null and different, copied there).  One-shot writes to `out`.  Plain launches, CTAs of
+ * equal index synchronise through the flags.  Spins on peers: one rank per GPU.                   */
 int mtb_allreduce_u32(int algo, int rank, int world, void* const* bufs, void* const* flags, int64_t count,
                       int64_t cap, uint32_t epoch, uint32_t* out, void* stream);
 

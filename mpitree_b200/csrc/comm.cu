@@ -13,14 +13,13 @@
 //              2 x (P-1)/P x bytes per GPU.
 //
 // Integer sums are order independent, so results are bit-identical on every rank.
-// Each rank's symmetric area is [in: cap u32][res: cap u32]; flags are u32[world] per rank.
+// Each rank's symmetric area is [in: cap u32][res: cap u32] (cap a multiple of 4, inputs are read
+// in 16-byte units, so the pad words of the last unit must be readable); flags are
+// u32[512][16] per rank (one row per CTA index).
 // Kernels spin on peers: every rank must launch on its own GPU (never as several waiting
 // kernels on one device).
-#include <cooperative_groups.h>
-
 #include "common.cuh"
 
-namespace cg = cooperative_groups;
 using namespace mtb;
 
 namespace {
@@ -34,71 +33,81 @@ struct ArArgs {
   uint32_t* out;
 };
 
-// kGrid = false: single-CTA launch (small messages), block barriers instead of grid syncs
-template <bool kGrid>
-__device__ void ar_barrier(const ArArgs& a, uint32_t epoch) {
-  if (kGrid) cg::this_grid().sync(); else __syncthreads();
-  if (blockIdx.x == 0 && threadIdx.x < (unsigned)a.world) {
+constexpr int kArMaxCtas = 512;  // flag words per rank: [kArMaxCtas][MTB_MAX_WORLD]
+
+// Barrier between the CTAs with the same index on every rank (all ranks launch the same grid).
+// No grid-wide sync is needed anywhere: a peer's input is ready as soon as any of its CTAs runs
+// (the kernel is stream-ordered after the producer), and a kernel only completes when all of its
+// CTAs have seen their counterparts finish, which together covers every peer CTA.
+__device__ void cta_peer_barrier(const ArArgs& a, uint32_t epoch) {
+  __syncthreads();
+  if (threadIdx.x < (unsigned)a.world) {
     __threadfence_system();
-    st_release_sys_u32(a.flags[threadIdx.x] + a.rank, epoch);
-    const uint32_t* mine = a.flags[a.rank] + threadIdx.x;
+    st_release_sys_u32(a.flags[threadIdx.x] + (size_t)blockIdx.x * MTB_MAX_WORLD + a.rank, epoch);
+    const uint32_t* mine = a.flags[a.rank] + (size_t)blockIdx.x * MTB_MAX_WORLD + threadIdx.x;
     while ((int32_t)(ld_acquire_sys_u32(mine) - epoch) < 0) {
     }
     __threadfence_system();
   }
-  if (kGrid) cg::this_grid().sync(); else __syncthreads();
+  __syncthreads();
 }
 
 __device__ __forceinline__ uint4 add4(uint4 a, uint4 b) {
   return make_uint4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w);
 }
 
-template <bool kGrid>
-__global__ void __launch_bounds__(512) k_allreduce_oneshot(const __grid_constant__ ArArgs a) {
-  ar_barrier<kGrid>(a, a.epoch + 1);  // every rank's input is in place
-  const int64_t n4 = a.count / 4;
-  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
-    uint4 acc = reinterpret_cast<const uint4*>(a.bufs[a.rank])[i];
-    for (int p = 1; p < a.world; ++p) {
-      const int q = (a.rank + p) % a.world;  // stagger peers so links are used evenly
-      acc = add4(acc, ld_nc_u4(reinterpret_cast<const uint4*>(a.bufs[q]) + i));
+// sum of element i over all ranks, peers' loads issued four at a time
+__device__ __forceinline__ uint4 gather_sum(const ArArgs& a, int64_t i) {
+  uint4 acc = reinterpret_cast<const uint4*>(a.bufs[a.rank])[i];
+#pragma unroll
+  for (int p0 = 1; p0 < MTB_MAX_WORLD; p0 += 4) {
+    if (p0 < a.world) {
+      uint4 y[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int p = p0 + j;
+        const int q = (a.rank + p) % a.world;  // stagger peers so links are used evenly
+        y[j] = p < a.world ? ld_nc_u4(reinterpret_cast<const uint4*>(a.bufs[q]) + i) : make_uint4(0, 0, 0, 0);
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) acc = add4(acc, y[j]);
     }
-    reinterpret_cast<uint4*>(a.out)[i] = acc;
   }
-  for (int64_t i = n4 * 4 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < a.count; i += stride) {
-    uint32_t acc = 0;
-    for (int q = 0; q < a.world; ++q) acc += a.bufs[q][i];
-    a.out[i] = acc;
-  }
-  ar_barrier<kGrid>(a, a.epoch + 2);  // nobody may overwrite its input before all have read it
+  return acc;
 }
 
-template <bool kGrid>
+__global__ void __launch_bounds__(512) k_allreduce_oneshot(const __grid_constant__ ArArgs a) {
+  cta_peer_barrier(a, a.epoch + 1);  // every rank's input is in place
+  const int64_t n4 = (a.count + 3) / 4;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
+    const uint4 v = gather_sum(a, i);
+    if (i * 4 + 4 <= a.count) {
+      reinterpret_cast<uint4*>(a.out)[i] = v;
+    } else {  // last, partial unit: the caller's buffer may end at `count`
+      const uint32_t e[4] = {v.x, v.y, v.z, v.w};
+      for (int j = 0; i * 4 + j < a.count; ++j) a.out[i * 4 + j] = e[j];
+    }
+  }
+  cta_peer_barrier(a, a.epoch + 2);  // nobody may overwrite its input before all have read it
+}
+
 __global__ void __launch_bounds__(512) k_allreduce_twoshot(const __grid_constant__ ArArgs a) {
-  ar_barrier<kGrid>(a, a.epoch + 1);
+  cta_peer_barrier(a, a.epoch + 1);
   // slice owned by this rank, in 16-byte units
   const int64_t n4 = (a.count + 3) / 4;
   const int64_t per = (n4 + a.world - 1) / a.world;
   const int64_t lo = per * a.rank, hi = min(n4, lo + per);
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t i = lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += stride) {
-    uint4 acc = reinterpret_cast<const uint4*>(a.bufs[a.rank])[i];
-    for (int p = 1; p < a.world; ++p) {
-      const int q = (a.rank + p) % a.world;
-      acc = add4(acc, ld_nc_u4(reinterpret_cast<const uint4*>(a.bufs[q]) + i));
-    }
+    const uint4 acc = gather_sum(a, i);
     // reduced slice -> every rank's result area (own one included)
     for (int p = 0; p < a.world; ++p) {
       const int q = (a.rank + p) % a.world;
       st_na_u4(reinterpret_cast<uint4*>(a.bufs[q] + a.cap) + i, acc);
     }
   }
-  ar_barrier<kGrid>(a, a.epoch + 2);  // all slices have landed in my result area
-  if (a.out != a.bufs[a.rank] + a.cap) {
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < a.count; i += stride)
-      a.out[i] = a.bufs[a.rank][a.cap + i];
-  }
+  cta_peer_barrier(a, a.epoch + 2);  // the slices of all peers' CTAs of this index have landed
 }
 
 }  // namespace
@@ -128,17 +137,23 @@ extern "C" int mtb_allreduce_u32(int algo, int rank, int world, void* const* buf
   int dev = 0, sms = 0;
   MTB_CHECK(cudaGetDevice(&dev));
   MTB_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-  // small messages: few CTAs (the two barriers dominate); large: fill the machine
+  // small messages: few CTAs (the two flag round trips dominate); large: fill the machine.
+  // Every rank computes the same grid (same count, same GPU model).
   int64_t want = (count / 4 + 4 * 512 - 1) / (4 * 512);  // >= 4 x 16 B per thread before adding CTAs
-  int blocks = (int)(want < 1 ? 1 : (want > 2 * sms ? 2 * sms : want));
-  if (blocks == 1) {  // latency path: plain launch, no grid-wide syncs
-    if (algo == 0) k_allreduce_oneshot<false><<<1, 512, 0, (cudaStream_t)stream>>>(a);
-    else k_allreduce_twoshot<false><<<1, 512, 0, (cudaStream_t)stream>>>(a);
-    MTB_CHECK(cudaGetLastError());
-    return 0;
+  int cap_ctas = 2 * sms < kArMaxCtas ? 2 * sms : kArMaxCtas;
+  int blocks = (int)(want < 1 ? 1 : (want > cap_ctas ? cap_ctas : want));
+  if (algo == 0) {
+    if (out == nullptr) {
+      mtb_set_error("allreduce", "one-shot needs an output pointer", __FILE__, __LINE__);
+      return -2;
+    }
+    k_allreduce_oneshot<<<blocks, 512, 0, (cudaStream_t)stream>>>(a);
+  } else {
+    k_allreduce_twoshot<<<blocks, 512, 0, (cudaStream_t)stream>>>(a);
+    if (out != nullptr && out != a.bufs[rank] + cap)
+      MTB_CHECK(cudaMemcpyAsync(out, a.bufs[rank] + cap, (size_t)count * 4, cudaMemcpyDeviceToDevice,
+                                (cudaStream_t)stream));
   }
-  void* args[] = {&a};
-  void* fn = algo == 0 ? (void*)k_allreduce_oneshot<true> : (void*)k_allreduce_twoshot<true>;
-  MTB_CHECK(cudaLaunchCooperativeKernel(fn, dim3(blocks), dim3(512), args, 0, (cudaStream_t)stream));
+  MTB_CHECK(cudaGetLastError());
   return 0;
 }

@@ -13,6 +13,8 @@ __all__ = ["PeerAllReduce"]
 
 
 class PeerAllReduce:
+    FLAG_BYTES = 512 * 16 * 4  # one row of world flags per CTA index
+
     """Symmetric buffers + flags for repeated all-reduces of up to ``max_count`` u32 values.
 
     Producers can write straight into :meth:`input_view` (zero-copy); :meth:`all_reduce`
@@ -29,7 +31,7 @@ class PeerAllReduce:
         self.comm = comm
         self.world, self.rank = comm.size, comm.rank
         self.cap = ((int(max_count) + 3) // 4) * 4
-        self.region = IpcRegion(2 * self.cap * 4 + 256, comm)
+        self.region = IpcRegion(2 * self.cap * 4 + self.FLAG_BYTES, comm)
         self._bufs = (ctypes.c_void_p * 16)(*[p for p in self.region.ptrs])
         self._flags = (ctypes.c_void_p * 16)(*[p + 2 * self.cap * 4 for p in self.region.ptrs])
         self._mem = self.region.buf.as_tensor()
@@ -45,7 +47,9 @@ class PeerAllReduce:
     def launch(self, count: int, algo: int = 1, out=None) -> None:
         """Reduce what is in :meth:`input_view`; result in ``out`` or :meth:`result_view`."""
         torch = self.torch
-        dst = out.data_ptr() if out is not None else self.region.ptrs[self.rank] + self.cap * 4
+        if out is None and algo == 0:  # one-shot writes its sums straight to the destination
+            out = self.result_view(count)
+        dst = out.data_ptr() if out is not None else 0
         rc = self.lib.mtb_allreduce_u32(
             ctypes.c_int(algo), ctypes.c_int(self.rank), ctypes.c_int(self.world), self._bufs, self._flags,
             ctypes.c_int64(count), ctypes.c_int64(self.cap), ctypes.c_uint32(self.epoch), ctypes.c_void_p(dst),
