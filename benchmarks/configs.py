@@ -89,7 +89,7 @@ def main():
         score = (X[:, 3].float() - 128) / 64 + (X[:, 70] % 3 == 0).float() * 1.5 - (X[:, 90] > 10).float() + \
             ((X[:, 10] > 100) & (X[:, 100] < 5)).float() * 2 + 1.2 * torch.randn(n, device=dev, generator=g)
         y = torch.bucketize(score, torch.tensor([-1.0, 0.0, 1.0, 2.0], device=dev)).to(torch.uint8)
-        for handoff in (2048, 0):
+        for handoff in (None, 2048):  # None = automatic (level-wise while the histogram slots fit)
             clf = ParallelDecisionTreeClassifier(max_depth=16, min_samples_split=2, data_layout="sharded", device="cuda",
                                                  handoff_rows=handoff)
             ms, launches = timed_fit(clf, X, y, max(1, a.steps - 1), 1, world, dev)

@@ -709,7 +709,13 @@ __device__ void finalize_phase(const MtbCtx& ctx, int* smem_warp) {
       t_feature[node] = bf;
       t_bin[node] = bb;
       t_gain[node] = split ? bgain : NAN;
-      part_flags[s] = pair ? ((tl ? 0 : 1) | (tr ? 0 : 2)) : 0;
+      // Which children's rows must be written by the partition.  With the fused partition +
+      // histogram path (part_child set) a child's histogram is accumulated while its parent's rows
+      // stream by, so its own rows are only needed if *its* children can be split again
+      // (depth + 2 < max_depth) or if it is handed to the subtree kernel.
+      const bool rows_needed = ctx.part_child == 0 || ctx.max_depth < 0 || depth + 2 < ctx.max_depth;
+      const bool keep_l = !tl && (rows_needed || hl), keep_r = !tr && (rows_needed || hr);
+      part_flags[s] = pair ? ((keep_l ? 1 : 0) | (keep_r ? 2 : 0)) : 0;
       if (ctx.part_child) ptr_of<int>(ctx.part_child)[s] = -1;
     } else if (s < n) {
       rec_feature[s] = -1;

@@ -139,7 +139,7 @@ extern "C" int mtb_allreduce_u32(int algo, int rank, int world, void* const* buf
   MTB_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   // small messages: few CTAs (the two flag round trips dominate); large: fill the machine.
   // Every rank computes the same grid (same count, same GPU model).
-  int64_t want = (count / 4 + 4 * 512 - 1) / (4 * 512);  // >= 4 x 16 B per thread before adding CTAs
+  int64_t want = (count / 4 + 511) / 512;  // one 16-byte unit per thread until the machine is full (remote latency bound)
   int cap_ctas = 2 * sms < kArMaxCtas ? 2 * sms : kArMaxCtas;
   int blocks = (int)(want < 1 ? 1 : (want > cap_ctas ? cap_ctas : want));
   if (algo == 0) {
