@@ -66,11 +66,22 @@ class ClockSampler:
                  "-i", str(self.gpu)], stdout=self.fh, stderr=subprocess.DEVNULL)
         except Exception:
             self.proc = None
+            return
+        # nvidia-smi needs a moment to start: wait for its first line so that samples fall
+        # inside the (possibly very short) timed region rather than after it
+        t0 = time.time()
+        while time.time() - t0 < 3.0:
+            try:
+                if os.path.getsize(self.path) > 0:
+                    break
+            except OSError:
+                pass
+            time.sleep(0.01)
 
     def stop(self):
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
+        time.sleep(0.03)
         self.proc.terminate()
         try:
             self.proc.wait(timeout=5)
