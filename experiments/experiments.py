@@ -4,7 +4,8 @@
 * cell 4  (``:184-189``): serial depth-5 tree, ``precision=1``
 * cell 5  (``:198-209``) + ``time_data.csv``: fit wall-time for n = 1, 11, ..., 241 distinct-class rows,
   serial and with k = 2, 5, 8 ranks; written to ``experiments/time_data.csv`` (rows: serial, k=2, k=5, k=8)
-* cells 3, 7 (plots) need matplotlib; they are drawn only when it is importable.
+* cell 3  (``:99-137``): decision boundaries for depth 2 and 5, written as PNG files by a tiny built-in writer
+* cell 7 (timing plot) needs matplotlib; it is drawn only when that is importable.
 
 Ranks are threads of this process (``ThreadComm``) so the script runs anywhere; under
 ``torchrun`` the same classes use the real process group.
@@ -40,6 +41,44 @@ def cell4():
     X, y = iris.data[:, :2], iris.target
     clf = DecisionTreeClassifier(max_depth=5, device="cpu").fit(X, y)
     print(clf.export_text(feature_names=iris.feature_names, class_names=iris.target_names, precision=1))
+
+
+def _write_png(path, rgb):
+    """Minimal PNG writer (zlib + struct) so the figures need no plotting library."""
+    import struct
+    import zlib
+
+    h, w, _ = rgb.shape
+    raw = b"".join(b"\x00" + rgb[i].astype(np.uint8).tobytes() for i in range(h))
+
+    def chunk(tag, data):
+        c = struct.pack(">I", len(data)) + tag + data
+        return c + struct.pack(">I", zlib.crc32(tag + data) & 0xFFFFFFFF)
+
+    png = b"\x89PNG\r\n\x1a\n" + chunk(b"IHDR", struct.pack(">IIBBBBB", w, h, 8, 2, 0, 0, 0))
+    png += chunk(b"IDAT", zlib.compress(raw, 9)) + chunk(b"IEND", b"")
+    pathlib.Path(path).write_bytes(png)
+
+
+def cell3(res: int = 300):
+    """Decision boundaries for max_depth 2 and 5 on iris[:, :2] (``experiments.ipynb:99-137``), as PNG files."""
+    iris = load_iris()
+    X, y = iris.data[:, :2], iris.target
+    fill = np.array([[0x97, 0xC4, 0x77], [0xFD, 0x91, 0x77], [0x97, 0x91, 0xDD]])
+    dots = np.array([[0x00, 0x80, 0x00], [0xFF, 0x00, 0x00], [0x00, 0x00, 0xFF]])
+    x0, x1 = X[:, 0].min() - 0.5, X[:, 0].max() + 0.5
+    y0, y1 = X[:, 1].min() - 0.5, X[:, 1].max() + 0.5
+    gx, gy = np.meshgrid(np.linspace(x0, x1, res), np.linspace(y1, y0, res))
+    for depth in (2, 5):
+        clf = DecisionTreeClassifier(max_depth=depth, device="cpu").fit(X, y)
+        img = fill[clf.predict(np.c_[gx.ravel(), gy.ravel()])].reshape(res, res, 3).copy()
+        px = ((X[:, 0] - x0) / (x1 - x0) * (res - 1)).astype(int)
+        py = ((y1 - X[:, 1]) / (y1 - y0) * (res - 1)).astype(int)
+        for dx in (-1, 0, 1):
+            for dy in (-1, 0, 1):
+                img[np.clip(py + dy, 0, res - 1), np.clip(px + dx, 0, res - 1)] = dots[y]
+        _write_png(HERE / f"decision_boundary_depth{depth}.png", img)
+        print(f"wrote decision_boundary_depth{depth}.png (training accuracy {clf.score(X, y):.4f})")
 
 
 def cell5(reps: int = 3):
@@ -90,5 +129,7 @@ if __name__ == "__main__":
     cell1()
     print()
     cell4()
+    print()
+    cell3()
     print()
     plots(*cell5())

@@ -61,12 +61,6 @@ def supports(*, numeric: bool, n_classes: int) -> Tuple[bool, str]:
     return True, ""
 
 
-def _lib():
-    from . import _lib as L
-
-    return L.load()
-
-
 def _call(name: str, *args) -> None:
     from . import _lib as L
 
@@ -424,7 +418,6 @@ class TreeBuilder:
             max_units = data.n_cap // 1024 + m_cap + 2
             self.part_child = z(m_cap)
             self.mask_words = z(max_units * 36)  # 144-byte unit records (32 bit words + 2 bases + pad)
-            self.unit_base = z(2)
         self._ctx_prev = None
         self._alloc_tree(self.node_cap)
 
@@ -523,7 +516,7 @@ class TreeBuilder:
         c.scalars, c.unit_prefix = _p(self.scalars), _p(self.unit_prefix)
         c.m_cap, c.node_cap = self.m_cap, self.node_cap
         if self.fuse_partition:
-            c.part_child, c.mask_words, c.unit_base = _p(self.part_child), _p(self.mask_words), _p(self.unit_base)
+            c.part_child, c.mask_words = _p(self.part_child), _p(self.mask_words)
 
     def _launch(self, name: str) -> None:
         _call(name, ctypes.byref(self.ctx), _stream_ptr())

@@ -15,8 +15,6 @@ results (``mpitree/tree/decision_tree.py:447-477``); here
 from __future__ import annotations
 
 import ctypes
-from typing import List, Optional
-
 import numpy as np
 
 from ..models.flat_tree import FlatTree

@@ -17,7 +17,7 @@ Two implementations with the same attributes (``world``, ``rank``, ``ptrs``):
 from __future__ import annotations
 
 import ctypes
-from typing import List, Optional
+from typing import List
 
 __all__ = ["IpcRegion", "LocalRegion", "RawBuffer"]
 
