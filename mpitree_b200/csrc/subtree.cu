@@ -120,6 +120,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_subtree(const __grid_constant__
   uint8_t* lab = reinterpret_cast<uint8_t*>(idx2 + T);
   __shared__ Best s_best[kWarps];
   __shared__ uint32_t s_cnt[MTB_MAX_CLASSES];
+  __shared__ uint32_t s_cm[MTB_MAX_CLASSES];  // tiny nodes: lanes (rows) of each class
   __shared__ int s_ctl[8];  // 0: item, 1: rel, 2: lo, 3: hi, 4: curL, 5: curR, 6: sp, 7: nn
 
   const int tid = threadIdx.x, lane = lane_id(), w = warp_id();
@@ -186,31 +187,82 @@ __global__ void __launch_bounds__(kThreads, 1) k_subtree(const __grid_constant__
                                          ptr_of<const double>(a.plogp), (uint32_t)a.plogp_n)
                               : fast_impurity(C, [&](int c) { return cnt[c]; }, (uint32_t)m, (int)a.criterion, klogk);
       Best mine{0.0, -1, -1};
-      for (int g = 0; g < G; ++g) {
-        for (int s = 0; s < S; ++s) {
-          const int f0 = g * 16 + s * FT;
-          if (f0 >= F) break;
-          for (int i = tid; i < tile_words; i += kThreads) tile[i] = 0;
-          __syncthreads();
-          for (int i = lo + tid; i < hi; i += kThreads) {
-            const int r = idx[i];
-            const uint4 v = codes[(int64_t)g * a.n_cap + begin + r];
-            const int l = lab[r];
-#pragma unroll
-            for (int k = 0; k < FT; ++k)
-              if (f0 + k < F) atomicAdd(&tile[(k * B + (int)code_byte(v, s * FT + k)) * C + l], 1u);
+      if (m <= 32) {
+        // ---- tiny node: no histogram at all.  Lane j holds row j; a warp evaluates one feature from
+        // registers: the "goes left" set of candidate i is a ballot, class counts are popcounts
+        // against per-class lane masks.  Same candidates, costs and tie-breaks as the tile path.
+        const bool have = lane < m;
+        const int r = have ? idx[lo + lane] : 0;
+        const int l = have ? lab[r] : -1;
+        if (w == 0)
+          for (int c = 0; c < C; ++c) {
+            const uint32_t cm = __ballot_sync(0xffffffffu, l == c);
+            if (lane == 0) s_cm[c] = cm;
           }
-          __syncthreads();
-          for (int k = w; k < FT && f0 + k < F; k += kWarps) {
-            double cost;
-            int bin;
-            eval_feature(a, tile + k * B * C, (uint32_t)m, cost, bin);
-            if (bin >= 0) {
-              const double gain = __dsub_rn(hp, cost);
-              if (better(gain, f0 + k, mine)) mine = Best{gain, f0 + k, bin};
+        __syncthreads();
+        const double* plogp = ptr_of<const double>(a.plogp);
+        for (int f = w; f < F; f += kWarps) {
+          int code = -1;
+          if (have) code = reinterpret_cast<const uint8_t*>(codes + (int64_t)(f >> 4) * a.n_cap + begin + r)[f & 15];
+          uint32_t left_set = 0;
+          for (int i = 0; i < m; ++i) {
+            const int t = __shfl_sync(0xffffffffu, code, i);
+            const uint32_t bm = __ballot_sync(0xffffffffu, have && code <= t);
+            if (lane == i) left_set = bm;
+          }
+          double cost = INFINITY;
+          int bin = 0x7fffffff;
+          const uint32_t nl = __popc(left_set), nr = (uint32_t)m - nl;
+          if (have && nr != 0) {
+            const double hl = impurity(C, [&](int c) { return (uint32_t)__popc(left_set & s_cm[c]); }, nl,
+                                       (int)a.criterion, plogp, (uint32_t)a.plogp_n);
+            const double hr = impurity(C, [&](int c) { return cnt[c] - (uint32_t)__popc(left_set & s_cm[c]); }, nr,
+                                       (int)a.criterion, plogp, (uint32_t)a.plogp_n);
+            cost = split_cost(nl, nr, hl, hr, (int)a.dot_mode);
+            bin = code;
+          }
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) {
+            const double oc = __shfl_xor_sync(0xffffffffu, cost, o);
+            const int ob = __shfl_xor_sync(0xffffffffu, bin, o);
+            if (oc < cost || (oc == cost && ob < bin)) {
+              cost = oc;
+              bin = ob;
             }
           }
-          __syncthreads();
+          if (bin != 0x7fffffff) {
+            const double gain = __dsub_rn(hp, cost);
+            if (better(gain, f, mine)) mine = Best{gain, f, bin};
+          }
+        }
+        __syncthreads();
+      } else {
+      for (int g = 0; g < G; ++g) {
+          for (int s = 0; s < S; ++s) {
+            const int f0 = g * 16 + s * FT;
+            if (f0 >= F) break;
+            for (int i = tid; i < tile_words; i += kThreads) tile[i] = 0;
+            __syncthreads();
+            for (int i = lo + tid; i < hi; i += kThreads) {
+              const int r = idx[i];
+              const uint4 v = codes[(int64_t)g * a.n_cap + begin + r];
+              const int l = lab[r];
+#pragma unroll
+              for (int k = 0; k < FT; ++k)
+                if (f0 + k < F) atomicAdd(&tile[(k * B + (int)code_byte(v, s * FT + k)) * C + l], 1u);
+            }
+            __syncthreads();
+            for (int k = w; k < FT && f0 + k < F; k += kWarps) {
+              double cost;
+              int bin;
+              eval_feature(a, tile + k * B * C, (uint32_t)m, cost, bin);
+              if (bin >= 0) {
+                const double gain = __dsub_rn(hp, cost);
+                if (better(gain, f0 + k, mine)) mine = Best{gain, f0 + k, bin};
+              }
+            }
+            __syncthreads();
+          }
         }
       }
       if (lane == 0) s_best[w] = mine;
