@@ -288,11 +288,12 @@ def run_reference(a):
         return time.perf_counter() - t0
 
     # calibrate on a small problem, then take the largest size that fits the time budget
-    t_small = fit_time(250)
+    base = 60
+    t_small = fit_time(base)
     fits = a.steps + a.warmup
-    n = 250
-    for cand in (8000, 4000, 2000, 1000, 500):
-        est = t_small * (cand / 250) ** 1.7
+    n = base
+    for cand in (8000, 4000, 2000, 1000, 500, 250, 125):
+        est = t_small * (cand / base) ** 1.7
         if est * fits <= a.ref_budget_s:
             n = cand
             break
