@@ -774,9 +774,10 @@ class _Stages:
 
 
 def _sample_rows(n: int, cap: int = SAMPLE_ROWS) -> Optional[np.ndarray]:
+    """Indices of an evenly strided sample of ``cap`` rows (``None`` = use every row)."""
     if n <= cap:
         return None
-    return np.unique(np.linspace(0, n - 1, cap).astype(np.int64))
+    return (np.arange(cap, dtype=np.int64) * n) // cap  # strictly increasing because n > cap
 
 
 def _fit_mapper_numpy(X: np.ndarray, max_bins: int, comm=None) -> BinMapper:
