@@ -139,6 +139,63 @@ __global__ void __launch_bounds__(kStagedThreads) k_predict_staged(const T* __re
   }
 }
 
+// Compact variant for one-byte codes: a node is ONE 32-bit word
+//   [31:24] feature (255 = leaf)   [23:16] threshold code   [15:0] left child id (leaf: unused)
+// so every level costs one 4-byte shared-memory load per lane instead of a 16-byte one (random
+// 16-byte loads take at least four wavefronts per warp).  Needs F <= 255 and <= 65,536 nodes;
+// labels are looked up once at the end.
+__global__ void __launch_bounds__(kStagedThreads) k_predict_u8_compact(const uint8_t* __restrict__ X, int64_t n,
+                                                                       int F, const int4* __restrict__ nodes,
+                                                                       const int* __restrict__ thr, int n_nodes,
+                                                                       int* __restrict__ out_leaf,
+                                                                       int* __restrict__ out_label) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  const int cpr = F / 16;
+  const int stride = (F / 4) | 1;
+  uint32_t* s_rec = reinterpret_cast<uint32_t*>(smem);
+  uint32_t* s_rows = s_rec + ((n_nodes + 3) & ~3);
+  for (int i = threadIdx.x; i < n_nodes; i += kStagedThreads) {
+    const int4 r = nodes[i];
+    const uint32_t f = r.x < 0 ? 255u : (uint32_t)r.x;
+    // a negative threshold sends every code right: encode it as "always <=" into the right child
+    const bool all_right = r.x >= 0 && thr[i] < 0;
+    const uint32_t t = (r.x < 0 || all_right) ? 255u : (uint32_t)min(thr[i], 255);
+    s_rec[i] = (f << 24) | (t << 16) | ((uint32_t)(max(r.y, 0) + (all_right ? 1 : 0)) & 0xffffu);
+  }
+  __syncthreads();
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  uint32_t* mine = s_rows + (size_t)w * 32 * stride;
+  const int64_t tiles = (n + 31) / 32;
+  const int64_t wstride = (int64_t)gridDim.x * (kStagedThreads / 32);
+  for (int64_t tile = (int64_t)blockIdx.x * (kStagedThreads / 32) + w; tile < tiles; tile += wstride) {
+    const int64_t row0 = tile * 32;
+    const int rows = (int)min((int64_t)32, n - row0);
+    const uint4* src = reinterpret_cast<const uint4*>(X + row0 * F);
+    const int chunks = rows * cpr;
+    for (int q = lane; q < chunks; q += 32) {
+      const uint4 v = mtb::ld_nc_u4(src + q);
+      const int r = q / cpr, c = q - r * cpr;
+      uint32_t* d = mine + r * stride + c * 4;
+      d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
+    }
+    __syncwarp();
+    if (lane < rows) {
+      const uint32_t* x = mine + lane * stride;
+      int node = 0;
+      uint32_t rec = s_rec[0];
+      while ((rec >> 24) != 255u) {
+        const uint32_t f = rec >> 24;
+        const uint32_t v = (x[f >> 2] >> ((f & 3) * 8)) & 0xffu;
+        node = (int)(rec & 0xffffu) + (v <= ((rec >> 16) & 0xffu) ? 0 : 1);
+        rec = s_rec[node];
+      }
+      if (out_leaf) out_leaf[row0 + lane] = node;
+      if (out_label) out_label[row0 + lane] = nodes[node].z;
+    }
+    __syncwarp();
+  }
+}
+
 __global__ void k_pack_nodes(const int* feature, const int* left, const int* label, int n, int4* out) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) out[i] = make_int4(feature[i], left[i], label ? label[i] : 0, 0);
@@ -150,6 +207,22 @@ int launch(const void* X, int64_t n, int64_t F, int64_t ldx, const int4* nodes, 
   int64_t blocks = (n + kThreads - 1) / kThreads;
   if (blocks > 148 * 8) blocks = 148 * 8;
   const int64_t rowbytes = F * (int64_t)sizeof(T);
+  if constexpr (sizeof(T) == 1) {
+    if (ldx == F && F % 16 == 0 && F <= 240 && n_nodes <= 65536 && ((uintptr_t)X % 16) == 0) {
+      const int stride = (int)(F / 4) | 1;
+      const int smem = ((n_nodes + 3) & ~3) * 4 + (kStagedThreads / 32) * 32 * stride * 4 + 16;
+      if (smem <= 220 * 1024) {
+        MTB_CHECK(cudaFuncSetAttribute(k_predict_u8_compact, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       smem > 48 * 1024 ? smem : 48 * 1024));
+        int64_t sblocks = ((n + 31) / 32 + (kStagedThreads / 32) - 1) / (kStagedThreads / 32);
+        if (sblocks > 148 * 2) sblocks = 148 * 2;
+        k_predict_u8_compact<<<(unsigned)sblocks, kStagedThreads, smem, stream>>>(
+            (const uint8_t*)X, n, (int)F, nodes, (const int*)thr, n_nodes, out_leaf, out_label);
+        MTB_CHECK(cudaGetLastError());
+        return 0;
+      }
+    }
+  }
   if (ldx == F && rowbytes % 16 == 0 && rowbytes <= 1024 && ((uintptr_t)X % 16) == 0) {
     const int stride = (int)(rowbytes / 4) | 1;
     const int rows_smem = (kStagedThreads / 32) * 32 * stride * 4;
