@@ -121,8 +121,9 @@ typedef struct MtbCtx {
   int64_t ho_node, ho_begin, ho_end, ho_side; /* i32 [ho_cap]                                 */
   /* ---- fused partition + next-level histogram (mtb_level_fused2) ----
    * part_child: i32 [m_cap] first child slot of a split slot that keeps rows, else -1
-   * mask_words: u32 [max_units][36] per 1024-row partition unit: 32 "row goes left" bit words, the
-   *             rows already placed left / right before the unit, 2 pad words (144 B, fetched by TMA)
+   * mask_words: u32 [max_units][68] per 1024-row partition unit: 32 "row goes left" bit words, 32
+   *             exclusive left-count prefixes, the rows already placed left / right before the
+   *             unit, 2 pad words (272 B, fetched by TMA next to the rows)
    * unit_base : unused (kept for layout compatibility)                                        */
   int64_t part_child, mask_words, unit_base;
   int64_t reserved[1];

@@ -932,7 +932,7 @@ struct PartUnit {
   int slot, chunk, r0, r1;
 };
 
-constexpr int kMetaWords = 36;  // per partition unit: 32 "goes left" words, base_l, base_r, 2 pad (144 B)
+constexpr int kMetaWords = 68;  // per partition unit: 32 "goes left" words, 32 exclusive left-count prefixes, base_l, base_r, 2 pad (272 B)
 
 // One warp per 1024-row unit, no block-wide syncs: lane i ends up holding bit word i, the unit's
 // destination bases are reserved with one atomic pair, and the 144-byte unit record is written
@@ -974,9 +974,11 @@ __device__ void prepass_phase(const MtbCtx& P) {
     }
     uint32_t* rec = meta + (int64_t)u * kMetaWords;
     rec[lane] = mine;
+    const uint32_t pc = __popc(mine);
+    rec[32 + lane] = warp_incl_scan(pc) - pc;  // lefts before word `lane`: ranks need no scan later
     if (lane == 0) {
-      rec[32] = atomicAdd(&cursors[2 * slot], nl);
-      rec[33] = atomicAdd(&cursors[2 * slot + 1], nv - nl);
+      rec[64] = atomicAdd(&cursors[2 * slot], nl);
+      rec[65] = atomicAdd(&cursors[2 * slot + 1], nv - nl);
     }
   }
 }
@@ -1032,7 +1034,7 @@ struct MoveCursor {
 };
 
 constexpr int kLabelStage = 1056;                               // 1024 labels + alignment slack
-constexpr int kStage2Bytes = kStageBytes + kLabelStage + 160;   // + 144-byte unit record, 16-byte multiple
+constexpr int kStage2Bytes = kStageBytes + kLabelStage + kMetaWords * 4;  // + unit record (272 B), 16-byte multiple
 
 __host__ __device__ inline HistGeom move_geom(int FT, int B, int C) {
   HistGeom g;
@@ -1143,17 +1145,15 @@ __device__ void move_hist_phase(const MtbCtx& P, const MtbCtx& C, uint8_t* smem)
     const uint8_t* slab = sbuf + kStageBytes + ((uint32_t)cur.row0 & 15u);
     const uint32_t* rec = reinterpret_cast<const uint32_t*>(sbuf + kStageBytes + kLabelStage);
     // rank rows from the unit's "goes left" bits
-    const uint32_t word = rec[lane];
-    const uint32_t base_l = rec[32], base_r = rec[33];
+    const uint32_t w0 = rec[2 * w], w1 = rec[2 * w + 1];
+    const uint32_t before0 = rec[32 + 2 * w];  // lefts before word 2w (from the prepass)
+    const uint32_t base_l = rec[64], base_r = rec[65];
     uint4 xa = make_uint4(0, 0, 0, 0), xb = xa;
     uint32_t lab_a = 0, lab_b = 0;
     if (va_ok) { xa = rows[ra]; lab_a = slab[ra]; }
     if (vb_ok) { xb = rows[rb]; lab_b = slab[rb]; }
     __syncwarp();
     if (lane == 0) mbar_arrive(&empty[st]);
-    const uint32_t inc = warp_incl_scan(__popc(word));
-    const uint32_t w0 = __shfl_sync(0xffffffffu, word, 2 * w), w1 = __shfl_sync(0xffffffffu, word, 2 * w + 1);
-    const uint32_t before0 = __shfl_sync(0xffffffffu, inc, 2 * w) - __popc(w0);  // lefts before word 2w
     const uint32_t below = (1u << lane) - 1u;
     const bool la = (w0 >> lane) & 1u, lb = (w1 >> lane) & 1u;
     const uint32_t lefts_a = before0 + __popc(w0 & below);

@@ -417,7 +417,7 @@ class TreeBuilder:
         if self.fuse_partition:
             max_units = data.n_cap // 1024 + m_cap + 2
             self.part_child = z(m_cap)
-            self.mask_words = z(max_units * 36)  # 144-byte unit records (32 bit words + 2 bases + pad)
+            self.mask_words = z(max_units * 68)  # 272-byte unit records (32 bit words, 32 prefixes, 2 bases, pad)
         self._ctx_prev = None
         self._alloc_tree(self.node_cap)
 
