@@ -49,27 +49,77 @@ def parse():
 
 # ----------------------------------------------------------------------------- clocks
 class ClockSampler:
+    """SM clock + throttle reasons sampled DURING the timed region.
+
+    Uses NVML in-process (a thread polling two cheap queries every few milliseconds).  Spawning
+    ``nvidia-smi`` instead was measured to disturb short multi-GPU timed regions: its start-up
+    enumerates every GPU of the box and its polling takes driver locks, which stalls the
+    cooperative launches of all eight ranks (10 ms fits were reported as 30+ ms).  ``nvidia-smi``
+    remains the fallback when NVML cannot be imported.
+    """
+
     QUERY = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
              "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
 
     def __init__(self, gpu_index: int = 0):
-        self.proc = None
         self.gpu = gpu_index
+        self.proc = None
+        self.nvml = None
+        self.samples = []
         self.path = f"/tmp/mtb_clocks_{os.getpid()}.csv"
+        try:
+            import pynvml
+
+            pynvml.nvmlInit()
+            self.nvml = pynvml
+            self.handle = pynvml.nvmlDeviceGetHandleByIndex(self._physical_index(gpu_index))
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.handle, pynvml.NVML_CLOCK_SM))
+        except Exception:  # noqa: BLE001
+            self.nvml = None
+
+    @staticmethod
+    def _physical_index(i: int) -> int:
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        if vis:
+            try:
+                return int(vis.split(",")[i])
+            except (ValueError, IndexError):
+                pass
+        return i
+
+    def _poll(self):
+        nv = self.nvml
+        while not self._stop.is_set():
+            try:
+                mhz = float(nv.nvmlDeviceGetClockInfo(self.handle, nv.NVML_CLOCK_SM))
+                try:
+                    mask = int(nv.nvmlDeviceGetCurrentClocksEventReasons(self.handle))
+                except Exception:  # noqa: BLE001  (older bindings)
+                    mask = int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.handle))
+                self.samples.append((mhz, mask))
+            except Exception:  # noqa: BLE001
+                pass
+            self._stop.wait(0.005)
 
     def start(self):
+        if self.nvml is not None:
+            import threading
+
+            self._stop = threading.Event()
+            self.thread = threading.Thread(target=self._poll, daemon=True)
+            self.thread.start()
+            return
         try:
             self.fh = open(self.path, "w")
             self.proc = subprocess.Popen(
-                ["nvidia-smi", f"--query-gpu={self.QUERY}", "--format=csv,noheader,nounits", "-lms", "20",
+                ["nvidia-smi", f"--query-gpu={self.QUERY}", "--format=csv,noheader,nounits", "-lms", "100",
                  "-i", str(self.gpu)], stdout=self.fh, stderr=subprocess.DEVNULL)
-        except Exception:
+        except Exception:  # noqa: BLE001
             self.proc = None
             return
-        # nvidia-smi needs a moment to start: wait for its first line so that samples fall
-        # inside the (possibly very short) timed region rather than after it
-        t0 = time.time()
+        t0 = time.time()  # wait for nvidia-smi's first line so its start-up is outside the timed region
         while time.time() - t0 < 3.0:
             try:
                 if os.path.getsize(self.path) > 0:
@@ -79,13 +129,21 @@ class ClockSampler:
             time.sleep(0.01)
 
     def stop(self):
+        if self.nvml is not None:
+            self._stop.set()
+            self.thread.join(timeout=2)
+            if not self.samples:
+                return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": ["no samples"], "source": "nvml"}
+            reasons = sorted({name for _, m in self.samples for bit, name in self.REASONS.items() if m & bit})
+            return {"sm_mhz": statistics.median(v for v, _ in self.samples), "sm_max_mhz": self.max_mhz,
+                    "reasons": reasons, "samples": len(self.samples), "source": "nvml"}
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         time.sleep(0.03)
         self.proc.terminate()
         try:
             self.proc.wait(timeout=5)
-        except Exception:
+        except Exception:  # noqa: BLE001
             self.proc.kill()
         self.fh.close()
         sm, mx, reasons = [], [], set()
@@ -107,7 +165,8 @@ class ClockSampler:
             pass
         if not sm:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
-        return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm)}
+        return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm),
+                "source": "nvidia-smi"}
 
 
 # ------------------------------------------------------------------------------ ours
@@ -165,10 +224,10 @@ def run_ours(a):
         torch.cuda.synchronize()
 
     def timed(fit_fn, steps, warmup, sample_clocks):
+        sampler = ClockSampler(local) if (sample_clocks and rank == 0) else None  # NVML init before warm-up
         for _ in range(warmup):
             fit_fn()
         barrier()
-        sampler = ClockSampler(local) if (sample_clocks and rank == 0) else None
         if sampler:
             sampler.start()
         l0 = cuda_engine.KERNEL_LAUNCHES["count"]
