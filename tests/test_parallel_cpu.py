@@ -120,6 +120,8 @@ deep = ParallelDecisionTreeClassifier(device="cpu", handoff_rows=60).fit(iris.da
 assert deep.export_text() == DecisionTreeClassifier(device="cpu").fit(iris.data, iris.target).export_text()
 sub = clf._get_cyclic_dist(clf.WORLD_COMM, n_blocks=2)
 assert sub.size == 1
+meta = clf.WORLD_COMM.allgather_ints([dist.get_rank(), 7])
+assert meta.tolist() == [[0, 7], [1, 7]]
 if dist.get_rank() == 0:
     print("GLOO_OK", clf.score(iris.data, iris.target))
 dist.destroy_process_group()
