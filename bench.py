@@ -391,9 +391,24 @@ def run_reference(a):
         }))
 
 
+def _shutdown_process_groups():
+    """Leave cleanly: exiting with live gloo sub-groups (the shim's ``Split``) can abort a rank at teardown."""
+    try:
+        import torch.distributed as dist
+
+        if dist.is_available() and dist.is_initialized():
+            dist.barrier()
+            dist.destroy_process_group()
+    except Exception:  # noqa: BLE001
+        pass
+
+
 if __name__ == "__main__":
     args = parse()
     if args.impl == "reference":
-        run_reference(args)
+        try:
+            run_reference(args)
+        finally:
+            _shutdown_process_groups()
     else:
         run_ours(args)
