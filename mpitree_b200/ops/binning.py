@@ -164,10 +164,11 @@ def _quantile_edges(uniques: np.ndarray, col: np.ndarray, max_bins: int) -> np.n
     if col.dtype == object:
         idx = np.linspace(0, len(uniques) - 1, max_bins).round().astype(np.int64)
         return uniques[np.unique(idx)]
+    # "higher" order statistics (every edge is an actual data value): element ceil(q (n-1)) of the
+    # sorted column, which is what np.quantile(..., method="higher") returns, without its overhead
     qs = np.linspace(0.0, 1.0, max_bins + 1)[1:]
-    # 'higher' keeps every edge an actual data value
-    e = np.quantile(col, qs, method="higher")
-    e = np.unique(e)
+    pos = np.ceil(qs * (len(col) - 1)).astype(np.int64)
+    e = np.unique(np.partition(col, np.unique(pos))[pos])
     if e[-1] < uniques[-1]:
         e[-1] = uniques[-1]
     return e.astype(col.dtype, copy=False)

@@ -232,12 +232,13 @@ def _level_histograms(codes, y, slot, n_slots, B, C, comm) -> np.ndarray:
     hist = np.zeros((n_slots, F, B, C), dtype=np.int64)
     rows = np.flatnonzero(slot >= 0)
     if rows.size:
-        base = (slot[rows].astype(np.int64) * F) * (B * C) + y[rows]
+        # one bincount per feature over that feature's (slot, bin, class) cells only
+        base = slot[rows].astype(np.int64) * (B * C) + y[rows]
         sub = codes[rows]
-        flat = hist.reshape(-1)
+        cells = n_slots * B * C
         for f in range(F):
-            idx = base + (f * B + sub[:, f].astype(np.int64)) * C
-            flat += np.bincount(idx, minlength=flat.size)
+            idx = base + sub[:, f].astype(np.int64) * C
+            hist[:, f] = np.bincount(idx, minlength=cells).reshape(n_slots, B, C)
     if comm is not None and comm.size > 1:
         hist = comm.allreduce_sum(hist)
     return hist
