@@ -48,6 +48,9 @@ from ._base import Node
 
 __all__ = ["DecisionTreeClassifier", "ParallelDecisionTreeClassifier"]
 
+#: replicated inputs with at most this many rows are fitted redundantly on every rank (no messages)
+REPLICATED_SERIAL_ROWS = 4096
+
 
 def _is_torch_tensor(x) -> bool:
     return type(x).__module__.startswith("torch") and hasattr(x, "is_cuda")
@@ -429,6 +432,8 @@ class ParallelDecisionTreeClassifier(DecisionTreeClassifier):
         self.comm = comm
 
     def _communicator(self):
+        if getattr(self, "_solo", False):
+            return None  # tiny replicated problem: no communication (see ``fit``)
         return self.comm if self.comm is not None else _comm.world()
 
     def _get_cyclic_dist(self, comm=None, *, n_blocks: int = 1):
@@ -461,6 +466,23 @@ class ParallelDecisionTreeClassifier(DecisionTreeClassifier):
             self.__dict__.pop("tree_", None)
             self.flat_tree_ = self._fit_flat(X, y, comm=comm)
             return self
+        if (
+            self.data_layout == "replicated"
+            and comm.size > 1
+            and not _is_torch_tensor(X)
+            and self.handoff_rows is None  # an explicit hand-off size asks for the cooperative path
+            and np.shape(X)[0] <= REPLICATED_SERIAL_ROWS
+        ):
+            # Tiny replicated problem: every rank already holds all rows, so each one simply builds
+            # the (deterministic, identical) tree itself.  This is the reference's own behaviour at
+            # the top of its recursion (redundant split search on every rank, ``:408-419``) and
+            # costs no communication at all.
+            serial = DecisionTreeClassifier.fit
+            self._solo = True
+            try:
+                return serial(self, X, y)
+            finally:
+                self._solo = False
         return super().fit(X, y)
 
     def _make_tree(self, X, y, *, parent=None, depth=0, comm=None):
