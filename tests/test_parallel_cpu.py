@@ -116,6 +116,8 @@ clf = ParallelDecisionTreeClassifier(max_depth=3, device="cpu").fit(iris.data, i
 assert clf.WORLD_SIZE == 2 and clf.WORLD_RANK == dist.get_rank()
 want = DecisionTreeClassifier(max_depth=3, device="cpu").fit(iris.data, iris.target).export_text()
 assert clf.export_text() == want, clf.export_text()
+coop = ParallelDecisionTreeClassifier(max_depth=3, device="cpu", handoff_rows=0).fit(iris.data, iris.target)
+assert coop.export_text() == want  # row-sharded histograms + all-reduce on every level
 deep = ParallelDecisionTreeClassifier(device="cpu", handoff_rows=60).fit(iris.data, iris.target)
 assert deep.export_text() == DecisionTreeClassifier(device="cpu").fit(iris.data, iris.target).export_text()
 sub = clf._get_cyclic_dist(clf.WORLD_COMM, n_blocks=2)
