@@ -77,3 +77,27 @@ def test_stitch_arrays_equals_full_tree(iris):
     assert merged.n_nodes == full.n_nodes
     for k in ("feature", "counts", "left", "right", "depth", "parent"):
         assert np.array_equal(getattr(merged, k), getattr(full, k)), k
+
+
+def test_flat_tree_apply_codes_and_object_columns():
+    from mpitree_b200.ops.binning import BinMapper
+
+    X = np.array([["b", 3.0], ["a", 1.0], ["c", 2.0], ["a", 3.0], ["c", 1.0], ["b", 2.0]], dtype=object)
+    y = np.array([1, 0, 2, 0, 2, 1])
+    clf = DecisionTreeClassifier(device="cpu").fit(X, y)
+    assert clf.engine_ == "cpu" and clf.predict(X).tolist() == y.tolist()
+    mapper = clf.bin_mapper_
+    assert mapper.edges[0].tolist() == ["a", "b", "c"]  # ordinal codes in sorted order
+    codes = mapper.transform(X)
+    assert np.array_equal(clf.flat_tree_.apply_codes(codes), clf.apply(X))
+    # unseen category falls into the bin of the next larger known value
+    assert BinMapper.transform(mapper, np.array([["bb", 2.0]], dtype=object))[0, 0] == 2
+
+
+def test_assign_owners_edge_cases():
+    from mpitree_b200.parallel.handoff import assign_owners, default_handoff_rows
+
+    assert assign_owners([], 4) == []
+    assert assign_owners([5], 1) == [0]
+    assert sorted(assign_owners([1, 1, 1, 1], 4)) == [0, 1, 2, 3]
+    assert default_handoff_rows(64, 256, 10, 1) == 0 and default_handoff_rows(64, 256, 10, 8) == 10240
