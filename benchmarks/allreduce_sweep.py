@@ -1,5 +1,8 @@
 """u32 histogram all-reduce sweep 4 KB - 256 MB: peer one-shot / two-shot vs ncclAllReduce.
 
+``MTB_SWEEP_NVLS=1`` adds the in-switch variant (multimem.ld_reduce / multimem.st over a multicast
+mapping; staged until it has run on hardware) as a fourth column.
+
 Run under torchrun, one rank per GPU.  Times are CUDA-event device times, max over ranks;
 bus bandwidth uses the usual all-reduce convention 2 (P-1)/P x bytes / time.
 """
@@ -37,7 +40,8 @@ def main():
     rank, world = comm.rank, comm.size
     dev = torch.device("cuda", torch.cuda.current_device())
     max_bytes = int(os.environ.get("MTB_SWEEP_MAX", 256 << 20))
-    ar = PeerAllReduce(comm, max_bytes // 4)
+    use_nvls = os.environ.get("MTB_SWEEP_NVLS") == "1"
+    ar = PeerAllReduce(comm, max_bytes // 4, nvls=use_nvls)
     rows = []
     size = 4 << 10
     while size <= max_bytes:
@@ -47,7 +51,7 @@ def main():
         want = x.clone()
         dist.all_reduce(want)
         ok = []
-        for algo in (0, 1):
+        for algo in (0, 1, 2) if use_nvls else (0, 1):
             ar.launch(n, algo)
             torch.cuda.synchronize()
             ok.append(bool(torch.equal(ar.result_view(n), want)))
@@ -56,14 +60,16 @@ def main():
         t_nccl = timed(lambda: dist.all_reduce(y), iters, dev)
         t_one = timed(lambda: ar.launch(n, 0), iters, dev) if size <= (64 << 20) else float("nan")
         t_two = timed(lambda: ar.launch(n, 1), iters, dev)
+        t_nvls = timed(lambda: ar.launch(n, 2), iters, dev) if use_nvls else float("nan")
         bus = lambda ms: 2 * (world - 1) / world * size / (ms * 1e-3) / 1e9  # noqa: E731
         rows.append({"bytes": size, "nccl_us": t_nccl * 1e3, "oneshot_us": t_one * 1e3, "twoshot_us": t_two * 1e3,
                      "nccl_busbw_GBs": bus(t_nccl), "oneshot_busbw_GBs": bus(t_one), "twoshot_busbw_GBs": bus(t_two),
-                     "correct": all(ok)})
+                     "nvls_us": t_nvls * 1e3, "nvls_busbw_GBs": bus(t_nvls), "correct": all(ok)})
         if rank == 0:
             r = rows[-1]
             print(f"{size:>10d} B  nccl {r['nccl_us']:9.1f} us  one-shot {r['oneshot_us']:9.1f} us  two-shot {r['twoshot_us']:9.1f} us"
-                  f"  busbw nccl/1s/2s = {r['nccl_busbw_GBs']:7.1f} {r['oneshot_busbw_GBs']:7.1f} {r['twoshot_busbw_GBs']:7.1f} GB/s  ok={r['correct']}",
+                  f"  busbw nccl/1s/2s = {r['nccl_busbw_GBs']:7.1f} {r['oneshot_busbw_GBs']:7.1f} {r['twoshot_busbw_GBs']:7.1f} GB/s  ok={r['correct']}"
+                  + (f"  nvls {r['nvls_us']:9.1f} us {r['nvls_busbw_GBs']:7.1f} GB/s" if use_nvls else ""),
                   flush=True)
         size *= 4
     if rank == 0:

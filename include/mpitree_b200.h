@@ -142,6 +142,11 @@ int mtb_set_device(int device);
 int mtb_encode_float(const void* X, int dtype, int64_t n, int64_t F, int64_t ldx, const double* edges,
                      const int32_t* n_bins, uint8_t* codes, int64_t n_cap, int64_t row0,
                      unsigned long long* mismatch, void* stream);
+/* float32 rows with F % 4 == 0, ldx % 4 == 0 and a 16-byte aligned base: same codes as
+ * mtb_encode_float(dtype 0), one lane per (row, 4 features), 128-bit loads.  Opt-in
+ * (MTB_ENCODE=quads) until it has been timed on hardware.                             */
+int mtb_encode_f32_quads(const float* X, int64_t n, int64_t F, int64_t ldx, const double* edges,
+                         const int32_t* n_bins, uint8_t* codes, int64_t n_cap, int64_t row0, void* stream);
 /* uint8 input; lut: u8 [F][256] value->code, or NULL for identity.                    */
 int mtb_encode_u8(const uint8_t* X, int64_t n, int64_t F, int64_t ldx, const uint8_t* lut, uint8_t* codes,
                   int64_t n_cap, int64_t row0, void* stream);
@@ -218,6 +223,12 @@ int mtb_memset_async(void* ptr, int value, int64_t bytes, void* stream);
  * equal index synchronise through the flags.  Spins on peers: one rank per GPU.                   */
 int mtb_allreduce_u32(int algo, int rank, int world, void* const* bufs, void* const* flags, int64_t count,
                       int64_t cap, uint32_t epoch, uint32_t* out, void* stream);
+/* Same contract, reduced inside the NVSwitch: the symmetric areas must come from a VMM allocation
+ * bound to a multicast object (parallel/nvls.py) and `mc_buf` is that object's mapping (the same
+ * layout seen through one address).  Each rank sums its 1/world slice with multimem.ld_reduce and
+ * broadcasts it with multimem.st.  Staged: compiles for sm_100a, not yet run on hardware.         */
+int mtb_allreduce_u32_nvls(int rank, int world, void* const* bufs, void* const* flags, void* mc_buf, int64_t count,
+                           int64_t cap, uint32_t epoch, uint32_t* out, void* stream);
 
 #ifdef __cplusplus
 }

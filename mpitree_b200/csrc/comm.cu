@@ -110,7 +110,81 @@ __global__ void __launch_bounds__(512) k_allreduce_twoshot(const __grid_constant
   cta_peer_barrier(a, a.epoch + 2);  // the slices of all peers' CTAs of this index have landed
 }
 
+// ---- NVLS variant (staged: compiled and inspected, not yet run on hardware) ----------------------
+// The symmetric area is also mapped through an NVSwitch multicast object (parallel/nvls.py), so one
+// address names the same word on every rank.  A rank takes its slice, asks the switch for the sum
+// over all ranks (multimem.ld_reduce, SASS LDGMC.ADD) and writes it to every rank's result area
+// with one multicast store.  Per GPU this moves bytes/P in and bytes/P out instead of
+// (P-1)/P x bytes each way.  Integer ld_reduce is scalar only, so counts travel as u64 pairs:
+// exact while every global sum is below 2^32, which the u32 histograms require anyway.
+__device__ __forceinline__ uint64_t mm_ld_reduce_add_u64(const uint64_t* mc) {
+  uint64_t v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.u64 %0, [%1];" : "=l"(v) : "l"(mc) : "memory");
+  return v;
+}
+__device__ __forceinline__ void mm_st_u64(uint64_t* mc, uint64_t v) {
+  asm volatile("multimem.st.relaxed.sys.global.u64 [%0], %1;" ::"l"(mc), "l"(v) : "memory");
+}
+
+__global__ void __launch_bounds__(512) k_allreduce_nvls(const __grid_constant__ ArArgs a, uint32_t* mc) {
+  cta_peer_barrier(a, a.epoch + 1);  // every rank's input is in place
+  const int64_t n2 = (a.count + 1) / 2;  // 8-byte units (the pad word of an odd count is readable: cap % 4 == 0)
+  const int64_t per = (n2 + a.world - 1) / a.world;
+  const int64_t lo = per * a.rank, hi = min(n2, lo + per);
+  const uint64_t* in = reinterpret_cast<const uint64_t*>(mc);
+  uint64_t* res = reinterpret_cast<uint64_t*>(mc + a.cap);
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  int64_t i = lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  for (; i + 3 * stride < hi; i += 4 * stride) {  // four independent switch round trips in flight per lane
+    uint64_t v[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) v[j] = mm_ld_reduce_add_u64(in + i + j * stride);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) mm_st_u64(res + i + j * stride, v[j]);
+  }
+  for (; i < hi; i += stride) mm_st_u64(res + i, mm_ld_reduce_add_u64(in + i));
+  cta_peer_barrier(a, a.epoch + 2);  // the slices of all peers' CTAs of this index have landed
+}
+
 }  // namespace
+
+extern "C" int mtb_allreduce_u32_nvls(int rank, int world, void* const* bufs, void* const* flags, void* mc_buf,
+                                      int64_t count, int64_t cap, uint32_t epoch, uint32_t* out, void* stream) {
+  if (world < 1 || world > MTB_MAX_WORLD || mc_buf == nullptr) {
+    mtb_set_error("allreduce_nvls", "world size must be in [1, 16] and the multicast pointer non-null", __FILE__,
+                  __LINE__);
+    return -2;
+  }
+  if (count > cap || (cap % 4) != 0) {
+    mtb_set_error("allreduce_nvls", "count exceeds the symmetric buffer capacity (or capacity not a multiple of 4)",
+                  __FILE__, __LINE__);
+    return -2;
+  }
+  ArArgs a;
+  for (int q = 0; q < world; ++q) {
+    a.bufs[q] = (uint32_t*)bufs[q];
+    a.flags[q] = (uint32_t*)flags[q];
+  }
+  a.rank = rank;
+  a.world = world;
+  a.count = count;
+  a.cap = cap;
+  a.epoch = epoch;
+  a.out = out;
+  int dev = 0, sms = 0;
+  MTB_CHECK(cudaGetDevice(&dev));
+  MTB_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  // this rank only touches count / world words: size the grid for its slice (same on every rank)
+  int64_t want = ((count + 1) / 2 / world + 511) / 512;
+  int cap_ctas = 2 * sms < kArMaxCtas ? 2 * sms : kArMaxCtas;
+  int blocks = (int)(want < 1 ? 1 : (want > cap_ctas ? cap_ctas : want));
+  k_allreduce_nvls<<<blocks, 512, 0, (cudaStream_t)stream>>>(a, (uint32_t*)mc_buf);
+  MTB_CHECK(cudaGetLastError());
+  if (out != nullptr && out != a.bufs[rank] + cap)
+    MTB_CHECK(cudaMemcpyAsync(out, a.bufs[rank] + cap, (size_t)count * 4, cudaMemcpyDeviceToDevice,
+                              (cudaStream_t)stream));
+  return 0;
+}
 
 extern "C" int mtb_allreduce_u32(int algo, int rank, int world, void* const* bufs, void* const* flags, int64_t count,
                                  int64_t cap, uint32_t epoch, uint32_t* out, void* stream) {

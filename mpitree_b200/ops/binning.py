@@ -15,7 +15,7 @@ still reported as a data value (``decision_tree.py:88-91`` returns
 * string / object columns          -> ordinal codes in sorted-unique order, the
   same order Python's ``<=`` gives the reference on object arrays.
 
-The CUDA counterpart (``mpitree_b200/csrc/binning.cu``) implements the encode
+The CUDA counterpart (``mpitree_b200/csrc/encode.cu``) implements the encode
 pass; edges are always computed from (a sample of) the data with the code here
 or with its device twin in :mod:`mpitree_b200.ops.cuda_engine`.
 """

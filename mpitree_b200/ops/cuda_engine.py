@@ -13,6 +13,7 @@ are reached through the C ABI in ``include/mpitree_b200.h``.
 from __future__ import annotations
 
 import ctypes
+import os
 import time
 from dataclasses import dataclass, field
 from typing import Dict, List, Optional, Tuple
@@ -181,6 +182,28 @@ class DeviceDataset:
             self._nbins = torch.from_numpy(mapper.n_bins.astype(np.int32)).to(self.device)
             self._edges_key = key
         dtype = {torch.float32: 0, torch.float64: 1}[X.dtype]
+        if (
+            os.environ.get("MTB_ENCODE") == "quads"
+            and dtype == 0
+            and mismatch is None
+            and self.n_features % 4 == 0
+            and X.stride(0) % 4 == 0
+            and X.data_ptr() % 16 == 0
+        ):
+            _call(
+                "mtb_encode_f32_quads",
+                ctypes.c_void_p(_p(X)),
+                ctypes.c_int64(X.shape[0]),
+                ctypes.c_int64(self.n_features),
+                ctypes.c_int64(X.stride(0)),
+                ctypes.c_void_p(_p(self._edges)),
+                ctypes.c_void_p(_p(self._nbins)),
+                ctypes.c_void_p(_p(self.codes[self.cur])),
+                ctypes.c_int64(self.n_cap),
+                ctypes.c_int64(row0),
+                _stream_ptr(),
+            )
+            return
         _call(
             "mtb_encode_float",
             ctypes.c_void_p(_p(X)),

@@ -9,32 +9,49 @@ from __future__ import annotations
 
 import ctypes
 
-__all__ = ["PeerAllReduce"]
+__all__ = ["PeerAllReduce", "ALGO_ONESHOT", "ALGO_TWOSHOT", "ALGO_NVLS"]
+
+
+ALGO_ONESHOT, ALGO_TWOSHOT, ALGO_NVLS = 0, 1, 2
 
 
 class PeerAllReduce:
-    FLAG_BYTES = 512 * 16 * 4  # one row of world flags per CTA index
-
     """Symmetric buffers + flags for repeated all-reduces of up to ``max_count`` u32 values.
 
     Producers can write straight into :meth:`input_view` (zero-copy); :meth:`all_reduce`
     copies from an ordinary tensor first.
+
+    ``nvls=True`` (staged, not yet run on hardware) places the buffers in an
+    :class:`mpitree_b200.parallel.nvls.NvlsRegion` so that ``algo=2`` can reduce inside the
+    NVSwitch; algorithms 0 and 1 work on either kind of region.
     """
 
-    def __init__(self, comm, max_count: int):
+    FLAG_BYTES = 512 * 16 * 4  # one row of world flags per CTA index
+
+    def __init__(self, comm, max_count: int, nvls: bool = False):
         import torch
 
         from ..ops import _lib as L
-        from .symm import IpcRegion
 
         self.L, self.lib = L, L.load()
         self.comm = comm
         self.world, self.rank = comm.size, comm.rank
         self.cap = ((int(max_count) + 3) // 4) * 4
-        self.region = IpcRegion(2 * self.cap * 4 + self.FLAG_BYTES, comm)
+        nbytes = 2 * self.cap * 4 + self.FLAG_BYTES
+        if nvls:
+            from .nvls import NvlsRegion
+
+            self.region = NvlsRegion(nbytes, comm)
+            self._mem = self.region.as_tensor()
+            self._mc = int(self.region.mc_ptr)
+        else:
+            from .symm import IpcRegion
+
+            self.region = IpcRegion(nbytes, comm)
+            self._mem = self.region.buf.as_tensor()
+            self._mc = 0
         self._bufs = (ctypes.c_void_p * 16)(*[p for p in self.region.ptrs])
         self._flags = (ctypes.c_void_p * 16)(*[p + 2 * self.cap * 4 for p in self.region.ptrs])
-        self._mem = self.region.buf.as_tensor()
         self.epoch = 0
         self.torch = torch
 
@@ -50,6 +67,17 @@ class PeerAllReduce:
         if out is None and algo == 0:  # one-shot writes its sums straight to the destination
             out = self.result_view(count)
         dst = out.data_ptr() if out is not None else 0
+        if algo == ALGO_NVLS:
+            if not self._mc:
+                raise ValueError("algo=2 needs PeerAllReduce(..., nvls=True)")
+            rc = self.lib.mtb_allreduce_u32_nvls(
+                ctypes.c_int(self.rank), ctypes.c_int(self.world), self._bufs, self._flags, ctypes.c_void_p(self._mc),
+                ctypes.c_int64(count), ctypes.c_int64(self.cap), ctypes.c_uint32(self.epoch), ctypes.c_void_p(dst),
+                ctypes.c_void_p(torch.cuda.current_stream().cuda_stream),
+            )
+            self.epoch = (self.epoch + 2) & 0x7FFFFFFF
+            self.L.check(rc, "mtb_allreduce_u32_nvls")
+            return
         rc = self.lib.mtb_allreduce_u32(
             ctypes.c_int(algo), ctypes.c_int(self.rank), ctypes.c_int(self.world), self._bufs, self._flags,
             ctypes.c_int64(count), ctypes.c_int64(self.cap), ctypes.c_uint32(self.epoch), ctypes.c_void_p(dst),

@@ -103,6 +103,33 @@ def test_stitch_renumbers_breadth_first(iris):
     assert merged.structurally_equal(full)
 
 
+def _fd_rank(comm):
+    import tempfile
+
+    from mpitree_b200.parallel.fdpass import allgather_fds
+
+    files = []
+    for k in range(comm.rank % 3):  # ranks contribute 0, 1 or 2 descriptors
+        fh = tempfile.TemporaryFile()
+        fh.write(f"rank{comm.rank}-{k}".encode())
+        fh.flush()
+        files.append(fh)
+    got = allgather_fds(comm, [fh.fileno() for fh in files], "t")
+    out = []
+    for fds in got:
+        out.append([os.pread(fd, 64, 0).decode() for fd in fds])
+        for fd in fds:
+            os.close(fd)
+    comm.barrier()
+    return out
+
+
+@pytest.mark.parametrize("world", [1, 2, 5, 16])
+def test_descriptor_allgather_thread_ranks(world):
+    want = [[f"rank{q}-{k}" for k in range(q % 3)] for q in range(world)]
+    assert run_threaded(world, _fd_rank) == [want] * world
+
+
 _WORKER = r"""
 import os, sys
 sys.path.insert(0, os.environ["REPO"])
@@ -124,6 +151,15 @@ sub = clf._get_cyclic_dist(clf.WORLD_COMM, n_blocks=2)
 assert sub.size == 1
 meta = clf.WORLD_COMM.allgather_ints([dist.get_rank(), 7])
 assert meta.tolist() == [[0, 7], [1, 7]]
+# descriptors cross the process boundary (what the VMM / multicast handle exchange relies on)
+import tempfile
+from mpitree_b200.parallel.fdpass import allgather_fds
+with tempfile.TemporaryFile() as fh:
+    fh.write(b"from rank %d" % dist.get_rank()); fh.flush()
+    got = allgather_fds(clf.WORLD_COMM, [fh.fileno()], "test")
+assert [os.pread(g[0], 32, 0) for g in got] == [b"from rank 0", b"from rank 1"]
+for g in got:
+    os.close(g[0])
 if dist.get_rank() == 0:
     print("GLOO_OK", clf.score(iris.data, iris.target))
 dist.destroy_process_group()
