@@ -126,7 +126,10 @@ typedef struct MtbCtx {
    *             unit, 2 pad words (272 B, fetched by TMA next to the rows)
    * unit_base : unused (kept for layout compatibility)                                        */
   int64_t part_child, mask_words, unit_base;
-  int64_t reserved[1];
+  /* shared-memory histogram tile: 0 = [f][B][C] (default), 1 = [B*C][16] interleaved by feature
+   * (FT == 16 only; opt-in until it has been timed on hardware).  Slabs in global memory are
+   * [f][B][C] either way.                                                                      */
+  int64_t tile_layout;
 } MtbCtx;
 
 const char* mtb_last_error(void);

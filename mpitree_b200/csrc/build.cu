@@ -201,10 +201,40 @@ struct UnitCursor {
   }
 };
 
+// Interleaved-tile histogram update of one row (16 codes in `x`, label `lab`).  Lane l takes the
+// features in the order l, l+1, ... (mod 16): in every one of the 16 instructions the 32 lanes of
+// a warp address 16 different features, two lanes each, and a feature's counters live in banks
+// f and 16 + f only.  Worst case per instruction is therefore a 2-way conflict (the two lanes of
+// a feature hitting the same bank with different cells) instead of the ~3.6-way average that
+// random (bin, class) addresses give the [f][B][C] tile.  The row's 16 bytes are rotated once by
+// the lane's offset so that step k reads the statically indexed byte k.
+__device__ __forceinline__ void tile_count_il(uint32_t* tile, uint4 x, uint32_t lab, int C, int lane) {
+  const int rot = lane & 15;
+  uint32_t w0 = x.x, w1 = x.y, w2 = x.z, w3 = x.w;
+  if (rot & 4) { const uint32_t t = w0; w0 = w1; w1 = w2; w2 = w3; w3 = t; }
+  if (rot & 8) { uint32_t t = w0; w0 = w2; w2 = t; t = w1; w1 = w3; w3 = t; }
+  const uint32_t sel = 0x3210u + 0x1111u * (uint32_t)(rot & 3);
+  const uint4 y = make_uint4(__byte_perm(w0, w1, sel), __byte_perm(w1, w2, sel), __byte_perm(w2, w3, sel),
+                             __byte_perm(w3, w0, sel));  // byte k of y = byte (k + rot) mod 16 of x
+  uint32_t* base = tile + lab * 16u;
+  const int cell_stride = C * 16;
+#pragma unroll
+  for (int k = 0; k < 16; ++k)
+    atomicAdd(base + (int)code_byte(y, k) * cell_stride + ((k + rot) & 15), 1u);
+}
+
 // Flush a finished [FT][B][C] tile into the slot's slab.  When this CTA processed every
 // row of the tile it simply stores it (128-bit, no atomics, no zero-skipping); otherwise
 // several CTAs share the tile and merge with red.global.add.
-template <int FT>
+//
+// IL (interleaved tile, FT == 16 only, opt-in): the tile is kept as [B*C][16] with the feature
+// index in the low address bits, so the 16 features own two banks each and the lanes of one
+// histogram instruction, which work on 16 different features (see tile_count_il), cannot collide
+// across features.  The slab in global memory keeps the [f][B][C] layout, so the flush
+// transposes: a warp takes 32 (bin, class) cells x 16 features at a time, reads them with four
+// conflict-free 128-bit loads per lane and writes, per store instruction, four fully used
+// 32-byte sectors (8 consecutive cells of 4 features).
+template <int FT, bool IL = false>
 __device__ void flush_tile(const MtbCtx& ctx, uint32_t* tile, int slot, int gs, int tid, bool exclusive) {
   View v(ctx);
   const int S = 16 / FT;
@@ -212,6 +242,32 @@ __device__ void flush_tile(const MtbCtx& ctx, uint32_t* tile, int slot, int gs, 
   const int64_t f0 = (int64_t)g * 16 + (int64_t)s * FT;
   const int words = FT * (int)ctx.B * (int)ctx.C;
   uint32_t* dst = v.hist_cur() + (int64_t)slot * v.slab_words() + f0 * ctx.B * ctx.C;
+  if constexpr (IL) {
+    static_assert(FT == 16, "the interleaved tile covers one whole feature group");
+    const int BC = (int)ctx.B * (int)ctx.C;
+    const int lane = tid & 31, w = tid >> 5;
+    const int q = lane & 3, r = lane >> 2;
+    const uint4 zero = make_uint4(0, 0, 0, 0);
+    for (int c0 = w * 32; c0 < BC; c0 += kConsumerWarps * 32) {
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int cell = c0 + r + 8 * i;
+        if (cell < BC) {
+          uint4* src = reinterpret_cast<uint4*>(tile + cell * 16 + 4 * q);
+          const uint4 x = *src;
+          *src = zero;
+          const uint32_t e[4] = {x.x, x.y, x.z, x.w};
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            uint32_t* d = dst + (int64_t)(4 * q + j) * BC + cell;
+            if (exclusive) *d = e[j];
+            else if (e[j]) red_add_u32(d, e[j]);
+          }
+        }
+      }
+    }
+    return;
+  }
   if (exclusive) {
     uint4* d4 = reinterpret_cast<uint4*>(dst);
     uint4* t4 = reinterpret_cast<uint4*>(tile);
@@ -231,7 +287,7 @@ __device__ void flush_tile(const MtbCtx& ctx, uint32_t* tile, int slot, int gs, 
   }
 }
 
-template <int FT>
+template <int FT, bool IL = false>
 __device__ void hist_phase(const MtbCtx& ctx, uint8_t* smem) {
   View v(ctx);
   const int B = (int)ctx.B, C = (int)ctx.C;
@@ -292,7 +348,7 @@ __device__ void hist_phase(const MtbCtx& ctx, uint8_t* smem) {
       if (cur.slot != cur_slot || cur.gs != cur_gs) {
         if (cur_slot >= 0) {
           named_bar_sync(1, kConsumers);
-          flush_tile<FT>(ctx, tile, cur_slot, cur_gs, tid, cur_excl);
+          flush_tile<FT, IL>(ctx, tile, cur_slot, cur_gs, tid, cur_excl);
           named_bar_sync(1, kConsumers);
         }
         cur_slot = cur.slot;
@@ -313,27 +369,32 @@ __device__ void hist_phase(const MtbCtx& ctx, uint8_t* smem) {
       if (r_b < nrows) vb = rows[r_b];
       __syncwarp();
       if (lane_id() == 0) mbar_arrive(&empty[st]);  // tile is in registers: release the stage
-      if (r_a < nrows) {
+      if constexpr (IL) {
+        if (r_a < nrows) tile_count_il(tile, va, lab_a, C, tid);
+        if (r_b < nrows) tile_count_il(tile, vb, lab_b, C, tid);
+      } else {
+        if (r_a < nrows) {
 #pragma unroll
-        for (int k = 0; k < FT; ++k) atomicAdd(&tile[(k * B + (int)code_byte(va, sub + k)) * C + (int)lab_a], 1u);
-      }
-      if (r_b < nrows) {
+          for (int k = 0; k < FT; ++k) atomicAdd(&tile[(k * B + (int)code_byte(va, sub + k)) * C + (int)lab_a], 1u);
+        }
+        if (r_b < nrows) {
 #pragma unroll
-        for (int k = 0; k < FT; ++k) atomicAdd(&tile[(k * B + (int)code_byte(vb, sub + k)) * C + (int)lab_b], 1u);
+          for (int k = 0; k < FT; ++k) atomicAdd(&tile[(k * B + (int)code_byte(vb, sub + k)) * C + (int)lab_b], 1u);
+        }
       }
       if (++st == stages) { st = 0; ph ^= 1; }
     }
     if (cur_slot >= 0) {
       named_bar_sync(1, kConsumers);
-      flush_tile<FT>(ctx, tile, cur_slot, cur_gs, tid, cur_excl);
+      flush_tile<FT, IL>(ctx, tile, cur_slot, cur_gs, tid, cur_excl);
     }
   }
 }
 
-template <int FT>
+template <int FT, bool IL = false>
 __global__ void __launch_bounds__(kHistThreads, 1) k_hist(const __grid_constant__ MtbCtx ctx) {
   extern __shared__ __align__(128) uint8_t smem[];
-  hist_phase<FT>(ctx, smem);
+  hist_phase<FT, IL>(ctx, smem);
 }
 
 // ------------------------------------------------------------------------ gain
@@ -1047,7 +1108,7 @@ __host__ __device__ inline HistGeom move_geom(int FT, int B, int C) {
   return g;
 }
 
-template <int FT>
+template <int FT, bool IL = false>
 __device__ void move_hist_phase(const MtbCtx& P, const MtbCtx& C, uint8_t* smem) {
   View vp(P);
   const int B = (int)P.B, Cn = (int)P.C;
@@ -1120,7 +1181,7 @@ __device__ void move_hist_phase(const MtbCtx& P, const MtbCtx& C, uint8_t* smem)
     if (cur.slot != cur_slot || cur.gs != cur_gs) {
       if (build_child >= 0) {
         named_bar_sync(1, kConsumers);
-        flush_tile<FT>(C, tile, build_child, cur_gs, tid, cur_excl);
+        flush_tile<FT, IL>(C, tile, build_child, cur_gs, tid, cur_excl);
         named_bar_sync(1, kConsumers);
       }
       cur_slot = cur.slot;
@@ -1174,20 +1235,25 @@ __device__ void move_hist_phase(const MtbCtx& P, const MtbCtx& C, uint8_t* smem)
       }
     }
     if (build_child >= 0) {
-      if (va_ok && (int)(!la) == build_side) {
+      if constexpr (IL) {
+        if (va_ok && (int)(!la) == build_side) tile_count_il(tile, xa, lab_a, Cn, lane);
+        if (vb_ok && (int)(!lb) == build_side) tile_count_il(tile, xb, lab_b, Cn, lane);
+      } else {
+        if (va_ok && (int)(!la) == build_side) {
 #pragma unroll
-        for (int k = 0; k < FT; ++k) atomicAdd(&tile[(k * B + (int)code_byte(xa, sub + k)) * Cn + (int)lab_a], 1u);
-      }
-      if (vb_ok && (int)(!lb) == build_side) {
+          for (int k = 0; k < FT; ++k) atomicAdd(&tile[(k * B + (int)code_byte(xa, sub + k)) * Cn + (int)lab_a], 1u);
+        }
+        if (vb_ok && (int)(!lb) == build_side) {
 #pragma unroll
-        for (int k = 0; k < FT; ++k) atomicAdd(&tile[(k * B + (int)code_byte(xb, sub + k)) * Cn + (int)lab_b], 1u);
+          for (int k = 0; k < FT; ++k) atomicAdd(&tile[(k * B + (int)code_byte(xb, sub + k)) * Cn + (int)lab_b], 1u);
+        }
       }
     }
     if (++st == stages) { st = 0; ph ^= 1; }
   }
   if (build_child >= 0) {
     named_bar_sync(1, kConsumers);
-    flush_tile<FT>(C, tile, build_child, cur_gs, tid, cur_excl);
+    flush_tile<FT, IL>(C, tile, build_child, cur_gs, tid, cur_excl);
   }
 }
 
@@ -1204,7 +1270,7 @@ __device__ __forceinline__ void stamp(const MtbCtx& ctx, int i) {
   }
 }
 
-template <int FT>
+template <int FT, bool IL = false>
 __global__ void __launch_bounds__(kHistThreads, 1) k_level_fused(const __grid_constant__ MtbCtx ctx) {
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ int smem_warp[33];
@@ -1216,7 +1282,7 @@ __global__ void __launch_bounds__(kHistThreads, 1) k_level_fused(const __grid_co
   if (blockIdx.x == 0) plan_phase(ctx, smem_warp);
   grid.sync();
   stamp(ctx, 1);
-  hist_phase<FT>(ctx, smem);
+  hist_phase<FT, IL>(ctx, smem);
   if (ctx.world > 1) {
     grid.sync();
     stamp(ctx, 2);
@@ -1240,7 +1306,7 @@ __global__ void __launch_bounds__(kHistThreads, 1) k_level_fused(const __grid_co
   stamp(ctx, 6);
 }
 
-template <int FT>
+template <int FT, bool IL = false>
 __global__ void __launch_bounds__(kHistThreads, 1) k_level_fused2(const __grid_constant__ MtbCtx P,
                                                                   const __grid_constant__ MtbCtx C) {
   extern __shared__ __align__(128) uint8_t smem[];
@@ -1255,7 +1321,7 @@ __global__ void __launch_bounds__(kHistThreads, 1) k_level_fused2(const __grid_c
   prepass_phase(P);
   grid.sync();
   stamp(C, 8);
-  move_hist_phase<FT>(P, C, smem);
+  move_hist_phase<FT, IL>(P, C, smem);
   grid.sync();
   commit_phase(P);
   if (blockIdx.x == 0 && threadIdx.x == 0) ptr_of<int>(P.scalars)[0] = ptr_of<int>(P.scalars)[1];
@@ -1305,8 +1371,19 @@ int gain_smem(const MtbCtx* ctx) { return kGainWarps * ((int)ctx->B * (int)ctx->
 
 }  // namespace
 
+// ctx->tile_layout == 1 selects the interleaved shared-memory tile (FT == 16 only; opt-in).
+static bool interleaved(const MtbCtx* ctx) { return ctx->tile_layout == 1 && ctx->FT == 16; }
+
 template <int FT>
 static int launch_hist(const MtbCtx* ctx, const HistGeom& g, cudaStream_t stream) {
+  if constexpr (FT == 16) {
+    if (interleaved(ctx)) {
+      if (set_smem(k_hist<16, true>, g.smem_bytes)) return -1;
+      k_hist<16, true><<<sm_count(), kHistThreads, g.smem_bytes, stream>>>(*ctx);
+      MTB_CHECK(cudaGetLastError());
+      return 0;
+    }
+  }
   if (set_smem(k_hist<FT>, g.smem_bytes)) return -1;
   k_hist<FT><<<sm_count(), kHistThreads, g.smem_bytes, stream>>>(*ctx);
   MTB_CHECK(cudaGetLastError());
@@ -1315,9 +1392,17 @@ static int launch_hist(const MtbCtx* ctx, const HistGeom& g, cudaStream_t stream
 
 template <int FT>
 static int launch_fused(const MtbCtx* ctx, int smem, cudaStream_t stream) {
-  if (set_smem(k_level_fused<FT>, smem)) return -1;
   MtbCtx local = *ctx;
   void* args[] = {&local};
+  if constexpr (FT == 16) {
+    if (interleaved(ctx)) {
+      if (set_smem(k_level_fused<16, true>, smem)) return -1;
+      MTB_CHECK(cudaLaunchCooperativeKernel((void*)k_level_fused<16, true>, dim3(sm_count()), dim3(kHistThreads), args,
+                                            smem, stream));
+      return 0;
+    }
+  }
+  if (set_smem(k_level_fused<FT>, smem)) return -1;
   MTB_CHECK(cudaLaunchCooperativeKernel((void*)k_level_fused<FT>, dim3(sm_count()), dim3(kHistThreads), args, smem,
                                         stream));
   return 0;
@@ -1325,9 +1410,17 @@ static int launch_fused(const MtbCtx* ctx, int smem, cudaStream_t stream) {
 
 template <int FT>
 static int launch_fused2(const MtbCtx* P, const MtbCtx* C, int smem, cudaStream_t stream) {
-  if (set_smem(k_level_fused2<FT>, smem)) return -1;
   MtbCtx p = *P, c = *C;
   void* args[] = {&p, &c};
+  if constexpr (FT == 16) {
+    if (interleaved(P)) {
+      if (set_smem(k_level_fused2<16, true>, smem)) return -1;
+      MTB_CHECK(cudaLaunchCooperativeKernel((void*)k_level_fused2<16, true>, dim3(sm_count()), dim3(kHistThreads), args,
+                                            smem, stream));
+      return 0;
+    }
+  }
+  if (set_smem(k_level_fused2<FT>, smem)) return -1;
   MTB_CHECK(cudaLaunchCooperativeKernel((void*)k_level_fused2<FT>, dim3(sm_count()), dim3(kHistThreads), args, smem,
                                         stream));
   return 0;

@@ -266,6 +266,7 @@ class BuildStats:
     reduce: str = "none"
     world: int = 1
     handed_off: int = 0
+    tile_layout: str = "planar"
 
 
 _EPOCH = {"next": 0}  # barrier epochs are monotonic for the life of the process
@@ -304,6 +305,7 @@ class TreeBuilder:
         async_levels: bool = True,
         small_rows: Optional[int] = None,
         fuse_partition: bool = True,
+        tile_layout: Optional[str] = None,
     ):
         import torch
 
@@ -367,6 +369,13 @@ class TreeBuilder:
                 break
         else:
             raise ValueError("bins x classes too large for a shared-memory histogram tile")
+        # shared-memory tile layout: "planar" = [f][B][C] (validated default); "interleaved" =
+        # [B*C][16], two banks per feature (staged, FT == 16 only; MTB_TILE=interleaved or the keyword)
+        layout = tile_layout or os.environ.get("MTB_TILE", "planar")
+        if layout not in ("planar", "interleaved"):
+            raise ValueError(f"unknown tile layout {layout!r}")
+        ctx.tile_layout = 1 if (layout == "interleaved" and self.stats.FT == 16) else 0
+        self.stats.tile_layout = "interleaved" if ctx.tile_layout else "planar"
 
         slab_words = G * 16 * B * C
         self.slab_words = slab_words

@@ -93,3 +93,31 @@ def test_nvls_allreduce_equals_nccl(tmp_path):
     res = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=300)
     assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
     assert f"NVLS_OK {world}" in res.stdout or "NVLS_UNSUPPORTED" in res.stdout
+
+
+def _same_tree(a, b):
+    assert a.n_nodes == b.n_nodes
+    for name in ("feature", "bin", "counts", "left", "right", "depth"):
+        assert np.array_equal(getattr(a, name), getattr(b, name)), name
+    assert np.array_equal(np.nan_to_num(a.gain, nan=-1.0), np.nan_to_num(b.gain, nan=-1.0))
+
+
+@pytest.mark.parametrize("shape", [(5000, 7, 3, 6), (300_000, 40, 10, 9), (1_200_000, 64, 10, 8), (60_000, 33, 2, 12)])
+@pytest.mark.parametrize("mode", [dict(fused=True), dict(fused=True, fuse_partition=False), dict(fused=False)])
+def test_interleaved_tile_equals_planar(shape, mode):
+    """Same tree, bit for bit, from the [B*C][16] shared-memory tile as from the [f][B][C] one."""
+    from mpitree_b200.ops import cuda_engine
+    from mpitree_b200.ops.cpu_engine import SplitParams
+
+    n, F, k, depth = shape
+    rng = np.random.default_rng(n + F)
+    X = rng.integers(0, 256, size=(n, F), dtype=np.uint8)
+    X[:, 1] = rng.integers(0, 3, size=n)  # a few heavily repeated codes: same-address increments
+    w = rng.normal(size=F)
+    s = X.astype(np.float64) @ w + rng.normal(scale=200, size=n)
+    y = np.digitize(s, np.quantile(s, np.linspace(0, 1, k + 1)[1:-1])).astype(np.int64)
+    params = SplitParams(max_depth=depth)
+    want, _ = cuda_engine.fit_from_host(X, y, k, params, builder_kwargs=dict(mode, tile_layout="planar"))
+    got, _ = cuda_engine.fit_from_host(X, y, k, params, builder_kwargs=dict(mode, tile_layout="interleaved"))
+    assert cuda_engine.fit_from_host.last_stats.tile_layout == "interleaved"
+    _same_tree(got, want)
