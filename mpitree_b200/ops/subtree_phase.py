@@ -249,12 +249,31 @@ def _run_subtrees(builder, lib, L, dev, mine, it_side, it_begin, it_end, depth, 
     KERNEL_LAUNCHES["count"] += 1
     L.check(rc, "mtb_subtree_build")
     torch.cuda.synchronize()
+    return _compact_records(o_nn, offs, o_feature, o_bin, o_left, o_gain, o_counts.view(total, C))
+
+
+def _compact_records(o_nn, offs, o_feature, o_bin, o_left, o_gain, o_counts) -> dict:
+    """Keep only the records the kernel wrote: item ``i`` used ``o_nn[i]`` of its ``2 rows - 1`` slots.
+
+    The output arrays are sized for the worst case (every row its own leaf); a depth-limited subtree
+    uses a small part of that, so the used records are gathered on the device and only those cross
+    PCIe (and, with several ranks, the all-gather).  Child ids are relative to the item's first
+    record, so they stay valid; ``offs`` becomes the running sum of the used counts.
+    """
+    import torch
+
+    nn_d = o_nn.to(torch.int64)
+    nn = nn_d.cpu().numpy()
+    used = int(nn.sum())
+    starts = np.concatenate([[0], np.cumsum(nn)[:-1]]).astype(np.int64)
+    shift = torch.from_numpy(np.asarray(offs, np.int64) - starts).to(o_nn.device)
+    idx = torch.repeat_interleave(shift, nn_d, output_size=used) + torch.arange(used, device=o_nn.device)
     return {
-        "offs": offs,
-        "nn": o_nn.cpu().numpy().astype(np.int64),
-        "feature": o_feature.cpu().numpy(),
-        "bin": o_bin.cpu().numpy(),
-        "left": o_left.cpu().numpy(),
-        "gain": o_gain.cpu().numpy(),
-        "counts": o_counts.cpu().numpy().view(np.uint32).reshape(total, C),
+        "offs": starts,
+        "nn": nn,
+        "feature": o_feature[idx].cpu().numpy(),
+        "bin": o_bin[idx].cpu().numpy(),
+        "left": o_left[idx].cpu().numpy(),
+        "gain": o_gain[idx].cpu().numpy(),
+        "counts": o_counts[idx].cpu().numpy().view(np.uint32),
     }

@@ -101,3 +101,27 @@ def test_assign_owners_edge_cases():
     assert assign_owners([5], 1) == [0]
     assert sorted(assign_owners([1, 1, 1, 1], 4)) == [0, 1, 2, 3]
     assert default_handoff_rows(64, 256, 10, 1) == 0 and default_handoff_rows(64, 256, 10, 8) == 10240
+
+
+def test_subtree_record_compaction_keeps_used_prefixes():
+    """Phase 2 copies only the records a subtree kernel wrote (ops/subtree_phase.py::_compact_records)."""
+    import torch
+
+    from mpitree_b200.ops.subtree_phase import _compact_records
+
+    rng = np.random.default_rng(0)
+    rows = rng.integers(1, 50, size=20)
+    cap = 2 * rows - 1  # worst-case records per item
+    offs = np.concatenate([[0], np.cumsum(cap)[:-1]])
+    total, C = int(cap.sum()), 5
+    nn = np.array([rng.integers(1, c + 1) for c in cap])
+    nn[3] = cap[3]
+    f = torch.arange(total, dtype=torch.int32)
+    cnt = torch.arange(total * C, dtype=torch.int32).view(total, C)
+    out = _compact_records(torch.from_numpy(nn.astype(np.int32)), offs, f, f + 1, f + 2, f.double(), cnt)
+    want = np.concatenate([np.arange(o, o + k) for o, k in zip(offs, nn)])
+    assert np.array_equal(out["feature"], want) and np.array_equal(out["bin"], want + 1)
+    assert np.array_equal(out["left"], want + 2) and np.array_equal(out["gain"], want.astype(float))
+    assert out["counts"].dtype == np.uint32 and np.array_equal(out["counts"][:, 0], want * C)
+    assert np.array_equal(out["offs"], np.concatenate([[0], np.cumsum(nn)[:-1]]))
+    assert np.array_equal(out["nn"], nn)
