@@ -138,6 +138,10 @@ class BinMapper:
                     codes[:, f] = [lut[v] for v in col.tolist()]
                 except KeyError:
                     codes[:, f] = [_bisect_obj(e, v) for v in col.tolist()]
+            elif col.dtype == np.uint8:
+                # 256 possible inputs: encode the value range once and look rows up
+                lut = np.minimum(np.searchsorted(e, np.arange(256), side="left"), len(e) - 1).astype(np.uint8)
+                codes[:, f] = lut[col]
             else:
                 c = np.searchsorted(e, col, side="left")
                 np.minimum(c, len(e) - 1, out=c)

@@ -120,6 +120,39 @@ def _impurity_rows(counts: np.ndarray, totals: np.ndarray, criterion: str) -> np
     return 1.0 - (p * p).sum(axis=-1)
 
 
+_KLOGK_MAX = 1 << 23  # table of k*log2(k) up to 8M rows per node (64 MB); larger nodes use log2 directly
+_klogk_cache = {"table": np.zeros(1)}
+
+
+def _klogk_table(n: int) -> Optional[np.ndarray]:
+    """``g[k] = k * log2(k)`` for ``k = 0 .. n`` (``g[0] = 0``), grown on demand; None when ``n`` is too large."""
+    if n > _KLOGK_MAX:
+        return None
+    t = _klogk_cache["table"]
+    if t.shape[0] <= n:
+        size = min(_KLOGK_MAX, max(n, 2 * t.shape[0])) + 1
+        k = np.arange(size, dtype=np.float64)
+        t = np.zeros(size)
+        np.multiply(k[1:], np.log2(k[1:]), out=t[1:])
+        _klogk_cache["table"] = t
+    return t
+
+
+def _approx_cost(left: np.ndarray, right: np.ndarray, n_left: np.ndarray, n_right: np.ndarray, n: int,
+                 criterion: str) -> np.ndarray:
+    """Weighted child impurity of every candidate, good to ~1e-13 (ties are settled by exact_cost).
+
+    Entropy uses ``n*cost = g(nL) + g(nR) - sum g(kL) - sum g(kR)`` with ``g(k) = k log2 k`` (the same
+    algebra as the device kernel's large-node path, ``csrc/impurity.cuh``): table gathers and sums, no
+    division, logarithm or masking per cell.
+    """
+    if criterion == "entropy":
+        g = _klogk_table(n)
+        if g is not None:
+            return (g[n_left] + g[n_right] - g[left].sum(axis=-1) - g[right].sum(axis=-1)) / n
+    return (n_left / n) * _impurity_rows(left, n_left, criterion) + (n_right / n) * _impurity_rows(right, n_right, criterion)
+
+
 def best_split(
     hist: np.ndarray, n_bins: np.ndarray, criterion: str = "entropy"
 ) -> Optional[Tuple[int, int, float, np.ndarray]]:
@@ -132,17 +165,15 @@ def best_split(
     total = hist[0].sum(axis=0)
     n = int(total.sum())
     left = np.cumsum(hist, axis=1)  # (F, B, C)
-    n_left = left.sum(axis=-1)  # (F, B)
+    per_bin = hist.sum(axis=-1)  # (F, B)
+    n_left = np.cumsum(per_bin, axis=1)
     n_right = n - n_left
-    present = hist.sum(axis=-1) > 0
+    present = per_bin > 0
     cand = present & (n_right > 0)
     if not cand.any():
         return None
     right = total[None, None, :] - left
-    h_left = _impurity_rows(left, n_left, criterion)
-    h_right = _impurity_rows(right, n_right, criterion)
-    cost = (n_left / n) * h_left + (n_right / n) * h_right
-    cost = np.where(cand, cost, np.inf)
+    cost = np.where(cand, _approx_cost(left, right, n_left, n_right, n, criterion), np.inf)
     fmin = cost.min(axis=1)  # per feature
     best_approx = fmin.min()
     tol = _TOL * (1.0 + abs(best_approx))
@@ -189,7 +220,7 @@ def best_split_rows(
         n_left = left.sum(axis=1)
         n_right = m - n_left
         right = total[None, :] - left
-        cost = (n_left / m) * _impurity_rows(left, n_left, criterion) + (n_right / m) * _impurity_rows(right, n_right, criterion)
+        cost = _approx_cost(left, right, n_left, n_right, m, criterion)
         per_feature.append((f, cs[ends].astype(np.int64), left, right, cost))
         best_approx = min(best_approx, float(cost.min()))
     if not per_feature:
