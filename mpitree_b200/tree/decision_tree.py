@@ -296,14 +296,24 @@ class DecisionTreeClassifier(ClassifierMixin, BaseEstimator):
         if _is_torch_tensor(X):
             from ..ops import cuda_engine
 
+            self._check_n_features(X)
             return cuda_engine.predict_leaf_ids(flat, X)
         X = _as_feature_matrix(check_array(X, dtype=None, ensure_all_finite=True))
+        self._check_n_features(X)
         if X.dtype != object and getattr(self, "engine_", "cpu") == "cuda" and self.device != "cpu":
             from ..ops import cuda_engine
 
             if cuda_engine.available():
                 return cuda_engine.predict_leaf_ids(flat, X)
         return flat.apply_raw(X)
+
+    def _check_n_features(self, X) -> None:
+        # (the reference indexes whatever it is given; a wrong width is always a caller bug)
+        want = getattr(self, "n_features_in_", None)
+        if want is not None and X.ndim == 2 and X.shape[1] != want:
+            raise ValueError(
+                f"X has {X.shape[1]} features, but {type(self).__name__} is expecting {want} features as input."
+            )
 
     def _flat(self) -> FlatTree:
         check_is_fitted(self)
@@ -336,7 +346,9 @@ class DecisionTreeClassifier(ClassifierMixin, BaseEstimator):
         if _is_torch_tensor(X):
             from ..ops import cuda_engine
 
-            return cuda_engine.predict_leaf_ids(self._flat(), X, want="label")  # label looked up in-kernel
+            flat = self._flat()
+            self._check_n_features(X)
+            return cuda_engine.predict_leaf_ids(flat, X, want="label")  # label looked up in-kernel
         ids = self._leaf_ids(X)
         labels = self._flat().expanded_counts().argmax(axis=1)
         return labels[ids]

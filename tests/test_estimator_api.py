@@ -119,3 +119,11 @@ def test_parallel_serial_world_equals_serial(iris):
     b = DecisionTreeClassifier(max_depth=3, device="cpu").fit(iris.data, iris.target)
     assert a.export_text() == b.export_text()
     assert "comm" in a.get_params() and pickle.loads(pickle.dumps(a)).export_text() == b.export_text()
+
+
+def test_predict_rejects_wrong_feature_count(iris):
+    clf = DecisionTreeClassifier(max_depth=2, device="cpu").fit(iris.data, iris.target)
+    with pytest.raises(ValueError, match="expecting 4 features"):
+        clf.predict(iris.data[:, :3])
+    with pytest.raises(ValueError, match="expecting 4 features"):
+        clf.predict_proba(np.hstack([iris.data, iris.data[:, :1]]))
