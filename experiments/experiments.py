@@ -82,9 +82,18 @@ def cell3(res: int = 300):
 
 
 def cell5(reps: int = 3):
+    """Timing table.  Parallel rows come from ``parallel_timing.py`` (real processes under torchrun)
+    when its CSV files are present; thread-ranks share one interpreter lock, so timing them would
+    measure the GIL rather than the algorithm and is only the fallback."""
     x_dim = np.arange(1, 250, 10)
     rows = []
     for k in (1, 2, 5, 8):
+        measured = HERE / f"time_data_k{k}_processes.csv"
+        if k > 1 and measured.exists():
+            out = [float(v) for v in measured.read_text().split(",")]
+            rows.append(out)
+            print(f"k={k} ({measured.name}):", out)
+            continue
         out = []
         for n in x_dim:
             X = np.arange(n).reshape(-1, 1)
@@ -104,6 +113,38 @@ def cell5(reps: int = 3):
     return x_dim, rows
 
 
+def _plot_without_matplotlib(x_dim, rows, w: int = 640, h: int = 420):
+    """Line chart of the four timing series drawn straight into an RGB array (no plotting library)."""
+    img = np.full((h, w, 3), 255, dtype=np.uint8)
+    left, right, top, bottom = 50, 20, 20, 40
+    colors = [(0x1F, 0x77, 0xB4), (0xFF, 0x7F, 0x0E), (0x2C, 0xA0, 0x2C), (0xD6, 0x27, 0x28)]
+    xs = np.asarray(x_dim, dtype=float)
+    ymax = max(max(r) for r in rows) * 1.05 or 1.0
+
+    def to_px(x, y):
+        px = left + (x - xs[0]) / max(xs[-1] - xs[0], 1e-9) * (w - left - right)
+        py = h - bottom - y / ymax * (h - top - bottom)
+        return px, py
+
+    img[h - bottom, left : w - right] = 0  # axes
+    img[top : h - bottom, left] = 0
+    for frac in (0.25, 0.5, 0.75, 1.0):  # dashed horizontal grid
+        gy = int(h - bottom - frac * (h - top - bottom))
+        img[gy, left : w - right : 4] = 200
+    for r, col in zip(rows, colors):
+        pts = [to_px(x, y) for x, y in zip(xs, r)]
+        for (ax_, ay_), (bx_, by_) in zip(pts, pts[1:]):
+            steps = int(max(abs(bx_ - ax_), abs(by_ - ay_))) + 1
+            lx = np.linspace(ax_, bx_, steps).round().astype(int)
+            ly = np.linspace(ay_, by_, steps).round().astype(int)
+            img[np.clip(ly, 0, h - 1), np.clip(lx, 0, w - 1)] = col
+        for px, py in pts:  # markers
+            img[int(py) - 2 : int(py) + 3, int(px) - 2 : int(px) + 3] = col
+    _write_png(HERE / "timing.png", img)
+    print(f"wrote timing.png (series: serial, k=2, k=5, k=8; x = n_samples {int(xs[0])}..{int(xs[-1])}, "
+          f"y = 0..{ymax:.1f} ms)")
+
+
 def plots(x_dim, rows):
     try:
         import matplotlib
@@ -111,7 +152,7 @@ def plots(x_dim, rows):
         matplotlib.use("Agg")
         import matplotlib.pyplot as plt
     except ImportError:
-        print("matplotlib not installed: skipping the figures")
+        _plot_without_matplotlib(x_dim, rows)
         return
     fig = plt.figure()
     ax = fig.add_subplot()

@@ -37,3 +37,17 @@ def test_bench_reference_arm_prints_one_json_line():
         for key in ("metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "config"):
             assert key in rec
         assert rec["value"] > 0 and rec["config"]["rows"] >= 60
+
+
+def test_notebook_holds_the_reference_goldens():
+    """experiments/experiments.ipynb is stored with outputs; its two trees are the reference's goldens."""
+    from .goldens import IRIS2_DEPTH3, IRIS2_DEPTH5_P1
+
+    nb = json.load(open(os.path.join(ROOT, "experiments", "experiments.ipynb"), encoding="utf-8"))
+    assert nb["nbformat"] == 4
+    texts = ["".join(o["text"]) for c in nb["cells"] if c["cell_type"] == "code"
+             for o in c["outputs"] if o["output_type"] == "stream"]
+    assert IRIS2_DEPTH3.strip() in [t.strip() for t in texts]
+    assert IRIS2_DEPTH5_P1.strip() in [t.strip() for t in texts]
+    images = [o for c in nb["cells"] if c["cell_type"] == "code" for o in c["outputs"] if o["output_type"] == "display_data"]
+    assert len(images) == 3  # two decision boundaries and the timing plot
