@@ -41,7 +41,7 @@ def parse():
     ap.add_argument("--features", type=int, default=64)
     ap.add_argument("--classes", type=int, default=10)
     ap.add_argument("--depth", type=int, default=10)
-    ap.add_argument("--reduce", default=os.environ.get("MTB_REDUCE", "auto"), choices=["auto", "p2p", "nccl"])
+    ap.add_argument("--reduce", default=os.environ.get("MTB_REDUCE", "auto"), choices=["auto", "p2p", "nccl", "nvls"])
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--ref-budget-s", type=float, default=float(os.environ.get("MTB_REF_BUDGET_S", "150")))
     return ap.parse_args()

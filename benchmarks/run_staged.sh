@@ -37,6 +37,12 @@ if [ "$N" -gt 1 ] && [ "$TESTS_OK" = "0" ]; then
   say "=== allreduce sweep with the NVLS column, world=$N"
   MTB_SWEEP_NVLS=1 timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node "$N" --master-addr 127.0.0.1 \
     --master-port 29566 benchmarks/allreduce_sweep.py 2>&1 | grep " B  nccl" | tee -a "$OUT"
+  say "=== fit_probe world=$N, peer push vs in-switch reduction"
+  for red in p2p nvls; do
+    say "--- reduce=$red"
+    timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node "$N" --master-addr 127.0.0.1 \
+      --master-port 29568 benchmarks/fit_probe.py --rows 100000000 --reps 3 --reduce $red 2>&1 | grep -v -i warn | tail -13 | tee -a "$OUT"
+  done
   say "=== fit_probe p2p world=$N, planar vs interleaved"
   for layout in planar interleaved; do
     say "--- MTB_TILE=$layout"

@@ -130,6 +130,10 @@ typedef struct MtbCtx {
    * (FT == 16 only; opt-in until it has been timed on hardware).  Slabs in global memory are
    * [f][B][C] either way.                                                                      */
   int64_t tile_layout;
+  /* world > 1, opt-in: multicast (NVSwitch) mappings of hist[0] / hist[1].  When set, the fused level
+   * kernels skip the peer push and the owners read cross-rank sums with multimem.ld_reduce.  The
+   * slabs must then live in a VMM allocation bound to the multicast object (parallel/nvls.py). 0 = off. */
+  int64_t mc_hist[2];
 } MtbCtx;
 
 const char* mtb_last_error(void);

@@ -467,6 +467,12 @@ __global__ void __launch_bounds__(512) k_push(const __grid_constant__ MtbCtx ctx
 // One warp per (slot, owned feature).  `slab` is this warp's padded shared-memory copy of
 // the feature's [B][C] counts: lane L owns bins [L*BPL, (L+1)*BPL) at offset
 // L*(BPL*C+1) so that lane-sequential walks are bank-conflict free.
+//
+// NV (opt-in, staged): the local partial slabs live in memory that is also bound to an NVSwitch
+// multicast object (ctx.mc_hist = the multicast mapping of ctx.hist).  Nothing is pushed; the
+// owner asks the switch for the sum over all ranks with multimem.ld_reduce (SASS LDGMC.ADD), two
+// packed u32 counts per 64-bit load (integer ld_reduce has no vector form).
+template <bool NV = false>
 __device__ void gain_pair(const MtbCtx& ctx, uint32_t* slab, int slot, int f) {
   View v(ctx);
   const int B = (int)ctx.B, C = (int)ctx.C, F = (int)ctx.F;
@@ -508,6 +514,14 @@ __device__ void gain_pair(const MtbCtx& ctx, uint32_t* slab, int slot, int f) {
     // reduced counts of `s`: own partial + what the peers pushed.  The staged loads are issued
     // four at a time (fixed unroll over the maximum world size) so their latencies overlap.
     auto reduced4 = [&](int s, int q) -> uint4 {
+      if constexpr (NV) {
+        const uint64_t* mc = reinterpret_cast<const uint64_t*>(ptr_of<const uint32_t>(ctx.mc_hist[ctx.hcur]) +
+                                                               (int64_t)s * v.slab_words() + (int64_t)f * B * C) + 2 * q;
+        uint64_t lo, hi;
+        asm volatile("multimem.ld_reduce.relaxed.sys.global.add.u64 %0, [%1];" : "=l"(lo) : "l"(mc) : "memory");
+        asm volatile("multimem.ld_reduce.relaxed.sys.global.add.u64 %0, [%1];" : "=l"(hi) : "l"(mc + 1) : "memory");
+        return make_uint4((uint32_t)lo, (uint32_t)(lo >> 32), (uint32_t)hi, (uint32_t)(hi >> 32));
+      }
       uint4 x = reinterpret_cast<const uint4*>(v.hist_cur() + (int64_t)s * v.slab_words() + (int64_t)f * B * C)[q];
       const uint32_t* cell = stage + (int64_t)s * region + q * 4;
       const int64_t src_stride = ctx.h_cap * region;
@@ -645,6 +659,7 @@ __device__ void gain_pair(const MtbCtx& ctx, uint32_t* slab, int slot, int f) {
 
 // pass -1: every pair (the normal case); 0 / 1: BUILD+NONE / DERIVE slots only (kept for
 // experiments: pairs never depend on one another, see gain_pair).
+template <bool NV = false>
 __device__ void gain_phase(const MtbCtx& ctx, uint8_t* smem, int warps_per_block, int pass) {
   View v(ctx);
   const int F = (int)ctx.F;
@@ -667,7 +682,7 @@ __device__ void gain_phase(const MtbCtx& ctx, uint8_t* smem, int warps_per_block
     if (p >= n_pairs) break;
     const int slot = p / n_own;
     if (pass >= 0 && (mode[slot] == MTB_MODE_DERIVE) != (pass == 1)) continue;
-    gain_pair(ctx, slab, slot, f_lo + p % n_own);
+    gain_pair<NV>(ctx, slab, slot, f_lo + p % n_own);
   }
 }
 
@@ -1270,7 +1285,7 @@ __device__ __forceinline__ void stamp(const MtbCtx& ctx, int i) {
   }
 }
 
-template <int FT, bool IL = false>
+template <int FT, bool IL = false, bool NV = false>
 __global__ void __launch_bounds__(kHistThreads, 1) k_level_fused(const __grid_constant__ MtbCtx ctx) {
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ int smem_warp[33];
@@ -1286,10 +1301,10 @@ __global__ void __launch_bounds__(kHistThreads, 1) k_level_fused(const __grid_co
   if (ctx.world > 1) {
     grid.sync();
     stamp(ctx, 2);
-    push_phase(ctx);
+    if constexpr (!NV) push_phase(ctx);
     peer_barrier(ctx, grid, (uint32_t)ctx.epoch + 1u);
     stamp(ctx, 3);
-    gain_phase(ctx, smem, kFusedGainWarps, -1);
+    gain_phase<NV>(ctx, smem, kFusedGainWarps, -1);
     stamp(ctx, 4);
     peer_barrier(ctx, grid, (uint32_t)ctx.epoch + 2u);
     stamp(ctx, 5);
@@ -1306,7 +1321,7 @@ __global__ void __launch_bounds__(kHistThreads, 1) k_level_fused(const __grid_co
   stamp(ctx, 6);
 }
 
-template <int FT, bool IL = false>
+template <int FT, bool IL = false, bool NV = false>
 __global__ void __launch_bounds__(kHistThreads, 1) k_level_fused2(const __grid_constant__ MtbCtx P,
                                                                   const __grid_constant__ MtbCtx C) {
   extern __shared__ __align__(128) uint8_t smem[];
@@ -1331,10 +1346,10 @@ __global__ void __launch_bounds__(kHistThreads, 1) k_level_fused2(const __grid_c
   if (C.world > 1) {
     grid.sync();
     stamp(C, 2);
-    push_phase(C);
+    if constexpr (!NV) push_phase(C);
     peer_barrier(C, grid, (uint32_t)C.epoch + 1u);
     stamp(C, 3);
-    gain_phase(C, smem, kFusedGainWarps, -1);
+    gain_phase<NV>(C, smem, kFusedGainWarps, -1);
     stamp(C, 4);
     peer_barrier(C, grid, (uint32_t)C.epoch + 2u);
     stamp(C, 5);
@@ -1373,6 +1388,8 @@ int gain_smem(const MtbCtx* ctx) { return kGainWarps * ((int)ctx->B * (int)ctx->
 
 // ctx->tile_layout == 1 selects the interleaved shared-memory tile (FT == 16 only; opt-in).
 static bool interleaved(const MtbCtx* ctx) { return ctx->tile_layout == 1 && ctx->FT == 16; }
+// ctx->mc_hist set (world > 1): the histogram slabs are multicast-mapped and the owners reduce in the switch.
+static bool in_switch(const MtbCtx* ctx) { return ctx->world > 1 && ctx->mc_hist[ctx->hcur] != 0; }
 
 template <int FT>
 static int launch_hist(const MtbCtx* ctx, const HistGeom& g, cudaStream_t stream) {
@@ -1395,12 +1412,18 @@ static int launch_fused(const MtbCtx* ctx, int smem, cudaStream_t stream) {
   MtbCtx local = *ctx;
   void* args[] = {&local};
   if constexpr (FT == 16) {
-    if (interleaved(ctx)) {
-      if (set_smem(k_level_fused<16, true>, smem)) return -1;
-      MTB_CHECK(cudaLaunchCooperativeKernel((void*)k_level_fused<16, true>, dim3(sm_count()), dim3(kHistThreads), args,
-                                            smem, stream));
+    const bool il = interleaved(ctx), nv = in_switch(ctx);
+    if (il || nv) {
+      void* fn = il ? (nv ? (void*)k_level_fused<16, true, true> : (void*)k_level_fused<16, true, false>)
+                    : (void*)k_level_fused<16, false, true>;
+      MTB_CHECK(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+      MTB_CHECK(cudaLaunchCooperativeKernel(fn, dim3(sm_count()), dim3(kHistThreads), args, smem, stream));
       return 0;
     }
+  }
+  if (in_switch(ctx)) {
+    mtb_set_error("fused", "the in-switch reduction is only built for 16-feature tiles", __FILE__, __LINE__);
+    return -2;
   }
   if (set_smem(k_level_fused<FT>, smem)) return -1;
   MTB_CHECK(cudaLaunchCooperativeKernel((void*)k_level_fused<FT>, dim3(sm_count()), dim3(kHistThreads), args, smem,
@@ -1413,12 +1436,18 @@ static int launch_fused2(const MtbCtx* P, const MtbCtx* C, int smem, cudaStream_
   MtbCtx p = *P, c = *C;
   void* args[] = {&p, &c};
   if constexpr (FT == 16) {
-    if (interleaved(P)) {
-      if (set_smem(k_level_fused2<16, true>, smem)) return -1;
-      MTB_CHECK(cudaLaunchCooperativeKernel((void*)k_level_fused2<16, true>, dim3(sm_count()), dim3(kHistThreads), args,
-                                            smem, stream));
+    const bool il = interleaved(P), nv = in_switch(C);
+    if (il || nv) {
+      void* fn = il ? (nv ? (void*)k_level_fused2<16, true, true> : (void*)k_level_fused2<16, true, false>)
+                    : (void*)k_level_fused2<16, false, true>;
+      MTB_CHECK(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+      MTB_CHECK(cudaLaunchCooperativeKernel(fn, dim3(sm_count()), dim3(kHistThreads), args, smem, stream));
       return 0;
     }
+  }
+  if (in_switch(C)) {
+    mtb_set_error("fused2", "the in-switch reduction is only built for 16-feature tiles", __FILE__, __LINE__);
+    return -2;
   }
   if (set_smem(k_level_fused2<FT>, smem)) return -1;
   MTB_CHECK(cudaLaunchCooperativeKernel((void*)k_level_fused2<FT>, dim3(sm_count()), dim3(kHistThreads), args, smem,

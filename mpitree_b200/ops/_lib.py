@@ -49,7 +49,7 @@ class MtbCtx(ctypes.Structure):
     _fields_ = (
         [(n, ctypes.c_int64) for n in _names]
         + [("peer_hist", ctypes.c_int64 * 16), ("peer_rec", ctypes.c_int64 * 16), ("peer_flags", ctypes.c_int64 * 16)]
-        + [("epoch", ctypes.c_int64), ("plogp", ctypes.c_int64), ("plogp_n", ctypes.c_int64), ("h_cap", ctypes.c_int64), ("fpo", ctypes.c_int64), ("timers", ctypes.c_int64), ("klogk", ctypes.c_int64), ("klogk_n", ctypes.c_int64), ("rstore", ctypes.c_int64 * 2), ("small_rows", ctypes.c_int64), ("ho_cap", ctypes.c_int64), ("ho_node", ctypes.c_int64), ("ho_begin", ctypes.c_int64), ("ho_end", ctypes.c_int64), ("ho_side", ctypes.c_int64), ("part_child", ctypes.c_int64), ("mask_words", ctypes.c_int64), ("unit_base", ctypes.c_int64), ("tile_layout", ctypes.c_int64)]
+        + [("epoch", ctypes.c_int64), ("plogp", ctypes.c_int64), ("plogp_n", ctypes.c_int64), ("h_cap", ctypes.c_int64), ("fpo", ctypes.c_int64), ("timers", ctypes.c_int64), ("klogk", ctypes.c_int64), ("klogk_n", ctypes.c_int64), ("rstore", ctypes.c_int64 * 2), ("small_rows", ctypes.c_int64), ("ho_cap", ctypes.c_int64), ("ho_node", ctypes.c_int64), ("ho_begin", ctypes.c_int64), ("ho_end", ctypes.c_int64), ("ho_side", ctypes.c_int64), ("part_child", ctypes.c_int64), ("mask_words", ctypes.c_int64), ("unit_base", ctypes.c_int64), ("tile_layout", ctypes.c_int64), ("mc_hist", ctypes.c_int64 * 2)]
     )
 
 

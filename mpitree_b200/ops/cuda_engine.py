@@ -38,6 +38,7 @@ __all__ = [
 MAX_CLASSES = 128
 SMALL_ROWS_DEFAULT = 2048  # hand a node to the subtree kernel at or below this many rows
 SMALL_ROWS_MAX = 8192      # row indices live in shared memory as uint16 next to the histogram tile
+NVLS_MAX_SLOTS = 2048      # histogram slabs per rank bound to the multicast object in reduce="nvls"
 SAMPLE_ROWS = 1 << 18
 ENCODE_CHUNK_ROWS = 1 << 22
 
@@ -329,9 +330,15 @@ class TreeBuilder:
             reduce = "none"
         elif reduce == "auto":
             reduce = "p2p"
+        # "nvls" (staged): the p2p protocol with the histogram slabs in multicast-bound memory, so
+        # the owners read cross-rank sums from the switch instead of receiving pushed partials
+        want_nvls = reduce == "nvls"
+        if want_nvls:
+            reduce = "p2p"
         if reduce not in ("none", "p2p", "nccl", "lockstep"):
-            raise ValueError("reduce must be 'auto', 'p2p' or 'nccl'")
+            raise ValueError("reduce must be 'auto', 'p2p', 'nccl' or 'nvls'")
         self.reduce = reduce
+        self.nvls = False
         dev = data.device
         F, C, G = data.n_features, data.n_classes, data.G
         if C > MAX_CLASSES:
@@ -389,6 +396,8 @@ class TreeBuilder:
             # single rank: two ping-pong sides; peers: one side of local partials + staging + 2/P reduced
             per_slot = slab_words * 4 * (2.0 + 2.0 / P if peer_mode else 2.0)
             h_cap = min(depth_cap, rows_cap, max(2, int(hist_budget_bytes // per_slot)))
+            if want_nvls:
+                h_cap = min(h_cap, NVLS_MAX_SLOTS)  # the slabs are bound to a multicast object: keep it modest
             h_cap = max(2, h_cap + (h_cap & 1))
             if comm is not None and comm.size > 1 and not agreed:
                 h_cap = min(comm.allgather_object(h_cap))  # every rank must use the same layout
@@ -434,7 +443,14 @@ class TreeBuilder:
         z = lambda n, dt=i32: torch.zeros(max(int(n), 1), dtype=dt, device=dev)  # noqa: E731
         if reduce == "p2p":
             # peers never read the previous level's local partials (reduced slabs live in rstore)
-            one = z(self.h_cap * slab_words)
+            if want_nvls and fused and self.stats.FT == 16:
+                reg = _nvls_region(self.h_cap * slab_words * 4, comm)
+                one = reg.as_tensor()[: self.h_cap * slab_words * 4].view(i32)
+                ctx.mc_hist[0] = ctx.mc_hist[1] = int(reg.mc_ptr)
+                self.nvls = True
+                self.stats.reduce = "nvls"
+            else:
+                one = z(self.h_cap * slab_words)
             self.hist = [one, one]
         else:
             self.hist = [z(self.h_cap * slab_words), z(self.h_cap * slab_words)]
@@ -710,6 +726,20 @@ class TreeBuilder:
 
 
 _REGIONS: dict = {}
+
+
+def _nvls_region(nbytes: int, comm):
+    """Multicast-bound region for the histogram slabs, reused across fits like :func:`_shared_region`."""
+    from ..parallel.nvls import NvlsRegion
+
+    key = ("nvls", comm.size, comm.rank)
+    reg = _REGIONS.get(key)
+    if reg is None or reg.nbytes < int(nbytes):
+        if reg is not None:
+            reg.close()
+        reg = NvlsRegion(int(nbytes), comm)
+        _REGIONS[key] = reg
+    return reg
 
 
 def _shared_region(nbytes: int, comm):

@@ -121,3 +121,65 @@ def test_interleaved_tile_equals_planar(shape, mode):
     got, _ = cuda_engine.fit_from_host(X, y, k, params, builder_kwargs=dict(mode, tile_layout="interleaved"))
     assert cuda_engine.fit_from_host.last_stats.tile_layout == "interleaved"
     _same_tree(got, want)
+
+
+_NVLS_TREE_WORKER = r"""
+import os, sys
+sys.path.insert(0, os.environ["REPO"])
+import numpy as np, torch, torch.distributed as dist
+from mpitree_b200.ops import cuda_engine
+from mpitree_b200.parallel.comm import init_process_group_from_env
+from mpitree_b200.parallel.nvls import nvls_available
+from mpitree_b200.tree import ParallelDecisionTreeClassifier
+assert init_process_group_from_env("nccl")
+rank, world = dist.get_rank(), dist.get_world_size()
+if not nvls_available(torch.cuda.current_device()):
+    if rank == 0:
+        print("NVLS_UNSUPPORTED")
+    dist.destroy_process_group()
+    sys.exit(0)
+rng = np.random.default_rng(0)
+n = 400_000
+X = rng.integers(0, 256, size=(n, 48), dtype=np.uint8)
+s = X[:, :6].astype(np.float64) @ np.array([1, -1, .5, .5, -.25, 2.0]) + rng.normal(scale=60, size=n)
+y = np.digitize(s, np.quantile(s, np.linspace(0, 1, 6)[1:-1]))
+lo, hi = n * rank // world, n * (rank + 1) // world
+trees = {}
+for reduce in ("p2p", "nvls"):
+    for tile in ("planar", "interleaved"):
+        clf = ParallelDecisionTreeClassifier(max_depth=9, device="cuda", data_layout="sharded")
+        clf.builder_kwargs = {"reduce": reduce, "tile_layout": tile}
+        for _ in range(2):  # the second fit reuses the cached regions with later epochs
+            clf.fit(X[lo:hi], y[lo:hi])
+        st = cuda_engine.fit_from_host.last_stats
+        assert st.reduce == reduce and st.tile_layout == tile, (st.reduce, st.tile_layout)
+        trees[(reduce, tile)] = clf.flat_tree_
+want = trees[("p2p", "planar")]
+for key, t in trees.items():
+    assert t.structurally_equal(want), key
+    assert np.array_equal(t.counts, want.counts), key
+dist.barrier()
+if rank == 0:
+    print("NVLS_TREE_OK", world)
+dist.destroy_process_group()
+"""
+
+
+@pytest.mark.multigpu
+def test_nvls_tree_equals_p2p(tmp_path):
+    import subprocess
+    import sys
+
+    import torch
+
+    world = min(torch.cuda.device_count(), 8)
+    if world < 2:
+        pytest.skip("needs at least two GPUs")
+    script = tmp_path / "nvls_tree_worker.py"
+    script.write_text(_NVLS_TREE_WORKER)
+    env = dict(os.environ, REPO=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
+           "--master-addr", "127.0.0.1", "--master-port", "29657", str(script)]
+    res = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=600)
+    assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
+    assert f"NVLS_TREE_OK {world}" in res.stdout or "NVLS_UNSUPPORTED" in res.stdout

@@ -2,6 +2,7 @@
 import io
 
 import numpy as np
+import pytest
 
 from mpitree_b200.tree import DecisionTreeClassifier
 from mpitree_b200.utils.checkpoint import load_model, save_model
@@ -125,3 +126,30 @@ def test_subtree_record_compaction_keeps_used_prefixes():
     assert out["counts"].dtype == np.uint32 and np.array_equal(out["counts"][:, 0], want * C)
     assert np.array_equal(out["offs"], np.concatenate([[0], np.cumsum(nn)[:-1]]))
     assert np.array_equal(out["nn"], nn)
+
+
+def test_ctypes_mirror_matches_the_c_header(tmp_path):
+    """``MtbCtx`` / ``MtbSubtreeArgs`` are filled from Python: the mirrors must have the C layout."""
+    import ctypes
+    import os
+    import shutil
+    import subprocess
+
+    from mpitree_b200.ops import _lib as L
+
+    cxx = shutil.which("g++") or shutil.which("c++")
+    if cxx is None:
+        pytest.skip("no C++ compiler")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    src = tmp_path / "sz.cpp"
+    src.write_text(
+        '#include "mpitree_b200.h"\n#include <cstdio>\n#include <cstddef>\n'
+        'int main() { std::printf("%zu %zu %zu\\n", sizeof(MtbCtx), offsetof(MtbCtx, tile_layout), '
+        "offsetof(MtbCtx, peer_hist)); }\n"
+    )
+    exe = tmp_path / "sz"
+    subprocess.run([cxx, "-I", os.path.join(root, "include"), str(src), "-o", str(exe)], check=True)
+    size, off_tile, off_peer = map(int, subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.split())
+    assert ctypes.sizeof(L.MtbCtx) == size
+    assert L.MtbCtx.tile_layout.offset == off_tile
+    assert L.MtbCtx.peer_hist.offset == off_peer
