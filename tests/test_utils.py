@@ -153,3 +153,35 @@ def test_ctypes_mirror_matches_the_c_header(tmp_path):
     assert ctypes.sizeof(L.MtbCtx) == size
     assert L.MtbCtx.tile_layout.offset == off_tile
     assert L.MtbCtx.peer_hist.offset == off_peer
+
+
+def test_tree_builder_host_setup_runs_without_a_gpu():
+    """The CUDA engine's host-side set-up (sizing, context struct, buffer binding) on CPU tensors.
+
+    No kernel is launched; this catches Python-level mistakes in the GPU driver code on the CPU box.
+    """
+    import torch
+
+    from mpitree_b200.ops import _lib as L
+    from mpitree_b200.ops import cuda_engine as ce
+    from mpitree_b200.ops.cpu_engine import SplitParams
+
+    try:
+        L.load()
+    except Exception as exc:  # noqa: BLE001  (no nvcc and no prebuilt library)
+        pytest.skip(f"native library unavailable: {exc}")
+
+    class Data:
+        device = torch.device("cpu")
+        n_features, n_classes, G, n_cap, n_local, cur = 64, 10, 4, 4096, 4000, 0
+        codes = [torch.zeros(4 * 4096 * 16, dtype=torch.uint8) for _ in range(2)]
+        labels = [torch.zeros(4096, dtype=torch.uint8) for _ in range(2)]
+
+    for kw, layout in ((dict(), 0), (dict(tile_layout="interleaved"), 1), (dict(fused=False), 0)):
+        b = ce.TreeBuilder(Data(), 256, SplitParams(max_depth=5), hist_budget_bytes=64 << 20, **kw)
+        b._bind()
+        assert b.stats.FT == 16 and b.ctx.tile_layout == layout and not b.nvls
+        assert list(b.ctx.mc_hist) == [0, 0] and b.ctx.world == 1
+        assert b.h_cap == 16
+    with pytest.raises(ValueError):
+        ce.TreeBuilder(Data(), 256, SplitParams(max_depth=5), hist_budget_bytes=64 << 20, tile_layout="diagonal")
