@@ -26,7 +26,9 @@ unchanged wherever the reference succeeds; see DESIGN.md "Quirk policy"):
 * ``export_text`` prints string thresholds instead of raising (``:276``);
 * base-class order makes ``sklearn.base.is_classifier`` true (``:17``);
 * importing the package needs neither MPI nor a GPU (``:313`` imports mpi4py in
-  the class body).
+  the class body);
+* ``predict`` / ``predict_proba`` raise ``ValueError`` when the input has a different
+  number of features than ``fit`` saw (the reference has no check, ``:206``).
 """
 
 from __future__ import annotations
