@@ -38,12 +38,14 @@ __all__ = [
     "exact_entropy",
     "exact_cost",
     "best_split",
+    "best_split_many",
     "build_tree_cpu",
     "probe_dot_mode",
     "SplitParams",
 ]
 
 _TOL = 1e-9
+_BATCH_CELLS = 1 << 20  # histogram cells evaluated per vectorised batch of nodes (8 MB of int64 temporaries)
 
 
 @dataclass(frozen=True)
@@ -106,6 +108,19 @@ def exact_cost(left: np.ndarray, right: np.ndarray, criterion: str = "entropy") 
     return np.dot(weights, impurity)
 
 
+def _exact_cost_cached(cache: dict, left: np.ndarray, right: np.ndarray, criterion: str) -> float:
+    """``exact_cost`` memoised on the left count vector (the right one is ``total - left``).
+
+    Near-tied candidates of a small node very often share their class counts (the same rows end up
+    on the left for several features or thresholds), and equal counts give the same float64 cost.
+    """
+    key = left.tobytes()
+    hit = cache.get(key)
+    if hit is None:
+        hit = cache[key] = exact_cost(left, right, criterion)
+    return hit
+
+
 # --------------------------------------------------------------------------
 # vectorised approximate impurity
 # --------------------------------------------------------------------------
@@ -147,7 +162,7 @@ def _approx_cost(left: np.ndarray, right: np.ndarray, n_left: np.ndarray, n_righ
     division, logarithm or masking per cell.
     """
     if criterion == "entropy":
-        g = _klogk_table(n)
+        g = _klogk_table(int(np.max(n)))  # ``n`` may be one count or an array broadcast against the candidates
         if g is not None:
             return (g[n_left] + g[n_right] - g[left].sum(axis=-1) - g[right].sum(axis=-1)) / n
     return (n_left / n) * _impurity_rows(left, n_left, criterion) + (n_right / n) * _impurity_rows(right, n_right, criterion)
@@ -161,29 +176,48 @@ def best_split(
     ``hist`` is the node's (F, B, C) count histogram.  ``None`` means no feature
     has two non-empty bins, i.e. all rows are identical -> the node is a leaf.
     """
-    F, B, C = hist.shape
-    total = hist[0].sum(axis=0)
-    n = int(total.sum())
-    left = np.cumsum(hist, axis=1)  # (F, B, C)
-    per_bin = hist.sum(axis=-1)  # (F, B)
-    n_left = np.cumsum(per_bin, axis=1)
-    n_right = n - n_left
-    present = per_bin > 0
-    cand = present & (n_right > 0)
-    if not cand.any():
-        return None
-    right = total[None, None, :] - left
-    cost = np.where(cand, _approx_cost(left, right, n_left, n_right, n, criterion), np.inf)
-    fmin = cost.min(axis=1)  # per feature
+    return best_split_many(hist[None], n_bins, criterion)[0]
+
+
+def best_split_many(hist: np.ndarray, n_bins: np.ndarray, criterion: str = "entropy") -> list:
+    """:func:`best_split` for a stack of nodes ``(S, F, B, C)``: the prefix sums and the candidate
+    costs of all nodes are formed by the same array operations, only the tie resolution is per node."""
+    S = hist.shape[0]
+    group = max(1, _BATCH_CELLS // max(int(np.prod(hist.shape[1:])), 1))
+    if S > group:  # keep the temporaries of one batch cache-resident
+        out: list = []
+        for s0 in range(0, S, group):
+            out.extend(best_split_many(hist[s0 : s0 + group], n_bins, criterion))
+        return out
+    total = hist[:, 0].sum(axis=1)  # (S, C)
+    n = total.sum(axis=1)  # (S,)
+    left = np.cumsum(hist, axis=2)  # (S, F, B, C)
+    per_bin = hist.sum(axis=-1)  # (S, F, B)
+    n_left = np.cumsum(per_bin, axis=2)
+    n_right = n[:, None, None] - n_left
+    cand = (per_bin > 0) & (n_right > 0)
+    right = total[:, None, None, :] - left
+    safe_n = np.maximum(n, 1)[:, None, None]
+    cost = np.where(cand, _approx_cost(left, right, n_left, n_right, safe_n, criterion), np.inf)
+    fmin_all = cost.min(axis=2)  # (S, F)
+    return [
+        _resolve_ties(cost[s], fmin_all[s], left[s], right[s], total[s], criterion) if cand[s].any() else None
+        for s in range(S)
+    ]
+
+
+def _resolve_ties(cost, fmin, left, right, total, criterion):
+    """Exact re-evaluation of the candidates within rounding distance of the best approximate cost."""
     best_approx = fmin.min()
     tol = _TOL * (1.0 + abs(best_approx))
 
     imp = exact_entropy if criterion == "entropy" else exact_gini
     h_parent = imp(total)
     best = None  # (gain, feature, bin)
+    cache: dict = {}
     for f in np.flatnonzero(fmin <= best_approx + tol):
         bins = np.flatnonzero(cost[f] <= fmin[f] + tol)
-        costs = [exact_cost(left[f, b], right[f, b], criterion) for b in bins]
+        costs = [_exact_cost_cached(cache, left[f, b], right[f, b], criterion) for b in bins]
         k = int(np.argmin(costs))  # first arg-min over ascending thresholds
         gain = h_parent - costs[k]
         if best is None or gain > best[0]:  # strict: first arg-max over features
@@ -199,46 +233,41 @@ def best_split_rows(
 
     For a node with few rows the (F, B, C) histogram is mostly zeros; sorting the node's rows per
     feature and taking class prefix counts at the distinct values costs ``O(F m log m)`` instead of
-    ``O(F B C)``.  Candidates, tie-breaks and the exact re-evaluation are identical.
+    ``O(F B C)``.  All features are handled by the same few array operations (one stable argsort of
+    the ``(m, F)`` code block, one cumulative sum).  Candidates, tie-breaks and the exact
+    re-evaluation are identical.
     """
     m, F = codes.shape
+    if m < 2:
+        return None
+    order = np.argsort(codes, axis=0, kind="stable")  # (m, F)
+    cs = np.take_along_axis(codes, order, axis=0)
+    boundary = cs[1:] != cs[:-1]  # (m-1, F): sorted position i is the last row of its value, a larger value follows
+    if not boundary.any():
+        return None  # every feature is constant in this node
     present, yi = np.unique(y, return_inverse=True)
     Cp = len(present)
     total = np.bincount(yi, minlength=Cp).astype(np.int64)
     onehot = np.zeros((m, Cp), dtype=np.int64)
     onehot[np.arange(m), yi] = 1
-    per_feature = []  # (f, bins, left, cost)
-    best_approx = np.inf
-    for f in range(F):
-        col = codes[:, f]
-        order = np.argsort(col, kind="stable")
-        cs = col[order]
-        ends = np.flatnonzero(cs[1:] != cs[:-1])  # last index of every distinct value but the largest
-        if ends.size == 0:
-            continue  # constant in this node: no usable candidate
-        left = np.cumsum(onehot[order], axis=0)[ends]
-        n_left = left.sum(axis=1)
-        n_right = m - n_left
-        right = total[None, :] - left
-        cost = _approx_cost(left, right, n_left, n_right, m, criterion)
-        per_feature.append((f, cs[ends].astype(np.int64), left, right, cost))
-        best_approx = min(best_approx, float(cost.min()))
-    if not per_feature:
-        return None
+    left = np.cumsum(onehot[order], axis=0)[:-1]  # (m-1, F, Cp) class counts of sorted positions <= i
+    right = total - left
+    n_left = np.broadcast_to(np.arange(1, m, dtype=np.int64)[:, None], (m - 1, F))
+    cost = np.where(boundary, _approx_cost(left, right, n_left, m - n_left, m, criterion), np.inf)
+    fmin = cost.min(axis=0)
+    best_approx = float(fmin.min())
     tol = _TOL * (1.0 + abs(best_approx))
     imp = exact_entropy if criterion == "entropy" else exact_gini
     h_parent = imp(total)
     best = None
-    for f, bins, left, right, cost in per_feature:
-        fmin = cost.min()
-        if fmin > best_approx + tol:
-            continue
-        near = np.flatnonzero(cost <= fmin + tol)
-        costs = [exact_cost(left[i], right[i], criterion) for i in near]
+    cache: dict = {}
+    for f in np.flatnonzero(fmin <= best_approx + tol):  # ascending feature index
+        near = np.flatnonzero(cost[:, f] <= fmin[f] + tol)  # ascending position == ascending threshold
+        costs = [_exact_cost_cached(cache, left[i, f], right[i, f], criterion) for i in near]
         k = int(np.argmin(costs))
         gain = h_parent - costs[k]
         if best is None or gain > best[0]:
-            best = (gain, f, int(bins[near[k]]), left[near[k]])
+            best = (gain, int(f), int(cs[near[k], f]), left[near[k], f])
     gain, f, b, left_present = best
     left_counts = np.zeros(n_classes, dtype=np.int64)
     left_counts[present] = left_present
@@ -354,8 +383,8 @@ def build_tree_cpu(
             remap[part] = np.arange(len(part))
             local_slot = remap[np.where(slot >= 0, slot, len(frontier))]
             hist = _level_histograms(codes, y, local_slot, len(part), B, C, comm)
-            for j, s_ in enumerate(part):
-                decisions[frontier[s_]] = best_split(hist[j], n_bins, params.criterion)
+            for s_, dec in zip(part, best_split_many(hist, n_bins, params.criterion)):
+                decisions[frontier[s_]] = dec
 
         next_frontier: List[int] = []
         # per current slot: (feature, bin, left slot or -1, right slot or -1)
