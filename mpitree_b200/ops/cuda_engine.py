@@ -424,6 +424,8 @@ class TreeBuilder:
         # Default: only when the level-wise frontier could outgrow the histogram slot capacity.
         if small_rows is None:
             small_rows = 0 if (worst_frontier is not None and worst_frontier <= self.h_cap) else SMALL_ROWS_DEFAULT
+            if small_rows and os.environ.get("MTB_SMALL_ROWS"):  # tuning knob for the hand-off size
+                small_rows = max(1, int(os.environ["MTB_SMALL_ROWS"]))
         if small_rows and reduce in ("lockstep", "nccl"):
             small_rows = 0
         if small_rows and self.lib.mtb_subtree_config(ctypes.c_int64(B), ctypes.c_int64(C)) == 0:
