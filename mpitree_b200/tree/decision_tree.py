@@ -80,6 +80,42 @@ def _validate_labels(y: np.ndarray) -> np.ndarray:
     return y.astype(np.int64, copy=False)
 
 
+def _restore_zero_signs(flat: FlatTree, X: np.ndarray) -> None:
+    """Give a zero threshold the sign the reference would print (``-0.00`` vs ``0.00``).
+
+    ``-0.0 == 0.0``, so both land in one bin and every decision is unaffected; only the printed
+    threshold differs.  The reference takes its thresholds from ``np.unique`` of the *node's* object
+    column (``:73``), which keeps whichever zero its sort puts first; the same call on the same rows
+    in the same order reproduces that choice.  Only runs when a split column really holds both
+    signs (rare: rounded negative values), and only for a single-rank fit, where this rank sees the
+    node's rows in the reference's order.
+    """
+    if X.dtype.kind != "f" or X.shape[0] == 0:
+        return
+    nodes = [i for i in range(flat.n_nodes) if flat.feature[i] >= 0 and flat.thresholds[i] == 0]
+    mixed = set()
+    for f in {int(flat.feature[i]) for i in nodes}:
+        neg = np.signbit(X[X[:, f] == 0, f])
+        if neg.any() and not neg.all():
+            mixed.add(f)
+    nodes = [i for i in nodes if int(flat.feature[i]) in mixed]
+    if not nodes:
+        return
+    thr = np.array([np.nan if t is None else float(t) for t in flat.thresholds])
+    at = np.zeros(X.shape[0], dtype=np.int64)  # node every row currently sits in, advanced level by level
+    todo = {int(flat.depth[i]): [] for i in nodes}
+    for i in nodes:
+        todo[int(flat.depth[i])].append(i)
+    for depth in range(max(todo) + 1):
+        for i in todo.get(depth, ()):
+            col = X[at == i, int(flat.feature[i])].astype(object)
+            flat.thresholds[i] = next(v for v in np.unique(col) if v == 0)
+        inner = flat.feature[at] >= 0
+        rows = np.flatnonzero(inner)
+        go_left = X[rows, flat.feature[at[rows]]] <= thr[at[rows]]
+        at[rows] = np.where(go_left, flat.left[at[rows]], flat.right[at[rows]])
+
+
 def _as_feature_matrix(X: np.ndarray) -> np.ndarray:
     """Keep numeric dtypes numeric; leave genuine object/string columns as objects."""
     if X.dtype.kind in "US":
@@ -241,6 +277,8 @@ class DecisionTreeClassifier(ClassifierMixin, BaseEstimator):
             None if flat.feature[i] < 0 else mapper.threshold_of(int(flat.feature[i]), int(flat.bin[i]))
             for i in range(flat.n_nodes)
         ]
+        if comm is None or comm.size == 1:
+            _restore_zero_signs(flat, X)
         if not local:
             self.bin_mapper_ = mapper
             self.engine_ = engine

@@ -112,15 +112,29 @@ def test_random_integer_datasets_match_reference(ref, data, depth, mss):
 @given(seed=st.integers(0, 10_000), n=st.integers(20, 120), k=st.integers(2, 9))
 def test_random_continuous_match_reference(ref, seed, n, k):
     rng = np.random.default_rng(seed)
-    # `+ 0.0` folds -0.0 into 0.0: with both zeros in a column the sign the reference prints depends on
-    # the row order inside its object-array sort (values compare equal, trees are the same)
-    X = rng.normal(size=(n, 3)).round(2) + 0.0
+    X = rng.normal(size=(n, 3)).round(2)  # rounding leaves negative zeros in: their printed sign must match too
     y = rng.integers(0, k, size=n)
     y[:k] = np.arange(k)  # contiguous labels so the reference's predict works
     ours = DecisionTreeClassifier(max_depth=4, device="cpu").fit(X, y)
     theirs = ref.DecisionTreeClassifier(max_depth=4).fit(X, y)
     assert ours.export_text() == theirs.export_text()
     assert np.array_equal(ours.predict_proba(X), theirs.predict_proba(X))
+
+
+@pytest.mark.parametrize("seed", [8, 9, 24, 1284, 100023])
+def test_signed_zero_thresholds_print_like_the_reference(ref, seed):
+    """A column with both -0.0 and 0.0: the reference prints whichever its per-node np.unique keeps."""
+    rng = np.random.default_rng(seed)
+    n = int(rng.integers(40, 120))
+    X = rng.normal(size=(n, 3)).round(1)
+    X[rng.random((n, 3)) < 0.15] = 0.0
+    X[rng.random((n, 3)) < 0.15] = -0.0
+    y = rng.integers(0, 3, size=n)
+    ours = DecisionTreeClassifier(device="cpu").fit(X, y)
+    theirs = ref.DecisionTreeClassifier().fit(X, y)
+    assert "0.00]" in theirs.export_text()
+    assert ours.export_text() == theirs.export_text()
+    assert ours.export_text(precision=1) == theirs.export_text(precision=1)
 
 
 def test_string_features_ordinal(ref):
