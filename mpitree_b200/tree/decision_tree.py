@@ -121,10 +121,21 @@ def _as_feature_matrix(X: np.ndarray) -> np.ndarray:
     if X.dtype.kind in "US":
         return X.astype(object)
     if X.dtype == object:
-        try:
-            return X.astype(np.float64)
-        except (TypeError, ValueError):
-            return X
+        # An object array whose columns all hold one kind of number becomes that numeric dtype
+        # (thresholds keep their Python type: int stays int).  Anything else stays an object
+        # array and takes the ordinal path: strings (also numeric-looking ones, which the
+        # reference orders as text), mixed int / float columns, ints beyond 64 bits.
+        kinds = set()
+        for f in range(X.shape[1]):
+            try:
+                kinds.add(np.array(X[:, f].tolist()).dtype.kind)
+            except (TypeError, ValueError):
+                return X
+        if len(kinds) == 1 and next(iter(kinds)) in "biuf":
+            out = np.array(X.tolist())
+            if out.shape == X.shape and out.dtype.kind in "biuf":
+                return out
+        return X
     return X
 
 

@@ -137,6 +137,26 @@ def test_signed_zero_thresholds_print_like_the_reference(ref, seed):
     assert ours.export_text(precision=1) == theirs.export_text(precision=1)
 
 
+def test_object_arrays_keep_the_reference_semantics(ref):
+    """Numeric-looking strings are ordered as text, object ints keep int thresholds (found by a random sweep)."""
+    X = np.array([["10"], ["9"], ["100"], ["9"], ["10"], ["8"]], dtype=object)
+    y = np.array([0, 1, 0, 1, 0, 1])
+    ours = DecisionTreeClassifier(device="cpu").fit(X, y)
+    theirs = ref.DecisionTreeClassifier().fit(X, y)
+    assert ours.tree_.threshold == theirs.tree_.threshold == "100"
+    assert np.array_equal(ours.predict(X), theirs.predict(X))
+    rng = np.random.default_rng(3)
+    X = rng.integers(0, 4, size=(40, 2)).astype(object)
+    y = rng.integers(0, 3, size=40)
+    ours = DecisionTreeClassifier(device="cpu").fit(X, y)
+    theirs = ref.DecisionTreeClassifier().fit(X, y)
+    assert ours.export_text() == theirs.export_text()
+    _trees_equal(ours.tree_, theirs.tree_)  # includes type(threshold) is int
+    mixed = np.array([[1, 2.5], [2, 0.5], [3, 1.5], [1, 2.0]], dtype=object)  # int column next to a float column
+    ym = np.array([0, 1, 1, 0])
+    _trees_equal(DecisionTreeClassifier(device="cpu").fit(mixed, ym).tree_, ref.DecisionTreeClassifier().fit(mixed, ym).tree_)
+
+
 def test_string_features_ordinal(ref):
     X = np.array([["apple", "x"], ["banana", "y"], ["cherry", "x"], ["date", "y"], ["elder", "x"], ["fig", "y"]], dtype=object)
     y = np.array([0, 0, 0, 1, 1, 1])
