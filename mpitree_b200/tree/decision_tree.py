@@ -194,7 +194,9 @@ class DecisionTreeClassifier(ClassifierMixin, BaseEstimator):
         if md is not None:
             if not isinstance(md, numbers.Integral) or md < 0:
                 raise ValueError("max_depth must be a non-negative integer or None")
-            md = max(int(md) - depth_offset, 0)
+            # the reference stops on ``max_depth == depth`` (``:121``): a subtree started below
+            # max_depth never meets the test and grows without a depth limit
+            md = int(md) - depth_offset if int(md) >= depth_offset else None
         return SplitParams(max_depth=md, min_samples_split=int(self.min_samples_split), criterion=self.criterion)
 
     def _communicator(self):
@@ -236,17 +238,20 @@ class DecisionTreeClassifier(ClassifierMixin, BaseEstimator):
         hist = np.zeros((1, B, C), dtype=np.int64)
         np.add.at(hist[0], (codes, y_codes), 1)
         res = best_split(hist, mapper.n_bins, self.criterion)
+        as_input = (lambda t: X.dtype.type(t)) if X.dtype != object and X.dtype.kind in "biuf" else (lambda t: t)
         if res is None:
-            return 0.0, mapper.threshold_of(0, B - 1)
+            return 0.0, as_input(mapper.threshold_of(0, B - 1))
         _, b, gain, _ = res
-        return max(gain, 0.0) if gain < 0 else gain, mapper.threshold_of(0, b)
+        return max(gain, 0.0) if gain < 0 else gain, as_input(mapper.threshold_of(0, b))
 
     def _make_tree(self, X, y, *, parent=None, depth=0):
         """Build the subtree for ``(X, y)`` and return its root ``Node`` (reference ``:93-166``)."""
-        flat = self._fit_flat(np.asarray(X), np.asarray(y), depth_offset=depth, comm=None, local=True)
+        X = np.asarray(X)
+        flat = self._fit_flat(X, np.asarray(y), depth_offset=depth, comm=None, local=True)
         root = flat.to_nodes()
         if parent is not None or depth:
             _reparent(root, parent, depth)
+        _match_threshold_types(root, X)
         return root
 
     # ------------------------------------------------------------------- fit
@@ -425,9 +430,21 @@ class DecisionTreeClassifier(ClassifierMixin, BaseEstimator):
         return tags
 
 
+def _match_threshold_types(root: Node, X: np.ndarray) -> None:
+    """Thresholds are elements of ``np.unique(X[:, f])`` in the reference (``:73``, ``:91``): numpy
+    scalars when ``_make_tree`` is handed a numeric array, Python objects after ``fit``'s object cast."""
+    if X.dtype == object or X.dtype.kind not in "biuf":
+        return
+    for n in root.iter_preorder():
+        if not n.is_leaf:
+            n.threshold = X.dtype.type(n.threshold)
+
+
 def _reparent(root: Node, parent: Optional[Node], depth: int) -> None:
     root.parent = parent
-    base = parent.depth + 1 if parent is not None else depth
+    # Node.depth follows the parent chain only (reference ``_base.py:59-61``); the ``depth`` argument
+    # of ``_make_tree`` feeds the max_depth stop rule and nothing else (``:121``)
+    base = parent.depth + 1 if parent is not None else 0
     for n in root.iter_preorder():
         n.depth = base if n is root else n.parent.depth + 1
 

@@ -157,6 +157,36 @@ def test_object_arrays_keep_the_reference_semantics(ref):
     _trees_equal(DecisionTreeClassifier(device="cpu").fit(mixed, ym).tree_, ref.DecisionTreeClassifier().fit(mixed, ym).tree_)
 
 
+@pytest.mark.parametrize("depth,max_depth", [(0, 2), (1, 2), (2, 2), (3, 2), (1, None)])
+def test_make_tree_called_directly_matches_reference(ref, depth, max_depth):
+    """``_make_tree(X, y, parent=, depth=)`` as a public-ish entry point (reference ``:93-166``).
+
+    ``depth`` only feeds the ``max_depth == depth`` stop test (a start below max_depth never stops on
+    depth); ``Node.depth`` follows the parent chain; thresholds of a numeric array are numpy scalars.
+    """
+    rng = np.random.default_rng(11)
+    X = rng.normal(size=(60, 3)).round(1)
+    y = rng.integers(0, 3, size=60)
+    ours, theirs = DecisionTreeClassifier(max_depth=max_depth, device="cpu"), ref.DecisionTreeClassifier(max_depth=max_depth)
+    for clf in (ours, theirs):
+        clf.classes_, clf.n_features_ = np.unique(y), 3
+    a, b = ours._make_tree(X, y, depth=depth), theirs._make_tree(X, y, depth=depth)
+    _trees_equal(a, b)
+    assert a.depth == b.depth == 0 and a.parent is None
+    if not b.is_leaf:
+        assert type(a.threshold) is type(b.threshold) is np.float64
+    from mpitree_b200.tree._base import Node
+
+    RefNode = type(theirs._make_tree(X, y))  # the reference's own Node class
+    pa, pb = Node(value=0, threshold=0.0, depth=4), RefNode(value=0, threshold=0.0, depth=4)
+    a, b = ours._make_tree(X, y, parent=pa, depth=depth), theirs._make_tree(X, y, parent=pb, depth=depth)
+    _trees_equal(a, b)
+    assert a.depth == b.depth == 5 and a.parent is pa
+    for f in range(3):
+        ga, gb = ours._compute_information_gain(X, y, f), theirs._compute_information_gain(X, y, f)
+        assert ga == gb and type(ga[1]) is type(gb[1])
+
+
 def test_string_features_ordinal(ref):
     X = np.array([["apple", "x"], ["banana", "y"], ["cherry", "x"], ["date", "y"], ["elder", "x"], ["fig", "y"]], dtype=object)
     y = np.array([0, 0, 0, 1, 1, 1])
@@ -180,4 +210,5 @@ def test_internal_helpers_match_reference(ref, iris):
     ours.n_features_ = theirs.n_features_ = 4
     sub = ours._make_tree(X[:100], y[:100], depth=1)
     sub_ref = theirs._make_tree(Xo[:100], y[:100], depth=1)
-    assert sub.depth == 1 and int(sub.value) == int(sub_ref.value) and sub.threshold == sub_ref.threshold
+    # Node.depth follows the parent chain (none here); the depth argument only feeds the stop rule
+    assert sub.depth == sub_ref.depth == 0 and int(sub.value) == int(sub_ref.value) and sub.threshold == sub_ref.threshold
