@@ -72,27 +72,30 @@ class BinMapper:
     ) -> "BinMapper":
         """Compute edges from ``X`` (n_rows, n_features).
 
-        ``summaries`` optionally carries, per *other* rank, a list of per-feature
-        value arrays (uniques or quantile sketches) to merge with the local
-        ones so that every rank derives identical edges (the cross-rank "edge
-        agreement" step of K1).
+        ``summaries`` (multi-rank fits) is the all-gathered list of every rank's
+        :meth:`local_summary`, own rank included, in rank order.  The edges are then derived from
+        the summaries alone, with the same operations in the same order on every rank, so all
+        ranks end up with identical bins (the cross-rank "edge agreement" step of K1) whatever
+        their local rows are.
         """
         if not 2 <= max_bins <= 256:
             raise ValueError("max_bins must be in [2, 256]")
         n_features = X.shape[1]
         edges, lossless = [], np.zeros(n_features, dtype=bool)
         for f in range(n_features):
-            values = _column_uniques(X[:, f]) if X.shape[0] else np.zeros(0, X.dtype)
             if summaries:
-                parts = [values] + [np.asarray(s[f]) for s in summaries]
+                parts = [np.asarray(s[f]) for s in summaries]
                 parts = [p for p in parts if len(p)]
-                if parts:
-                    values = _column_uniques(np.concatenate(parts))
+                values = _column_uniques(np.concatenate(parts)) if parts else np.zeros(0, X.dtype)
+                weighted = values  # the summaries carry no multiplicities: quantiles over distinct values
+            else:
+                values = _column_uniques(X[:, f]) if X.shape[0] else np.zeros(0, X.dtype)
+                weighted = X[:, f]
             if len(values) <= max_bins:
                 edges.append(values)
                 lossless[f] = True
             else:
-                edges.append(_quantile_edges(values, X[:, f], max_bins))
+                edges.append(_quantile_edges(values, weighted, max_bins))
         return cls(edges=edges, lossless=lossless, max_bins=max_bins)
 
     @staticmethod

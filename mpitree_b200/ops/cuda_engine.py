@@ -850,7 +850,7 @@ def _fit_mapper_numpy(X: np.ndarray, max_bins: int, comm=None) -> BinMapper:
     summaries = None
     if comm is not None and comm.size > 1:
         mine = BinMapper.local_summary(sample)
-        summaries = [s for r, s in enumerate(comm.allgather_object(mine)) if r != comm.rank]
+        summaries = comm.allgather_object(mine)  # every rank, own one included, in rank order
     mapper = BinMapper.fit(sample, max_bins=max_bins, summaries=summaries)
     if idx is not None and X.shape[0]:
         # cover values the sample did not see: the last edge must be the column maximum

@@ -276,7 +276,7 @@ class DecisionTreeClassifier(ClassifierMixin, BaseEstimator):
             summaries = None
             if comm is not None and comm.size > 1:
                 mine = BinMapper.local_summary(X)
-                summaries = [s for r, s in enumerate(comm.allgather_object(mine)) if r != comm.rank]
+                summaries = comm.allgather_object(mine)  # every rank, own one included, in rank order
             mapper = BinMapper.fit(X, max_bins=self.max_bins, summaries=summaries)
             codes = mapper.transform(X)
             flat = fit_flat_tree_host(
@@ -310,9 +310,12 @@ class DecisionTreeClassifier(ClassifierMixin, BaseEstimator):
         self.n_features_ = X.shape[1]
         self.n_features_in_ = X.shape[1]
         self.classes_ = np.unique(y)
+        X_all = X
         X, y = self._shard(X, y, comm)
         self.__dict__.pop("tree_", None)
         self.flat_tree_ = self._fit_flat(X, y, comm=comm)
+        if X is not X_all:  # replicated layout on several ranks: every rank still holds all rows
+            _restore_zero_signs(self.flat_tree_, _as_feature_matrix(X_all))
         return self
 
     def _fit_torch(self, X, y, comm):
@@ -537,7 +540,8 @@ class ParallelDecisionTreeClassifier(DecisionTreeClassifier):
         comm = self._communicator()
         if self.data_layout == "sharded" and comm.size > 1 and not _is_torch_tensor(X):
             # classes must be agreed on globally before encoding labels
-            X, y = check_X_y(X, y, dtype=None, ensure_all_finite=True)
+            # a rank may legitimately hold no rows of a small sharded data set
+            X, y = check_X_y(X, y, dtype=None, ensure_all_finite=True, ensure_min_samples=0)
             y = _validate_labels(y)
             parts = comm.allgather_object(np.unique(y))
             self.n_features_ = X.shape[1]

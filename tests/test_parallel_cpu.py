@@ -178,3 +178,46 @@ def test_two_process_gloo_torchrun(tmp_path):
     res = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=300)
     assert res.returncode == 0, res.stdout + res.stderr
     assert "GLOO_OK 0.97" in res.stdout
+
+
+def _fit_sharded(comm, X, y, kw):
+    cuts = [X.shape[0] * r // comm.size for r in range(comm.size + 1)]
+    lo, hi = cuts[comm.rank], cuts[comm.rank + 1]
+    clf = ParallelDecisionTreeClassifier(comm=comm, device="cpu", data_layout="sharded", **kw).fit(X[lo:hi], y[lo:hi])
+    return clf.export_text(), clf.predict(X).tolist()
+
+
+def test_sharded_quantile_bins_agree_across_ranks():
+    """More distinct values than bins: every rank must derive the same edges from the merged summaries
+    (a random sweep found rank-local quantiles, i.e. different histogram shapes per rank)."""
+    rng = np.random.default_rng(542)
+    X = rng.random((293, 2)) * 1000
+    y = rng.integers(0, 4, size=293)
+    for world in (2, 4):
+        out = run_threaded(world, _fit_sharded, X, y, dict(max_depth=3, handoff_rows=0))
+        assert all(o == out[0] for o in out)
+    out = run_threaded(3, _fit_rank, X, y, dict(max_depth=3, handoff_rows=1000))  # replicated layout, hand-off path
+    assert all(o == out[0] for o in out)
+
+
+def test_sharded_ranks_may_hold_no_rows():
+    X = np.array([[0.0, 1.0], [1.0, 0.0], [2.0, 1.0], [3.0, 0.0]])
+    y = np.array([0, 0, 1, 1])
+    want = DecisionTreeClassifier(device="cpu").fit(X, y)
+    out = run_threaded(7, _fit_sharded, X, y, {})
+    assert all(o == (want.export_text(), want.predict(X).tolist()) for o in out)
+
+
+def test_ranks_agree_on_the_printed_sign_of_zero():
+    """-0.0 and 0.0 in one column: replicated fits print the reference's choice, sharded fits at least
+    the same text on every rank."""
+    rng = np.random.default_rng(540)
+    X = rng.normal(size=(99, 2)).round(1)
+    y = rng.integers(0, 2, size=99)
+    assert np.signbit(X[X == 0]).any() and not np.signbit(X[X == 0]).all()
+    want = DecisionTreeClassifier(device="cpu").fit(X, y).export_text()
+    out = run_threaded(7, _fit_rank, X, y, dict(handoff_rows=0))
+    assert [o[0] for o in out] == [want] * 7
+    out = run_threaded(3, _fit_sharded, X, y, dict(handoff_rows=0))
+    assert all(o == out[0] for o in out)
+    assert out[0][0].replace("-0.00", "0.00") == want.replace("-0.00", "0.00")
