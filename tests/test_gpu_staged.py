@@ -183,3 +183,50 @@ def test_nvls_tree_equals_p2p(tmp_path):
     res = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=600)
     assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
     assert f"NVLS_TREE_OK {world}" in res.stdout or "NVLS_UNSUPPORTED" in res.stdout
+
+
+_FLOAT_SHARD_WORKER = r"""
+import os, sys
+sys.path.insert(0, os.environ["REPO"])
+import numpy as np, torch, torch.distributed as dist
+from mpitree_b200.parallel.comm import TorchComm, init_process_group_from_env
+from mpitree_b200.tree import ParallelDecisionTreeClassifier
+assert init_process_group_from_env("nccl")
+rank, world = dist.get_rank(), dist.get_world_size()
+rng = np.random.default_rng(0)
+n = 300_000
+X = rng.normal(size=(n, 12)).astype(np.float32)            # far more distinct values than bins
+y = (X[:, 0] + X[:, 3] * X[:, 5] + rng.normal(scale=0.5, size=n) > 0).astype(np.int64)
+lo, hi = n * rank // world, n * (rank + 1) // world
+clf = ParallelDecisionTreeClassifier(max_depth=8, device="cuda", data_layout="sharded").fit(X[lo:hi], y[lo:hi])
+texts = TorchComm().allgather_object(clf.export_text())
+assert all(t == texts[0] for t in texts), "ranks derived different trees (bin edges must be agreed on)"
+acc = float((clf.predict(X[:20000]) == y[:20000]).mean())
+assert acc > 0.8, acc
+dist.barrier()
+if rank == 0:
+    print("FLOAT_SHARD_OK", world, round(acc, 3))
+dist.destroy_process_group()
+"""
+
+
+@pytest.mark.multigpu
+def test_sharded_float_numpy_ranks_agree(tmp_path):
+    """numpy float input, row-sharded: every rank must bin with the same edges (fixed on the host path
+    after a CPU sweep; this is the same code feeding the CUDA engine)."""
+    import subprocess
+    import sys
+
+    import torch
+
+    world = min(torch.cuda.device_count(), 8)
+    if world < 2:
+        pytest.skip("needs at least two GPUs")
+    script = tmp_path / "float_shard_worker.py"
+    script.write_text(_FLOAT_SHARD_WORKER)
+    env = dict(os.environ, REPO=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
+           "--master-addr", "127.0.0.1", "--master-port", "29659", str(script)]
+    res = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=600)
+    assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
+    assert f"FLOAT_SHARD_OK {world}" in res.stdout
