@@ -151,6 +151,13 @@ sub = clf._get_cyclic_dist(clf.WORLD_COMM, n_blocks=2)
 assert sub.size == 1
 meta = clf.WORLD_COMM.allgather_ints([dist.get_rank(), 7])
 assert meta.tolist() == [[0, 7], [1, 7]]
+# row-sharded continuous data (more distinct values than bins): both processes must bin identically
+rng = np.random.default_rng(0)
+Xc, yc = rng.random((400, 3)) * 100, rng.integers(0, 3, size=400)
+half = slice(0, 200) if dist.get_rank() == 0 else slice(200, 400)
+sh = ParallelDecisionTreeClassifier(max_depth=4, device="cpu", data_layout="sharded").fit(Xc[half], yc[half])
+texts = clf.WORLD_COMM.allgather_object(sh.export_text())
+assert texts[0] == texts[1]
 # descriptors cross the process boundary (what the VMM / multicast handle exchange relies on)
 import tempfile
 from mpitree_b200.parallel.fdpass import allgather_fds
