@@ -192,12 +192,19 @@ class DecisionTreeClassifier(ClassifierMixin, BaseEstimator):
             raise ValueError("criterion must be 'entropy' or 'gini'")
         md = self.max_depth
         if md is not None:
-            if not isinstance(md, numbers.Integral) or md < 0:
-                raise ValueError("max_depth must be a non-negative integer or None")
+            if isinstance(md, bool) or not isinstance(md, numbers.Real):
+                raise ValueError("max_depth must be a number or None")
+            # the reference's only use of max_depth is ``max_depth == depth`` (``:121``): 2.0 acts like 2,
+            # a negative or fractional value never equals a depth and therefore never stops the growth
+            if md < 0 or md != int(md):
+                md = None
+        if md is not None:
             # the reference stops on ``max_depth == depth`` (``:121``): a subtree started below
             # max_depth never meets the test and grows without a depth limit
             md = int(md) - depth_offset if int(md) >= depth_offset else None
-        return SplitParams(max_depth=md, min_samples_split=int(self.min_samples_split), criterion=self.criterion)
+        # ``n_samples < min_samples_split`` (``:122``) with a fractional value equals the test against its ceiling
+        mss = int(np.ceil(self.min_samples_split))
+        return SplitParams(max_depth=md, min_samples_split=mss, criterion=self.criterion)
 
     def _communicator(self):
         return None

@@ -212,3 +212,13 @@ def test_internal_helpers_match_reference(ref, iris):
     sub_ref = theirs._make_tree(Xo[:100], y[:100], depth=1)
     # Node.depth follows the parent chain (none here); the depth argument only feeds the stop rule
     assert sub.depth == sub_ref.depth == 0 and int(sub.value) == int(sub_ref.value) and sub.threshold == sub_ref.threshold
+
+
+@pytest.mark.parametrize("kw", [dict(max_depth=-1), dict(max_depth=2.0), dict(max_depth=2.5), dict(min_samples_split=2.5),
+                                dict(min_samples_split=7.0), dict(min_samples_split=0), dict(max_depth=0)])
+def test_unusual_parameter_values_act_like_the_reference(ref, kw):
+    """max_depth is only ever compared with ``==`` and min_samples_split with ``<`` (reference ``:121-122``)."""
+    rng = np.random.default_rng(0)
+    X = rng.integers(0, 5, size=(40, 3)).astype(float)
+    y = rng.integers(0, 3, size=40)
+    assert DecisionTreeClassifier(device="cpu", **kw).fit(X, y).export_text() == ref.DecisionTreeClassifier(**kw).fit(X, y).export_text()
