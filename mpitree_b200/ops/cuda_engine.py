@@ -879,6 +879,12 @@ def _fit_mapper_device(sample, max_bins: int, comm=None, col_max=None) -> BinMap
     import torch
 
     K, F = int(sample.shape[0]), int(sample.shape[1])
+    if K == 0:  # a rank without rows still takes part in the agreement, with nothing to contribute
+        np_dtype = np.float64 if sample.dtype == torch.float64 else np.float32
+        parts = [(np.zeros(F, np.int64), np.full((F, 256), np.inf, np_dtype), np.zeros((0, F), np_dtype))]
+        if comm is not None and comm.size > 1:
+            parts = comm.allgather_object(parts[0])
+        return _merge_edge_candidates(parts, F, max_bins, np_dtype, col_max)
     srt = sample.t().contiguous().sort(dim=1).values  # [F, K], rows sorted
     # sorted rows end in +inf / nan when the input has them: one check on the extremes
     if not bool(torch.isfinite(srt[:, [0, -1]]).all()):
@@ -900,6 +906,13 @@ def _fit_mapper_device(sample, max_bins: int, comm=None, col_max=None) -> BinMap
         parts = comm.allgather_object((distinct_h, uniq_h, cand_h))
     else:
         parts = [(distinct_h, uniq_h, cand_h)]
+    return _merge_edge_candidates(parts, F, max_bins, np_dtype, col_max)
+
+
+def _merge_edge_candidates(parts, F: int, max_bins: int, np_dtype, col_max) -> BinMapper:
+    """Reduce every rank's ``(distinct counts, distinct values, order statistics)`` to one edge set.
+
+    Pure function of ``parts`` (in rank order), so every rank derives identical bins."""
     edges, lossless = [], np.zeros(F, dtype=bool)
     for f in range(F):
         all_small = all(int(p[0][f]) <= 256 for p in parts)
@@ -910,6 +923,9 @@ def _fit_mapper_device(sample, max_bins: int, comm=None, col_max=None) -> BinMap
                 lossless[f] = len(parts) == 1 and col_max is None
                 continue
         merged = np.sort(np.concatenate([p[2][:, f] for p in parts]))
+        if len(merged) == 0:  # no rank has any row
+            edges.append(np.zeros(0, dtype=np_dtype))
+            continue
         if len(parts) > 1 or len(merged) > max_bins:
             pick = np.ceil(np.linspace(0.0, 1.0, max_bins + 1)[1:] * (len(merged) - 1)).astype(np.int64)
             merged = merged[pick]

@@ -228,3 +228,25 @@ def test_ranks_agree_on_the_printed_sign_of_zero():
     out = run_threaded(3, _fit_sharded, X, y, dict(handoff_rows=0))
     assert all(o == out[0] for o in out)
     assert out[0][0].replace("-0.00", "0.00") == want.replace("-0.00", "0.00")
+
+
+def test_device_edge_agreement_with_an_empty_rank():
+    """``_fit_mapper_device`` (the torch-tensor front end's K1 agreement) on CPU tensors: three ranks, one
+    of them without rows, must end with identical edges that cover all the data."""
+    import torch
+
+    from mpitree_b200.ops.cuda_engine import _fit_mapper_device
+
+    rng = np.random.default_rng(0)
+    X = np.c_[rng.normal(size=(900, 2)), rng.integers(0, 5, size=(900, 1))].astype(np.float32)
+    shards = [X[:500], X[:0], X[500:]]
+
+    def work(comm):
+        m = _fit_mapper_device(torch.from_numpy(shards[comm.rank]), 64, comm)
+        return [e.tolist() for e in m.edges]
+
+    out = run_threaded(3, work)
+    assert out[0] == out[1] == out[2]
+    assert out[0][2] == [0.0, 1.0, 2.0, 3.0, 4.0]  # few distinct values: kept exactly
+    assert all(2 <= len(e) <= 64 and e == sorted(e) for e in out[0])
+    assert out[0][0][-1] >= np.quantile(X[:, 0], 0.98)
