@@ -250,3 +250,23 @@ def test_device_edge_agreement_with_an_empty_rank():
     assert out[0][2] == [0.0, 1.0, 2.0, 3.0, 4.0]  # few distinct values: kept exactly
     assert all(2 <= len(e) <= 64 and e == sorted(e) for e in out[0])
     assert out[0][0][-1] >= np.quantile(X[:, 0], 0.98)
+
+
+def test_numpy_front_end_edge_agreement_on_thread_ranks():
+    """``_fit_mapper_numpy`` feeds the CUDA engine for numpy inputs: the merged summaries must give every
+    rank the same edges (uneven shards, one empty), and the edges must cover every value."""
+    from mpitree_b200.ops import cuda_engine as ce
+
+    rng = np.random.default_rng(1)
+    X = np.c_[rng.normal(size=(5000, 2)), rng.integers(0, 7, size=(5000, 1))].astype(np.float32)
+    X[4999, 0] = 1e6
+    cuts = [0, 700, 700, 3100, 5000]  # uneven shards, one of them empty
+
+    def work(comm):
+        m = ce._fit_mapper_numpy(X[cuts[comm.rank] : cuts[comm.rank + 1]], 32, comm)
+        return [e.tolist() for e in m.edges]
+
+    out = run_threaded(4, work)
+    assert all(o == out[0] for o in out)
+    assert out[0][2] == [0.0, 1.0, 2.0, 3.0, 4.0, 5.0, 6.0]
+    assert out[0][0][-1] == 1e6 and all(len(e) <= 32 for e in out[0])
