@@ -837,8 +837,9 @@ class _Stages:
             print("[mtb timing] " + "  ".join(f"{n}={ms:.2f}ms" for n, ms in self.rows), flush=True)
 
 
-def _sample_rows(n: int, cap: int = SAMPLE_ROWS) -> Optional[np.ndarray]:
+def _sample_rows(n: int, cap: Optional[int] = None) -> Optional[np.ndarray]:
     """Indices of an evenly strided sample of ``cap`` rows (``None`` = use every row)."""
+    cap = SAMPLE_ROWS if cap is None else cap
     if n <= cap:
         return None
     return (np.arange(cap, dtype=np.int64) * n) // cap  # strictly increasing because n > cap
@@ -852,11 +853,17 @@ def _fit_mapper_numpy(X: np.ndarray, max_bins: int, comm=None) -> BinMapper:
         mine = BinMapper.local_summary(sample)
         summaries = comm.allgather_object(mine)  # every rank, own one included, in rank order
     mapper = BinMapper.fit(sample, max_bins=max_bins, summaries=summaries)
-    if idx is not None and X.shape[0]:
-        # cover values the sample did not see: the last edge must be the column maximum
-        col_max = X.max(axis=0)
-        if comm is not None and comm.size > 1:
-            col_max = np.max(np.stack(comm.allgather_object(col_max)), axis=0)
+    # cover values the sample did not see: the last edge must be the column maximum.  With several
+    # ranks the exchange is unconditional (a collective inside a rank-local test would hang when
+    # only some shards are large enough to be sampled) and applies when any rank sampled.
+    sampled = idx is not None
+    col_max = X.max(axis=0) if X.shape[0] else None
+    if comm is not None and comm.size > 1:
+        got = comm.allgather_object((sampled, col_max))
+        sampled = any(g[0] for g in got)
+        maxima = [g[1] for g in got if g[1] is not None]
+        col_max = np.max(np.stack(maxima), axis=0) if maxima else None
+    if sampled and col_max is not None:
         for f, e in enumerate(mapper.edges):
             if len(e) and col_max[f] > e[-1]:
                 if len(e) < max_bins:
@@ -1060,11 +1067,14 @@ def fit_from_torch(X, y, params: SplitParams, *, max_bins: int = 256, comm=None,
     else:
         idx = _sample_rows(n)
         sample = X if idx is None else X[torch.from_numpy(idx).to(X.device)]
-        col_max = None
-        if idx is not None:
-            col_max = X.max(dim=0).values.cpu().numpy()
-            if comm is not None and comm.size > 1:
-                col_max = np.max(np.stack(comm.allgather_object(col_max)), axis=0)
+        col_max = X.max(dim=0).values.cpu().numpy() if idx is not None else None
+        if comm is not None and comm.size > 1 and int(meta[:, 1].max()) > SAMPLE_ROWS:
+            # some rank sampled its rows: every rank joins the exchange of column maxima (the shard
+            # sizes come from the all-gather above, so the decision is the same everywhere)
+            if col_max is None and n:
+                col_max = X.max(dim=0).values.cpu().numpy()
+            maxima = [m for m in comm.allgather_object(col_max) if m is not None]
+            col_max = np.max(np.stack(maxima), axis=0)
         mapper = _fit_mapper_device(sample.to(dev, non_blocking=True), max_bins, comm, col_max)
 
     st.mark("meta+mapper")

@@ -270,3 +270,24 @@ def test_numpy_front_end_edge_agreement_on_thread_ranks():
     assert all(o == out[0] for o in out)
     assert out[0][2] == [0.0, 1.0, 2.0, 3.0, 4.0, 5.0, 6.0]
     assert out[0][0][-1] == 1e6 and all(len(e) <= 32 for e in out[0])
+
+
+def test_numpy_front_end_sampling_decision_is_collective(monkeypatch):
+    """Only one shard is large enough to be sampled: the maximum exchange must still involve every rank."""
+    from mpitree_b200.ops import cuda_engine as ce
+
+    monkeypatch.setattr(ce, "SAMPLE_ROWS", 256)
+    rng = np.random.default_rng(2)
+    X = rng.normal(size=(3000, 2)).astype(np.float32)
+    X[2999, 1] = 77.0  # odd position in the big shard: a strided sample skips it
+    cuts = [0, 100, 3000]
+
+    def work(comm):
+        lo, hi = cuts[comm.rank], cuts[comm.rank + 1]
+        idx = ce._sample_rows(hi - lo, 256)
+        m = ce._fit_mapper_numpy(X[lo:hi], 16, comm)
+        return idx is not None, [e.tolist() for e in m.edges]
+
+    out = run_threaded(2, work)
+    assert [o[0] for o in out] == [False, True]
+    assert out[0][1] == out[1][1] and out[0][1][1][-1] == 77.0
