@@ -300,6 +300,10 @@ class DecisionTreeClassifier(ClassifierMixin, BaseEstimator):
             None if flat.feature[i] < 0 else mapper.threshold_of(int(flat.feature[i]), int(flat.bin[i]))
             for i in range(flat.n_nodes)
         ]
+        if engine == "cuda" and X.dtype.kind in "iub":
+            # the CUDA engine bins integer columns through a float edge table: hand thresholds back in
+            # the column's own type, as the host engine and the reference do (int stays int)
+            flat.thresholds = [None if t is None else X.dtype.type(t).item() for t in flat.thresholds]
         if comm is None or comm.size == 1:
             _restore_zero_signs(flat, X)
         if not local:
