@@ -185,3 +185,63 @@ def test_tree_builder_host_setup_runs_without_a_gpu():
         assert b.h_cap == 16
     with pytest.raises(ValueError):
         ce.TreeBuilder(Data(), 256, SplitParams(max_depth=5), hist_budget_bytes=64 << 20, tile_layout="diagonal")
+
+
+def test_interleaved_tile_index_arithmetic_host_emulation():
+    """Host emulation of ``tile_count_il`` + the interleaved ``flush_tile`` (csrc/build.cu, staged path).
+
+    Mirrors the kernel's integer arithmetic step by step: the per-lane byte rotation
+    (word swaps + ``__byte_perm``), the ``[cell][16]`` tile address, and the flush's lane -> (cell, feature
+    quad) mapping.  Checks that every (feature, bin, class) count lands in the ``[f][B][C]`` slab exactly
+    once.  It pins the index algebra, not the CUDA code itself (that is ``tests/test_gpu_staged.py``).
+    """
+
+    def byte_perm(a, b, sel):
+        by = [(a >> (8 * i)) & 255 for i in range(4)] + [(b >> (8 * i)) & 255 for i in range(4)]
+        return sum(by[(sel >> (4 * n)) & 7] << (8 * n) for n in range(4))
+
+    rng = np.random.default_rng(0)
+    B, C = 256, 10
+    BC = B * C
+    tile = np.zeros(BC * 16, np.int64)
+    want = np.zeros((16, B, C), np.int64)
+    for row in range(1500):
+        lane = row % 32
+        codes = rng.integers(0, 256, 16)
+        lab = int(rng.integers(0, C))
+        w = [int(sum(int(codes[4 * i + j]) << (8 * j) for j in range(4))) for i in range(4)]
+        rot = lane & 15
+        if rot & 4:
+            w = [w[1], w[2], w[3], w[0]]
+        if rot & 8:
+            w = [w[2], w[3], w[0], w[1]]
+        sel = 0x3210 + 0x1111 * (rot & 3)
+        y = [byte_perm(w[i], w[(i + 1) & 3], sel) for i in range(4)]
+        for k in range(16):
+            f = (k + rot) & 15
+            code = (y[k >> 2] >> ((k & 3) * 8)) & 255
+            assert code == codes[f]
+            tile[lab * 16 + code * C * 16 + f] += 1
+        want[np.arange(16), codes, lab] += 1
+    slab = np.zeros(16 * BC, np.int64)
+    hits = np.zeros(16 * BC, np.int64)
+    for warp in range(16):
+        for c0 in range(warp * 32, BC, 16 * 32):
+            for lane in range(32):
+                q, r = lane & 3, lane >> 2
+                for i in range(4):
+                    cell = c0 + r + 8 * i
+                    if cell < BC:
+                        for j in range(4):
+                            slab[(4 * q + j) * BC + cell] += tile[cell * 16 + 4 * q + j]
+                            hits[(4 * q + j) * BC + cell] += 1
+    assert (hits == 1).all()
+    assert np.array_equal(slab.reshape(16, B, C), want)
+    # bank view: in one instruction (fixed k) the 32 lanes touch 16 features, two lanes each,
+    # and feature f only ever maps to banks f and 16 + f
+    for k in range(16):
+        feats = [(k + (lane & 15)) & 15 for lane in range(32)]
+        assert sorted(feats) == sorted(list(range(16)) * 2)
+    cells = rng.integers(0, BC, 1000)
+    for f in range(16):
+        assert set(((cells * 16 + f) % 32).tolist()) <= {f, 16 + f}
