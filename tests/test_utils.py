@@ -245,3 +245,36 @@ def test_interleaved_tile_index_arithmetic_host_emulation():
     cells = rng.integers(0, BC, 1000)
     for f in range(16):
         assert set(((cells * 16 + f) % 32).tolist()) <= {f, 16 + f}
+
+
+def test_quad_encoder_search_host_emulation():
+    """Host emulation of ``k_encode_f32_quads`` (csrc/encode.cu, staged path): a fixed 8-step branch-free
+    lower bound in a float32 copy of the edge table (edges converted with round-toward-minus-infinity,
+    padded with +inf), clamped to the last real bin, must give the codes of ``BinMapper.transform``."""
+    from mpitree_b200.ops.binning import BinMapper
+
+    rng = np.random.default_rng(0)
+    X = rng.normal(size=(20000, 3)).astype(np.float32)
+    X[:, 2] = rng.integers(0, 9, size=20000)
+    mapper = BinMapper.fit(X[:5000].astype(np.float64) * (1 + 1e-9), max_bins=200)  # float64 edges, not float32 values
+    edges64 = mapper.edges_matrix(np.float64)  # [F][256], +inf padded
+    e32 = edges64.astype(np.float32)
+    too_big = e32.astype(np.float64) > edges64  # round-to-nearest went up: step down to the float32 below
+    e32[too_big] = np.nextafter(e32[too_big], np.float32(-np.inf))
+    assert (e32.astype(np.float64) <= edges64).all()
+    Xs = X.copy()
+    Xs[::101, 0], Xs[::103, 1], Xs[::107, 0] = np.inf, -np.inf, np.nan
+    for f in range(3):
+        x = Xs[:, f]
+        lo = np.zeros(len(x), np.int64)
+        step = 128
+        while step:
+            with np.errstate(invalid="ignore"):
+                lo += np.where(~(e32[f][lo + step - 1] >= x), step, 0)
+            step >>= 1
+        got = np.minimum(lo, mapper.n_bins[f] - 1)
+        finite = np.isfinite(x)
+        want = mapper.transform(Xs[finite].astype(np.float64))[:, f]
+        assert np.array_equal(got[finite], want)
+        assert (got[np.isnan(x)] == mapper.n_bins[f] - 1).all() and (got[x == -np.inf] == 0).all()
+        assert (got[x == np.inf] == mapper.n_bins[f] - 1).all()
