@@ -239,6 +239,17 @@ class FlatTree:
             class_labels=labels if labels.size else None,
         )
 
+    # wire form between ranks of one fit: the arrays as they are (the communicator pickles them);
+    # a subtree exchanged mid-fit carries bin codes, never thresholds, and no compression pass
+    _WIRE = ("feature", "bin", "left", "right", "parent", "depth", "counts", "gain")
+
+    def to_wire(self) -> dict:
+        return {k: getattr(self, k) for k in self._WIRE}
+
+    @classmethod
+    def from_wire(cls, d: dict) -> "FlatTree":
+        return cls(thresholds=[None] * len(d["feature"]), **{k: d[k] for k in cls._WIRE})
+
     def structurally_equal(self, other: "FlatTree") -> bool:
         return (
             self.n_nodes == other.n_nodes

@@ -26,7 +26,7 @@ from ..models.flat_tree import FlatTree
 from ..ops.cpu_engine import SplitParams, build_tree_cpu
 from .handoff import Graft, assign_owners, default_handoff_rows, stitch_subtrees
 
-__all__ = ["fit_flat_tree_host", "resolve_engine"]
+__all__ = ["fit_flat_tree_host", "fit_flat_tree_replicated", "resolve_engine"]
 
 
 def resolve_engine(device: Optional[str], *, numeric: bool, n_classes: int, is_cuda_input: bool = False) -> str:
@@ -80,8 +80,8 @@ def fit_flat_tree_host(
         if comm.rank == 0:
             all_codes = np.concatenate([s[0] for s in shards])
             all_y = np.concatenate([s[1] for s in shards])
-            blob = build_tree_cpu(all_codes, all_y, n_bins, n_classes, params, None).to_bytes()
-        return FlatTree.from_bytes(comm.broadcast_object(blob, src=0))
+            blob = build_tree_cpu(all_codes, all_y, n_bins, n_classes, params, None).to_wire()
+        return FlatTree.from_wire(comm.broadcast_object(blob, src=0))
 
     pending: dict = {}
     trunk = build_tree_cpu(
@@ -121,7 +121,47 @@ def fit_flat_tree_host(
         mine.append((nid, sub))
 
     # phase 2d: exchange finished subtrees (flat arrays) and stitch
-    everyone = comm.allgather_object([(nid, sub.to_bytes()) for nid, sub in mine])
-    grafts = [Graft(nid, FlatTree.from_bytes(blob)) for box in everyone for nid, blob in box]
+    return _exchange_and_stitch(trunk, mine, comm)
+
+
+def _exchange_and_stitch(trunk: FlatTree, mine, comm) -> FlatTree:
+    everyone = comm.allgather_object([(nid, sub.to_wire()) for nid, sub in mine])
+    grafts = [Graft(nid, FlatTree.from_wire(blob)) for box in everyone for nid, blob in box]
     grafts.sort(key=lambda g: g.node_id)
     return stitch_subtrees(trunk, grafts)
+
+
+def fit_flat_tree_replicated(
+    codes: np.ndarray, y: np.ndarray, n_bins: np.ndarray, n_classes: int, params: SplitParams, comm
+) -> FlatTree:
+    """Every rank holds *all* rows (the reference's data layout, ``:356``): no row ever moves.
+
+    The top of the tree is grown redundantly on every rank, with no messages, until nodes are down
+    to ``n / world`` rows (the reference also searches the top splits redundantly, ``:408-419``);
+    those subtrees are then dealt out by size, finished independently from the local copy of the
+    data, and exchanged with a single all-gather of flat arrays (the reference: pickled ``Node``
+    graphs, ``:456-466``).  One collective per fit, and the deep, node-rich part of the tree — where
+    the host engine spends most of its time — is divided among the ranks.
+    """
+    world = comm.size
+    n = int(codes.shape[0])
+    pending: dict = {}
+    trunk = build_tree_cpu(
+        codes, y, n_bins, n_classes, params, None, handoff_rows=max(n // world, 1), pending_out=pending
+    )
+    node_ids = sorted(pending)
+    node_rows = [int(trunk.counts[nid].sum()) for nid in node_ids]
+    owners = assign_owners(node_rows, world) if node_ids else []
+    mine = []
+    for k, nid in enumerate(node_ids):
+        if owners[k] != comm.rank:
+            continue
+        rows = pending[nid]
+        depth0 = int(trunk.depth[nid])
+        sub_params = SplitParams(
+            max_depth=None if params.max_depth is None else params.max_depth - depth0,
+            min_samples_split=params.min_samples_split,
+            criterion=params.criterion,
+        )
+        mine.append((nid, build_tree_cpu(codes[rows], y[rows], n_bins, n_classes, sub_params, None)))
+    return _exchange_and_stitch(trunk, mine, comm)

@@ -45,13 +45,15 @@ from ..models.flat_tree import FlatTree
 from ..ops.binning import BinMapper
 from ..ops.cpu_engine import SplitParams, best_split, exact_entropy
 from ..parallel import comm as _comm
-from ..parallel.scheduler import fit_flat_tree_host, resolve_engine
+from ..parallel.scheduler import fit_flat_tree_host, fit_flat_tree_replicated, resolve_engine
 from ._base import Node
 
 __all__ = ["DecisionTreeClassifier", "ParallelDecisionTreeClassifier"]
 
 #: replicated inputs with at most this many rows are fitted redundantly on every rank (no messages)
 REPLICATED_SERIAL_ROWS = 4096
+#: ... and from this many rows on the subtrees below the redundantly built top are dealt out to the ranks
+REPLICATED_SPLIT_MIN_ROWS = 64
 
 
 def _is_torch_tensor(x) -> bool:
@@ -109,7 +111,8 @@ def _restore_zero_signs(flat: FlatTree, X: np.ndarray) -> None:
     for depth in range(max(todo) + 1):
         for i in todo.get(depth, ()):
             col = X[at == i, int(flat.feature[i])].astype(object)
-            flat.thresholds[i] = next(v for v in np.unique(col) if v == 0)
+            # (a quantile-binned column can have an edge of 0 in a node that holds no zero itself)
+            flat.thresholds[i] = next((v for v in np.unique(col) if v == 0), flat.thresholds[i])
         inner = flat.feature[at] >= 0
         rows = np.flatnonzero(inner)
         go_left = X[rows, flat.feature[at[rows]]] <= thr[at[rows]]
@@ -286,15 +289,14 @@ class DecisionTreeClassifier(ClassifierMixin, BaseEstimator):
                 summaries = comm.allgather_object(mine)  # every rank, own one included, in rank order
             mapper = BinMapper.fit(X, max_bins=self.max_bins, summaries=summaries)
             codes = mapper.transform(X)
-            flat = fit_flat_tree_host(
-                codes,
-                y_codes,
-                mapper.n_bins,
-                len(classes),
-                params,
-                comm,
-                handoff_rows=getattr(self, "handoff_rows", None),
-            )
+            split_comm = getattr(self, "_split_comm", None)
+            if split_comm is not None:  # replicated rows: redundant trunk, subtrees dealt out (see ``fit``)
+                flat = fit_flat_tree_replicated(codes, y_codes, mapper.n_bins, len(classes), params, split_comm)
+            else:
+                flat = fit_flat_tree_host(
+                    codes, y_codes, mapper.n_bins, len(classes), params, comm,
+                    handoff_rows=getattr(self, "handoff_rows", None),
+                )
         flat.class_labels = np.asarray(classes, dtype=np.int64)
         flat.thresholds = [
             None if flat.feature[i] < 0 else mapper.threshold_of(int(flat.feature[i]), int(flat.bin[i]))
@@ -568,16 +570,20 @@ class ParallelDecisionTreeClassifier(DecisionTreeClassifier):
             and self.handoff_rows is None  # an explicit hand-off size asks for the cooperative path
             and np.shape(X)[0] <= REPLICATED_SERIAL_ROWS
         ):
-            # Tiny replicated problem: every rank already holds all rows, so each one simply builds
-            # the (deterministic, identical) tree itself.  This is the reference's own behaviour at
-            # the top of its recursion (redundant split search on every rank, ``:408-419``) and
-            # costs no communication at all.
+            # Small replicated problem: every rank already holds all rows, so nothing has to be
+            # sharded or reduced.  The top of the tree is built redundantly on every rank (the
+            # reference does the same at the top of its recursion, ``:408-419``), the subtrees below
+            # are dealt out and finished independently, and one all-gather distributes them
+            # (``parallel/scheduler.py::fit_flat_tree_replicated``).  Inputs too small to be worth a
+            # collective are simply fitted by every rank.
             serial = DecisionTreeClassifier.fit
             self._solo = True
+            self._split_comm = comm if np.shape(X)[0] >= REPLICATED_SPLIT_MIN_ROWS else None
             try:
                 return serial(self, X, y)
             finally:
                 self._solo = False
+                self._split_comm = None
         return super().fit(X, y)
 
     def _make_tree(self, X, y, *, parent=None, depth=0, comm=None):

@@ -127,3 +127,14 @@ def test_predict_rejects_wrong_feature_count(iris):
         clf.predict(iris.data[:, :3])
     with pytest.raises(ValueError, match="expecting 4 features"):
         clf.predict_proba(np.hstack([iris.data, iris.data[:, :1]]))
+
+
+def test_zero_edge_of_a_quantile_binned_column_without_zero_rows():
+    """More distinct values than bins, both signed zeros present: a node can split at the edge 0 without
+    holding a zero itself (this used to raise StopIteration while restoring the printed sign)."""
+    rng = np.random.default_rng(0)
+    X = rng.normal(size=(3000, 8)).round(2)
+    y = (X[:, 0] + X[:, 1] * X[:, 2] + rng.normal(scale=0.7, size=3000) > 0).astype(int) + (X[:, 3] > 1)
+    assert np.signbit(X[X == 0]).any() and not np.signbit(X[X == 0]).all()
+    clf = DecisionTreeClassifier(device="cpu").fit(X, y)
+    assert clf.score(X, y) > 0.95
