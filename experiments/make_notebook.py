@@ -55,6 +55,16 @@ parallel rows are measured with real processes by `parallel_timing.py` (one `tor
 per `k`); all ranks receive the full data, like the reference.""", None),
     ("code", """x_dim, rows = experiments.cell5()
 experiments.plots(x_dim, rows)""", ["timing.png"]),
+    ("markdown", """A larger replicated problem (3000 x 8 continuous features, unlimited depth), same processes: every
+rank builds the top of the tree redundantly, the subtrees below `n / k` rows are dealt out, one
+all-gather returns them (`parallel/scheduler.py::fit_flat_tree_replicated`).""", None),
+    ("code", """import json, pathlib
+for k in (2, 5, 8):
+    f = pathlib.Path(experiments.HERE) / f"timing_large_k{k}.json"
+    if f.exists():
+        r = json.loads(f.read_text())
+        print(f"k={k}: serial {r['serial_ms']:.0f} ms, parallel {r['parallel_ms']:.0f} ms "
+              f"({r['serial_ms'] / r['parallel_ms']:.1f}x)")""", None),
 ]
 
 
