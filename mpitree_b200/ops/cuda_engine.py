@@ -412,9 +412,7 @@ class TreeBuilder:
         # enqueued without reading anything back between levels (kernels of levels that turn
         # out to be empty return immediately).
         worst_frontier = None if params.max_depth is None else 1 << max(int(params.max_depth) - 1, 0)
-        import os as _os
-
-        if _os.environ.get("MTB_ASYNC") == "0":
+        if os.environ.get("MTB_ASYNC") == "0":
             async_levels = False
         self.async_levels = bool(
             async_levels and not profile and params.max_depth is not None and int(params.max_depth) >= 1
@@ -816,8 +814,6 @@ class _Stages:
     """Optional wall-clock stage timer for ``fit`` (``MTB_TIMING=1``): syncs the device at each mark."""
 
     def __init__(self):
-        import os
-
         self.on = os.environ.get("MTB_TIMING") == "1"
         self.t = time.perf_counter()
         self.rows = []
