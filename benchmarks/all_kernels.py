@@ -1,7 +1,6 @@
 """Exercise every kernel once on moderate shapes (used under ncu to capture one profile per kernel)."""
 import sys
 
-import numpy as np
 import torch
 
 sys.path.insert(0, ".")

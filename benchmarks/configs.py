@@ -12,7 +12,6 @@ import argparse
 import json
 import os
 import sys
-import time
 
 import torch
 import torch.distributed as dist

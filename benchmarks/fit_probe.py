@@ -3,11 +3,9 @@ import argparse
 import json
 import time
 
-import numpy as np
 import torch
 
 from mpitree_b200.ops import cuda_engine
-from mpitree_b200.ops.binning import BinMapper
 from mpitree_b200.ops.cpu_engine import SplitParams
 
 
