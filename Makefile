@@ -16,6 +16,12 @@ bench:            ## headline benchmark on one GPU
 reference:        ## install the unmodified reference for the oracle / reference arm
 	$(PY) baseline/install_ref.py
 
+sweep:            ## random parity sweeps against the unmodified reference (minutes)
+	for m in fit dtypes internals api parallel; do $(PY) tools/parity_sweep.py $$m 0 1000 || exit 1; done
+
+staged:           ## validate and time the opt-in paths of DESIGN.md section 9 (needs a B200)
+	bash benchmarks/run_staged.sh 1
+
 lint:
 	ruff check mpitree_b200 tests bench.py
 
@@ -23,4 +29,4 @@ clean:
 	rm -rf mpitree_b200/lib build *.egg-info .pytest_cache .ruff_cache .hypothesis
 	find . -name __pycache__ -type d -prune -exec rm -rf {} +
 
-.PHONY: build test test-gpu bench reference lint clean
+.PHONY: build test test-gpu bench reference sweep staged lint clean
