@@ -39,6 +39,8 @@ __all__ = [
     "exact_cost",
     "best_split",
     "best_split_many",
+    "best_split_rows",
+    "best_split_rows_many",
     "build_tree_cpu",
     "probe_dot_mode",
     "SplitParams",
@@ -274,6 +276,55 @@ def best_split_rows(
     return f, b, float(gain), left_counts
 
 
+def best_split_rows_many(codes: np.ndarray, y: np.ndarray, n_classes: int, criterion: str = "entropy") -> list:
+    """:func:`best_split_rows` for ``S`` nodes that all hold ``m`` rows: ``codes`` (S, m, F), ``y`` (S, m).
+
+    Deep levels consist of very many small nodes; stacking the nodes of equal size turns their sorts,
+    prefix counts and candidate costs into one set of array operations.  Tie resolution stays per node.
+    """
+    S, m, F = codes.shape
+    if m < 2:
+        return [None] * S
+    group = max(1, _BATCH_CELLS // max(m * F * n_classes, 1))
+    if S > group:
+        out: list = []
+        for s0 in range(0, S, group):
+            out.extend(best_split_rows_many(codes[s0 : s0 + group], y[s0 : s0 + group], n_classes, criterion))
+        return out
+    order = np.argsort(codes, axis=1, kind="stable")  # (S, m, F)
+    cs = np.take_along_axis(codes, order, axis=1)
+    boundary = cs[:, 1:] != cs[:, :-1]  # (S, m-1, F)
+    onehot = np.zeros((S, m, n_classes), dtype=np.int64)
+    onehot[np.arange(S)[:, None], np.arange(m)[None, :], y] = 1
+    total = onehot.sum(axis=1)  # (S, C)
+    left = np.cumsum(onehot[np.arange(S)[:, None, None], order], axis=1)[:, :-1]  # (S, m-1, F, C)
+    right = total[:, None, None, :] - left
+    n_left = np.broadcast_to(np.arange(1, m, dtype=np.int64)[None, :, None], (S, m - 1, F))
+    cost = np.where(boundary, _approx_cost(left, right, n_left, m - n_left, m, criterion), np.inf)
+    fmin_all = cost.min(axis=1)  # (S, F)
+    imp = exact_entropy if criterion == "entropy" else exact_gini
+    results = []
+    for s in range(S):
+        if not boundary[s].any():
+            results.append(None)  # every feature is constant in this node
+            continue
+        fmin = fmin_all[s]
+        best_approx = float(fmin.min())
+        tol = _TOL * (1.0 + abs(best_approx))
+        h_parent = imp(total[s])
+        best = None
+        cache: dict = {}
+        for f in np.flatnonzero(fmin <= best_approx + tol):  # ascending feature index
+            near = np.flatnonzero(cost[s, :, f] <= fmin[f] + tol)  # ascending position == ascending threshold
+            costs = [_exact_cost_cached(cache, left[s, i, f], right[s, i, f], criterion) for i in near]
+            k = int(np.argmin(costs))
+            gain = h_parent - costs[k]
+            if best is None or gain > best[0]:
+                best = (gain, int(f), int(cs[s, near[k], f]), left[s, near[k], f].copy())
+        results.append((best[1], best[2], float(best[0]), best[3]))
+    return results
+
+
 # --------------------------------------------------------------------------
 # level-wise builder
 # --------------------------------------------------------------------------
@@ -370,13 +421,20 @@ def build_tree_cpu(
             order = active[np.argsort(slot[active], kind="stable")]
             bounds = np.searchsorted(slot[order], np.arange(len(frontier) + 1))
             dense = []
-            for s_, nid in enumerate(frontier):
-                lo, hi = bounds[s_], bounds[s_ + 1]
-                if (hi - lo) * 8 < B * C:
-                    rows_ = order[lo:hi]
-                    decisions[nid] = best_split_rows(codes[rows_], y[rows_], C, params.criterion)
+            by_size: dict = {}  # row count -> slots of that size (searched together)
+            for s_ in range(len(frontier)):
+                m_ = int(bounds[s_ + 1] - bounds[s_])
+                if m_ * 8 < B * C:
+                    by_size.setdefault(m_, []).append(s_)
                 else:
                     dense.append(s_)
+            for m_, slots_ in by_size.items():
+                rows_ = order[(bounds[slots_][:, None] + np.arange(m_)[None, :]).reshape(-1)]
+                found = best_split_rows_many(
+                    codes[rows_].reshape(len(slots_), m_, F), y[rows_].reshape(len(slots_), m_), C, params.criterion
+                )
+                for s_, dec in zip(slots_, found):
+                    decisions[frontier[s_]] = dec
         for c0 in range(0, len(dense), chunk):
             part = dense[c0 : c0 + chunk]
             remap = np.full(len(frontier) + 1, -1, dtype=np.int64)
