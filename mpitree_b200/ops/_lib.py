@@ -49,7 +49,11 @@ class MtbCtx(ctypes.Structure):
     _fields_ = (
         [(n, ctypes.c_int64) for n in _names]
         + [("peer_hist", ctypes.c_int64 * 16), ("peer_rec", ctypes.c_int64 * 16), ("peer_flags", ctypes.c_int64 * 16)]
-        + [("epoch", ctypes.c_int64), ("plogp", ctypes.c_int64), ("plogp_n", ctypes.c_int64), ("h_cap", ctypes.c_int64), ("fpo", ctypes.c_int64), ("timers", ctypes.c_int64), ("klogk", ctypes.c_int64), ("klogk_n", ctypes.c_int64), ("rstore", ctypes.c_int64 * 2), ("small_rows", ctypes.c_int64), ("ho_cap", ctypes.c_int64), ("ho_node", ctypes.c_int64), ("ho_begin", ctypes.c_int64), ("ho_end", ctypes.c_int64), ("ho_side", ctypes.c_int64), ("part_child", ctypes.c_int64), ("mask_words", ctypes.c_int64), ("unit_base", ctypes.c_int64), ("tile_layout", ctypes.c_int64), ("mc_hist", ctypes.c_int64 * 2)]
+        + [(n, ctypes.c_int64) for n in "epoch plogp plogp_n h_cap fpo timers klogk klogk_n".split()]
+        + [("rstore", ctypes.c_int64 * 2)]
+        + [(n, ctypes.c_int64) for n in
+           "small_rows ho_cap ho_node ho_begin ho_end ho_side part_child mask_words unit_base tile_layout".split()]
+        + [("mc_hist", ctypes.c_int64 * 2)]
     )
 
 
