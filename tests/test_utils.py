@@ -129,7 +129,7 @@ def test_subtree_record_compaction_keeps_used_prefixes():
 
 
 def test_ctypes_mirror_matches_the_c_header(tmp_path):
-    """``MtbCtx`` / ``MtbSubtreeArgs`` are filled from Python: the mirrors must have the C layout."""
+    """``MtbCtx`` is filled from Python: every field of the mirror must sit at the C struct's offset."""
     import ctypes
     import os
     import shutil
@@ -141,18 +141,19 @@ def test_ctypes_mirror_matches_the_c_header(tmp_path):
     if cxx is None:
         pytest.skip("no C++ compiler")
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-    src = tmp_path / "sz.cpp"
-    src.write_text(
-        '#include "mpitree_b200.h"\n#include <cstdio>\n#include <cstddef>\n'
-        'int main() { std::printf("%zu %zu %zu\\n", sizeof(MtbCtx), offsetof(MtbCtx, tile_layout), '
-        "offsetof(MtbCtx, peer_hist)); }\n"
-    )
-    exe = tmp_path / "sz"
-    subprocess.run([cxx, "-I", os.path.join(root, "include"), str(src), "-o", str(exe)], check=True)
-    size, off_tile, off_peer = map(int, subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.split())
-    assert ctypes.sizeof(L.MtbCtx) == size
-    assert L.MtbCtx.tile_layout.offset == off_tile
-    assert L.MtbCtx.peer_hist.offset == off_peer
+    # codes0/codes1 etc. in the mirror are the elements of the C arrays codes[2] etc.
+    c_name = {"codes0": "codes[0]", "codes1": "codes[1]", "labels0": "labels[0]", "labels1": "labels[1]",
+              "hist0": "hist[0]", "hist1": "hist[1]"}
+    names = [f[0] for f in L.MtbCtx._fields_]
+    prints = "".join(f'  std::printf("%zu\\n", offsetof(MtbCtx, {c_name.get(n, n)}));\n' for n in names)
+    src = tmp_path / "layout.cpp"
+    src.write_text('#include "mpitree_b200.h"\n#include <cstdio>\n#include <cstddef>\n'
+                   f'int main() {{\n  std::printf("%zu\\n", sizeof(MtbCtx));\n{prints}  return 0;\n}}\n')
+    exe = tmp_path / "layout"
+    subprocess.run([cxx, "-Wno-invalid-offsetof", "-I", os.path.join(root, "include"), str(src), "-o", str(exe)], check=True)
+    out = [int(v) for v in subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.split()]
+    assert ctypes.sizeof(L.MtbCtx) == out[0]
+    assert [getattr(L.MtbCtx, n).offset for n in names] == out[1:]
 
 
 def test_tree_builder_host_setup_runs_without_a_gpu():
