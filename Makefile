@@ -17,7 +17,7 @@ reference:        ## install the unmodified reference for the oracle / reference
 	$(PY) baseline/install_ref.py
 
 sweep:            ## random parity sweeps against the unmodified reference (minutes)
-	for m in fit dtypes internals api parallel; do $(PY) tools/parity_sweep.py $$m 0 1000 || exit 1; done
+	for m in engines fit dtypes internals api parallel; do $(PY) tools/parity_sweep.py $$m 0 1000 || exit 1; done
 
 staged:           ## validate and time the opt-in paths of DESIGN.md section 9 (needs a B200)
 	bash benchmarks/run_staged.sh 1

@@ -5,6 +5,7 @@
     python tools/parity_sweep.py internals 0 1500     # _compute_entropy / _compute_information_gain / _make_tree
     python tools/parity_sweep.py api       0 1500     # export_text options, unseen rows, score
     python tools/parity_sweep.py parallel  0 1200     # thread-rank fits (layouts, hand-off sizes) vs serial
+    python tools/parity_sweep.py engines   0 5000     # dense / row / batched-row split search agree (both criteria)
 
 Arguments: mode, first seed, number of seeds.  Every case is generated from its seed alone, so a
 reported seed reproduces on its own (``... <mode> <seed> 1``).  Cases on which the reference itself
@@ -191,7 +192,35 @@ def case_parallel(_ref, s):
     return all(o == (want.export_text(), want.predict(X).tolist(), want.flat_tree_.counts.tolist()) for o in out)
 
 
-CASES = {"fit": case_fit, "dtypes": case_dtypes, "internals": case_internals, "api": case_api, "parallel": case_parallel}
+def case_engines(_ref, s):
+    """The three split-search paths of the host engine (dense histogram, rows, rows batched) on one node,
+    both criteria: same feature, bin, gain bits and left counts."""
+    from mpitree_b200.ops.cpu_engine import best_split, best_split_rows, best_split_rows_many
+
+    rng = np.random.default_rng(s)
+    m, F, C = int(rng.integers(1, 60)), int(rng.integers(1, 6)), int(rng.integers(1, 7))
+    B = int(rng.integers(2, 40))
+    codes = rng.integers(0, B, size=(m, F)).astype(np.uint8)
+    if rng.random() < 0.3:
+        codes[:, 0] = codes[0, 0]  # a constant feature
+    y = rng.integers(0, C, size=m)
+    hist = np.zeros((F, B, C), dtype=np.int64)
+    for f in range(F):
+        np.add.at(hist[f], (codes[:, f], y), 1)
+    ok = True
+    for crit in ("entropy", "gini"):
+        a = best_split(hist, np.full(F, B), crit)
+        b = best_split_rows(codes, y, C, crit)
+        c = best_split_rows_many(np.stack([codes, codes[::-1]]), np.stack([y, y[::-1]]), C, crit)
+        for other in (b, c[0], c[1]):
+            if a is None or other is None:
+                ok = ok and a is None and other is None
+            else:
+                ok = ok and a[0] == other[0] and a[1] == other[1] and a[2] == other[2] and np.array_equal(a[3], other[3])
+    return ok
+
+
+CASES = {"engines": case_engines, "fit": case_fit, "dtypes": case_dtypes, "internals": case_internals, "api": case_api, "parallel": case_parallel}
 
 
 def main():
