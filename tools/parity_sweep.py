@@ -175,15 +175,16 @@ def case_parallel(_ref, s):
     world = int(rng.choice([2, 3, 4, 7]))
     handoff = [None, 0, 1, 8, 40, 1000][int(rng.integers(0, 6))]
     layout = ["replicated", "sharded"][int(rng.integers(0, 2))]
+    crit = ["entropy", "entropy", "gini"][int(rng.integers(0, 3))]
     if layout == "sharded":
         X = X + 0.0  # the printed sign of a zero threshold is only reproduced when a rank sees all rows
-    want = DecisionTreeClassifier(max_depth=depth, min_samples_split=mss, device="cpu").fit(X, y)
+    want = DecisionTreeClassifier(max_depth=depth, min_samples_split=mss, criterion=crit, device="cpu").fit(X, y)
     cuts = [n * r // world for r in range(world + 1)]
 
     def work(comm):
         lo, hi = (0, n) if layout == "replicated" else (cuts[comm.rank], cuts[comm.rank + 1])
-        clf = ParallelDecisionTreeClassifier(max_depth=depth, min_samples_split=mss, device="cpu", comm=comm,
-                                             handoff_rows=handoff, data_layout=layout).fit(X[lo:hi], y[lo:hi])
+        clf = ParallelDecisionTreeClassifier(max_depth=depth, min_samples_split=mss, criterion=crit, device="cpu",
+                                             comm=comm, handoff_rows=handoff, data_layout=layout).fit(X[lo:hi], y[lo:hi])
         return clf.export_text(), clf.predict(X).tolist(), clf.flat_tree_.counts.tolist()
 
     out = run_threaded(world, work)
