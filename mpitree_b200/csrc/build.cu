@@ -216,11 +216,18 @@ __device__ __forceinline__ void tile_count_il(uint32_t* tile, uint4 x, uint32_t 
   const uint32_t sel = 0x3210u + 0x1111u * (uint32_t)(rot & 3);
   const uint4 y = make_uint4(__byte_perm(w0, w1, sel), __byte_perm(w1, w2, sel), __byte_perm(w2, w3, sel),
                              __byte_perm(w3, w0, sel));  // byte k of y = byte (k + rot) mod 16 of x
-  uint32_t* base = tile + lab * 16u;
-  const int cell_stride = C * 16;
+  // byte offsets throughout: one byte-extract (PRMT), one add of the lane's feature offset (loop
+  // invariant per k, kept in registers across rows) and one multiply-add per increment
+  // (shared-window addresses, so the tile base folds into the per-row term)
+  const uint32_t row_base = smem_u32(tile) + lab * 64u;
+  const uint32_t stride_b = (uint32_t)C * 64u;
+  const uint32_t yw[4] = {y.x, y.y, y.z, y.w};
 #pragma unroll
-  for (int k = 0; k < 16; ++k)
-    atomicAdd(base + (int)code_byte(y, k) * cell_stride + ((k + rot) & 15), 1u);
+  for (int k = 0; k < 16; ++k) {
+    const uint32_t code = __byte_perm(yw[k >> 2], 0u, 0x4440u | (uint32_t)(k & 3));
+    const uint32_t addr = code * stride_b + (row_base + (uint32_t)(((k + rot) & 15) * 4));
+    asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(addr), "r"(1u) : "memory");
+  }
 }
 
 // Flush a finished [FT][B][C] tile into the slot's slab.  When this CTA processed every
