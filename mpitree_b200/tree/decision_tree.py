@@ -82,25 +82,33 @@ def _validate_labels(y: np.ndarray) -> np.ndarray:
     return y.astype(np.int64, copy=False)
 
 
-def _restore_zero_signs(flat: FlatTree, X: np.ndarray) -> None:
+def _restore_zero_signs(flat: FlatTree, X: np.ndarray, comm=None) -> None:
     """Give a zero threshold the sign the reference would print (``-0.00`` vs ``0.00``).
 
     ``-0.0 == 0.0``, so both land in one bin and every decision is unaffected; only the printed
     threshold differs.  The reference takes its thresholds from ``np.unique`` of the *node's* object
     column (``:73``), which keeps whichever zero its sort puts first; the same call on the same rows
-    in the same order reproduces that choice.  Only runs when a split column really holds both
-    signs (rare: rounded negative values), and only for a single-rank fit, where this rank sees the
-    node's rows in the reference's order.
+    in the same order reproduces that choice.  Only does anything when a split column really holds
+    both signs (rare: rounded negative values).  With several ranks ``X`` is this rank's shard and
+    the node's column is assembled in rank order (one small all-gather to find out whether any
+    column is affected, then one per tree level that has an affected node); every rank takes the
+    same decisions, so the collectives match up.
     """
-    if X.dtype.kind != "f" or X.shape[0] == 0:
+    multi = comm is not None and comm.size > 1
+    if X.dtype.kind != "f":
         return
     nodes = [i for i in range(flat.n_nodes) if flat.feature[i] >= 0 and flat.thresholds[i] == 0]
-    mixed = set()
-    for f in {int(flat.feature[i]) for i in nodes}:
+    if not nodes:
+        return
+    feats = sorted({int(flat.feature[i]) for i in nodes})
+    signs = {}
+    for f in feats:
         neg = np.signbit(X[X[:, f] == 0, f])
-        if neg.any() and not neg.all():
-            mixed.add(f)
-    nodes = [i for i in nodes if int(flat.feature[i]) in mixed]
+        signs[f] = (bool(neg.any()), bool((~neg).any()))
+    if multi:
+        everyone = comm.allgather_object(signs)
+        signs = {f: (any(e[f][0] for e in everyone), any(e[f][1] for e in everyone)) for f in feats}
+    nodes = [i for i in nodes if all(signs[int(flat.feature[i])])]
     if not nodes:
         return
     thr = np.array([np.nan if t is None else float(t) for t in flat.thresholds])
@@ -109,10 +117,14 @@ def _restore_zero_signs(flat: FlatTree, X: np.ndarray) -> None:
     for i in nodes:
         todo[int(flat.depth[i])].append(i)
     for depth in range(max(todo) + 1):
-        for i in todo.get(depth, ()):
-            col = X[at == i, int(flat.feature[i])].astype(object)
-            # (a quantile-binned column can have an edge of 0 in a node that holds no zero itself)
-            flat.thresholds[i] = next((v for v in np.unique(col) if v == 0), flat.thresholds[i])
+        if depth in todo:
+            cols = {i: X[at == i, int(flat.feature[i])] for i in todo[depth]}
+            if multi:
+                everyone = comm.allgather_object(cols)
+                cols = {i: np.concatenate([e[i] for e in everyone]) for i in todo[depth]}
+            for i, col in cols.items():
+                # (a quantile-binned column can have an edge of 0 in a node that holds no zero itself)
+                flat.thresholds[i] = next((v for v in np.unique(col.astype(object)) if v == 0), flat.thresholds[i])
         inner = flat.feature[at] >= 0
         rows = np.flatnonzero(inner)
         go_left = X[rows, flat.feature[at[rows]]] <= thr[at[rows]]
@@ -306,8 +318,7 @@ class DecisionTreeClassifier(ClassifierMixin, BaseEstimator):
             # the CUDA engine bins integer columns through a float edge table: hand thresholds back in
             # the column's own type, as the host engine and the reference do (int stays int)
             flat.thresholds = [None if t is None else X.dtype.type(t).item() for t in flat.thresholds]
-        if comm is None or comm.size == 1:
-            _restore_zero_signs(flat, X)
+        _restore_zero_signs(flat, X, comm)
         if not local:
             self.bin_mapper_ = mapper
             self.engine_ = engine
@@ -323,12 +334,9 @@ class DecisionTreeClassifier(ClassifierMixin, BaseEstimator):
         self.n_features_ = X.shape[1]
         self.n_features_in_ = X.shape[1]
         self.classes_ = np.unique(y)
-        X_all = X
         X, y = self._shard(X, y, comm)
         self.__dict__.pop("tree_", None)
         self.flat_tree_ = self._fit_flat(X, y, comm=comm)
-        if X is not X_all:  # replicated layout on several ranks: every rank still holds all rows
-            _restore_zero_signs(self.flat_tree_, _as_feature_matrix(X_all))
         return self
 
     def _fit_torch(self, X, y, comm):

@@ -216,8 +216,7 @@ def test_sharded_ranks_may_hold_no_rows():
 
 
 def test_ranks_agree_on_the_printed_sign_of_zero():
-    """-0.0 and 0.0 in one column: replicated fits print the reference's choice, sharded fits at least
-    the same text on every rank."""
+    """-0.0 and 0.0 in one column: replicated and row-sharded fits both print the reference's choice."""
     rng = np.random.default_rng(540)
     X = rng.normal(size=(99, 2)).round(1)
     y = rng.integers(0, 2, size=99)
@@ -225,9 +224,8 @@ def test_ranks_agree_on_the_printed_sign_of_zero():
     want = DecisionTreeClassifier(device="cpu").fit(X, y).export_text()
     out = run_threaded(7, _fit_rank, X, y, dict(handoff_rows=0))
     assert [o[0] for o in out] == [want] * 7
-    out = run_threaded(3, _fit_sharded, X, y, dict(handoff_rows=0))
-    assert all(o == out[0] for o in out)
-    assert out[0][0].replace("-0.00", "0.00") == want.replace("-0.00", "0.00")
+    out = run_threaded(3, _fit_sharded, X, y, dict(handoff_rows=0))  # the node's column is assembled in rank order
+    assert [o[0] for o in out] == [want] * 3
 
 
 def test_device_edge_agreement_with_an_empty_rank():
