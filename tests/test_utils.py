@@ -279,3 +279,57 @@ def test_quad_encoder_search_host_emulation():
         assert np.array_equal(got[finite], want)
         assert (got[np.isnan(x)] == mapper.n_bins[f] - 1).all() and (got[x == -np.inf] == 0).all()
         assert (got[x == np.inf] == mapper.n_bins[f] - 1).all()
+
+
+def test_level_loop_dry_run_launch_sequences(monkeypatch):
+    """The CUDA engine's level loop with every native call replaced by a recorder (CPU tensors, no GPU).
+
+    Exercises set-up, per-level binding, side swapping and the read-back code of each mode and pins the
+    launch sequence a fit enqueues: one cooperative launch per level on the fused path.
+    """
+    import ctypes
+
+    import torch
+
+    from mpitree_b200.ops import _lib as L
+    from mpitree_b200.ops import cuda_engine as ce
+    from mpitree_b200.ops.cpu_engine import SplitParams
+
+    try:
+        L.load()
+    except Exception as exc:  # noqa: BLE001
+        pytest.skip(f"native library unavailable: {exc}")
+    calls = []
+
+    class Stream:
+        def synchronize(self):
+            pass
+
+    monkeypatch.setattr(ce, "_call", lambda name, *a: calls.append(name))
+    monkeypatch.setattr(ce, "_stream_ptr", lambda: ctypes.c_void_p(0))
+    monkeypatch.setattr(torch.cuda, "current_stream", lambda *a, **k: Stream())
+    monkeypatch.setattr(torch.cuda, "synchronize", lambda *a, **k: None)
+    monkeypatch.setattr(torch.Tensor, "pin_memory", lambda self, *a, **k: self)
+
+    class Data:
+        device = torch.device("cpu")
+        n_features, n_classes, G, n_cap, n_local, cur = 64, 10, 4, 4096, 4000, 0
+        codes = [torch.zeros(4 * 4096 * 16, dtype=torch.uint8) for _ in range(2)]
+        labels = [torch.zeros(4096, dtype=torch.uint8) for _ in range(2)]
+
+    def run(**kw):
+        calls.clear()
+        b = ce.TreeBuilder(Data(), 256, SplitParams(max_depth=4), hist_budget_bytes=64 << 20, **kw)
+        monkeypatch.setattr(b, "_launch", lambda name: calls.append(name))
+        flat = b.build()
+        assert flat.n_nodes == 1  # nothing ran: the zero-initialised tree is a single root
+        return b.async_levels, list(calls)
+
+    assert run() == (True, ["mtb_level_fused"] + ["mtb_level_fused2"] * 3)
+    assert run(tile_layout="interleaved")[1] == ["mtb_level_fused"] + ["mtb_level_fused2"] * 3
+    assert run(fuse_partition=False)[1] == ["mtb_level_fused", "mtb_level_partition", "mtb_level_commit"] * 4
+    unfused = ["mtb_level_plan", "mtb_level_hist", "mtb_level_gain", "mtb_level_finalize", "mtb_level_partition",
+               "mtb_level_commit"]
+    assert run(fused=False)[1] == unfused * 4
+    sync, seq = run(small_rows=64)  # hand-off on: level-by-level with a read-back, stops when the frontier is empty
+    assert not sync and seq == ["mtb_level_fused"]
