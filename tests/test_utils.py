@@ -333,3 +333,71 @@ def test_level_loop_dry_run_launch_sequences(monkeypatch):
     assert run(fused=False)[1] == unfused * 4
     sync, seq = run(small_rows=64)  # hand-off on: level-by-level with a read-back, stops when the frontier is empty
     assert not sync and seq == ["mtb_level_fused"]
+
+
+def test_multi_rank_builder_wiring_dry_run(monkeypatch):
+    """Peer (``p2p``) and in-switch (``nvls``, staged) set-up of the CUDA engine with a fake communicator
+    and fake symmetric regions: which buffers the context points at, and that the level loop is the same."""
+    import ctypes
+
+    import torch
+
+    from mpitree_b200.ops import _lib as L
+    from mpitree_b200.ops import cuda_engine as ce
+    from mpitree_b200.ops.cpu_engine import SplitParams
+
+    try:
+        L.load()
+    except Exception as exc:  # noqa: BLE001
+        pytest.skip(f"native library unavailable: {exc}")
+    calls, regions = [], []
+
+    class Stream:
+        def synchronize(self):
+            pass
+
+    class Comm:
+        size, rank = 4, 1
+
+        def allgather_object(self, obj):
+            return [obj] * 4
+
+        def barrier(self):
+            pass
+
+    class Region:
+        def __init__(self, nbytes):
+            self.nbytes, self.mem = nbytes, torch.zeros(nbytes, dtype=torch.uint8)
+            self.mc_ptr, self.ptrs = 0xABC000, [self.mem.data_ptr()] * 4
+
+        def as_tensor(self):
+            return self.mem
+
+    monkeypatch.setattr(ce, "_call", lambda name, *a: calls.append(name))
+    monkeypatch.setattr(ce, "_stream_ptr", lambda: ctypes.c_void_p(0))
+    monkeypatch.setattr(ce, "_nvls_region", lambda n, c: regions.append(Region(n)) or regions[-1])
+    monkeypatch.setattr(ce, "_shared_region", lambda n, c: Region(n))
+    monkeypatch.setattr(torch.cuda, "current_stream", lambda *a, **k: Stream())
+    monkeypatch.setattr(torch.cuda, "synchronize", lambda *a, **k: None)
+    monkeypatch.setattr(torch.cuda, "mem_get_info", lambda *a, **k: (8 << 30, 16 << 30))
+    monkeypatch.setattr(torch.Tensor, "pin_memory", lambda self, *a, **k: self)
+
+    class Data:
+        device = torch.device("cpu")
+        n_features, n_classes, G, n_cap, n_local, cur = 64, 10, 4, 4096, 4000, 0
+        codes = [torch.zeros(4 * 4096 * 16, dtype=torch.uint8) for _ in range(2)]
+        labels = [torch.zeros(4096, dtype=torch.uint8) for _ in range(2)]
+
+    for reduce in ("p2p", "nvls"):
+        calls.clear()
+        b = ce.TreeBuilder(Data(), 256, SplitParams(max_depth=4), comm=Comm(), reduce=reduce, n_global=16000)
+        monkeypatch.setattr(b, "_launch", lambda name: calls.append(name))
+        b.build()
+        assert calls == ["mtb_level_fused"] + ["mtb_level_fused2"] * 3
+        assert (b.ctx.world, b.ctx.rank, b.ctx.fpo, b.stats.reduce) == (4, 1, 16, reduce)
+        if reduce == "nvls":  # the slabs live in the multicast-bound region and the kernels get its alias
+            assert b.nvls and list(b.ctx.mc_hist) == [0xABC000] * 2
+            assert b.hist[0].data_ptr() == regions[-1].mem.data_ptr() and b.ctx.hist0 == b.ctx.hist1
+            assert regions[-1].nbytes == b.h_cap * b.slab_words * 4
+        else:
+            assert not b.nvls and list(b.ctx.mc_hist) == [0, 0]
