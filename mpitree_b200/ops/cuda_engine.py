@@ -1026,8 +1026,11 @@ def fit_from_torch(X, y, params: SplitParams, *, max_bins: int = 256, comm=None,
     if y_dev.dtype.is_floating_point or y_dev.dtype == torch.bool:
         raise TypeError("class labels must be non-negative integers")
     if y_dev.numel() == 0:
-        raise ValueError("Found array with 0 sample(s)")
-    y_min, y_max = int(y_dev.min()), int(y_dev.max())
+        if comm is None or comm.size <= 1:
+            raise ValueError("Found array with 0 sample(s)")
+        y_min, y_max = 0, -1  # a rank of a sharded fit may hold no rows; it still joins every exchange
+    else:
+        y_min, y_max = int(y_dev.min()), int(y_dev.max())
     if y_min < 0:
         raise ValueError("class labels must be non-negative integers")
     st.mark("labels")

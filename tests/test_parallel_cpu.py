@@ -289,3 +289,61 @@ def test_numpy_front_end_sampling_decision_is_collective(monkeypatch):
     out = run_threaded(2, work)
     assert [o[0] for o in out] == [False, True]
     assert out[0][1] == out[1][1] and out[0][1][1][-1] == 77.0
+
+
+def test_torch_front_end_dry_run_on_thread_ranks(monkeypatch):
+    """``fit_from_torch`` on three thread-ranks with every native call replaced by a recorder (CPU tensors):
+    uneven shards (one empty, only one large enough to be sampled) must pass through the label range,
+    class and bin-edge agreements without a rank waiting in a collective the others skip, and end with
+    identical bin edges."""
+    import ctypes
+
+    import torch
+
+    from mpitree_b200.ops import _lib as L
+    from mpitree_b200.ops import cuda_engine as ce
+    from mpitree_b200.ops.cpu_engine import SplitParams
+
+    try:
+        L.load()
+    except Exception as exc:  # noqa: BLE001
+        pytest.skip(f"native library unavailable: {exc}")
+
+    class Stream:
+        def synchronize(self):
+            pass
+
+    class Region:
+        def __init__(self, nbytes):
+            self.nbytes, self.mem = nbytes, torch.zeros(nbytes, dtype=torch.uint8)
+            self.ptrs = [self.mem.data_ptr()] * 3
+
+    monkeypatch.setattr(ce, "SAMPLE_ROWS", 256)
+    monkeypatch.setattr(ce, "_call", lambda name, *a: None)
+    monkeypatch.setattr(ce, "_stream_ptr", lambda: ctypes.c_void_p(0))
+    monkeypatch.setattr(ce, "_device", lambda: torch.device("cpu"))
+    monkeypatch.setattr(ce, "_dist_group", lambda comm: None)
+    monkeypatch.setattr(ce, "_shared_region", lambda n, c: Region(n))
+    monkeypatch.setattr(ce.DeviceDataset, "encode_float", lambda self, *a, **k: None)
+    monkeypatch.setattr(ce.DeviceDataset, "encode_u8", lambda self, *a, **k: None)
+    monkeypatch.setattr(ce.TreeBuilder, "_launch", lambda self, name: None)
+    monkeypatch.setattr(torch.cuda, "current_stream", lambda *a, **k: Stream())
+    monkeypatch.setattr(torch.cuda, "synchronize", lambda *a, **k: None)
+    monkeypatch.setattr(torch.cuda, "mem_get_info", lambda *a, **k: (8 << 30, 16 << 30))
+    monkeypatch.setattr(torch.Tensor, "pin_memory", lambda self, *a, **k: self)
+
+    rng = np.random.default_rng(0)
+    X = rng.normal(size=(3000, 4)).astype(np.float32)
+    X[2999, 2] = 55.0
+    y = rng.integers(0, 3, size=3000) * 1000  # label range too wide for the lazy path: classes are gathered
+    cuts = [0, 100, 100, 3000]
+
+    def work(comm):
+        lo, hi = cuts[comm.rank], cuts[comm.rank + 1]
+        flat, mapper, classes = ce.fit_from_torch(torch.from_numpy(X[lo:hi]), torch.from_numpy(y[lo:hi]),
+                                                  SplitParams(max_depth=3), comm=comm)
+        return [e.tolist() for e in mapper.edges], classes.tolist(), flat.n_nodes
+
+    out = run_threaded(3, work)
+    assert out[0] == out[1] == out[2]
+    assert out[0][1] == [0, 1000, 2000] and out[0][0][2][-1] == 55.0
