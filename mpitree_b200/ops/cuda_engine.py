@@ -1030,7 +1030,8 @@ def fit_from_torch(X, y, params: SplitParams, *, max_bins: int = 256, comm=None,
             raise ValueError("Found array with 0 sample(s)")
         y_min, y_max = 0, -1  # a rank of a sharded fit may hold no rows; it still joins every exchange
     else:
-        y_min, y_max = int(y_dev.min()), int(y_dev.max())
+        lo_hi = torch.stack(torch.aminmax(y_dev)).tolist()  # one reduction, one read-back
+        y_min, y_max = int(lo_hi[0]), int(lo_hi[1])
     if y_min < 0:
         raise ValueError("class labels must be non-negative integers")
     st.mark("labels")
