@@ -40,6 +40,7 @@ def cpu_driver(monkeypatch):
     monkeypatch.setattr(torch.cuda, "current_stream", lambda *a, **k: Stream())
     monkeypatch.setattr(torch.cuda, "synchronize", lambda *a, **k: None)
     monkeypatch.setattr(torch.cuda, "current_device", lambda: 0)
+    monkeypatch.setattr(torch.cuda, "mem_get_info", lambda *a, **k: (1 << 30, 2 << 30))
     monkeypatch.setattr(torch.Tensor, "pin_memory", lambda self, *a, **k: self)
     return ce, L, monkeypatch
 
@@ -101,3 +102,93 @@ def test_unbounded_depth_with_and_without_hand_off(cpu_driver, small_rows):
     assert not b.async_levels and (b.stats.levels > 8 or small_rows)
     assert (b.stats.handed_off > 10) == bool(small_rows) and fake.launches == (1 if small_rows else 0)
     _same(got, want)
+
+
+def _emulate_encode(ce, monkeypatch):
+    """``encode_float`` / ``encode_u8`` stand-ins: host binning written into the tiled planes."""
+    import torch
+
+    def write(self, codes, row0):
+        n, F = codes.shape
+        view = self.codes[self.cur].numpy()[: self.G * self.n_cap * 16].reshape(self.G, self.n_cap, 16)
+        for f in range(F):
+            view[f // 16, row0 : row0 + n, f % 16] = codes[:, f]
+
+    def encode_float(self, X, mapper, row0=0, mismatch=None):
+        write(self, mapper.transform(X.numpy()), row0)
+
+    def encode_u8(self, X, lut=None, row0=0):
+        assert lut is None
+        write(self, X.numpy(), row0)
+
+    monkeypatch.setattr(ce.DeviceDataset, "encode_float", encode_float)
+    monkeypatch.setattr(ce.DeviceDataset, "encode_u8", encode_u8)
+    monkeypatch.setattr(ce, "_device", lambda: torch.device("cpu"))
+    monkeypatch.setattr(ce, "_dist_group", lambda comm: None)
+    monkeypatch.setattr(ce, "_WORKSPACE", {})
+
+
+@pytest.mark.parametrize("kind", ["float32", "int64", "uint8", "negative zeros"])
+def test_estimator_through_the_cuda_front_end(cpu_driver, kind):
+    """``DecisionTreeClassifier(device="cuda").fit`` on numpy input with the native layer emulated: front end
+    (binning, label codes, thresholds in the input's type, printed zero signs) + driver == host estimator."""
+    import mpitree_b200.tree.decision_tree as dt
+    from mpitree_b200.tree import DecisionTreeClassifier
+
+    ce, L, monkeypatch = cpu_driver
+    _emulate_encode(ce, monkeypatch)
+    real = L.load()
+
+    class Hybrid(_FakeLib):  # phase 2 entry points emulated, everything else (host-only queries) from the real library
+        def __getattr__(self, name):
+            return getattr(real, name)
+
+    hybrid = Hybrid(np.full(5, 256), "entropy")
+    monkeypatch.setattr(L, "load", lambda: hybrid)
+    monkeypatch.setattr(L, "check", lambda rc, what: None)
+    monkeypatch.setattr(dt, "resolve_engine", lambda device, **kw: "cuda" if device == "cuda" else "cpu")
+    rng = np.random.default_rng(3)
+    n = 900
+    if kind == "float32":
+        X = rng.normal(size=(n, 5)).astype(np.float32).round(1)
+    elif kind == "int64":
+        X = rng.integers(-20, 20, size=(n, 5))
+    elif kind == "uint8":
+        X = rng.integers(0, 40, size=(n, 5)).astype(np.uint8)
+    else:
+        X = rng.normal(size=(n, 5)).round(1)
+        X[rng.random((n, 5)) < 0.1] = -0.0
+        X[rng.random((n, 5)) < 0.1] = 0.0
+    y = (X[:, 0].astype(float) + X[:, 1] * 0.5 + rng.normal(scale=3 if kind in ("int64", "uint8") else 0.5, size=n) > X[:, 0].mean()) * 1
+    y = y + 2 * (X[:, 2] > np.median(X[:, 2]))  # labels 0..3
+    for max_depth in (3, None):
+        want = DecisionTreeClassifier(max_depth=max_depth, device="cpu").fit(X, y)
+        got = DecisionTreeClassifier(max_depth=max_depth, device="cuda").fit(X, y)
+        assert got.engine_ == "cuda" and want.engine_ == "cpu"
+        assert got.export_text() == want.export_text()
+        assert [type(t) for t in got.flat_tree_.thresholds] == [type(t) for t in want.flat_tree_.thresholds]
+        assert np.array_equal(got.classes_, want.classes_) and np.array_equal(got.flat_tree_.counts, want.flat_tree_.counts)
+
+
+@pytest.mark.parametrize("labels", ["dense", "gappy", "wide"])
+def test_estimator_from_torch_tensors(cpu_driver, labels):
+    """The torch-tensor front end (labels used as class codes and read back from the root's counts, or
+    gathered when their range is wide) with the native layer emulated."""
+    import torch
+
+    import mpitree_b200.tree.decision_tree as dt
+    from mpitree_b200.tree import DecisionTreeClassifier
+
+    ce, _, monkeypatch = cpu_driver
+    _emulate_encode(ce, monkeypatch)
+    monkeypatch.setattr(dt, "resolve_engine", lambda device, **kw: "cuda" if device == "cuda" else "cpu")
+    rng = np.random.default_rng(4)
+    X = rng.integers(0, 30, size=(1200, 6)).astype(np.uint8)
+    y = (X[:, 0] > 14).astype(np.int64) + 2 * (X[:, 3] > 20)
+    y = {"dense": y, "gappy": y * 3, "wide": y * 1000}[labels]
+    want = DecisionTreeClassifier(max_depth=5, device="cpu").fit(X, y)
+    got = DecisionTreeClassifier(max_depth=5, device="cuda").fit(torch.from_numpy(X), torch.from_numpy(y))
+    assert got.export_text() == want.export_text()
+    assert np.array_equal(got.classes_, want.classes_)
+    assert np.array_equal(got.flat_tree_.counts, want.flat_tree_.counts)
+    assert np.array_equal(got.predict(X), want.predict(X))  # numpy input: host walk over the same flat tree
