@@ -192,3 +192,45 @@ def test_estimator_from_torch_tensors(cpu_driver, labels):
     assert np.array_equal(got.classes_, want.classes_)
     assert np.array_equal(got.flat_tree_.counts, want.flat_tree_.counts)
     assert np.array_equal(got.predict(X), want.predict(X))  # numpy input: host walk over the same flat tree
+
+
+def test_slot_capacity_is_enforced_or_avoided_by_hand_off(cpu_driver):
+    """A frontier that outgrows the histogram slots raises with hand-off switched off; the automatic policy
+    (hand-off whenever the depth is unbounded) keeps the same fit within capacity."""
+    ce, L, monkeypatch = cpu_driver
+    codes, y = _data(6, n=2000)
+    params = SplitParams(max_depth=None)
+    want = build_tree_cpu(codes, y, np.full(20, 32), 4, params)
+    b = ce.TreeBuilder(_dataset(codes, y, 4), 32, params, h_cap=16, small_rows=0)
+    with pytest.raises(RuntimeError, match="exceeds the histogram slot capacity"):
+        b.build()
+    real = L.load()
+
+    class Hybrid(_FakeLib):
+        def __getattr__(self, name):
+            return getattr(real, name)
+
+    monkeypatch.setattr(L, "load", lambda: Hybrid(np.full(20, 32), "entropy"))
+    monkeypatch.setattr(L, "check", lambda rc, what: None)
+    monkeypatch.setenv("MTB_SMALL_ROWS", "300")
+    b = ce.TreeBuilder(_dataset(codes, y, 4), 32, params, h_cap=16)
+    assert b.small_rows == 300
+    got = b.build()
+    assert b.stats.handed_off > 4
+    _same(got, want)
+
+
+def test_tree_arrays_grow_with_the_tree(cpu_driver, monkeypatch):
+    """Unbounded depth starts with a modest node capacity and reallocates the tree arrays as levels are added."""
+    ce, _, _ = cpu_driver
+    codes, y = _data(7, n=1500)
+    params = SplitParams(max_depth=None)
+    want = build_tree_cpu(codes, y, np.full(20, 32), 4, params)
+    b = ce.TreeBuilder(_dataset(codes, y, 4), 32, params, hist_budget_bytes=512 << 20, small_rows=0)
+    b._alloc_tree(8)  # force several reallocations
+    grown = []
+    orig = b._alloc_tree
+    monkeypatch.setattr(b, "_alloc_tree", lambda cap, old=None: (grown.append(cap), orig(cap, old))[1])
+    got = b.build()
+    assert len(grown) >= 3 and b.node_cap >= want.n_nodes
+    _same(got, want)
