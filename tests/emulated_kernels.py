@@ -54,8 +54,12 @@ def _terminal(cnt, depth, c):
     return (cnt > 0).sum() <= 1 or (c.max_depth >= 0 and depth >= c.max_depth) or int(cnt.sum()) < c.min_samples_split
 
 
-def search_and_finalize(c):
-    """plan + histogram + gain + finalize of the current level (``mtb_level_fused`` without the kernels' insides)."""
+def search_and_finalize(c, reduce=None):
+    """plan + histogram + gain + finalize of the current level (``mtb_level_fused`` without the kernels' insides).
+
+    ``reduce`` (several ranks): callable that sums a list of arrays across the ranks, standing in for the
+    peer push + owner reduction + record broadcast; every rank then finalizes redundantly, as the kernels do.
+    """
     criterion = "gini" if c.criterion else "entropy"
     x = Ctx(c)
     n = int(x.scal[0])
@@ -66,6 +70,17 @@ def search_and_finalize(c):
     x.cursors[: 2 * n] = 0
     nodes0 = int(x.scal[2])
     n_split = n_pair = units = 0
+    searched = [s for s in range(n) if int(x.slot["mode"][s]) in (BUILD, DERIVE)]
+    hists = []
+    for s in searched:
+        codes, y = x.rows(cur, int(x.slot["begin"][s]), int(x.slot["end"][s]))
+        hist = np.zeros((F, B, C), dtype=np.int64)
+        for f in range(F):
+            np.add.at(hist[f], (codes[:, f], y), 1)
+        hists.append(hist)
+    if reduce is not None:
+        hists = reduce(hists)
+    hist_of = dict(zip(searched, hists))
     for s in range(n):
         mode = int(x.slot["mode"][s])
         x.rec_feature[s], x.rec_bin[s], x.part_flags[s] = -1, -1, 0
@@ -74,14 +89,11 @@ def search_and_finalize(c):
         if mode not in (BUILD, DERIVE):
             continue
         node, b, e = int(x.slot["node"][s]), int(x.slot["begin"][s]), int(x.slot["end"][s])
-        codes, y = x.rows(cur, b, e)
-        cnt = np.bincount(y, minlength=C).astype(np.int64)
+        hist = hist_of[s]
+        cnt = hist[0].sum(axis=0)
         x.t_counts[node] = cnt
         split = None
         if not _terminal(cnt, depth, c):
-            hist = np.zeros((F, B, C), dtype=np.int64)
-            for f in range(F):
-                np.add.at(hist[f], (codes[:, f], y), 1)
             split = best_split(hist, np.full(F, B), criterion)
         x.t["feature"][node], x.t["bin"][node], x.t_gain[node] = -1, -1, np.nan
         if split is None:
@@ -172,16 +184,21 @@ def partition_and_commit(c):
     x.scal[0] = x.scal[1]
 
 
-def dispatch():
-    """Replacement for ``cuda_engine._call``: routes native entry-point names to the stand-ins."""
+def dispatch(reduce_of_thread=None):
+    """Replacement for ``cuda_engine._call``: routes native entry-point names to the stand-ins.
+
+    ``reduce_of_thread``: optional dict ``thread id -> reduce callable`` for thread-rank tests (one patched
+    ``_call`` serves all ranks of the process)."""
+    import threading
 
     def call(name, *args):
         ctx = args[0]._obj
+        reduce = (reduce_of_thread or {}).get(threading.get_ident())
         if name == "mtb_level_fused" or name == "mtb_level_finalize":
-            search_and_finalize(ctx)
+            search_and_finalize(ctx, reduce)
         elif name == "mtb_level_fused2":  # (parents, children): partition the parents' rows, then search the children
             partition_and_commit(ctx)
-            search_and_finalize(args[1]._obj)
+            search_and_finalize(args[1]._obj, reduce)
         elif name == "mtb_level_commit":
             partition_and_commit(ctx)
         elif name in ("mtb_level_plan", "mtb_level_hist", "mtb_level_gain", "mtb_level_partition"):

@@ -234,3 +234,58 @@ def test_tree_arrays_grow_with_the_tree(cpu_driver, monkeypatch):
     got = b.build()
     assert len(grown) >= 3 and b.node_cap >= want.n_nodes
     _same(got, want)
+
+
+@pytest.mark.parametrize("layout,max_depth", [("sharded", 5), ("replicated", 5), ("sharded", None)])
+def test_parallel_estimator_on_thread_ranks_through_the_cuda_engine(cpu_driver, layout, max_depth):
+    """Three thread-ranks through ``ParallelDecisionTreeClassifier(device="cuda")``: numpy front end with its
+    agreements, multi-rank builder set-up, level loop, and (unbounded depth) the multi-rank hand-off phase.
+    The peer reduction inside the level kernel is replaced by a sum over the ranks' local histograms."""
+    import threading
+
+    import torch
+
+    import mpitree_b200.tree.decision_tree as dt
+    from mpitree_b200.parallel import symm
+    from mpitree_b200.parallel.comm import run_threaded
+    from mpitree_b200.tree import DecisionTreeClassifier, ParallelDecisionTreeClassifier
+
+    from .test_phase2_dry_run import _fake_gather_rows, _ThreadRegion
+
+    ce, L, monkeypatch = cpu_driver
+    _emulate_encode(ce, monkeypatch)
+    reducers: dict = {}
+    call = emu.dispatch(reducers)
+    monkeypatch.setattr(ce, "_call", call)
+    monkeypatch.setattr(ce.TreeBuilder, "_launch", lambda self, name: call(name, ctypes.byref(self.ctx)))
+    monkeypatch.setattr(dt, "resolve_engine", lambda device, **kw: "cuda" if device == "cuda" else "cpu")
+    monkeypatch.setattr(dt, "REPLICATED_SERIAL_ROWS", 0)  # take the cooperative path for the replicated layout too
+    monkeypatch.setattr(ce, "_shared_region", lambda nbytes, comm: _ThreadRegion(nbytes, comm))
+    monkeypatch.setattr(symm, "IpcRegion", _ThreadRegion)
+    real = L.load()
+
+    class Hybrid(_FakeLib):
+        def __getattr__(self, name):
+            return getattr(real, name)
+
+    hybrid = Hybrid(np.full(6, 256), "entropy")
+    hybrid.mtb_gather_rows = _fake_gather_rows
+    monkeypatch.setattr(L, "load", lambda: hybrid)
+    monkeypatch.setattr(L, "check", lambda rc, what: None)
+
+    rng = np.random.default_rng(8)
+    n = 1500
+    X = rng.integers(0, 25, size=(n, 6)).astype(np.float32)
+    y = (X[:, 0] > 12).astype(np.int64) + 2 * (X[:, 2] + X[:, 4] > 24)
+    want = DecisionTreeClassifier(max_depth=max_depth, device="cpu").fit(X, y)
+    cuts = [0, 300, 1100, n]
+
+    def work(comm):
+        reducers[threading.get_ident()] = lambda hists: [sum(parts) for parts in zip(*comm.allgather_object(hists))]
+        lo, hi = (0, n) if layout == "replicated" else (cuts[comm.rank], cuts[comm.rank + 1])
+        clf = ParallelDecisionTreeClassifier(max_depth=max_depth, device="cuda", comm=comm, data_layout=layout)
+        clf.fit(X[lo:hi], y[lo:hi])
+        return clf.export_text(), clf.flat_tree_.counts.tolist(), clf.engine_
+
+    out = run_threaded(3, work)
+    assert all(o == (want.export_text(), want.flat_tree_.counts.tolist(), "cuda") for o in out)
