@@ -6,6 +6,7 @@ read-backs), ping-pong sides, context copies for the fused partition, tree growt
 hand-off phase — and must return the tree the host engine builds.
 """
 import ctypes
+import os
 import types
 
 import numpy as np
@@ -289,3 +290,32 @@ def test_parallel_estimator_on_thread_ranks_through_the_cuda_engine(cpu_driver, 
 
     out = run_threaded(3, work)
     assert all(o == (want.export_text(), want.flat_tree_.counts.tolist(), "cuda") for o in out)
+
+
+@pytest.mark.parametrize("seed", range(int(os.environ.get("MTB_FUZZ_CASES", "24"))))
+def test_random_shapes_and_modes(cpu_driver, seed):
+    """Seeded fuzz of the driver: random shapes, stop rules, launch modes and hand-off sizes
+    (``MTB_FUZZ_CASES=1000`` runs a longer sweep)."""
+    ce, L, monkeypatch = cpu_driver
+    rng = np.random.default_rng(1000 + seed)
+    n, F, C, B = int(rng.integers(1, 900)), int(rng.integers(1, 40)), int(rng.integers(1, 6)), int(rng.integers(2, 64))
+    codes = rng.integers(0, B, size=(n, F)).astype(np.uint8)
+    if rng.random() < 0.3:
+        codes[:, 0] = 3 % B  # a constant feature
+    y = rng.integers(0, C, size=n)
+    max_depth = [None, 0, 1, 3, 7][int(rng.integers(0, 5))]
+    params = SplitParams(max_depth=max_depth, min_samples_split=int(rng.choice([2, 2, 5, 30])),
+                         criterion=["entropy", "gini"][int(rng.integers(0, 2))])
+    mode = [dict(), dict(fuse_partition=False), dict(fused=False), dict(async_levels=False)][int(rng.integers(0, 4))]
+    small_rows = [0, 0, 16, 100][int(rng.integers(0, 4))]
+    want = build_tree_cpu(codes, y, np.full(F, B), C, params)
+    real = L.load()
+
+    class Hybrid(_FakeLib):
+        def __getattr__(self, name):
+            return getattr(real, name)
+
+    monkeypatch.setattr(L, "load", lambda: Hybrid(np.full(F, 64), params.criterion))
+    monkeypatch.setattr(L, "check", lambda rc, what: None)
+    b = ce.TreeBuilder(_dataset(codes, y, C), B, params, hist_budget_bytes=1 << 30, small_rows=small_rows, **mode)
+    _same(b.build(), want)
