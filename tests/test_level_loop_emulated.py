@@ -319,3 +319,43 @@ def test_random_shapes_and_modes(cpu_driver, seed):
     monkeypatch.setattr(L, "check", lambda rc, what: None)
     b = ce.TreeBuilder(_dataset(codes, y, C), B, params, hist_budget_bytes=1 << 30, small_rows=small_rows, **mode)
     _same(b.build(), want)
+
+
+@pytest.mark.parametrize("layout", ["sharded", "replicated"])
+def test_parallel_estimator_from_torch_tensors_on_thread_ranks(cpu_driver, layout):
+    """The torch-tensor front end on three thread-ranks (uneven shards, one of them empty in the sharded case)."""
+    import threading
+
+    import torch
+
+    import mpitree_b200.tree.decision_tree as dt
+    from mpitree_b200.parallel.comm import run_threaded
+    from mpitree_b200.tree import DecisionTreeClassifier, ParallelDecisionTreeClassifier
+
+    from .test_phase2_dry_run import _ThreadRegion
+
+    ce, L, monkeypatch = cpu_driver
+    _emulate_encode(ce, monkeypatch)
+    reducers: dict = {}
+    call = emu.dispatch(reducers)
+    monkeypatch.setattr(ce, "_call", call)
+    monkeypatch.setattr(ce.TreeBuilder, "_launch", lambda self, name: call(name, ctypes.byref(self.ctx)))
+    monkeypatch.setattr(dt, "resolve_engine", lambda device, **kw: "cuda" if device == "cuda" else "cpu")
+    monkeypatch.setattr(ce, "_shared_region", lambda nbytes, comm: _ThreadRegion(nbytes, comm))
+
+    rng = np.random.default_rng(12)
+    n = 1400
+    X = rng.integers(0, 50, size=(n, 5)).astype(np.uint8)
+    y = (X[:, 1] > 20).astype(np.int64) * 3 + (X[:, 4] > 35)  # labels 0, 1, 3, 4: read back from the root counts
+    want = DecisionTreeClassifier(max_depth=6, device="cpu").fit(X, y)
+    cuts = [0, 0, 600, n]
+
+    def work(comm):
+        reducers[threading.get_ident()] = lambda hists: [sum(parts) for parts in zip(*comm.allgather_object(hists))]
+        lo, hi = (0, n) if layout == "replicated" else (cuts[comm.rank], cuts[comm.rank + 1])
+        clf = ParallelDecisionTreeClassifier(max_depth=6, device="cuda", comm=comm, data_layout=layout)
+        clf.fit(torch.from_numpy(X[lo:hi]), torch.from_numpy(y[lo:hi]))
+        return clf.export_text(), clf.classes_.tolist(), clf.flat_tree_.counts.tolist()
+
+    out = run_threaded(3, work)
+    assert all(o == (want.export_text(), want.classes_.tolist(), want.flat_tree_.counts.tolist()) for o in out)
