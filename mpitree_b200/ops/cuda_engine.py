@@ -450,10 +450,12 @@ class TreeBuilder:
                 self.nvls = True
                 self.stats.reduce = "nvls"
             else:
-                one = z(self.h_cap * slab_words)
+                one = torch.empty(self.h_cap * slab_words, dtype=i32, device=dev)
             self.hist = [one, one]
         else:
-            self.hist = [z(self.h_cap * slab_words), z(self.h_cap * slab_words)]
+            # no initial fill: every level zeroes the slabs it is going to accumulate into (prepare_level /
+            # _build_async) and overwrites the derived ones; hundreds of MB of memset per fit saved
+            self.hist = [torch.empty(self.h_cap * slab_words, dtype=i32, device=dev) for _ in range(2)]
         self.slots = [{k: z(m_cap) for k in ("node", "begin", "end", "mode", "parent", "sibling")} for _ in range(2)]
         self.nslot_src = z(m_cap)
         self.rec_feature, self.rec_bin, self.part_flags = z(m_cap), z(m_cap), z(m_cap)
