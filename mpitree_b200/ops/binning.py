@@ -156,6 +156,33 @@ class BinMapper:
         v = self.edges[feature][bin_code]
         return v.item() if isinstance(v, np.generic) else v
 
+    def thresholds_of(self, feature: np.ndarray, bin_code: np.ndarray) -> list:
+        """:meth:`threshold_of` for whole node arrays (``feature < 0`` marks a leaf -> ``None``).
+
+        One gather (one per feature when the features' value types differ) instead of one Python-level lookup per node: for a
+        2,047-node tree this is tens of microseconds instead of more than a millisecond, which is
+        visible next to a 10 ms multi-GPU fit.
+        """
+        feature = np.asarray(feature)
+        bin_code = np.asarray(bin_code)
+        out = np.full(feature.shape[0], None, dtype=object)
+        inner = np.flatnonzero(feature >= 0)
+        dtypes = {e.dtype for e in self.edges}
+        if len(dtypes) == 1 and next(iter(dtypes)) != object:
+            # one dtype for every feature: a single gather from the padded (F, max bins) edge matrix
+            table = self.__dict__.get("_edge_table")
+            if table is None:
+                table = np.zeros((len(self.edges), max(max(len(e) for e in self.edges), 1)), dtype=next(iter(dtypes)))
+                for f, e in enumerate(self.edges):
+                    table[f, : len(e)] = e
+                self.__dict__["_edge_table"] = table
+            out[inner] = table[feature[inner], bin_code[inner]].tolist()  # tolist: plain Python objects, like .item()
+            return out.tolist()
+        for f in np.unique(feature[inner]):
+            idx = np.flatnonzero(feature == f)
+            out[idx] = self.edges[int(f)][bin_code[idx]].tolist()
+        return out.tolist()
+
     def edges_matrix(self, dtype=np.float64) -> np.ndarray:
         """(n_features, 256) array of edges padded with +inf (device encode table)."""
         out = np.full((self.n_features, 256), np.inf, dtype=dtype)

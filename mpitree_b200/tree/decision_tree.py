@@ -310,10 +310,7 @@ class DecisionTreeClassifier(ClassifierMixin, BaseEstimator):
                     handoff_rows=getattr(self, "handoff_rows", None),
                 )
         flat.class_labels = np.asarray(classes, dtype=np.int64)
-        flat.thresholds = [
-            None if flat.feature[i] < 0 else mapper.threshold_of(int(flat.feature[i]), int(flat.bin[i]))
-            for i in range(flat.n_nodes)
-        ]
+        flat.thresholds = mapper.thresholds_of(flat.feature, flat.bin)
         if engine == "cuda" and X.dtype.kind in "iub":
             # the CUDA engine bins integer columns through a float edge table: hand thresholds back in
             # the column's own type, as the host engine and the reference do (int stays int)
@@ -360,10 +357,7 @@ class DecisionTreeClassifier(ClassifierMixin, BaseEstimator):
         self.n_features_in_ = int(X.shape[1])
         self.classes_ = classes
         flat.class_labels = np.asarray(classes, dtype=np.int64)
-        flat.thresholds = [
-            None if flat.feature[i] < 0 else mapper.threshold_of(int(flat.feature[i]), int(flat.bin[i]))
-            for i in range(flat.n_nodes)
-        ]
+        flat.thresholds = mapper.thresholds_of(flat.feature, flat.bin)
         self.bin_mapper_ = mapper
         self.engine_ = "cuda"
         self.__dict__.pop("tree_", None)
