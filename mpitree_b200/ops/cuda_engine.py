@@ -469,6 +469,7 @@ class TreeBuilder:
             self.part_child = z(m_cap)
             self.mask_words = z(max_units * 68)  # 272-byte unit records (32 bit words, 32 prefixes, 2 bases, pad)
         self._ctx_prev = None
+        self._bound_tree = None  # tree arrays the context currently points at (see _bind)
         self._alloc_tree(self.node_cap)
 
         # record mailbox: fb_cost | fb_bin | fb_left | node_cnt (layout shared with the kernels)
@@ -542,31 +543,37 @@ class TreeBuilder:
         self.node_cap = cap
 
     def _bind(self) -> None:
+        """Point the context at this level's buffers.
+
+        Most pointers never change during a fit: they are written once (again after the tree arrays
+        were reallocated); per level only the ping-pong selectors and the two slot tables swap.
+        """
         c, d = self.ctx, self.data
-        c.codes0, c.codes1 = _p(d.codes[0]), _p(d.codes[1])
-        c.labels0, c.labels1 = _p(d.labels[0]), _p(d.labels[1])
-        c.cur = d.cur
-        c.hist0, c.hist1, c.hcur = _p(self.hist[0]), _p(self.hist[1]), self.hcur
-        cur, nxt = self.slots[self.side], self.slots[self.side ^ 1]
-        c.slot_node, c.slot_begin, c.slot_end = _p(cur["node"]), _p(cur["begin"]), _p(cur["end"])
-        c.slot_mode, c.slot_parent, c.slot_sibling = _p(cur["mode"]), _p(cur["parent"]), _p(cur["sibling"])
-        c.nslot_node, c.nslot_begin, c.nslot_end = _p(nxt["node"]), _p(nxt["begin"]), _p(nxt["end"])
-        c.nslot_mode, c.nslot_parent, c.nslot_sibling = _p(nxt["mode"]), _p(nxt["parent"]), _p(nxt["sibling"])
-        c.nslot_src = _p(self.nslot_src)
-        mb = self._mailbox_ptr
-        c.fb_cost, c.fb_bin, c.fb_left, c.node_cnt = (mb + o for o in self._rec_off)
-        c.rec_feature, c.rec_bin, c.part_flags, c.cursors = (
-            _p(self.rec_feature), _p(self.rec_bin), _p(self.part_flags), _p(self.cursors),
-        )
-        t = self.tree
-        c.t_feature, c.t_bin, c.t_left, c.t_parent, c.t_depth = (
-            _p(t["feature"]), _p(t["bin"]), _p(t["left"]), _p(t["parent"]), _p(t["depth"]),
-        )
-        c.t_gain, c.t_counts = _p(t["gain"]), _p(t["counts"])
-        c.scalars, c.unit_prefix = _p(self.scalars), _p(self.unit_prefix)
-        c.m_cap, c.node_cap = self.m_cap, self.node_cap
-        if self.fuse_partition:
-            c.part_child, c.mask_words = _p(self.part_child), _p(self.mask_words)
+        if self._bound_tree is not self.tree:
+            c.codes0, c.codes1 = _p(d.codes[0]), _p(d.codes[1])
+            c.labels0, c.labels1 = _p(d.labels[0]), _p(d.labels[1])
+            c.hist0, c.hist1 = _p(self.hist[0]), _p(self.hist[1])
+            c.nslot_src = _p(self.nslot_src)
+            mb = self._mailbox_ptr
+            c.fb_cost, c.fb_bin, c.fb_left, c.node_cnt = (mb + o for o in self._rec_off)
+            c.rec_feature, c.rec_bin, c.part_flags, c.cursors = (
+                _p(self.rec_feature), _p(self.rec_bin), _p(self.part_flags), _p(self.cursors),
+            )
+            t = self.tree
+            c.t_feature, c.t_bin, c.t_left, c.t_parent, c.t_depth = (
+                _p(t["feature"]), _p(t["bin"]), _p(t["left"]), _p(t["parent"]), _p(t["depth"]),
+            )
+            c.t_gain, c.t_counts = _p(t["gain"]), _p(t["counts"])
+            c.scalars, c.unit_prefix = _p(self.scalars), _p(self.unit_prefix)
+            c.m_cap, c.node_cap = self.m_cap, self.node_cap
+            if self.fuse_partition:
+                c.part_child, c.mask_words = _p(self.part_child), _p(self.mask_words)
+            keys = ("node", "begin", "end", "mode", "parent", "sibling")
+            self._slot_ptrs = [tuple(_p(tab[k]) for k in keys) for tab in self.slots]
+            self._bound_tree = self.tree
+        c.cur, c.hcur = d.cur, self.hcur
+        (c.slot_node, c.slot_begin, c.slot_end, c.slot_mode, c.slot_parent, c.slot_sibling) = self._slot_ptrs[self.side]
+        (c.nslot_node, c.nslot_begin, c.nslot_end, c.nslot_mode, c.nslot_parent, c.nslot_sibling) = self._slot_ptrs[self.side ^ 1]
 
     def _launch(self, name: str) -> None:
         _call(name, ctypes.byref(self.ctx), _stream_ptr())
