@@ -456,17 +456,31 @@ class TreeBuilder:
             # no initial fill: every level zeroes the slabs it is going to accumulate into (prepare_level /
             # _build_async) and overwrites the derived ones; hundreds of MB of memset per fit saved
             self.hist = [torch.empty(self.h_cap * slab_words, dtype=i32, device=dev) for _ in range(2)]
-        self.slots = [{k: z(m_cap) for k in ("node", "begin", "end", "mode", "parent", "sibling")} for _ in range(2)]
-        self.nslot_src = z(m_cap)
-        self.rec_feature, self.rec_bin, self.part_flags = z(m_cap), z(m_cap), z(m_cap)
-        self.cursors = z(2 * m_cap)
-        self.scalars = z(8)
-        self.unit_prefix = z(2 * (m_cap + 1))
+        # the per-slot int32 tables share one zero-filled allocation (one memset instead of twenty);
+        # every table starts on a 256-byte boundary
+        stride = _round_up(m_cap, 64)
+        names = [f"slot{side}_{k}" for side in range(2) for k in ("node", "begin", "end", "mode", "parent", "sibling")]
+        names += ["nslot_src", "rec_feature", "rec_bin", "part_flags", "part_child"]
+        sizes = {n: stride for n in names}
+        sizes.update(cursors=_round_up(2 * m_cap, 64), unit_prefix=_round_up(2 * (m_cap + 1), 64), scalars=64)
+        arena = z(sum(sizes.values()))
+        tables, off = {}, 0
+        for name, size in sizes.items():
+            tables[name] = arena[off : off + size]
+            off += size
+        self._arena = arena
+        self.slots = [{k: tables[f"slot{side}_{k}"][:m_cap] for k in ("node", "begin", "end", "mode", "parent", "sibling")}
+                      for side in range(2)]
+        self.nslot_src = tables["nslot_src"][:m_cap]
+        self.rec_feature, self.rec_bin, self.part_flags = (tables[k][:m_cap] for k in ("rec_feature", "rec_bin", "part_flags"))
+        self.cursors = tables["cursors"][: 2 * m_cap]
+        self.scalars = tables["scalars"][:8]
+        self.unit_prefix = tables["unit_prefix"][: 2 * (m_cap + 1)]
         # fused partition + next-level histogram (levels >= 1 of the fused paths)
         self.fuse_partition = bool(fuse_partition and fused and reduce in ("none", "p2p"))
         if self.fuse_partition:
             max_units = data.n_cap // 1024 + m_cap + 2
-            self.part_child = z(m_cap)
+            self.part_child = tables["part_child"][:m_cap]
             self.mask_words = z(max_units * 68)  # 272-byte unit records (32 bit words, 32 prefixes, 2 bases, pad)
         self._ctx_prev = None
         self._bound_tree = None  # tree arrays the context currently points at (see _bind)
