@@ -458,11 +458,11 @@ class TreeBuilder:
             self.hist = [torch.empty(self.h_cap * slab_words, dtype=i32, device=dev) for _ in range(2)]
         # the per-slot int32 tables share one zero-filled allocation (one memset instead of twenty);
         # every table starts on a 256-byte boundary
-        stride = _round_up(m_cap, 64)
+        stride = _round_up(m_cap + 64, 64)  # (with at least 256 bytes of slack behind it, as separate allocations had)
         names = [f"slot{side}_{k}" for side in range(2) for k in ("node", "begin", "end", "mode", "parent", "sibling")]
         names += ["nslot_src", "rec_feature", "rec_bin", "part_flags", "part_child"]
         sizes = {n: stride for n in names}
-        sizes.update(cursors=_round_up(2 * m_cap, 64), unit_prefix=_round_up(2 * (m_cap + 1), 64), scalars=64)
+        sizes.update(cursors=_round_up(2 * m_cap + 64, 64), unit_prefix=_round_up(2 * (m_cap + 1) + 64, 64), scalars=128)
         arena = z(sum(sizes.values()))
         tables, off = {}, 0
         for name, size in sizes.items():
