@@ -192,6 +192,10 @@ def dispatch(reduce_of_thread=None):
     import threading
 
     def call(name, *args):
+        if name == "mtb_pack_nodes":
+            return pack_nodes(*args)
+        if name == "mtb_predict":
+            return predict(*args)
         ctx = args[0]._obj
         reduce = (reduce_of_thread or {}).get(threading.get_ident())
         if name == "mtb_level_fused" or name == "mtb_level_finalize":
@@ -207,3 +211,34 @@ def dispatch(reduce_of_thread=None):
             raise NotImplementedError(name)
 
     return call
+
+
+def pack_nodes(feature, left, label, n, out, stream):
+    """``mtb_pack_nodes``: 16-byte node records {feature, left child, leaf label, 0}."""
+    n = n.value
+    rec = view(out.value, np.int32, 4 * n).reshape(n, 4)
+    rec[:, 0], rec[:, 1] = view(feature.value, np.int32, n), view(left.value, np.int32, n)
+    rec[:, 2], rec[:, 3] = view(label.value, np.int32, n), 0
+    return 0
+
+
+def predict(X, dtype, n, F, ldx, packed, thr, n_nodes, out_leaf, out_label, stream):
+    """``mtb_predict``: walk every row down the packed tree (``x <= threshold`` goes to the left child)."""
+    n, F, ldx, n_nodes = n.value, F.value, ldx.value, n_nodes.value
+    np_dt, ct = {0: (np.float32, ctypes.c_float), 1: (np.uint8, ctypes.c_uint8), 2: (np.float64, ctypes.c_double)}[dtype.value]
+    rows = np.ctypeslib.as_array(ctypes.cast(X.value, ctypes.POINTER(ct)), shape=(n * ldx,)).reshape(n, ldx)[:, :F]
+    rec = view(packed.value, np.int32, 4 * n_nodes).reshape(n_nodes, 4)
+    t_ct = {0: ctypes.c_float, 1: ctypes.c_int32, 2: ctypes.c_double}[dtype.value]
+    t = np.ctypeslib.as_array(ctypes.cast(thr.value, ctypes.POINTER(t_ct)), shape=(n_nodes,))
+    node = np.zeros(n, dtype=np.int64)
+    active = np.flatnonzero(rec[node, 0] >= 0)
+    while active.size:
+        cur = node[active]
+        go_left = rows[active, rec[cur, 0]] <= t[cur]
+        node[active] = rec[cur, 1] + np.where(go_left, 0, 1)
+        active = active[rec[node[active], 0] >= 0]
+    if out_leaf.value:
+        view(out_leaf.value, np.int32, n)[:] = node
+    if out_label.value:
+        view(out_label.value, np.int32, n)[:] = rec[node, 2]
+    return 0

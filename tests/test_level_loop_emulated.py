@@ -359,3 +359,35 @@ def test_parallel_estimator_from_torch_tensors_on_thread_ranks(cpu_driver, layou
 
     out = run_threaded(3, work)
     assert all(o == (want.export_text(), want.classes_.tolist(), want.flat_tree_.counts.tolist()) for o in out)
+
+
+@pytest.mark.parametrize("kind", ["uint8", "float32", "float64", "int64"])
+def test_predict_front_end(cpu_driver, kind):
+    """``predict`` / ``predict_proba`` / ``apply`` through the CUDA front end (node packing, thresholds per
+    input type, chunking, label look-up) with the predict kernel emulated, for numpy and torch inputs."""
+    import torch
+
+    import mpitree_b200.tree.decision_tree as dt
+    from mpitree_b200.tree import DecisionTreeClassifier
+
+    ce, _, monkeypatch = cpu_driver
+    _emulate_encode(ce, monkeypatch)
+    monkeypatch.setattr(dt, "resolve_engine", lambda device, **kw: "cuda" if device == "cuda" else "cpu")
+    monkeypatch.setattr(ce, "available", lambda: True)
+    monkeypatch.setattr(ce, "ENCODE_CHUNK_ROWS", 300)  # several chunks for host inputs
+    rng = np.random.default_rng(21)
+    n = 1000
+    X = {"uint8": rng.integers(0, 60, size=(n, 6)).astype(np.uint8), "float32": rng.normal(size=(n, 6)).astype(np.float32),
+         "float64": rng.normal(size=(n, 6)).round(3), "int64": rng.integers(-30, 30, size=(n, 6))}[kind]
+    y = ((X[:, 0] > np.median(X[:, 0])) * 2 + (X[:, 3] > np.median(X[:, 3]))) * 2  # labels 0, 2, 4, 6
+    want = DecisionTreeClassifier(max_depth=6, device="cpu").fit(X, y)
+    got = DecisionTreeClassifier(max_depth=6, device="cuda").fit(X, y)
+    Xn = np.concatenate([X, X[:50] + (1 if kind in ("uint8", "int64") else 0.37)]).astype(X.dtype)  # seen and unseen rows
+    assert np.array_equal(got.predict(Xn), want.predict(Xn))
+    assert np.array_equal(got.predict_proba(Xn), want.predict_proba(Xn))
+    assert np.array_equal(got.apply(Xn), want.apply(Xn))
+    Xt = torch.from_numpy(Xn)
+    assert np.array_equal(got.predict(Xt).numpy(), want.predict(Xn))
+    assert np.array_equal(got.predict_proba(Xt).numpy(), want.predict_proba(Xn))
+    with pytest.raises(ValueError, match="expecting 6 features"):
+        got.predict(Xt[:, :5])
