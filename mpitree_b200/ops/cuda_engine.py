@@ -286,6 +286,14 @@ class TreeBuilder:
       gain kernel (every rank evaluates every feature).
     * ``peers=<LocalRegion view>`` — several virtual ranks in one process, driven in
       lock-step by :func:`build_lockstep` (same kernels, phases launched separately).
+    * ``reduce="nvls"`` — staged: the ``p2p`` protocol with the slabs in a
+      multicast-bound region, owners read cross-rank sums with ``multimem.ld_reduce``.
+
+    Other switches: ``fused`` / ``fuse_partition`` select the launch decomposition (one cooperative
+    launch per level by default), ``async_levels`` enqueues a bounded-depth fit without read-backs,
+    ``small_rows`` is the hand-off size of phase 2 (``None`` = automatic, 0 = never),
+    ``h_cap`` / ``hist_budget_bytes`` size the histogram slots, ``tile_layout="interleaved"`` selects
+    the staged shared-memory tile, ``profile`` records per-phase times.
     """
 
     def __init__(
