@@ -183,3 +183,62 @@ def test_driver_errors_name_the_failing_call(monkeypatch):
     with pytest.raises(RuntimeError, match="cuMemCreate failed: FAKE_ERROR"):
         nvls._ck((1, None), "cuMemCreate")
     assert nvls._ck((0, 7), "x") == 7 and nvls._ck((0,), "x") == ()
+
+
+def test_peer_allreduce_nvls_front_end(monkeypatch):
+    """``PeerAllReduce(nvls=True)``: buffer layout, the multicast pointer handed to the native call, epochs."""
+    import ctypes
+
+    import torch
+
+    from mpitree_b200.ops import _lib as L
+    from mpitree_b200.parallel import allreduce, nvls
+
+    fake = FakeDriver()
+    calls = []
+
+    class Lib:
+        def mtb_allreduce_u32_nvls(self, rank, world, bufs, flags, mc, count, cap, epoch, out, stream):
+            calls.append(("nvls", rank.value, world.value, [bufs[i] for i in range(2)], [flags[i] for i in range(2)], mc.value,
+                          count.value, cap.value, epoch.value))
+            return 0
+
+        def mtb_allreduce_u32(self, algo, rank, world, bufs, flags, count, cap, epoch, out, stream):
+            calls.append(("peer", algo.value, epoch.value))
+            return 0
+
+    monkeypatch.setattr(nvls, "_driver", lambda: fake)
+    monkeypatch.setattr(nvls.NvlsRegion, "as_tensor", lambda self: torch.zeros(self.nbytes, dtype=torch.uint8))
+    monkeypatch.setattr(L, "load", lambda: Lib())
+    monkeypatch.setattr(L, "check", lambda rc, what: None)
+    monkeypatch.setattr(torch.cuda, "current_device", lambda: 0)
+    monkeypatch.setattr(torch.cuda, "synchronize", lambda *a, **k: None)
+    monkeypatch.setattr(torch.cuda, "current_stream",
+                        lambda *a, **k: types.SimpleNamespace(synchronize=lambda: None, cuda_stream=0))
+
+    def work(comm):
+        ar = allreduce.PeerAllReduce(comm, 1001, nvls=True)
+        assert ar.cap == 1004 and ar.region.nbytes == 2 * 1004 * 4 + ar.FLAG_BYTES
+        ar.launch(1001, allreduce.ALGO_NVLS)
+        ar.launch(10, allreduce.ALGO_TWOSHOT)
+        ar.launch(10, allreduce.ALGO_NVLS)
+        region = ar.region
+        plain = types.SimpleNamespace(lib=ar.lib, L=L, rank=0, world=2, _bufs=ar._bufs, _flags=ar._flags, _mc=0, cap=ar.cap,
+                                      epoch=0, torch=torch, result_view=lambda n: torch.zeros(n, dtype=torch.int32))
+        with pytest.raises(ValueError, match="nvls=True"):
+            allreduce.PeerAllReduce.launch(plain, 4, allreduce.ALGO_NVLS)
+        ptrs, mc = list(region.ptrs), region.mc_ptr  # close() clears them
+        comm.barrier()
+        ar.close()
+        return ptrs, mc, ar.epoch
+
+    calls_before = len(calls)
+    out = run_threaded(2, work)
+    assert calls_before == 0 and out[0][2] == out[1][2] == 6
+    first = [c for c in calls if c[0] == "nvls" and c[6] == 1001]
+    assert len(first) == 2
+    for c in first:
+        ptrs, mc = (out[c[1]][0], out[c[1]][1])
+        assert c[2] == 2 and c[3] == ptrs and c[4] == [p + 2 * 1004 * 4 for p in ptrs] and c[5] == mc and c[7] == 1004 and c[8] == 0
+    assert sorted(c[2] for c in calls if c[0] == "peer") == [2, 2]  # the peer algorithms run on the same region, later epoch
+    assert sorted(c[8] for c in calls if c[0] == "nvls" and c[6] == 10) == [4, 4]
