@@ -221,6 +221,8 @@ int mtb_can_access_peer(int device, int peer);
 int mtb_device_malloc(int64_t bytes, void** out);
 int mtb_device_free(void* ptr);
 int mtb_memset_async(void* ptr, int value, int64_t bytes, void* stream);
+/* device-to-device copy; either address may lie in a peer's region opened with mtb_ipc_open_handle */
+int mtb_memcpy_async(void* dst, const void* src, int64_t bytes, void* stream);
 /* u32 sum all-reduce over peer-mapped buffers (K5).  bufs[q] = rank q's symmetric area as mapped
  * in this process: [in: cap u32][res: cap u32]; flags[q] = rank q's flag words u32[512][16].  Every
  * rank writes its `count` inputs at the start of its own area, then all ranks call this with the

@@ -77,6 +77,14 @@ extern "C" int mtb_memset_async(void* ptr, int value, int64_t bytes, void* strea
   return 0;
 }
 
+// Device-to-device copy between any two mapped addresses (own memory or a peer's region opened with
+// mtb_ipc_open_handle); the driver routes peer addresses over NVLink.
+extern "C" int mtb_memcpy_async(void* dst, const void* src, int64_t bytes, void* stream) {
+  if (bytes <= 0) return 0;
+  MTB_CHECK(cudaMemcpyAsync(dst, src, (size_t)bytes, cudaMemcpyDefault, (cudaStream_t)stream));
+  return 0;
+}
+
 extern "C" int mtb_can_access_peer(int device, int peer) {
   int ok = 0;
   if (cudaDeviceCanAccessPeer(&ok, device, peer) != cudaSuccess) return -1;

@@ -182,9 +182,20 @@ def finish_subtrees(builder, trunk: FlatTree) -> FlatTree:
         n_cap = d.n_cap
 
     out = _run_subtrees(builder, lib, L, dev, mine, it_side, it_begin, it_end, depth[mine], root_counts[mine],
-                        codes_ptrs, labels_ptrs, n_cap)
+                        codes_ptrs, labels_ptrs, n_cap, on_device=P > 1)
     if P > 1:
-        everyone = comm.allgather_object((node[mine], out))
+        # small per-item lists travel as objects; the records go device to device once they are big
+        items = comm.allgather_object((node[mine], out["offs"], out["nn"]))
+        used_all = np.asarray([int(np.sum(it[2])) for it in items], dtype=np.int64)
+        rec_bytes = int(used_all.sum()) * (20 + 4 * C)
+        names = ("feature", "bin", "left", "gain", "counts")
+        if rec_bytes >= DEVICE_EXCHANGE_MIN_BYTES:
+            records = _exchange_records_on_device(comm, lib, L, dev, out, used_all, C)
+        else:
+            host = {k: out[k].cpu().numpy() for k in names}
+            host["counts"] = host["counts"].view(np.uint32)
+            records = comm.allgather_object(host)
+        everyone = [(it[0], {"offs": it[1], "nn": it[2], **rec}) for it, rec in zip(items, records)]
         comm.barrier()
         recv.close()
         roots = np.concatenate([e[0] for e in everyone])
@@ -204,7 +215,7 @@ def finish_subtrees(builder, trunk: FlatTree) -> FlatTree:
 
 
 def _run_subtrees(builder, lib, L, dev, mine, it_side, it_begin, it_end, depth, root_counts, codes_ptrs, labels_ptrs,
-                  n_cap) -> dict:
+                  n_cap, on_device: bool = False) -> dict:
     import torch
 
     from .cuda_engine import KERNEL_LAUNCHES, _stream_ptr
@@ -217,6 +228,10 @@ def _run_subtrees(builder, lib, L, dev, mine, it_side, it_begin, it_end, depth, 
     empty = {"offs": offs, "nn": np.zeros(n_items, np.int64), "feature": np.zeros(0, np.int32), "bin": np.zeros(0, np.int32),
              "left": np.zeros(0, np.int32), "gain": np.zeros(0), "counts": np.zeros((0, C), np.uint32)}
     if n_items == 0:
+        if on_device:  # same container types as a rank that has work
+            for k, dt in (("feature", torch.int32), ("bin", torch.int32), ("left", torch.int32), ("gain", torch.float64)):
+                empty[k] = torch.zeros(0, dtype=dt, device=dev)
+            empty["counts"] = torch.zeros((0, C), dtype=torch.int32, device=dev)
         return empty
     if total >= 2**31:
         raise RuntimeError("too many subtree nodes for 32-bit offsets")
@@ -249,16 +264,17 @@ def _run_subtrees(builder, lib, L, dev, mine, it_side, it_begin, it_end, depth, 
     KERNEL_LAUNCHES["count"] += 1
     L.check(rc, "mtb_subtree_build")
     torch.cuda.synchronize()
-    return _compact_records(o_nn, offs, o_feature, o_bin, o_left, o_gain, o_counts.view(total, C))
+    return _compact_records(o_nn, offs, o_feature, o_bin, o_left, o_gain, o_counts.view(total, C), on_device)
 
 
-def _compact_records(o_nn, offs, o_feature, o_bin, o_left, o_gain, o_counts) -> dict:
+def _compact_records(o_nn, offs, o_feature, o_bin, o_left, o_gain, o_counts, on_device: bool = False) -> dict:
     """Keep only the records the kernel wrote: item ``i`` used ``o_nn[i]`` of its ``2 rows - 1`` slots.
 
     The output arrays are sized for the worst case (every row its own leaf); a depth-limited subtree
     uses a small part of that, so the used records are gathered on the device and only those cross
-    PCIe (and, with several ranks, the all-gather).  Child ids are relative to the item's first
+    PCIe (and, with several ranks, the exchange).  Child ids are relative to the item's first
     record, so they stay valid; ``offs`` becomes the running sum of the used counts.
+    ``on_device`` leaves the five record arrays as device tensors.
     """
     import torch
 
@@ -268,12 +284,64 @@ def _compact_records(o_nn, offs, o_feature, o_bin, o_left, o_gain, o_counts) -> 
     starts = np.concatenate([[0], np.cumsum(nn)[:-1]]).astype(np.int64)
     shift = torch.from_numpy(np.asarray(offs, np.int64) - starts).to(o_nn.device)
     idx = torch.repeat_interleave(shift, nn_d, output_size=used) + torch.arange(used, device=o_nn.device)
-    return {
-        "offs": starts,
-        "nn": nn,
-        "feature": o_feature[idx].cpu().numpy(),
-        "bin": o_bin[idx].cpu().numpy(),
-        "left": o_left[idx].cpu().numpy(),
-        "gain": o_gain[idx].cpu().numpy(),
-        "counts": o_counts[idx].cpu().numpy().view(np.uint32),
-    }
+    rec = {"feature": o_feature[idx], "bin": o_bin[idx], "left": o_left[idx], "gain": o_gain[idx], "counts": o_counts[idx]}
+    if not on_device:
+        rec = {k: v.cpu().numpy() for k, v in rec.items()}
+        rec["counts"] = rec["counts"].view(np.uint32)
+    return {"offs": starts, "nn": nn, **rec}
+
+
+#: from this many bytes of finished-subtree records on, ranks exchange them device to device
+DEVICE_EXCHANGE_MIN_BYTES = 1 << 20
+
+
+def _exchange_records_on_device(comm, lib, L, dev, out: dict, used_all: np.ndarray, C: int) -> list:
+    """Every rank's compact records -> every rank, without a host round trip per record.
+
+    Each rank copies its five record arrays into its slice of a peer-mapped region (fixed layout, sized
+    for the largest rank), every rank then pulls all slices with plain device-to-device copies over
+    NVLink (``mtb_memcpy_async`` on the peer mappings) and reads the gathered buffer back once.  The
+    reference ships whole pickled ``Node`` graphs through ``allgather`` here (``:456-466``).
+    Returns one ``{"feature", "bin", "left", "gain", "counts"}`` dict of numpy arrays per rank.
+    """
+    import torch
+
+    from ..parallel.symm import IpcRegion
+    from .cuda_engine import KERNEL_LAUNCHES, _stream_ptr
+
+    P, rank = comm.size, comm.rank
+    U = int(used_all.max())
+    fields = (("gain", 8, np.float64), ("feature", 4, np.int32), ("bin", 4, np.int32), ("left", 4, np.int32),
+              ("counts", 4 * C, np.uint32))
+    offsets, off = {}, 0
+    for name, width, _ in fields:
+        offsets[name] = off
+        off += ((U * width + 255) // 256) * 256
+    section = max(off, 256)
+    region = IpcRegion(section, comm)
+    try:
+        mine = int(used_all[rank])
+        for name, width, _ in fields:
+            src = out[name].contiguous()
+            L.check(lib.mtb_memcpy_async(ctypes.c_void_p(region.ptrs[rank] + offsets[name]), ctypes.c_void_p(_p(src)),
+                                         ctypes.c_int64(mine * width), _stream_ptr()), "mtb_memcpy_async")
+            KERNEL_LAUNCHES["count"] += 1
+        torch.cuda.synchronize()
+        comm.barrier()  # every slice is complete before anybody pulls it
+        gathered = torch.empty(P * section, dtype=torch.uint8, device=dev)
+        for q in range(P):
+            L.check(lib.mtb_memcpy_async(ctypes.c_void_p(_p(gathered) + q * section), ctypes.c_void_p(region.ptrs[q]),
+                                         ctypes.c_int64(section), _stream_ptr()), "mtb_memcpy_async")
+            KERNEL_LAUNCHES["count"] += 1
+        torch.cuda.synchronize()
+        host = gathered.cpu().numpy()
+    finally:
+        region.close()  # (barrier inside: nobody frees a slice that is still being pulled)
+    result = []
+    for q in range(P):
+        u, base, rec = int(used_all[q]), q * section, {}
+        for name, width, dt in fields:
+            raw = host[base + offsets[name] : base + offsets[name] + u * width]
+            rec[name] = raw.view(dt).reshape(u, C) if name == "counts" else raw.view(dt)
+        result.append(rec)
+    return result

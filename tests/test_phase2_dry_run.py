@@ -157,9 +157,17 @@ def _fake_gather_rows(codes0, codes1, labels0, labels1, n_cap, G, side, begin, e
     return 0
 
 
-def test_finish_subtrees_on_thread_ranks_with_emulated_kernels(monkeypatch):
+def _fake_memcpy_async(dst, src, nbytes, stream):
+    """``mtb_memcpy_async``: thread-ranks share one address space, so a peer mapping is just a pointer."""
+    ctypes.memmove(dst.value, src.value, nbytes.value)
+    return 0
+
+
+@pytest.mark.parametrize("exchange", ["objects", "device"])
+def test_finish_subtrees_on_thread_ranks_with_emulated_kernels(monkeypatch, exchange):
     """Three ranks, row-sharded: owners by size, rows written into the owners' receive planes, subtrees
-    finished there, records exchanged, every rank stitches the same tree as a single level-wise build."""
+    finished there, records exchanged (as objects when small, device to device through a peer-mapped
+    region when large), every rank stitches the same tree as a single level-wise build."""
     import torch
 
     from mpitree_b200.ops import _lib as L
@@ -179,10 +187,12 @@ def test_finish_subtrees_on_thread_ranks_with_emulated_kernels(monkeypatch):
 
     lib = _FakeLib(n_bins, "entropy")
     lib.mtb_gather_rows = _fake_gather_rows
+    lib.mtb_memcpy_async = _fake_memcpy_async
     monkeypatch.setattr(L, "load", lambda: lib)
     monkeypatch.setattr(L, "check", lambda rc, what: None)
     monkeypatch.setattr(ce, "_stream_ptr", lambda: ctypes.c_void_p(0))
     monkeypatch.setattr(symm, "IpcRegion", _ThreadRegion)
+    monkeypatch.setattr(sp, "DEVICE_EXCHANGE_MIN_BYTES", 0 if exchange == "device" else 1 << 40)
     monkeypatch.setattr(torch.cuda, "synchronize", lambda *a, **k: None)
     monkeypatch.setattr(torch.cuda, "current_device", lambda: 0)
 
