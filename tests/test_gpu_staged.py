@@ -230,3 +230,52 @@ def test_sharded_float_numpy_ranks_agree(tmp_path):
     res = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=600)
     assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
     assert f"FLOAT_SHARD_OK {world}" in res.stdout
+
+
+_RECORD_EXCHANGE_WORKER = r"""
+import os, sys
+sys.path.insert(0, os.environ["REPO"])
+import numpy as np, torch, torch.distributed as dist
+from mpitree_b200.ops import subtree_phase
+from mpitree_b200.parallel.comm import init_process_group_from_env
+from mpitree_b200.tree import DecisionTreeClassifier, ParallelDecisionTreeClassifier
+assert init_process_group_from_env("nccl")
+rank, world = dist.get_rank(), dist.get_world_size()
+rng = np.random.default_rng(0)
+n = 60_000
+X = rng.integers(0, 256, size=(n, 24), dtype=np.uint8)
+s = X[:, :6].astype(np.float64) @ np.array([1, -1, .5, .5, -.25, 2.0]) + rng.normal(scale=60, size=n)
+y = np.digitize(s, np.quantile(s, np.linspace(0, 1, 5)[1:-1]))
+want = DecisionTreeClassifier(max_depth=14, device="cuda").fit(X, y)
+lo, hi = n * rank // world, n * (rank + 1) // world
+for threshold in (1 << 40, 0):  # records as objects, then device to device through a peer-mapped region
+    subtree_phase.DEVICE_EXCHANGE_MIN_BYTES = threshold
+    clf = ParallelDecisionTreeClassifier(max_depth=14, device="cuda", data_layout="sharded", handoff_rows=900)
+    clf.fit(X[lo:hi], y[lo:hi])
+    assert clf.flat_tree_.structurally_equal(want.flat_tree_), (threshold, rank)
+dist.barrier()
+if rank == 0:
+    print("RECORD_EXCHANGE_OK", world)
+dist.destroy_process_group()
+"""
+
+
+@pytest.mark.multigpu
+def test_handoff_record_exchange_paths(tmp_path):
+    """Phase 2 on real ranks with the finished-subtree records exchanged both ways (objects / device to device)."""
+    import subprocess
+    import sys
+
+    import torch
+
+    world = min(torch.cuda.device_count(), 8)
+    if world < 2:
+        pytest.skip("needs at least two GPUs")
+    script = tmp_path / "record_exchange_worker.py"
+    script.write_text(_RECORD_EXCHANGE_WORKER)
+    env = dict(os.environ, REPO=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
+           "--master-addr", "127.0.0.1", "--master-port", "29661", str(script)]
+    res = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=600)
+    assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
+    assert f"RECORD_EXCHANGE_OK {world}" in res.stdout
