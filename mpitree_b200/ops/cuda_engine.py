@@ -975,6 +975,15 @@ def _merge_edge_candidates(parts, F: int, max_bins: int, np_dtype, col_max) -> B
     return mapper
 
 
+def _byte_lut(mapper: BinMapper) -> np.ndarray:
+    """``(F, 256)`` uint8 table: byte value -> bin code (first edge >= value, clamped to the last bin)."""
+    lut = np.zeros((mapper.n_features, 256), dtype=np.uint8)
+    for f, e in enumerate(mapper.edges):
+        if len(e):
+            lut[f] = np.minimum(np.searchsorted(e, np.arange(256).astype(e.dtype), side="left"), len(e) - 1)
+    return lut
+
+
 def _device():
     import torch
 
@@ -1001,19 +1010,22 @@ def fit_from_host(X: np.ndarray, y_codes: np.ndarray, n_classes: int, params: Sp
     X = np.ascontiguousarray(X)
     if X.dtype not in (np.float32, np.float64, np.uint8):
         X = X.astype(np.float64 if X.dtype.itemsize > 4 or X.dtype.kind in "iu" and X.dtype.itemsize > 2 else np.float32)
-    if X.dtype == np.uint8:
-        Xf = X
+    lut = None
+    if X.dtype == np.uint8 and max_bins >= 256:
+        # one bin per byte value: codes are the values themselves
         mapper = BinMapper(edges=[np.arange(256, dtype=np.uint8) for _ in range(X.shape[1])],
                            lossless=np.ones(X.shape[1], bool), max_bins=256)
     else:
-        Xf = X
         mapper = _fit_mapper_numpy(X, max_bins, comm)
+        if X.dtype == np.uint8:  # fewer bins than byte values were asked for: encode through a value -> code table
+            lut = torch.from_numpy(_byte_lut(mapper)).to(dev)
+    Xf = X
     n, F = X.shape
     data = DeviceDataset.allocate(n, F, n_classes, dev)
     for r0 in range(0, n, ENCODE_CHUNK_ROWS):
         chunk = torch.from_numpy(Xf[r0 : r0 + ENCODE_CHUNK_ROWS]).to(dev, non_blocking=False)
         if X.dtype == np.uint8:
-            data.encode_u8(chunk, None, r0)
+            data.encode_u8(chunk, lut, r0)
         else:
             data.encode_float(chunk, mapper, r0)
     data.set_labels(torch.from_numpy(np.asarray(y_codes)).to(dev))
@@ -1093,11 +1105,14 @@ def fit_from_torch(X, y, params: SplitParams, *, max_bins: int = 256, comm=None,
             raise ValueError(f"the CUDA engine supports at most {MAX_CLASSES} classes")
         y_codes = torch.bucketize(y_dev.to(torch.int64), classes_t.to(torch.int64))
 
-    if X.dtype == torch.uint8:
+    lut = None
+    if X.dtype == torch.uint8 and max_bins >= 256:
         mapper = BinMapper(edges=[np.arange(256, dtype=np.uint8) for _ in range(F)], lossless=np.ones(F, bool), max_bins=256)
     else:
         idx = _sample_rows(n)
         sample = X if idx is None else X[torch.from_numpy(idx).to(X.device)]
+        if X.dtype == torch.uint8:
+            sample = sample.to(torch.float32)  # edge discovery works on floats; the rows stay bytes
         col_max = X.max(dim=0).values.cpu().numpy() if idx is not None else None
         if comm is not None and comm.size > 1 and int(meta[:, 1].max()) > SAMPLE_ROWS:
             # some rank sampled its rows: every rank joins the exchange of column maxima (the shard
@@ -1107,16 +1122,18 @@ def fit_from_torch(X, y, params: SplitParams, *, max_bins: int = 256, comm=None,
             maxima = [m for m in comm.allgather_object(col_max) if m is not None]
             col_max = np.max(np.stack(maxima), axis=0)
         mapper = _fit_mapper_device(sample.to(dev, non_blocking=True), max_bins, comm, col_max)
+        if X.dtype == torch.uint8:
+            lut = torch.from_numpy(_byte_lut(mapper)).to(dev)
 
     st.mark("meta+mapper")
     data = DeviceDataset.allocate(n, F, len(classes), dev)
     st.mark("alloc")
     if X.is_cuda:
-        (data.encode_u8(X, None, 0) if X.dtype == torch.uint8 else data.encode_float(X, mapper, 0))
+        (data.encode_u8(X, lut, 0) if X.dtype == torch.uint8 else data.encode_float(X, mapper, 0))
     else:
         for r0 in range(0, n, ENCODE_CHUNK_ROWS):
             chunk = X[r0 : r0 + ENCODE_CHUNK_ROWS].to(dev, non_blocking=True)
-            (data.encode_u8(chunk, None, r0) if X.dtype == torch.uint8 else data.encode_float(chunk, mapper, r0))
+            (data.encode_u8(chunk, lut, r0) if X.dtype == torch.uint8 else data.encode_float(chunk, mapper, r0))
     data.set_labels(y_codes)
     st.mark("encode")
     _dist_group(comm)

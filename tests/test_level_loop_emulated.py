@@ -119,8 +119,10 @@ def _emulate_encode(ce, monkeypatch):
         write(self, mapper.transform(X.numpy()), row0)
 
     def encode_u8(self, X, lut=None, row0=0):
-        assert lut is None
-        write(self, X.numpy(), row0)
+        codes = X.numpy()
+        if lut is not None:  # (F, 256) value -> code table
+            codes = np.take_along_axis(lut.numpy().T, codes.astype(np.int64), axis=0)
+        write(self, codes, row0)
 
     monkeypatch.setattr(ce.DeviceDataset, "encode_float", encode_float)
     monkeypatch.setattr(ce.DeviceDataset, "encode_u8", encode_u8)
@@ -193,6 +195,10 @@ def test_estimator_from_torch_tensors(cpu_driver, labels):
     assert np.array_equal(got.classes_, want.classes_)
     assert np.array_equal(got.flat_tree_.counts, want.flat_tree_.counts)
     assert np.array_equal(got.predict(X), want.predict(X))  # numpy input: host walk over the same flat tree
+    # fewer bins than byte values: the byte rows are encoded through a value -> code table
+    want8 = DecisionTreeClassifier(max_depth=5, max_bins=8, device="cpu").fit(X, y)
+    got8 = DecisionTreeClassifier(max_depth=5, max_bins=8, device="cuda").fit(torch.from_numpy(X), torch.from_numpy(y))
+    assert got8.export_text() == want8.export_text() and int(got8.bin_mapper_.n_bins.max()) <= 8
 
 
 def test_slot_capacity_is_enforced_or_avoided_by_hand_off(cpu_driver):
@@ -391,3 +397,39 @@ def test_predict_front_end(cpu_driver, kind):
     assert np.array_equal(got.predict_proba(Xt).numpy(), want.predict_proba(Xn))
     with pytest.raises(ValueError, match="expecting 6 features"):
         got.predict(Xt[:, :5])
+
+
+@pytest.mark.parametrize("seed", range(int(os.environ.get("MTB_FUZZ_CASES", "16"))))
+def test_estimator_fuzz_through_the_cuda_front_end(cpu_driver, seed):
+    """Seeded fuzz at estimator level: numeric dtypes, gappy labels, quantile-binned columns, stop rules."""
+    import mpitree_b200.tree.decision_tree as dt
+    from mpitree_b200.tree import DecisionTreeClassifier
+
+    ce, L, monkeypatch = cpu_driver
+    _emulate_encode(ce, monkeypatch)
+    monkeypatch.setattr(ce, "available", lambda: True)
+    monkeypatch.setattr(dt, "resolve_engine", lambda device, **kw: "cuda" if device == "cuda" else "cpu")
+    real = L.load()
+
+    class Hybrid(_FakeLib):
+        def __getattr__(self, name):
+            return getattr(real, name)
+
+    rng = np.random.default_rng(5000 + seed)
+    n, F, k = int(rng.integers(2, 700)), int(rng.integers(1, 9)), int(rng.integers(1, 6))
+    kind = int(rng.integers(0, 6))
+    X = [rng.normal(size=(n, F)).astype(np.float32), rng.normal(size=(n, F)).round(1), rng.integers(-9, 9, size=(n, F)),
+         rng.integers(0, 200, size=(n, F)).astype(np.uint8), rng.random((n, F)) < 0.3, rng.random((n, F)) * 1e4][kind]
+    y = rng.integers(0, k, size=n) * int(rng.integers(1, 4))
+    crit = ["entropy", "gini"][int(rng.integers(0, 2))]
+    kw = dict(max_depth=[None, 0, 2, 6][int(rng.integers(0, 4))], min_samples_split=int(rng.choice([2, 2, 7])),
+              max_bins=int(rng.choice([256, 256, 32, 5])), criterion=crit)
+    monkeypatch.setattr(L, "load", lambda: Hybrid(np.full(F, 256), crit))
+    monkeypatch.setattr(L, "check", lambda rc, what: None)
+    want = DecisionTreeClassifier(device="cpu", **kw).fit(X, y)
+    got = DecisionTreeClassifier(device="cuda", **kw).fit(X, y)
+    assert got.engine_ == "cuda"
+    assert got.export_text() == want.export_text()
+    assert [type(t) for t in got.flat_tree_.thresholds] == [type(t) for t in want.flat_tree_.thresholds]
+    assert np.array_equal(got.classes_, want.classes_)
+    assert np.array_equal(got.predict(X), want.predict(X)) and np.array_equal(got.predict_proba(X), want.predict_proba(X))
