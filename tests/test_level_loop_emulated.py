@@ -433,3 +433,64 @@ def test_estimator_fuzz_through_the_cuda_front_end(cpu_driver, seed):
     assert [type(t) for t in got.flat_tree_.thresholds] == [type(t) for t in want.flat_tree_.thresholds]
     assert np.array_equal(got.classes_, want.classes_)
     assert np.array_equal(got.predict(X), want.predict(X)) and np.array_equal(got.predict_proba(X), want.predict_proba(X))
+
+
+@pytest.mark.parametrize("seed", range(max(4, int(os.environ.get("MTB_FUZZ_CASES", "8")) // 2)))
+def test_parallel_estimator_fuzz_through_the_cuda_engine(cpu_driver, seed):
+    """Seeded fuzz of the multi-rank flow on thread-ranks: world size, layout, input type, shard sizes
+    (empty shards included), stop rules and hand-off sizes; every rank must end with the serial tree."""
+    import threading
+
+    import mpitree_b200.tree.decision_tree as dt
+    from mpitree_b200.parallel import symm
+    from mpitree_b200.parallel.comm import run_threaded
+    from mpitree_b200.tree import DecisionTreeClassifier, ParallelDecisionTreeClassifier
+
+    from .test_phase2_dry_run import _fake_gather_rows, _fake_memcpy_async, _ThreadRegion
+
+    ce, L, monkeypatch = cpu_driver
+    _emulate_encode(ce, monkeypatch)
+    reducers: dict = {}
+    call = emu.dispatch(reducers)
+    monkeypatch.setattr(ce, "_call", call)
+    monkeypatch.setattr(ce.TreeBuilder, "_launch", lambda self, name: call(name, ctypes.byref(self.ctx)))
+    monkeypatch.setattr(dt, "resolve_engine", lambda device, **kw: "cuda" if device == "cuda" else "cpu")
+    monkeypatch.setattr(dt, "REPLICATED_SERIAL_ROWS", 0)
+    monkeypatch.setattr(ce, "_shared_region", lambda nbytes, comm: _ThreadRegion(nbytes, comm))
+    monkeypatch.setattr(symm, "IpcRegion", _ThreadRegion)
+    real = L.load()
+
+    class Hybrid(_FakeLib):
+        def __getattr__(self, name):
+            return getattr(real, name)
+
+    rng = np.random.default_rng(9000 + seed)
+    n, F, k = int(rng.integers(3, 900)), int(rng.integers(1, 7)), int(rng.integers(1, 5))
+    kind = int(rng.integers(0, 3))
+    X = [rng.integers(0, 40, size=(n, F)).astype(np.uint8), rng.normal(size=(n, F)).round(1).astype(np.float32),
+         rng.integers(-5, 6, size=(n, F))][kind]
+    y = rng.integers(0, k, size=n)
+    world = int(rng.choice([2, 3, 4]))
+    layout = ["sharded", "replicated"][int(rng.integers(0, 2))]
+    crit = ["entropy", "gini"][int(rng.integers(0, 2))]
+    kw = dict(max_depth=[None, 1, 4, 8][int(rng.integers(0, 4))], min_samples_split=int(rng.choice([2, 2, 9])), criterion=crit)
+    handoff = [None, 0, 25, 200][int(rng.integers(0, 4))]
+    hybrid = Hybrid(np.full(F, 256), crit)
+    hybrid.mtb_gather_rows, hybrid.mtb_memcpy_async = _fake_gather_rows, _fake_memcpy_async
+    monkeypatch.setattr(L, "load", lambda: hybrid)
+    monkeypatch.setattr(L, "check", lambda rc, what: None)
+    from mpitree_b200.ops import subtree_phase
+
+    monkeypatch.setattr(subtree_phase, "DEVICE_EXCHANGE_MIN_BYTES", [0, 1 << 40][seed % 2])
+    want = DecisionTreeClassifier(device="cpu", **kw).fit(X, y)
+    cuts = np.sort(np.concatenate([[0, n], rng.integers(0, n + 1, size=world - 1)]))
+
+    def work(comm):
+        reducers[threading.get_ident()] = lambda hists: [sum(parts) for parts in zip(*comm.allgather_object(hists))]
+        lo, hi = (0, n) if layout == "replicated" else (int(cuts[comm.rank]), int(cuts[comm.rank + 1]))
+        clf = ParallelDecisionTreeClassifier(device="cuda", comm=comm, data_layout=layout, handoff_rows=handoff, **kw)
+        clf.fit(X[lo:hi], y[lo:hi])
+        return clf.export_text(), clf.flat_tree_.counts.tolist()
+
+    out = run_threaded(world, work)
+    assert all(o == (want.export_text(), want.flat_tree_.counts.tolist()) for o in out)
