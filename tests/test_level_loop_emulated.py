@@ -494,3 +494,41 @@ def test_parallel_estimator_fuzz_through_the_cuda_engine(cpu_driver, seed):
 
     out = run_threaded(world, work)
     assert all(o == (want.export_text(), want.flat_tree_.counts.tolist()) for o in out)
+
+
+@pytest.mark.parametrize("seed", range(int(os.environ.get("MTB_FUZZ_CASES", "12"))))
+def test_torch_front_end_fuzz(cpu_driver, seed):
+    """Seeded fuzz of fits from torch tensors: input and label dtypes, label ranges, stop rules, ``max_bins``."""
+    import torch
+
+    import mpitree_b200.tree.decision_tree as dt
+    from mpitree_b200.tree import DecisionTreeClassifier
+
+    ce, L, monkeypatch = cpu_driver
+    _emulate_encode(ce, monkeypatch)
+    monkeypatch.setattr(dt, "resolve_engine", lambda device, **kw: "cuda" if device == "cuda" else "cpu")
+    real = L.load()
+
+    class Hybrid(_FakeLib):
+        def __getattr__(self, name):
+            return getattr(real, name)
+
+    rng = np.random.default_rng(7000 + seed)
+    n, F, k = int(rng.integers(2, 600)), int(rng.integers(1, 8)), int(rng.integers(1, 6))
+    kind = int(rng.integers(0, 5))
+    X = [rng.integers(0, 90, size=(n, F)).astype(np.uint8), rng.normal(size=(n, F)).round(1).astype(np.float32),
+         rng.normal(size=(n, F)).round(2), rng.integers(-40, 40, size=(n, F)).astype(np.int32),
+         rng.integers(0, 1000, size=(n, F)).astype(np.int64)][kind]
+    y = rng.integers(0, k, size=n) * int(rng.choice([1, 1, 2, 500]))
+    y = y.astype([np.int64, np.int32, np.uint8][int(rng.integers(0, 3))] if y.max() < 256 else np.int64)
+    crit = ["entropy", "gini"][int(rng.integers(0, 2))]
+    kw = dict(max_depth=[None, 0, 3, 7][int(rng.integers(0, 4))], min_samples_split=int(rng.choice([2, 2, 6])),
+              max_bins=int(rng.choice([256, 256, 16])), criterion=crit)
+    monkeypatch.setattr(L, "load", lambda: Hybrid(np.full(F, 256), crit))
+    monkeypatch.setattr(L, "check", lambda rc, what: None)
+    if X.dtype.kind == "f":
+        X = X + 0.0  # the printed sign of a zero threshold is only reproduced for numpy inputs (DESIGN.md section 3)
+    want = DecisionTreeClassifier(device="cpu", **kw).fit(X, y)
+    got = DecisionTreeClassifier(device="cuda", **kw).fit(torch.from_numpy(X), torch.from_numpy(y))
+    assert got.export_text() == want.export_text()
+    assert np.array_equal(got.classes_, want.classes_) and np.array_equal(got.flat_tree_.counts, want.flat_tree_.counts)
