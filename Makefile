@@ -19,6 +19,9 @@ reference:        ## install the unmodified reference for the oracle / reference
 sweep:            ## random parity sweeps against the unmodified reference (minutes)
 	for m in engines fit dtypes internals api parallel; do $(PY) tools/parity_sweep.py $$m 0 1000 || exit 1; done
 
+fuzz:             ## long seeded fuzz of the CUDA engine's driver with emulated kernels (CPU, minutes)
+	MTB_FUZZ_CASES=2000 $(PY) -m pytest tests/test_level_loop_emulated.py -x -q -k "fuzz or random_shapes"
+
 staged:           ## validate and time the opt-in paths of DESIGN.md section 9 (needs a B200)
 	bash benchmarks/run_staged.sh 1
 
@@ -29,4 +32,4 @@ clean:
 	rm -rf mpitree_b200/lib build *.egg-info .pytest_cache .ruff_cache .hypothesis
 	find . -name __pycache__ -type d -prune -exec rm -rf {} +
 
-.PHONY: build test test-gpu bench reference sweep staged lint clean
+.PHONY: build test test-gpu bench reference sweep fuzz staged lint clean
