@@ -54,6 +54,8 @@ __all__ = ["DecisionTreeClassifier", "ParallelDecisionTreeClassifier"]
 REPLICATED_SERIAL_ROWS = 4096
 #: ... and from this many rows on the subtrees below the redundantly built top are dealt out to the ranks
 REPLICATED_SPLIT_MIN_ROWS = 64
+#: host torch inputs up to this many rows get the reference's printed sign for zero thresholds
+ZERO_SIGN_ROWS_MAX = 1 << 20
 
 
 def _is_torch_tensor(x) -> bool:
@@ -358,6 +360,10 @@ class DecisionTreeClassifier(ClassifierMixin, BaseEstimator):
         self.classes_ = classes
         flat.class_labels = np.asarray(classes, dtype=np.int64)
         flat.thresholds = mapper.thresholds_of(flat.feature, flat.bin)
+        if not X.is_cuda and X.shape[0] <= ZERO_SIGN_ROWS_MAX and not getattr(self, "data_layout", "") == "replicated":
+            # rows that live on the host can be looked at for free (see _restore_zero_signs); device
+            # inputs and very large host inputs keep the sign of the global bin edge
+            _restore_zero_signs(flat, X.numpy(), comm)
         self.bin_mapper_ = mapper
         self.engine_ = "cuda"
         self.__dict__.pop("tree_", None)

@@ -526,9 +526,9 @@ def test_torch_front_end_fuzz(cpu_driver, seed):
               max_bins=int(rng.choice([256, 256, 16])), criterion=crit)
     monkeypatch.setattr(L, "load", lambda: Hybrid(np.full(F, 256), crit))
     monkeypatch.setattr(L, "check", lambda rc, what: None)
-    if X.dtype.kind == "f":
-        X = X + 0.0  # the printed sign of a zero threshold is only reproduced for numpy inputs
+    if X.dtype.kind == "f" and any(len(np.unique(X[:, f])) > kw["max_bins"] for f in range(F)):
+        X = X + 0.0  # a quantile edge of 0 keeps the sign its mapper kept (host and device mappers may differ)
     want = DecisionTreeClassifier(device="cpu", **kw).fit(X, y)
     got = DecisionTreeClassifier(device="cuda", **kw).fit(torch.from_numpy(X), torch.from_numpy(y))
-    assert got.export_text() == want.export_text()
+    assert got.export_text() == want.export_text()  # incl. the printed sign of zero thresholds (host tensors)
     assert np.array_equal(got.classes_, want.classes_) and np.array_equal(got.flat_tree_.counts, want.flat_tree_.counts)
