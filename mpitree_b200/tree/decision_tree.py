@@ -360,10 +360,12 @@ class DecisionTreeClassifier(ClassifierMixin, BaseEstimator):
         self.classes_ = classes
         flat.class_labels = np.asarray(classes, dtype=np.int64)
         flat.thresholds = mapper.thresholds_of(flat.feature, flat.bin)
-        if not X.is_cuda and X.shape[0] <= ZERO_SIGN_ROWS_MAX and not getattr(self, "data_layout", "") == "replicated":
+        if not X.is_cuda and X.shape[0] <= ZERO_SIGN_ROWS_MAX:
             # rows that live on the host can be looked at for free (see _restore_zero_signs); device
-            # inputs and very large host inputs keep the sign of the global bin edge
-            _restore_zero_signs(flat, X.numpy(), comm)
+            # inputs and very large host inputs keep the sign of the global bin edge.  In the replicated
+            # layout every rank holds all rows, so nothing has to be gathered.
+            replicated = getattr(self, "data_layout", "sharded") == "replicated"
+            _restore_zero_signs(flat, X.numpy(), None if replicated else comm)
         self.bin_mapper_ = mapper
         self.engine_ = "cuda"
         self.__dict__.pop("tree_", None)

@@ -327,8 +327,9 @@ def test_random_shapes_and_modes(cpu_driver, seed):
     _same(b.build(), want)
 
 
+@pytest.mark.parametrize("signed_zeros", [False, True])
 @pytest.mark.parametrize("layout", ["sharded", "replicated"])
-def test_parallel_estimator_from_torch_tensors_on_thread_ranks(cpu_driver, layout):
+def test_parallel_estimator_from_torch_tensors_on_thread_ranks(cpu_driver, layout, signed_zeros):
     """The torch-tensor front end on three thread-ranks (uneven shards, one of them empty in the sharded case)."""
     import threading
 
@@ -353,6 +354,11 @@ def test_parallel_estimator_from_torch_tensors_on_thread_ranks(cpu_driver, layou
     n = 1400
     X = rng.integers(0, 50, size=(n, 5)).astype(np.uint8)
     y = (X[:, 1] > 20).astype(np.int64) * 3 + (X[:, 4] > 35)  # labels 0, 1, 3, 4: read back from the root counts
+    if signed_zeros:  # float rows holding both zeros: host tensors reproduce the printed sign in both layouts
+        X = rng.normal(size=(n, 5)).round(1).astype(np.float32)
+        X[rng.random((n, 5)) < 0.1] = -0.0
+        X[rng.random((n, 5)) < 0.1] = 0.0
+        y = (X[:, 1] > 0).astype(np.int64) * 3 + (X[:, 4] > 0.5)
     want = DecisionTreeClassifier(max_depth=6, device="cpu").fit(X, y)
     cuts = [0, 0, 600, n]
 
