@@ -14,7 +14,7 @@ OUT=gpurun_out/staged_${N}gpu.txt
 say() { echo "$@" | tee -a "$OUT"; }
 
 say "=== staged tests (MTB_STAGED=1), $N GPU(s)"
-MTB_STAGED=1 timeout 900 python -m pytest tests/test_gpu_staged.py -q -m gpu -x 2>&1 | tail -15 | tee -a "$OUT"
+timeout 900 python -m pytest tests/test_gpu_variants.py -q -m gpu -x 2>&1 | tail -15 | tee -a "$OUT"
 TESTS_OK=${PIPESTATUS[0]}
 
 if [ "$TESTS_OK" = "0" ]; then

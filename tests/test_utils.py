@@ -178,7 +178,7 @@ def test_tree_builder_host_setup_runs_without_a_gpu():
         codes = [torch.zeros(4 * 4096 * 16, dtype=torch.uint8) for _ in range(2)]
         labels = [torch.zeros(4096, dtype=torch.uint8) for _ in range(2)]
 
-    for kw, layout in ((dict(), 0), (dict(tile_layout="interleaved"), 1), (dict(fused=False), 0)):
+    for kw, layout in ((dict(), 1), (dict(tile_layout="planar"), 0), (dict(fused=False), 1)):
         b = ce.TreeBuilder(Data(), 256, SplitParams(max_depth=5), hist_budget_bytes=64 << 20, **kw)
         b._bind()
         assert b.stats.FT == 16 and b.ctx.tile_layout == layout and not b.nvls
@@ -194,7 +194,7 @@ def test_interleaved_tile_index_arithmetic_host_emulation():
     Mirrors the kernel's integer arithmetic step by step: the per-lane byte rotation
     (word swaps + ``__byte_perm``), the ``[cell][16]`` tile address, and the flush's lane -> (cell, feature
     quad) mapping.  Checks that every (feature, bin, class) count lands in the ``[f][B][C]`` slab exactly
-    once.  It pins the index algebra, not the CUDA code itself (that is ``tests/test_gpu_staged.py``).
+    once.  It pins the index algebra, not the CUDA code itself (that is ``tests/test_gpu_variants.py``).
     """
 
     def byte_perm(a, b, sel):
