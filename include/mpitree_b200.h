@@ -104,8 +104,10 @@ typedef struct MtbCtx {
   int64_t fpo;                        /* features per owner rank (F when world == 1)          */
   int64_t timers;                     /* u64[16] phase timestamps (%globaltimer) or 0         */
   /* Nodes with more than plogp_n rows use a cheaper, still deterministic evaluation:
-   * cost = (g(nL) + g(nR) - sum_c g(kL_c) - sum_c g(kR_c)) / n with g(k) = k*log2(k);
-   * klogk is the host's table of g(k) for k < klogk_n (0 = compute on device).            */
+   * cost = (g(nL) + g(nR) - sum_c g(kL_c) - sum_c g(kR_c)) / n with g(k) = k*log2(k), evaluated
+   * arithmetically (csrc/impurity.cuh).  klogk: f64 [128 + 32*128 + 6] constants built by the host
+   * (1/m0 per interval, e + log2 m0 per (exponent, interval), then the six coefficients of
+   * log2(1+r)); klogk_n = 128.                                                              */
   int64_t klogk;
   int64_t klogk_n;
   /* world > 1: the owner's reduced slabs for its own features, ping-pong by level:
@@ -123,12 +125,13 @@ typedef struct MtbCtx {
    * part_child: i32 [m_cap] first child slot of a split slot that keeps rows, else -1
    * mask_words: u32 [max_units][68] per 1024-row partition unit: 32 "row goes left" bit words, 32
    *             exclusive left-count prefixes, the rows already placed left / right before the
-   *             unit, 2 pad words (272 B, fetched by TMA next to the rows)
-   * unit_base : unused (kept for layout compatibility)                                        */
-  int64_t part_child, mask_words, unit_base;
-  /* shared-memory histogram tile: 0 = [f][B][C] (default), 1 = [B*C][16] interleaved by feature
-   * (FT == 16 only; opt-in until it has been timed on hardware).  Slabs in global memory are
-   * [f][B][C] either way.                                                                      */
+   *             unit, 2 pad words (272 B; written by the ranker warp while the split feature's
+   *             plane is moved, fetched by TMA next to the rows of the other planes)
+   * zero_next : mtb_level_fused only: also zero the slabs the next level accumulates into (set
+   *             when the next launch is mtb_level_fused2, which always does this for its successor) */
+  int64_t part_child, mask_words, zero_next;
+  /* shared-memory histogram tile: 0 = [f][B][C], 1 = [B*C][16] interleaved by feature (FT == 16
+   * only; the default there).  Slabs in global memory are [f][B][C] either way.                */
   int64_t tile_layout;
   /* world > 1, opt-in: multicast (NVSwitch) mappings of hist[0] / hist[1].  When set, the fused level
    * kernels skip the peer push and the owners read cross-rank sums with multimem.ld_reduce.  The
@@ -150,8 +153,8 @@ int mtb_encode_float(const void* X, int dtype, int64_t n, int64_t F, int64_t ldx
                      const int32_t* n_bins, uint8_t* codes, int64_t n_cap, int64_t row0,
                      unsigned long long* mismatch, void* stream);
 /* float32 rows with F % 4 == 0, ldx % 4 == 0 and a 16-byte aligned base: same codes as
- * mtb_encode_float(dtype 0), one lane per (row, 4 features), 128-bit loads.  Opt-in
- * (MTB_ENCODE=quads) until it has been timed on hardware.                             */
+ * mtb_encode_float(dtype 0), one lane per (row, 4 features), 128-bit loads (the default
+ * float32 path: 1.55 vs 4.45 ms on 10M x 32; MTB_ENCODE=scalar selects the other).     */
 int mtb_encode_f32_quads(const float* X, int64_t n, int64_t F, int64_t ldx, const double* edges,
                          const int32_t* n_bins, uint8_t* codes, int64_t n_cap, int64_t row0, void* stream);
 /* uint8 input; lut: u8 [F][256] value->code, or NULL for identity.                    */
@@ -171,8 +174,11 @@ int mtb_level_push(const MtbCtx* ctx, void* stream);      /* world > 1: push par
  * (view C, same buffers with the two slot sets / ping-pong sides swapped), then commit, plan,
  * peer push + barriers, gain and finalize for the children.                                  */
 int mtb_level_fused2(const MtbCtx* parents, const MtbCtx* children, void* stream);
-/* One cooperative launch doing plan + hist + (peer push + barriers) + gain + finalize. */
+/* One cooperative launch doing plan + hist + (peer push + barriers) + gain + finalize.  Zeroes the
+ * slabs it accumulates into itself (no host-side fill), and the next level's when ctx->zero_next. */
 int mtb_level_fused(const MtbCtx* ctx, void* stream);
+/* Test hook: out[i] = k[i] * log2(k[i]) by the device function of the gain phase (table = ctx.klogk). */
+int mtb_klogk_eval(const uint32_t* k, double* out, int64_t n, const double* table, void* stream);
 /* Shared memory / launch geometry the hist phase will use for this ctx (for reports). */
 int mtb_hist_config(const MtbCtx* ctx, int* threads, int* smem_bytes, int* stages, int* rows_per_stage);
 
@@ -235,7 +241,7 @@ int mtb_allreduce_u32(int algo, int rank, int world, void* const* bufs, void* co
 /* Same contract, reduced inside the NVSwitch: the symmetric areas must come from a VMM allocation
  * bound to a multicast object (parallel/nvls.py) and `mc_buf` is that object's mapping (the same
  * layout seen through one address).  Each rank sums its 1/world slice with multimem.ld_reduce and
- * broadcasts it with multimem.st.  Staged: compiles for sm_100a, not yet run on hardware.         */
+ * broadcasts it with multimem.st.                                                                 */
 int mtb_allreduce_u32_nvls(int rank, int world, void* const* bufs, void* const* flags, void* mc_buf, int64_t count,
                            int64_t cap, uint32_t epoch, uint32_t* out, void* stream);
 

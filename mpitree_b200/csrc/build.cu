@@ -471,16 +471,38 @@ __device__ void push_phase(const MtbCtx& ctx) {
 
 __global__ void __launch_bounds__(512) k_push(const __grid_constant__ MtbCtx ctx) { push_phase(ctx); }
 
-// One warp per (slot, owned feature).  `slab` is this warp's padded shared-memory copy of
-// the feature's [B][C] counts: lane L owns bins [L*BPL, (L+1)*BPL) at offset
-// L*(BPL*C+1) so that lane-sequential walks are bank-conflict free.
-//
-// NV (opt-in, staged): the local partial slabs live in memory that is also bound to an NVSwitch
-// multicast object (ctx.mc_hist = the multicast mapping of ctx.hist).  Nothing is pushed; the
-// owner asks the switch for the sum over all ranks with multimem.ld_reduce (SASS LDGMC.ADD), two
-// packed u32 counts per 64-bit load (integer ld_reduce has no vector form).
+// Gain phase.  One warp per (slot, owned feature) pair, no block-level synchronisation: the warps of
+// an SM work on independent pairs, which is what keeps the issue slots busy when a level has
+// thousands of pairs (a variant with one 256-thread group per pair, thread <-> bin, needed five
+// group barriers per pair and ran at a fifth of the issue rate: 1.30 ms instead of the 0.97 ms of
+// round 1 on the deepest level of 100M x 64).  `slab` is the warp's padded shared-memory copy of the
+// feature's [B][C] counts: lane L owns bins [L*BPL, (L+1)*BPL) at offset L*(BPL*C+1), so
+// lane-sequential walks are bank-conflict free.  Per pair:
+//   load     128-bit loads, four cells per lane in flight together: BUILD = own partial (+ the
+//            peers' staged partials, or one multimem.ld_reduce when the slabs are multicast-mapped),
+//            DERIVE = parent - sibling; the reduced counts also go back to global memory for the
+//            next level's subtraction
+//   scan     lane-local inclusive prefix over the lane's bins, per-class offsets by warp shuffles
+//   cost     float64 (reference rounding for small nodes, k log2 k form for large ones, evaluated
+//            arithmetically: no table gathers, no software log2), first arg-min by (cost, bin)
+//   publish  best-split record of the pair into every rank's mailbox
+struct GainGeom {
+  int warps;       // warps per CTA that take part
+  int slab_words;  // shared-memory words per warp
+};
+
+constexpr int kGainTabBytes = ((kKlogkTabDoubles * 8 + 127) / 128) * 128;
+
+__host__ __device__ inline GainGeom gain_geom(int B, int C, int warps, int smem_bytes) {
+  GainGeom g;
+  g.slab_words = (B * C + 32 + 3) & ~3;
+  int by_smem = (smem_bytes - kGainTabBytes) / (g.slab_words * 4);
+  g.warps = warps < by_smem ? warps : by_smem;
+  return g;
+}
+
 template <bool NV = false>
-__device__ void gain_pair(const MtbCtx& ctx, uint32_t* slab, int slot, int f) {
+__device__ void gain_pair(const MtbCtx& ctx, const KlogK& klogk, uint32_t* slab, int slot, int f) {
   View v(ctx);
   const int B = (int)ctx.B, C = (int)ctx.C, F = (int)ctx.F;
   const int P = (int)ctx.world, r = (int)ctx.rank;
@@ -489,7 +511,6 @@ __device__ void gain_pair(const MtbCtx& ctx, uint32_t* slab, int slot, int f) {
   const int lane = lane_id();
   const int mode = ptr_of<const int>(ctx.slot_mode)[slot];
   const int64_t rec = (int64_t)slot * F + f;
-  const unsigned divC = ((1u << 24) + (unsigned)C - 1u) / (unsigned)C;  // w / C == (w * divC) >> 24 for w < B*C
   if (mode == MTB_MODE_NONE || mode == MTB_MODE_HANDOFF) {
     if (lane < P) {
       Mailbox m = mailbox_at(ctx, P > 1 ? ctx.peer_rec[lane] : ctx.fb_cost);
@@ -498,92 +519,134 @@ __device__ void gain_pair(const MtbCtx& ctx, uint32_t* slab, int slot, int f) {
     }
     return;
   }
-  uint32_t* mine = v.hist_cur() + (int64_t)slot * v.slab_words() + (int64_t)f * B * C;
+  const unsigned divC = ((1u << 24) + (unsigned)C - 1u) / (unsigned)C;  // w / C == (w * divC) >> 24 for w < B*C
+  const unsigned divBPL = (unsigned)(__ffs(BPL) - 1);                   // shift when BPL is a power of two
+  const bool bpl_pow2 = (BPL & (BPL - 1)) == 0;
   const int words = B * C;
+  const int n4 = words / 4;
   // scatter 4 consecutive histogram words into the padded per-lane slab layout
   auto put4 = [&](const uint4& x, int w) {
     int b = (int)(((unsigned)w * divC) >> 24), c = w - b * C;
     const uint32_t xs[4] = {x.x, x.y, x.z, x.w};
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
-      slab[(b / BPL) * lane_stride + (b % BPL) * C + c] = xs[i];
+      const int bl = bpl_pow2 ? (b >> divBPL) : b / BPL;
+      slab[bl * lane_stride + (b - bl * BPL) * C + c] = xs[i];
       if (++c == C) { c = 0; ++b; }
     }
   };
+  const int64_t fBC = (int64_t)f * B * C;
+  constexpr int kBatch = 4;  // 128-bit cells per lane whose loads are issued together
   if (P > 1) {
-    // Multi-rank owner path.  Reduced slabs of the own features live in rstore (ping-pong by
-    // level); the local partial slabs are never modified, so BUILD and DERIVE pairs are
-    // independent of each other and run in one pass.
+    // Multi-rank owner path.  Reduced slabs of the own features live in rstore (ping-pong by level);
+    // the local partial slabs are never modified.
     const int fl = f - r * (int)ctx.fpo;
     const int64_t region = ctx.fpo * ctx.B * ctx.C;
     const uint32_t* stage = ptr_of<const uint32_t>(ctx.peer_hist[r]) + (int64_t)fl * B * C;
+    const int64_t src_stride = ctx.h_cap * region;
     uint4* out4 = reinterpret_cast<uint4*>(ptr_of<uint32_t>(ctx.rstore[ctx.hcur]) + (int64_t)slot * region + (int64_t)fl * B * C);
-    // reduced counts of `s`: own partial + what the peers pushed.  The staged loads are issued
-    // four at a time (fixed unroll over the maximum world size) so their latencies overlap.
-    auto reduced4 = [&](int s, int q) -> uint4 {
-      if constexpr (NV) {
-        const uint64_t* mc = reinterpret_cast<const uint64_t*>(ptr_of<const uint32_t>(ctx.mc_hist[ctx.hcur]) +
-                                                               (int64_t)s * v.slab_words() + (int64_t)f * B * C) + 2 * q;
-        uint64_t lo, hi;
-        asm volatile("multimem.ld_reduce.relaxed.sys.global.add.u64 %0, [%1];" : "=l"(lo) : "l"(mc) : "memory");
-        asm volatile("multimem.ld_reduce.relaxed.sys.global.add.u64 %0, [%1];" : "=l"(hi) : "l"(mc + 1) : "memory");
-        return make_uint4((uint32_t)lo, (uint32_t)(lo >> 32), (uint32_t)hi, (uint32_t)(hi >> 32));
-      }
-      uint4 x = reinterpret_cast<const uint4*>(v.hist_cur() + (int64_t)s * v.slab_words() + (int64_t)f * B * C)[q];
-      const uint32_t* cell = stage + (int64_t)s * region + q * 4;
-      const int64_t src_stride = ctx.h_cap * region;
+    const bool derive = mode == MTB_MODE_DERIVE;
+    const int src = derive ? ptr_of<const int>(ctx.slot_sibling)[slot] : slot;
+    const uint4* par4 = nullptr;
+    if (derive) {
+      const int par = ptr_of<const int>(ctx.slot_parent)[slot];
+      par4 = reinterpret_cast<const uint4*>(ptr_of<const uint32_t>(ctx.rstore[ctx.hcur ^ 1]) + (int64_t)par * region +
+                                            (int64_t)fl * B * C);
+    }
+    const uint4* own4 = reinterpret_cast<const uint4*>(v.hist_cur() + (int64_t)src * v.slab_words() + fBC);
+    const uint32_t* cell0 = stage + (int64_t)src * region;
+    for (int q0 = lane; q0 < n4; q0 += kBatch * 32) {
+      uint4 x[kBatch];
 #pragma unroll
-      for (int p0 = 0; p0 < MTB_MAX_WORLD; p0 += 4) {
-        if (p0 < P) {
-          uint4 y[4];
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            const int p = p0 + j;
-            y[j] = (p < P && p != r) ? ld_nc_u4(cell + (int64_t)p * src_stride) : make_uint4(0, 0, 0, 0);
+      for (int j = 0; j < kBatch; ++j) {
+        const int q = q0 + j * 32;
+        x[j] = make_uint4(0, 0, 0, 0);
+        if (q < n4) {
+          if constexpr (NV) {
+            const uint64_t* mc = reinterpret_cast<const uint64_t*>(ptr_of<const uint32_t>(ctx.mc_hist[ctx.hcur]) +
+                                                                   (int64_t)src * v.slab_words() + fBC) + 2 * q;
+            uint64_t lo, hi;
+            asm volatile("multimem.ld_reduce.relaxed.sys.global.add.u64 %0, [%1];" : "=l"(lo) : "l"(mc) : "memory");
+            asm volatile("multimem.ld_reduce.relaxed.sys.global.add.u64 %0, [%1];" : "=l"(hi) : "l"(mc + 1) : "memory");
+            x[j] = make_uint4((uint32_t)lo, (uint32_t)(lo >> 32), (uint32_t)hi, (uint32_t)(hi >> 32));
+          } else {
+            x[j] = ld_cg_u4(own4 + q);
           }
-#pragma unroll
-          for (int j = 0; j < 4; ++j) { x.x += y[j].x; x.y += y[j].y; x.z += y[j].z; x.w += y[j].w; }
         }
       }
-      return x;
-    };
-    if (mode == MTB_MODE_DERIVE) {
-      const int par = ptr_of<const int>(ctx.slot_parent)[slot];
-      const int sib = ptr_of<const int>(ctx.slot_sibling)[slot];
-      const uint4* hp4 = reinterpret_cast<const uint4*>(ptr_of<const uint32_t>(ctx.rstore[ctx.hcur ^ 1]) +
-                                                        (int64_t)par * region + (int64_t)fl * B * C);
-      for (int q = lane; q < words / 4; q += 32) {
-        const uint4 a = hp4[q], d = reduced4(sib, q);
-        const uint4 x = make_uint4(a.x - d.x, a.y - d.y, a.z - d.z, a.w - d.w);
-        out4[q] = x;
-        put4(x, q * 4);
+      if constexpr (!NV) {
+        // staged partials of the peers, one source (x kBatch cells) after the other: the loads of a
+        // source are independent of the running sums, so several sources overlap in flight
+        for (int p = 0; p < P; ++p) {
+          if (p == r) continue;
+          uint4 y[kBatch];
+#pragma unroll
+          for (int j = 0; j < kBatch; ++j) {
+            const int q = q0 + j * 32;
+            y[j] = q < n4 ? ld_cg_u4(cell0 + (int64_t)p * src_stride + q * 4) : make_uint4(0, 0, 0, 0);
+          }
+#pragma unroll
+          for (int j = 0; j < kBatch; ++j) { x[j].x += y[j].x; x[j].y += y[j].y; x[j].z += y[j].z; x[j].w += y[j].w; }
+        }
       }
-    } else {
-      for (int q = lane; q < words / 4; q += 32) {
-        const uint4 x = reduced4(slot, q);
-        out4[q] = x;
-        put4(x, q * 4);
+      if (derive) {
+        uint4 a[kBatch];
+#pragma unroll
+        for (int j = 0; j < kBatch; ++j) {
+          const int q = q0 + j * 32;
+          a[j] = q < n4 ? ld_cg_u4(par4 + q) : make_uint4(0, 0, 0, 0);
+        }
+#pragma unroll
+        for (int j = 0; j < kBatch; ++j)
+          x[j] = make_uint4(a[j].x - x[j].x, a[j].y - x[j].y, a[j].z - x[j].z, a[j].w - x[j].w);
+      }
+#pragma unroll
+      for (int j = 0; j < kBatch; ++j) {
+        const int q = q0 + j * 32;
+        if (q < n4) {
+          out4[q] = x[j];
+          put4(x[j], q * 4);
+        }
       }
     }
   } else if (mode == MTB_MODE_DERIVE) {
     const int par = ptr_of<const int>(ctx.slot_parent)[slot];
     const int sib = ptr_of<const int>(ctx.slot_sibling)[slot];
-    const uint32_t* hp = v.hist_prev() + (int64_t)par * v.slab_words() + (int64_t)f * B * C;
-    const uint32_t* hs = v.hist_cur() + (int64_t)sib * v.slab_words() + (int64_t)f * B * C;
-    const uint4* hp4 = reinterpret_cast<const uint4*>(hp);
-    const uint4* hs4 = reinterpret_cast<const uint4*>(hs);
-    uint4* mine4 = reinterpret_cast<uint4*>(mine);
-#pragma unroll 4
-    for (int q = lane; q < words / 4; q += 32) {
-      const uint4 a = hp4[q], d = hs4[q];
-      const uint4 x = make_uint4(a.x - d.x, a.y - d.y, a.z - d.z, a.w - d.w);
-      mine4[q] = x;
-      put4(x, q * 4);
+    const uint4* hp4 = reinterpret_cast<const uint4*>(v.hist_prev() + (int64_t)par * v.slab_words() + fBC);
+    const uint4* hs4 = reinterpret_cast<const uint4*>(v.hist_cur() + (int64_t)sib * v.slab_words() + fBC);
+    uint4* mine4 = reinterpret_cast<uint4*>(v.hist_cur() + (int64_t)slot * v.slab_words() + fBC);
+    for (int q0 = lane; q0 < n4; q0 += kBatch * 32) {
+      uint4 a[kBatch], d[kBatch];
+#pragma unroll
+      for (int j = 0; j < kBatch; ++j) {
+        const int q = q0 + j * 32;
+        if (q < n4) { a[j] = ld_cg_u4(hp4 + q); d[j] = ld_cg_u4(hs4 + q); }
+      }
+#pragma unroll
+      for (int j = 0; j < kBatch; ++j) {
+        const int q = q0 + j * 32;
+        if (q < n4) {
+          const uint4 z = make_uint4(a[j].x - d[j].x, a[j].y - d[j].y, a[j].z - d[j].z, a[j].w - d[j].w);
+          mine4[q] = z;
+          put4(z, q * 4);
+        }
+      }
     }
   } else {
-    const uint4* mine4 = reinterpret_cast<const uint4*>(mine);
-#pragma unroll 4
-    for (int q = lane; q < words / 4; q += 32) put4(mine4[q], q * 4);
+    const uint4* mine4 = reinterpret_cast<const uint4*>(v.hist_cur() + (int64_t)slot * v.slab_words() + fBC);
+    for (int q0 = lane; q0 < n4; q0 += kBatch * 32) {
+      uint4 a[kBatch];
+#pragma unroll
+      for (int j = 0; j < kBatch; ++j) {
+        const int q = q0 + j * 32;
+        if (q < n4) a[j] = ld_cg_u4(mine4 + q);
+      }
+#pragma unroll
+      for (int j = 0; j < kBatch; ++j) {
+        const int q = q0 + j * 32;
+        if (q < n4) put4(a[j], q * 4);
+      }
+    }
   }
   __syncwarp();
 
@@ -617,7 +680,49 @@ __device__ void gain_pair(const MtbCtx& ctx, uint32_t* slab, int slot, int f) {
   const uint32_t plogp_n = (uint32_t)ctx.plogp_n;
   // small nodes: the reference's exact float64 operation order; large nodes: the cheap form
   const bool exact = plogp == nullptr || n <= plogp_n;
-  const KlogK klogk{ptr_of<const double>(ctx.klogk), (uint32_t)ctx.klogk_n};
+  if (!exact && crit == 0) {
+    // Entropy, large node.  Four of the lane's bins are evaluated together: an fp64 operation has a
+    // latency of some 40 cycles here, so the eight independent g() chains per class are what keeps
+    // the pipe busy (one bin at a time ran at ~500 cycles per g()).  Per bin the summation order is
+    // that of fast_split_cost: s = g(nL) + g(nR), then s -= g(kL_c) + g(kR_c) for ascending c.
+    const double dn = u2d(n);
+    for (int j0 = 0; j0 < BPL; j0 += 4) {
+      uint32_t nl4[4] = {0, 0, 0, 0};
+      int jj[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) jj[u] = min(j0 + u, BPL - 1) * C;
+      for (int c = 0; c < C; ++c) {
+#pragma unroll
+        for (int u = 0; u < 4; ++u) nl4[u] += my[jj[u] + c];
+      }
+      double s4[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) s4[u] = __dadd_rn(klogk(nl4[u]), klogk(n - nl4[u]));
+      for (int c = 0; c < C; ++c) {
+        const uint32_t tc = last[c];
+        double a[4], b[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const uint32_t l = my[jj[u] + c];
+          a[u] = klogk(l);
+          b[u] = klogk(tc - l);
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) s4[u] = __dsub_rn(s4[u], __dadd_rn(a[u], b[u]));
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int j = j0 + u;
+        if (j < BPL && (present >> j & 1u) && nl4[u] != n) {  // an empty right side is not a usable split
+          const double cost = __ddiv_rn(s4[u], dn);
+          if (cost < best) {  // strict: first (lowest) bin wins ties inside the lane
+            best = cost;
+            best_bin = lane * BPL + j;
+          }
+        }
+      }
+    }
+  } else
   for (int j = 0; j < BPL; ++j) {
     if (!(present >> j & 1u)) continue;
     const uint32_t* L = my + j * C;
@@ -664,38 +769,42 @@ __device__ void gain_pair(const MtbCtx& ctx, uint32_t* slab, int slot, int f) {
   __syncwarp();
 }
 
-// pass -1: every pair (the normal case); 0 / 1: BUILD+NONE / DERIVE slots only (kept for
-// experiments: pairs never depend on one another, see gain_pair).
+// `warps`: warps of the CTA that may take part (the first ones); `smem_bytes`: dynamic shared memory
+// available to the phase (fewer warps work when their slabs do not all fit).  pass -1: every pair;
+// 0 / 1: BUILD+NONE / DERIVE slots only (kept for experiments: pairs never depend on one another).
 template <bool NV = false>
-__device__ void gain_phase(const MtbCtx& ctx, uint8_t* smem, int warps_per_block, int pass) {
+__device__ void gain_phase(const MtbCtx& ctx, uint8_t* smem, int warps, int smem_bytes, int pass) {
   View v(ctx);
   const int F = (int)ctx.F;
   const int f_lo = (int)(ctx.rank * ctx.fpo);
   const int f_hi = min(F, f_lo + (int)ctx.fpo);
   const int n_own = max(0, f_hi - f_lo);
   const int n_pairs = v.n_slots() * n_own;
-  const int slab_words = (int)ctx.B * (int)ctx.C + 32;
+  const GainGeom gg = gain_geom((int)ctx.B, (int)ctx.C, warps, smem_bytes);
+  // constants of g(k) = k log2 k into shared memory (33 KB), coefficients into registers
+  double* tab = reinterpret_cast<double*>(smem);
+  const double* gtab = ptr_of<const double>(ctx.klogk);
+  for (int i = threadIdx.x; i < kKlogkTabDoubles; i += blockDim.x) tab[i] = gtab[i];
+  __syncthreads();
   const int w = warp_id();
-  if (w >= warps_per_block) return;
-  uint32_t* slab = reinterpret_cast<uint32_t*>(smem) + (size_t)w * slab_words;
-  // a DERIVE pair reads a sibling slab completed in the hist phase: pairs are independent
+  if (w >= gg.warps) return;
+  KlogK klogk;
+  klogk.bind(tab, gtab);
+  uint32_t* slab = reinterpret_cast<uint32_t*>(smem + kGainTabBytes) + (size_t)w * gg.slab_words;
   const int* mode = ptr_of<const int>(ctx.slot_mode);
-  // dynamic scheduling: pairs differ a lot in cost (NONE slots are free, DERIVE reads two slabs)
-  int* counter = v.scalars() + (pass == 1 ? 7 : 6);
-  for (;;) {
-    int p = 0;
-    if (lane_id() == 0) p = atomicAdd(counter, 1);
-    p = __shfl_sync(0xffffffffu, p, 0);
-    if (p >= n_pairs) break;
+  const int total_warps = gg.warps * (int)gridDim.x;
+  // pairs are dealt round-robin, CTAs first: a level with few pairs spreads over the SMs, and the
+  // pairs of one slot (equal cost) spread over the warps
+  for (int p = w * (int)gridDim.x + (int)blockIdx.x; p < n_pairs; p += total_warps) {
     const int slot = p / n_own;
     if (pass >= 0 && (mode[slot] == MTB_MODE_DERIVE) != (pass == 1)) continue;
-    gain_pair<NV>(ctx, slab, slot, f_lo + p % n_own);
+    gain_pair<NV>(ctx, klogk, slab, slot, f_lo + p % n_own);
   }
 }
 
-__global__ void __launch_bounds__(kGainWarps * 32) k_gain(const __grid_constant__ MtbCtx ctx, int pass) {
+__global__ void __launch_bounds__(kGainWarps * 32) k_gain(const __grid_constant__ MtbCtx ctx, int pass, int smem_bytes) {
   extern __shared__ __align__(128) uint8_t smem[];
-  gain_phase(ctx, smem, kGainWarps, pass);
+  gain_phase(ctx, smem, kGainWarps, smem_bytes, pass);
 }
 
 // -------------------------------------------------------------------- finalize
@@ -760,22 +869,29 @@ __device__ void finalize_phase(const MtbCtx& ctx, int* smem_warp) {
       uint32_t ntot;
       if (!is_terminal([&](int c) { return cnt[c]; }, C, depth, ctx, ntot)) {
         const bool exact = ctx.plogp == 0 || ntot <= (uint32_t)ctx.plogp_n;
-        const KlogK klogk{ptr_of<const double>(ctx.klogk), (uint32_t)ctx.klogk_n};
+        KlogK klogk;
+        klogk.bind(ptr_of<const double>(ctx.klogk), ptr_of<const double>(ctx.klogk));  // a handful of evaluations per slot: global table
         const double hp = exact ? impurity(C, [&](int c) { return cnt[c]; }, ntot, (int)ctx.criterion,
                                            ptr_of<const double>(ctx.plogp), (uint32_t)ctx.plogp_n)
                                 : fast_impurity(C, [&](int c) { return cnt[c]; }, ntot, (int)ctx.criterion, klogk);
         bool have = false;
-        for (int f = 0; f < F; ++f) {
-          const double cost = fb_cost[(int64_t)s * F + f];
-          if (!(cost < INFINITY)) continue;
-          const double g = __dsub_rn(hp, cost);
-          if (!have || g > bgain) {  // strict: first (lowest) feature wins ties
-            have = true;
-            bgain = g;
-            bf = f;
-            bb = fb_bin[(int64_t)s * F + f];
+        // costs of eight features are loaded together: the loop is bound by load latency otherwise
+        for (int f0 = 0; f0 < F; f0 += 8) {
+          double cst[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) cst[j] = f0 + j < F ? fb_cost[(int64_t)s * F + f0 + j] : INFINITY;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            if (!(cst[j] < INFINITY)) continue;
+            const double g = __dsub_rn(hp, cst[j]);
+            if (!have || g > bgain) {  // strict: first (lowest) feature wins ties
+              have = true;
+              bgain = g;
+              bf = f0 + j;
+            }
           }
         }
+        if (have) bb = fb_bin[(int64_t)s * F + bf];
         if (have) {
           split = 1;
           const uint32_t* L = fb_left + ((int64_t)s * F + bf) * C;
@@ -1002,116 +1118,88 @@ __global__ void k_commit(const __grid_constant__ MtbCtx ctx) {
 
 // ------------------------------------------------ partition fused with the next level's histograms
 // Levels >= 1.  P is the finished parent level, C the same buffers seen from the children's
-// level.  Three grid-wide steps replace the separate partition kernel and the histogram phase:
+// level.  Two grid-wide steps replace the separate partition kernel and the histogram phase:
 //
-//   prepass  one pass over the split feature's plane only: "goes left" bits of every 1024-row
-//            unit and the unit's destination bases (atomic cursors per parent slot);
-//   move     every (parent slot, feature tile, unit): stream the plane tile with TMA, rank rows
-//            from the unit's bit words, write them to their child's segment, and - for rows of
-//            the child that is built directly - increment the child's shared-memory histogram
-//            tile.  Memory traffic and shared-memory atomics overlap instead of adding up;
+//   move A   the (parent slot, split feature's plane) tiles.  Rows, labels arrive by TMA; a
+//            *ranker* warp reads the split feature's byte of the unit's 1,024 rows from the staged
+//            tile, forms the "goes left" bit words and their prefix, reserves the unit's
+//            destination ranges with one atomic pair per unit, and hands the unit record to the
+//            consumer warps through shared memory (and to step B through global memory).  The
+//            consumers rank rows from the bit words, write them to their child's segment and - for
+//            rows of the child that is built directly - increment the child's histogram tile;
+//   move B   all other (parent slot, feature tile) pairs: same consumers, the unit record now
+//            arrives by TMA next to the rows.
 //   commit   children's row segments (+ hand-off list).
-struct PartUnit {
-  int slot, chunk, r0, r1;
-};
-
+//
+// Every plane is read exactly once per level (round 1 had a separate pre-pass over the split
+// feature's plane: 0.4 ms of a 3.4 ms level on 100M x 64).
 constexpr int kMetaWords = 68;  // per partition unit: 32 "goes left" words, 32 exclusive left-count prefixes, base_l, base_r, 2 pad (272 B)
+constexpr int kRankers = 3;  // ranker warps: a unit's record waits ~2 us for its atomics, units are dealt round-robin
+constexpr int kFusedThreads = kConsumers + 32 + 32 * kRankers;  // consumers + producer warp + ranker warps (20 warps:
+                                                                // five per scheduler, the same 96-register budget as 17)
 
-// One warp per 1024-row unit, no block-wide syncs: lane i ends up holding bit word i, the unit's
-// destination bases are reserved with one atomic pair, and the 144-byte unit record is written
-// in one go (it is later fetched by TMA next to the unit's rows).
-__device__ void prepass_phase(const MtbCtx& P) {
-  View v(P);
-  const int n_slots = v.n_slots();
-  const int total = v.scalars()[4];
-  const int* pprefix = ptr_of<const int>(P.unit_prefix) + (P.m_cap + 1);
-  const int* sb = ptr_of<const int>(P.slot_begin);
-  const int* se = ptr_of<const int>(P.slot_end);
-  const int* rec_feature = ptr_of<const int>(P.rec_feature);
-  const int* rec_bin = ptr_of<const int>(P.rec_bin);
-  uint32_t* cursors = ptr_of<uint32_t>(P.cursors);
-  uint32_t* meta = ptr_of<uint32_t>(P.mask_words);
-  const uint4* src = reinterpret_cast<const uint4*>(v.codes_cur());
-  const int64_t plane = P.n_cap;
-  const int lane = lane_id();
-  const int warps = blockDim.x >> 5;
-  for (int u = blockIdx.x * warps + warp_id(); u < total; u += gridDim.x * warps) {
-    const int slot = find_slot(pprefix, n_slots, u);
-    const int chunk = u - pprefix[slot];
-    const int e = se[slot];
-    const int r0 = sb[slot] + chunk * kPartRows;
-    const int f = rec_feature[slot], bin = rec_bin[slot];
-    const uint8_t* col = reinterpret_cast<const uint8_t*>(src + (int64_t)(f >> 4) * plane) + (f & 15);
-    uint32_t mine = 0, nl = 0, nv = 0;
-#pragma unroll 8
-    for (int i = 0; i < 32; ++i) {
-      const int row = r0 + i * 32 + lane;
-      const bool valid = row < e;
-      uint32_t code = 0;
-      if (valid) code = col[(int64_t)row * 16];
-      const uint32_t ml = __ballot_sync(0xffffffffu, valid && (int)code <= bin);
-      const uint32_t mv = __ballot_sync(0xffffffffu, valid);
-      if (lane == i) mine = ml;
-      nl += __popc(ml);
-      nv += __popc(mv);
-    }
-    uint32_t* rec = meta + (int64_t)u * kMetaWords;
-    rec[lane] = mine;
-    const uint32_t pc = __popc(mine);
-    rec[32 + lane] = warp_incl_scan(pc) - pc;  // lefts before word `lane`: ranks need no scan later
-    if (lane == 0) {
-      rec[64] = atomicAdd(&cursors[2 * slot], nl);
-      rec[65] = atomicAdd(&cursors[2 * slot + 1], nv - nl);
-    }
-  }
-}
-
-// cursor over (parent slot, feature tile gs, 1024-row unit) triples, slot-major
+// cursor over (parent slot, tile ordinal j, 1024-row unit) triples, slot-major; `tiles` ordinals per slot
 struct MoveCursor {
   const int* pprefix;
   const int* sb;
   const int* se;
-  int n_slots, GS;
+  int n_slots, tiles;
   int slot, slot_u0, slot_u1, chunks, begin, end;
-  int gs, chunk, row0, nrows;
+  int j, chunk, row0, nrows;
   __device__ __forceinline__ int find(int u) const {
     int lo = 0, hi = n_slots;
     while (hi - lo > 1) {
       const int mid = (lo + hi) >> 1;
-      if (pprefix[mid] * GS <= u) lo = mid; else hi = mid;
+      if (pprefix[mid] * tiles <= u) lo = mid; else hi = mid;
     }
     return lo;
   }
-  __device__ void init(const MtbCtx& P, int n_slots_) {
+  __device__ void init(const MtbCtx& P, int n_slots_, int tiles_) {
     pprefix = ptr_of<const int>(P.unit_prefix) + (P.m_cap + 1);
     sb = ptr_of<const int>(P.slot_begin);
     se = ptr_of<const int>(P.slot_end);
     n_slots = n_slots_;
-    GS = (int)(P.G * (16 / P.FT));
+    tiles = tiles_;
     slot = -1;
     slot_u0 = slot_u1 = 0;
   }
   __device__ __forceinline__ void seek(int u) {
     if (u >= slot_u1 || slot < 0) {
       slot = find(u);
-      slot_u0 = pprefix[slot] * GS;
-      slot_u1 = pprefix[slot + 1] * GS;
+      slot_u0 = pprefix[slot] * tiles;
+      slot_u1 = pprefix[slot + 1] * tiles;
       begin = sb[slot];
       end = se[slot];
       chunks = pprefix[slot + 1] - pprefix[slot];
       const int local = u - slot_u0;
-      gs = local / chunks;
-      chunk = local - gs * chunks;
+      j = local / chunks;
+      chunk = local - j * chunks;
     } else if (++chunk == chunks) {
       chunk = 0;
-      ++gs;
+      ++j;
     }
+    row0 = begin + chunk * kPartRows;
+    nrows = min(kPartRows, end - row0);
+  }
+  // position on an arbitrary unit (the rankers stride through the range)
+  __device__ __forceinline__ void seek_to(int u) {
+    if (u >= slot_u1 || slot < 0) {
+      slot = find(u);
+      slot_u0 = pprefix[slot] * tiles;
+      slot_u1 = pprefix[slot + 1] * tiles;
+      begin = sb[slot];
+      end = se[slot];
+      chunks = pprefix[slot + 1] - pprefix[slot];
+    }
+    const int local = u - slot_u0;
+    j = local / chunks;
+    chunk = local - j * chunks;
     row0 = begin + chunk * kPartRows;
     nrows = min(kPartRows, end - row0);
   }
   __device__ __forceinline__ int unit_index() const { return pprefix[slot] + chunk; }
   __device__ __forceinline__ bool owns_whole_tile(int u0, int u1) const {
-    const int t0 = slot_u0 + gs * chunks;
+    const int t0 = slot_u0 + j * chunks;
     return u0 <= t0 && t0 + chunks <= u1;
   }
 };
@@ -1130,58 +1218,129 @@ __host__ __device__ inline HistGeom move_geom(int FT, int B, int C) {
   return g;
 }
 
+// ring position of a pipeline role, carried from step A to step B
+struct Ring {
+  int st;
+  uint32_t ph;
+  __device__ __forceinline__ void next(int stages) {
+    if (++st == stages) { st = 0; ph ^= 1; }
+  }
+};
+
+struct MoveSmem {
+  uint32_t* tile;
+  uint8_t* stage_base;
+  uint64_t *full, *empty, *ready;
+  int stages;
+};
+
+__device__ __forceinline__ MoveSmem move_smem(uint8_t* smem, const HistGeom& geom) {
+  MoveSmem m;
+  m.tile = reinterpret_cast<uint32_t*>(smem);
+  m.stage_base = smem + (size_t)geom.tile_words * 4;
+  m.full = reinterpret_cast<uint64_t*>(m.stage_base + (size_t)geom.stages * kStage2Bytes);
+  m.empty = m.full + kMaxStages;
+  m.ready = m.empty + kMaxStages;
+  m.stages = geom.stages;
+  return m;
+}
+
+// step 0: the split feature's plane of every parent (ranker warp active); step 1: every other tile
 template <int FT, bool IL = false>
-__device__ void move_hist_phase(const MtbCtx& P, const MtbCtx& C, uint8_t* smem) {
+__device__ void move_hist_phase(const MtbCtx& P, const MtbCtx& C, uint8_t* smem, int step, Ring& ring) {
   View vp(P);
   const int B = (int)P.B, Cn = (int)P.C;
-  const HistGeom geom = move_geom(FT, B, Cn);
-  uint32_t* tile = reinterpret_cast<uint32_t*>(smem);
-  uint8_t* stage_base = smem + (size_t)geom.tile_words * 4;
-  uint64_t* full = reinterpret_cast<uint64_t*>(stage_base + (size_t)geom.stages * kStage2Bytes);
-  uint64_t* empty = full + kMaxStages;
-  const int stages = geom.stages;
+  const MoveSmem ms = move_smem(smem, move_geom(FT, B, Cn));
+  uint32_t* tile = ms.tile;
+  const int stages = ms.stages;
   const int n_slots = vp.n_slots();
   const int S = 16 / FT;
   const int GS = (int)(P.G * S);
-  const int total_units = vp.scalars()[4] * GS;
+  const int tiles = step == 0 ? 1 : GS - 1;
+  const int total_units = vp.scalars()[4] * tiles;
   const int u0 = (int)((int64_t)total_units * blockIdx.x / gridDim.x);
   const int u1 = (int)((int64_t)total_units * (blockIdx.x + 1) / gridDim.x);
   const int tid = threadIdx.x;
-  if (tid == 0) {
-    for (int i = 0; i < stages; ++i) {
-      mbar_init(&full[i], 1);
-      mbar_init(&empty[i], kConsumerWarps);
-    }
-    fence_barrier_init();
-  }
-  for (int i = tid; i < geom.tile_words; i += blockDim.x) tile[i] = 0;
-  __syncthreads();
 
   const uint8_t* codes = vp.codes_cur();
   const uint8_t* lsrc = vp.labels_cur();
-  const uint32_t* meta = ptr_of<const uint32_t>(P.mask_words);
+  uint32_t* meta = ptr_of<uint32_t>(P.mask_words);
+  const int* rec_feature = ptr_of<const int>(P.rec_feature);
   MoveCursor cur;
-  cur.init(P, n_slots);
+  cur.init(P, n_slots, tiles);
+  // feature tile of (slot, ordinal j): step 0 handles the split plane's first tile, step 1 skips it
+  auto tile_of = [&](int slot, int j) -> int {
+    const int gsA = (rec_feature[slot] >> 4) * S;
+    return step == 0 ? gsA : (j < gsA ? j : j + 1);
+  };
 
+  if (tid >= kConsumers + 32) {
+    // ===== ranker warps (step 0): "goes left" bits, prefixes and destination bases of each unit.
+    // Ranker k takes the units u0 + k, u0 + k + kRankers, ... and follows the stage ring on its own.
+    if (step != 0) return;
+    const int lane = tid & 31, rk = (tid - kConsumers - 32) >> 5;
+    const int* rec_bin = ptr_of<const int>(P.rec_bin);
+    uint32_t* cursors = ptr_of<uint32_t>(P.cursors);
+    Ring mine_ring = ring;
+    for (int i = 0; i < rk; ++i) mine_ring.next(stages);
+    for (int u = u0 + rk; u < u1; u += kRankers) {
+      cur.seek_to(u);
+      const int f = rec_feature[cur.slot], bin = rec_bin[cur.slot];
+      mbar_wait(&ms.full[mine_ring.st], mine_ring.ph);
+      uint8_t* sbuf = ms.stage_base + (size_t)mine_ring.st * kStage2Bytes;
+      const uint8_t* col = sbuf + (f & 15);
+      uint32_t mine = 0, nl = 0;
+#pragma unroll 8
+      for (int i = 0; i < 32; ++i) {
+        const int row = i * 32 + lane;
+        const bool valid = row < cur.nrows;
+        const uint32_t code = valid ? col[row * 16] : 0xffffu;
+        const uint32_t ml = __ballot_sync(0xffffffffu, valid && (int)code <= bin);
+        if (lane == i) mine = ml;
+        nl += __popc(ml);
+      }
+      const uint32_t pc = __popc(mine);
+      const uint32_t before = warp_incl_scan(pc) - pc;  // lefts before word `lane`: ranks need no scan later
+      uint32_t base_l = 0, base_r = 0;
+      if (lane == 0) {
+        base_l = atomicAdd(&cursors[2 * cur.slot], nl);
+        base_r = atomicAdd(&cursors[2 * cur.slot + 1], (uint32_t)cur.nrows - nl);
+      }
+      uint32_t* rec = reinterpret_cast<uint32_t*>(sbuf + kStageBytes + kLabelStage);
+      rec[lane] = mine;
+      rec[32 + lane] = before;
+      if (lane == 0) { rec[64] = base_l; rec[65] = base_r; }
+      if (GS > 1) {  // step B fetches the record by TMA
+        uint32_t* grec = meta + (int64_t)cur.unit_index() * kMetaWords;
+        grec[lane] = mine;
+        grec[32 + lane] = before;
+        if (lane == 0) { grec[64] = base_l; grec[65] = base_r; }
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&ms.ready[mine_ring.st]);
+#pragma unroll
+      for (int i = 0; i < kRankers; ++i) mine_ring.next(stages);
+    }
+    return;
+  }
   if (tid >= kConsumers) {
-    // ===== producer: rows of one plane, their labels and the unit record, all by TMA =====
+    // ===== producer: rows of one plane, their labels (and in step B the unit record), all by TMA =====
     if (tid == kConsumers) {
-      int st = 0;
-      uint32_t ph = 0;
       for (int u = u0; u < u1; ++u) {
         cur.seek(u);
-        const int g = cur.gs / S;
-        mbar_wait(&empty[st], ph ^ 1);
-        uint8_t* sbuf = stage_base + (size_t)st * kStage2Bytes;
+        const int g = tile_of(cur.slot, cur.j) / S;
+        mbar_wait(&ms.empty[ring.st], ring.ph ^ 1);
+        uint8_t* sbuf = ms.stage_base + (size_t)ring.st * kStage2Bytes;
         const uint32_t cbytes = (uint32_t)cur.nrows * 16u;
         const uint32_t loff = (uint32_t)cur.row0 & 15u;
         const uint32_t lbytes = (loff + (uint32_t)cur.nrows + 15u) & ~15u;
-        mbar_arrive_expect_tx(&full[st], cbytes + lbytes + kMetaWords * 4);
-        tma_load_1d(sbuf, codes + ((int64_t)g * P.n_cap + cur.row0) * 16, cbytes, &full[st]);
-        tma_load_1d(sbuf + kStageBytes, lsrc + (cur.row0 - (int)loff), lbytes, &full[st]);
-        tma_load_1d(sbuf + kStageBytes + kLabelStage, meta + (int64_t)cur.unit_index() * kMetaWords, kMetaWords * 4,
-                    &full[st]);
-        if (++st == stages) { st = 0; ph ^= 1; }
+        mbar_arrive_expect_tx(&ms.full[ring.st], cbytes + lbytes + (step ? kMetaWords * 4 : 0));
+        tma_load_1d(sbuf, codes + ((int64_t)g * P.n_cap + cur.row0) * 16, cbytes, &ms.full[ring.st]);
+        tma_load_1d(sbuf + kStageBytes, lsrc + (cur.row0 - (int)loff), lbytes, &ms.full[ring.st]);
+        if (step)
+          tma_load_1d(sbuf + kStageBytes + kLabelStage, meta + (int64_t)cur.unit_index() * kMetaWords, kMetaWords * 4,
+                      &ms.full[ring.st]);
+        ring.next(stages);
       }
     }
     return;
@@ -1194,20 +1353,20 @@ __device__ void move_hist_phase(const MtbCtx& P, const MtbCtx& C, uint8_t* smem)
   const int* part_child = ptr_of<const int>(P.part_child);
   const int* cmode = ptr_of<const int>(C.slot_mode);
   const int64_t plane = P.n_cap;
-  int st = 0;
-  uint32_t ph = 0;
-  int cur_slot = -1, cur_gs = -1, build_child = -1, build_side = -1, flags = 0;
+  uint64_t* avail = step == 0 ? ms.ready : ms.full;  // step A: the ranker has filled in the unit record
+  int cur_slot = -1, cur_j = -1, cur_gs = -1, build_child = -1, build_side = -1, flags = 0;
   bool cur_excl = false;
   for (int u = u0; u < u1; ++u) {
     cur.seek(u);
-    if (cur.slot != cur_slot || cur.gs != cur_gs) {
+    if (cur.slot != cur_slot || cur.j != cur_j) {
       if (build_child >= 0) {
         named_bar_sync(1, kConsumers);
         flush_tile<FT, IL>(C, tile, build_child, cur_gs, tid, cur_excl);
         named_bar_sync(1, kConsumers);
       }
       cur_slot = cur.slot;
-      cur_gs = cur.gs;
+      cur_j = cur.j;
+      cur_gs = tile_of(cur.slot, cur.j);
       cur_excl = cur.owns_whole_tile(u0, u1);
       flags = part_flags[cur_slot];
       const int a = part_child[cur_slot];
@@ -1218,25 +1377,25 @@ __device__ void move_hist_phase(const MtbCtx& P, const MtbCtx& C, uint8_t* smem)
         else if (cmode[a + 1] == MTB_MODE_BUILD) { build_child = a + 1; build_side = 1; }
       }
     }
-    const int g = cur.gs / S, sub = (cur.gs % S) * FT;
-    const bool mover = (cur.gs % S) == 0;  // one feature tile per plane moves the plane's bytes
+    const int g = cur_gs / S, sub = (cur_gs % S) * FT;
+    const bool mover = (cur_gs % S) == 0;  // one feature tile per plane moves the plane's bytes
     const int ra = w * 64 + lane, rb = ra + 32;
     const bool va_ok = ra < cur.nrows, vb_ok = rb < cur.nrows;
-    mbar_wait(&full[st], ph);
-    const uint8_t* sbuf = stage_base + (size_t)st * kStage2Bytes;
+    mbar_wait(&avail[ring.st], ring.ph);
+    const uint8_t* sbuf = ms.stage_base + (size_t)ring.st * kStage2Bytes;
     const uint4* rows = reinterpret_cast<const uint4*>(sbuf);
     const uint8_t* slab = sbuf + kStageBytes + ((uint32_t)cur.row0 & 15u);
     const uint32_t* rec = reinterpret_cast<const uint32_t*>(sbuf + kStageBytes + kLabelStage);
     // rank rows from the unit's "goes left" bits
     const uint32_t w0 = rec[2 * w], w1 = rec[2 * w + 1];
-    const uint32_t before0 = rec[32 + 2 * w];  // lefts before word 2w (from the prepass)
+    const uint32_t before0 = rec[32 + 2 * w];  // lefts before word 2w
     const uint32_t base_l = rec[64], base_r = rec[65];
     uint4 xa = make_uint4(0, 0, 0, 0), xb = xa;
     uint32_t lab_a = 0, lab_b = 0;
     if (va_ok) { xa = rows[ra]; lab_a = slab[ra]; }
     if (vb_ok) { xb = rows[rb]; lab_b = slab[rb]; }
     __syncwarp();
-    if (lane == 0) mbar_arrive(&empty[st]);
+    if (lane == 0) mbar_arrive(&ms.empty[ring.st]);
     const uint32_t below = (1u << lane) - 1u;
     const bool la = (w0 >> lane) & 1u, lb = (w1 >> lane) & 1u;
     const uint32_t lefts_a = before0 + __popc(w0 & below);
@@ -1271,7 +1430,7 @@ __device__ void move_hist_phase(const MtbCtx& P, const MtbCtx& C, uint8_t* smem)
         }
       }
     }
-    if (++st == stages) { st = 0; ph ^= 1; }
+    ring.next(stages);
   }
   if (build_child >= 0) {
     named_bar_sync(1, kConsumers);
@@ -1292,8 +1451,56 @@ __device__ __forceinline__ void stamp(const MtbCtx& ctx, int i) {
   }
 }
 
+// Grid-wide zero fill of `n_slabs` histogram slabs starting at `base` (128-bit stores).
+__device__ void zero_slabs(uint32_t* base, int64_t slab_words, int n_slabs) {
+  uint4* p = reinterpret_cast<uint4*>(base);
+  const int64_t n16 = slab_words * n_slabs / 4;
+  const uint4 z = make_uint4(0, 0, 0, 0);
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += (int64_t)gridDim.x * blockDim.x)
+    st_na_u4(p + i, z);
+}
+
+// After a level's search: the slabs the next level accumulates into must start at zero.  They are
+// the other ping-pong side (dead once this level's DERIVE pairs have read their parents); with
+// peers the one side is reused, dead once every rank has passed the second barrier.  The next
+// frontier has at most two slots per current slot.  Runs while CTA 0 finalizes.
+__device__ void zero_next_level(const MtbCtx& ctx) {
+  if (ctx.max_depth >= 0 && ctx.depth + 1 >= ctx.max_depth) return;
+  View v(ctx);
+  int64_t n = 2 * (int64_t)v.n_slots();
+  if (n > ctx.h_cap) n = ctx.h_cap;
+  zero_slabs(ptr_of<uint32_t>(ctx.hist[ctx.hcur ^ 1]), v.slab_words(), (int)n);
+}
+
+template <bool NV>
+__device__ __forceinline__ void search_tail(const MtbCtx& ctx, cg::grid_group& grid, uint8_t* smem, int smem_bytes,
+                                            int* smem_warp, bool zero_next) {
+  if (ctx.world > 1) {
+    grid.sync();
+    stamp(ctx, 2);
+    if constexpr (!NV) push_phase(ctx);
+    peer_barrier(ctx, grid, (uint32_t)ctx.epoch + 1u);
+    stamp(ctx, 3);
+    gain_phase<NV>(ctx, smem, kFusedGainWarps, smem_bytes, -1);
+    stamp(ctx, 4);
+    peer_barrier(ctx, grid, (uint32_t)ctx.epoch + 2u);
+    stamp(ctx, 5);
+  } else {
+    grid.sync();
+    stamp(ctx, 2);
+    stamp(ctx, 3);
+    gain_phase(ctx, smem, kFusedGainWarps, smem_bytes, -1);
+    grid.sync();
+    stamp(ctx, 4);
+    stamp(ctx, 5);
+  }
+  if (blockIdx.x == 0) finalize_phase(ctx, smem_warp);
+  stamp(ctx, 6);
+  if (zero_next) zero_next_level(ctx);
+}
+
 template <int FT, bool IL = false, bool NV = false>
-__global__ void __launch_bounds__(kHistThreads, 1) k_level_fused(const __grid_constant__ MtbCtx ctx) {
+__global__ void __launch_bounds__(kFusedThreads, 1) k_level_fused(const __grid_constant__ MtbCtx ctx, int smem_bytes) {
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ int smem_warp[33];
   cg::grid_group grid = cg::this_grid();
@@ -1302,35 +1509,19 @@ __global__ void __launch_bounds__(kHistThreads, 1) k_level_fused(const __grid_co
   if (ptr_of<const int>(ctx.scalars)[0] == 0) return;
   stamp(ctx, 0);
   if (blockIdx.x == 0) plan_phase(ctx, smem_warp);
+  {  // the slabs this level accumulates into start at zero (shared tiles are merged with red.add)
+    View v(ctx);
+    zero_slabs(v.hist_cur(), v.slab_words(), v.n_slots());
+  }
   grid.sync();
   stamp(ctx, 1);
   hist_phase<FT, IL>(ctx, smem);
-  if (ctx.world > 1) {
-    grid.sync();
-    stamp(ctx, 2);
-    if constexpr (!NV) push_phase(ctx);
-    peer_barrier(ctx, grid, (uint32_t)ctx.epoch + 1u);
-    stamp(ctx, 3);
-    gain_phase<NV>(ctx, smem, kFusedGainWarps, -1);
-    stamp(ctx, 4);
-    peer_barrier(ctx, grid, (uint32_t)ctx.epoch + 2u);
-    stamp(ctx, 5);
-  } else {
-    grid.sync();
-    stamp(ctx, 2);
-    stamp(ctx, 3);
-    gain_phase(ctx, smem, kFusedGainWarps, -1);
-    grid.sync();
-    stamp(ctx, 4);
-    stamp(ctx, 5);
-  }
-  if (blockIdx.x == 0) finalize_phase(ctx, smem_warp);
-  stamp(ctx, 6);
+  search_tail<NV>(ctx, grid, smem, smem_bytes, smem_warp, ctx.zero_next != 0);
 }
 
 template <int FT, bool IL = false, bool NV = false>
-__global__ void __launch_bounds__(kHistThreads, 1) k_level_fused2(const __grid_constant__ MtbCtx P,
-                                                                  const __grid_constant__ MtbCtx C) {
+__global__ void __launch_bounds__(kFusedThreads, 1) k_level_fused2(const __grid_constant__ MtbCtx P,
+                                                                   const __grid_constant__ MtbCtx C, int smem_bytes) {
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ int smem_warp[33];
   cg::grid_group grid = cg::this_grid();
@@ -1340,37 +1531,35 @@ __global__ void __launch_bounds__(kHistThreads, 1) k_level_fused2(const __grid_c
     return;
   }
   stamp(C, 0);
-  prepass_phase(P);
-  grid.sync();
-  stamp(C, 8);
-  move_hist_phase<FT, IL>(P, C, smem);
+  {
+    const HistGeom geom = move_geom(FT, (int)P.B, (int)P.C);
+    const MoveSmem ms = move_smem(smem, geom);
+    if (threadIdx.x == 0) {
+      for (int i = 0; i < geom.stages; ++i) {
+        mbar_init(&ms.full[i], 1);
+        mbar_init(&ms.empty[i], kConsumerWarps);
+        mbar_init(&ms.ready[i], 1);
+      }
+      fence_barrier_init();
+    }
+    for (int i = threadIdx.x; i < geom.tile_words; i += blockDim.x) ms.tile[i] = 0;
+    __syncthreads();
+  }
+  Ring ring{0, 0};
+  move_hist_phase<FT, IL>(P, C, smem, 0, ring);
+  if (P.G * (16 / FT) > 1) {
+    fence_proxy_async();  // the ranker's generic-proxy writes precede step B's TMA writes to the stages
+    grid.sync();          // unit records (global) and destination bases are complete
+    stamp(C, 8);
+    move_hist_phase<FT, IL>(P, C, smem, 1, ring);
+  }
   grid.sync();
   commit_phase(P);
   if (blockIdx.x == 0 && threadIdx.x == 0) ptr_of<int>(P.scalars)[0] = ptr_of<int>(P.scalars)[1];
   grid.sync();
   stamp(C, 1);
   if (blockIdx.x == 0) plan_phase(C, smem_warp);  // resets cursors and the gain work counters
-  if (C.world > 1) {
-    grid.sync();
-    stamp(C, 2);
-    if constexpr (!NV) push_phase(C);
-    peer_barrier(C, grid, (uint32_t)C.epoch + 1u);
-    stamp(C, 3);
-    gain_phase<NV>(C, smem, kFusedGainWarps, -1);
-    stamp(C, 4);
-    peer_barrier(C, grid, (uint32_t)C.epoch + 2u);
-    stamp(C, 5);
-  } else {
-    grid.sync();
-    stamp(C, 2);
-    stamp(C, 3);
-    gain_phase(C, smem, kFusedGainWarps, -1);
-    grid.sync();
-    stamp(C, 4);
-    stamp(C, 5);
-  }
-  if (blockIdx.x == 0) finalize_phase(C, smem_warp);
-  stamp(C, 6);
+  search_tail<NV>(C, grid, smem, smem_bytes, smem_warp, true);
 }
 
 int g_sm_count = 0;
@@ -1389,11 +1578,15 @@ int set_smem(K kernel, int bytes) {
   return 0;
 }
 
-int gain_smem(const MtbCtx* ctx) { return kGainWarps * ((int)ctx->B * (int)ctx->C + 32) * 4; }
+// unfused gain kernel: as many warps as fit in shared memory with their slabs
+int gain_smem(const MtbCtx* ctx) {
+  GainGeom g = gain_geom((int)ctx->B, (int)ctx->C, kGainWarps, 227 * 1024);
+  return g.warps < 1 ? -1 : kGainTabBytes + g.warps * g.slab_words * 4;
+}
 
 }  // namespace
 
-// ctx->tile_layout == 1 selects the interleaved shared-memory tile (FT == 16 only; opt-in).
+// ctx->tile_layout == 1 selects the interleaved shared-memory tile (FT == 16 only).
 static bool interleaved(const MtbCtx* ctx) { return ctx->tile_layout == 1 && ctx->FT == 16; }
 // ctx->mc_hist set (world > 1): the histogram slabs are multicast-mapped and the owners reduce in the switch.
 static bool in_switch(const MtbCtx* ctx) { return ctx->world > 1 && ctx->mc_hist[ctx->hcur] != 0; }
@@ -1417,48 +1610,38 @@ static int launch_hist(const MtbCtx* ctx, const HistGeom& g, cudaStream_t stream
 template <int FT>
 static int launch_fused(const MtbCtx* ctx, int smem, cudaStream_t stream) {
   MtbCtx local = *ctx;
-  void* args[] = {&local};
+  void* args[] = {&local, &smem};
+  void* fn = (void*)k_level_fused<FT>;
   if constexpr (FT == 16) {
     const bool il = interleaved(ctx), nv = in_switch(ctx);
-    if (il || nv) {
-      void* fn = il ? (nv ? (void*)k_level_fused<16, true, true> : (void*)k_level_fused<16, true, false>)
-                    : (void*)k_level_fused<16, false, true>;
-      MTB_CHECK(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-      MTB_CHECK(cudaLaunchCooperativeKernel(fn, dim3(sm_count()), dim3(kHistThreads), args, smem, stream));
-      return 0;
-    }
-  }
-  if (in_switch(ctx)) {
+    if (il || nv)
+      fn = il ? (nv ? (void*)k_level_fused<16, true, true> : (void*)k_level_fused<16, true, false>)
+              : (void*)k_level_fused<16, false, true>;
+  } else if (in_switch(ctx)) {
     mtb_set_error("fused", "the in-switch reduction is only built for 16-feature tiles", __FILE__, __LINE__);
     return -2;
   }
-  if (set_smem(k_level_fused<FT>, smem)) return -1;
-  MTB_CHECK(cudaLaunchCooperativeKernel((void*)k_level_fused<FT>, dim3(sm_count()), dim3(kHistThreads), args, smem,
-                                        stream));
+  MTB_CHECK(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  MTB_CHECK(cudaLaunchCooperativeKernel(fn, dim3(sm_count()), dim3(kFusedThreads), args, smem, stream));
   return 0;
 }
 
 template <int FT>
 static int launch_fused2(const MtbCtx* P, const MtbCtx* C, int smem, cudaStream_t stream) {
   MtbCtx p = *P, c = *C;
-  void* args[] = {&p, &c};
+  void* args[] = {&p, &c, &smem};
+  void* fn = (void*)k_level_fused2<FT>;
   if constexpr (FT == 16) {
     const bool il = interleaved(P), nv = in_switch(C);
-    if (il || nv) {
-      void* fn = il ? (nv ? (void*)k_level_fused2<16, true, true> : (void*)k_level_fused2<16, true, false>)
-                    : (void*)k_level_fused2<16, false, true>;
-      MTB_CHECK(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-      MTB_CHECK(cudaLaunchCooperativeKernel(fn, dim3(sm_count()), dim3(kHistThreads), args, smem, stream));
-      return 0;
-    }
-  }
-  if (in_switch(C)) {
+    if (il || nv)
+      fn = il ? (nv ? (void*)k_level_fused2<16, true, true> : (void*)k_level_fused2<16, true, false>)
+              : (void*)k_level_fused2<16, false, true>;
+  } else if (in_switch(C)) {
     mtb_set_error("fused2", "the in-switch reduction is only built for 16-feature tiles", __FILE__, __LINE__);
     return -2;
   }
-  if (set_smem(k_level_fused2<FT>, smem)) return -1;
-  MTB_CHECK(cudaLaunchCooperativeKernel((void*)k_level_fused2<FT>, dim3(sm_count()), dim3(kHistThreads), args, smem,
-                                        stream));
+  MTB_CHECK(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  MTB_CHECK(cudaLaunchCooperativeKernel(fn, dim3(sm_count()), dim3(kFusedThreads), args, smem, stream));
   return 0;
 }
 
@@ -1474,13 +1657,28 @@ static int launch_fused2(const MtbCtx* P, const MtbCtx* C, int smem, cudaStream_
       return -2;                                                                                       \
   }
 
+// Shared memory of the fused kernels: the larger of the histogram / move pipelines, grown if needed so
+// that at least one gain warp's slab fits.  -1: the shape does not fit (no FT helps: the gain slab is B x C).
+static int fused_smem(const MtbCtx* ctx, bool with_move) {
+  HistGeom g = hist_geom((int)ctx->FT, (int)ctx->B, (int)ctx->C);
+  int smem = g.smem_bytes;
+  if (with_move) {
+    HistGeom mg = move_geom((int)ctx->FT, (int)ctx->B, (int)ctx->C);
+    if (mg.smem_bytes > smem) smem = mg.smem_bytes;
+  }
+  GainGeom gg = gain_geom((int)ctx->B, (int)ctx->C, kFusedGainWarps, smem);
+  if (gg.warps < 1) smem = kGainTabBytes + gg.slab_words * 4;
+  return smem <= 227 * 1024 ? smem : -1;
+}
+
 extern "C" int mtb_hist_config(const MtbCtx* ctx, int* threads, int* smem_bytes, int* stages, int* rows_per_stage) {
   HistGeom g = hist_geom((int)ctx->FT, (int)ctx->B, (int)ctx->C);
-  if (threads) *threads = kHistThreads;
+  if (threads) *threads = kFusedThreads;
   if (smem_bytes) *smem_bytes = g.smem_bytes;
   if (stages) *stages = g.stages;
   if (rows_per_stage) *rows_per_stage = kRows;
-  return g.stages >= 2 ? 0 : -2;
+  if (g.stages < 2 || move_geom((int)ctx->FT, (int)ctx->B, (int)ctx->C).stages < 2) return -2;
+  return fused_smem(ctx, true) > 0 && gain_smem(ctx) > 0 ? 0 : -2;
 }
 
 extern "C" int mtb_level_plan(const MtbCtx* ctx, void* stream) {
@@ -1500,13 +1698,18 @@ extern "C" int mtb_level_hist(const MtbCtx* ctx, void* stream) {
 
 extern "C" int mtb_level_gain(const MtbCtx* ctx, void* stream) {
   const int smem = gain_smem(ctx);
+  if (smem < 0) {
+    mtb_set_error("gain", "bins x classes too large for a shared-memory gain slab", __FILE__, __LINE__);
+    return -2;
+  }
   if (set_smem(k_gain, smem)) return -1;
+  const GainGeom gg = gain_geom((int)ctx->B, (int)ctx->C, kGainWarps, smem);
   int64_t pairs = ctx->n_slots_host * (ctx->world > 1 ? ctx->fpo : ctx->F);
-  int blocks = (int)((pairs + kGainWarps - 1) / kGainWarps);
+  int blocks = (int)((pairs + gg.warps - 1) / gg.warps);
   int maxb = sm_count() * 2;
   if (blocks > maxb) blocks = maxb;
   if (blocks < 1) blocks = 1;
-  k_gain<<<blocks, kGainWarps * 32, smem, (cudaStream_t)stream>>>(*ctx, -1);
+  k_gain<<<blocks, kGainWarps * 32, smem, (cudaStream_t)stream>>>(*ctx, -1, smem);
   MTB_CHECK(cudaGetLastError());
   return 0;
 }
@@ -1537,38 +1740,48 @@ extern "C" int mtb_level_commit(const MtbCtx* ctx, void* stream) {
 }
 
 extern "C" int mtb_level_fused(const MtbCtx* ctx, void* stream) {
-  HistGeom g = hist_geom((int)ctx->FT, (int)ctx->B, (int)ctx->C);
-  if (g.stages < 2) {
+  if (hist_geom((int)ctx->FT, (int)ctx->B, (int)ctx->C).stages < 2) {
     mtb_set_error("hist", "histogram tile does not fit in shared memory", __FILE__, __LINE__);
     return -2;
   }
-  int smem = g.smem_bytes;
-  const int gsm = kFusedGainWarps * ((int)ctx->B * (int)ctx->C + 32) * 4;
-  if (gsm > smem) smem = gsm;
-  if (smem > 227 * 1024) {
-    mtb_set_error("fused", "gain slabs do not fit in shared memory", __FILE__, __LINE__);
+  const int smem = fused_smem(ctx, false);
+  if (smem < 0) {
+    mtb_set_error("fused", "gain slab does not fit in shared memory", __FILE__, __LINE__);
     return -2;
   }
   FT_SWITCH((int)ctx->FT, launch_fused, ctx, smem, (cudaStream_t)stream);
 }
 
 extern "C" int mtb_level_fused2(const MtbCtx* parents, const MtbCtx* children, void* stream) {
-  HistGeom g = hist_geom((int)parents->FT, (int)parents->B, (int)parents->C);
-  if (g.stages < 2) {
+  if (hist_geom((int)parents->FT, (int)parents->B, (int)parents->C).stages < 2) {
     mtb_set_error("hist", "histogram tile does not fit in shared memory", __FILE__, __LINE__);
     return -2;
   }
-  HistGeom mg = move_geom((int)parents->FT, (int)parents->B, (int)parents->C);
-  if (mg.stages < 2) {
+  if (move_geom((int)parents->FT, (int)parents->B, (int)parents->C).stages < 2) {
     mtb_set_error("fused2", "histogram tile leaves no room for two row stages", __FILE__, __LINE__);
     return -3;
   }
-  int smem = mg.smem_bytes > g.smem_bytes ? mg.smem_bytes : g.smem_bytes;
-  const int gsm = kFusedGainWarps * ((int)parents->B * (int)parents->C + 32) * 4;
-  if (gsm > smem) smem = gsm;
-  if (smem > 227 * 1024) {
-    mtb_set_error("fused", "gain slabs do not fit in shared memory", __FILE__, __LINE__);
+  const int smem = fused_smem(parents, true);
+  if (smem < 0) {
+    mtb_set_error("fused", "gain slab does not fit in shared memory", __FILE__, __LINE__);
     return -2;
   }
   FT_SWITCH((int)parents->FT, launch_fused2, parents, children, smem, (cudaStream_t)stream);
+}
+
+/* Test hook: out[i] = g(k[i]) = k log2 k evaluated by the device function the gain phase uses
+ * (one thread per value; `table` = the klogk constants).                                    */
+namespace {
+__global__ void k_klogk_eval(const uint32_t* k, double* out, int64_t n, const double* table) {
+  KlogK g;
+  g.bind(table, table);
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = g(k[i]);
+}
+}  // namespace
+extern "C" int mtb_klogk_eval(const uint32_t* k, double* out, int64_t n, const double* table, void* stream) {
+  if (n <= 0) return 0;
+  k_klogk_eval<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(k, out, n, table);
+  MTB_CHECK(cudaGetLastError());
+  return 0;
 }

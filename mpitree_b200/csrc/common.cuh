@@ -109,6 +109,15 @@ __device__ __forceinline__ uint4 ld_nc_u4(const void* p) {
                : "l"(p));
   return r;
 }
+// coherent 128-bit load served by L2 (data written earlier in the same launch or by peers)
+__device__ __forceinline__ uint4 ld_cg_u4(const void* p) {
+  uint4 r;
+  asm volatile("ld.global.cg.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p)
+               : "memory");
+  return r;
+}
 __device__ __forceinline__ void st_na_u4(void* p, uint4 v) {
   asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y),
                "r"(v.z), "r"(v.w)

@@ -71,7 +71,8 @@ __device__ void eval_feature(const MtbSubtreeArgs& a, uint32_t* h, uint32_t m, d
   const uint32_t* last = h + (B - 1) * C;  // inclusive prefix at the last bin == class totals
   const double* plogp = ptr_of<const double>(a.plogp);
   const bool exact = plogp == nullptr || m <= (uint32_t)a.plogp_n;
-  const KlogK klogk{ptr_of<const double>(a.klogk), (uint32_t)a.klogk_n};
+  KlogK klogk;
+  klogk.bind(ptr_of<const double>(a.klogk), ptr_of<const double>(a.klogk));
   const int crit = (int)a.criterion, dm = (int)a.dot_mode;
   double best = INFINITY;
   int best_bin = 0x7fffffff;
@@ -182,7 +183,8 @@ __global__ void __launch_bounds__(kThreads, 1) k_subtree(const __grid_constant__
       if (terminal) continue;  // stays a leaf (record already initialised)
 
       const bool exact = a.plogp == 0 || (uint32_t)m <= (uint32_t)a.plogp_n;
-      const KlogK klogk{ptr_of<const double>(a.klogk), (uint32_t)a.klogk_n};
+      KlogK klogk;
+      klogk.bind(ptr_of<const double>(a.klogk), ptr_of<const double>(a.klogk));
       const double hp = exact ? impurity(C, [&](int c) { return cnt[c]; }, (uint32_t)m, (int)a.criterion,
                                          ptr_of<const double>(a.plogp), (uint32_t)a.plogp_n)
                               : fast_impurity(C, [&](int c) { return cnt[c]; }, (uint32_t)m, (int)a.criterion, klogk);

@@ -52,7 +52,7 @@ class MtbCtx(ctypes.Structure):
         + [(n, ctypes.c_int64) for n in "epoch plogp plogp_n h_cap fpo timers klogk klogk_n".split()]
         + [("rstore", ctypes.c_int64 * 2)]
         + [(n, ctypes.c_int64) for n in
-           "small_rows ho_cap ho_node ho_begin ho_end ho_side part_child mask_words unit_base tile_layout".split()]
+           "small_rows ho_cap ho_node ho_begin ho_end ho_side part_child mask_words zero_next tile_layout".split()]
         + [("mc_hist", ctypes.c_int64 * 2)]
     )
 

@@ -42,6 +42,8 @@ __all__ = [
     "best_split_rows",
     "best_split_rows_many",
     "build_tree_cpu",
+    "klogk",
+    "klogk_constants",
     "probe_dot_mode",
     "SplitParams",
 ]
@@ -135,6 +137,49 @@ def _impurity_rows(counts: np.ndarray, totals: np.ndarray, criterion: str) -> np
             t = np.where(counts > 0, p * np.log2(np.where(counts > 0, p, 1.0)), 0.0)
         return -t.sum(axis=-1)
     return 1.0 - (p * p).sum(axis=-1)
+
+
+_KLOGK_IDX_BITS = 7
+
+
+@functools.lru_cache(maxsize=1)
+def klogk_constants() -> np.ndarray:
+    """Constants of the device ``k * log2(k)`` evaluation (``csrc/impurity.cuh::KlogK``), device layout:
+    ``inv[128] = 1/m0`` | ``el[32][128] = e + log2 m0`` | ``c1..c6`` for interval centres
+    ``m0 = 1 + (i + 1/2)/128`` and exponents ``e = 0..31``."""
+    n = 1 << _KLOGK_IDX_BITS
+    m0 = 1.0 + (np.arange(n, dtype=np.float64) + 0.5) / n  # exact
+    ln2 = float(np.log(2.0))
+    el = np.arange(32, dtype=np.float64)[:, None] + np.log2(m0)[None, :]
+    coef = [(1.0 if j % 2 else -1.0) / (j * ln2) for j in range(1, 7)]
+    return np.concatenate([1.0 / m0, el.ravel(), np.asarray(coef)])
+
+
+def klogk(k: np.ndarray) -> np.ndarray:
+    """``k * log2(k)`` for unsigned 32-bit counts by the device's formula (numpy twin of
+    ``csrc/impurity.cuh::KlogK``; the device fuses the Horner steps, so results agree to a few ulp).
+
+    ``floor(log2 k)`` comes from the exponent of ``float(k)``; the top 7 mantissa bits pick an interval
+    centre ``m0``; ``r = (m - m0) * fl(1/m0)``, ``|r| <= 2**-8``; ``log2(1 + r)`` is a degree-6 Horner
+    polynomial.  ``g(0) = g(1) = 0``.
+    """
+    n = 1 << _KLOGK_IDX_BITS
+    tab = klogk_constants()
+    inv, el, c = tab[:n], tab[n : n + 32 * n], tab[n + 32 * n :]
+    k = np.asarray(k, dtype=np.uint32)
+    kd = k.astype(np.float64)
+    bits = kd.view(np.int64)
+    hi = bits >> 32
+    top = (hi >> (20 - _KLOGK_IDX_BITS)) - (1023 << _KLOGK_IDX_BITS)
+    idx = top & (n - 1)
+    m = ((bits & 0x000FFFFFFFFFFFFF) | 0x3FF0000000000000).view(np.float64)
+    m0 = ((0x3FF00000 | (idx << (20 - _KLOGK_IDX_BITS)) | (1 << (19 - _KLOGK_IDX_BITS))) << 32).view(np.float64)
+    r = (m - m0) * inv[idx]
+    p = c[5] * r + c[4]
+    for j in (3, 2, 1, 0):
+        p = p * r + c[j]
+    out = kd * (p * r + el[np.clip(top, 0, 32 * n - 1)])
+    return np.where(k <= 1, 0.0, out)
 
 
 _KLOGK_MAX = 1 << 23  # table of k*log2(k) up to 8M rows per node (64 MB); larger nodes use log2 directly

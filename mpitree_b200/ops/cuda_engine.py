@@ -107,19 +107,23 @@ def plogp_table(device):
     return _PLOGP_CACHE[key]
 
 
-KLOGK_N = 1 << 16
+KLOGK_N = 128  # interval centres of the k*log2(k) evaluation (csrc/impurity.cuh)
 
 
 def klogk_table(device):
-    """Device table of ``k * log2(k)`` for ``k < KLOGK_N`` (``0`` at ``k = 0``), used for large nodes."""
+    """Device constants of the arithmetic ``k * log2(k)`` evaluation used for large nodes.
+
+    ``1/m0`` for the 128 interval centres ``m0 = 1 + (i + 1/2)/128``, ``e + log2 m0`` for every (exponent,
+    interval) and the six polynomial coefficients of ``log2(1 + r)``; see ``cpu_engine.klogk`` for the
+    numpy twin of the device function (``csrc/impurity.cuh::KlogK``).
+    """
     import torch
+
+    from .cpu_engine import klogk_constants
 
     key = ("klogk", str(device))
     if key not in _PLOGP_CACHE:
-        k = np.arange(KLOGK_N, dtype=np.float64)
-        with np.errstate(divide="ignore", invalid="ignore"):
-            t = np.where(k > 0, k * np.log2(np.where(k > 0, k, 1.0)), 0.0)
-        _PLOGP_CACHE[key] = torch.from_numpy(t).to(device)
+        _PLOGP_CACHE[key] = torch.from_numpy(klogk_constants()).to(device)
     return _PLOGP_CACHE[key]
 
 
@@ -491,6 +495,9 @@ class TreeBuilder:
             max_units = data.n_cap // 1024 + m_cap + 2
             self.part_child = tables["part_child"][:m_cap]
             self.mask_words = z(max_units * 68)  # 272-byte unit records (32 bit words, 32 prefixes, 2 bases, pad)
+        # one cooperative launch per level (these kernels zero the slabs they accumulate into)
+        self._coop = reduce == "p2p" or (reduce == "none" and fused)
+        ctx.zero_next = 1 if self.fuse_partition else 0
         self._ctx_prev = None
         self._bound_tree = None  # tree arrays the context currently points at (see _bind)
         self._alloc_tree(self.node_cap)
@@ -627,12 +634,14 @@ class TreeBuilder:
         self.ctx.depth = self.depth
         self.ctx.n_slots_host = n_slots
         self._bind()
-        # slabs of BUILD slots must start at zero (DERIVE slots are overwritten)
-        self.hist[self.hcur][: n_slots * self.slab_words].zero_()
+        # slabs of BUILD slots must start at zero (DERIVE slots are overwritten); the cooperative
+        # level kernels do that themselves
+        if not self._coop:
+            self.hist[self.hcur][: n_slots * self.slab_words].zero_()
 
     def search_level(self) -> None:
         """plan + histogram + reduction + gain + finalize for the current level."""
-        if self.reduce == "p2p" or (self.reduce == "none" and self.fused):
+        if self._coop:
             if self.reduce == "p2p":
                 self.ctx.epoch = _EPOCH["next"]
                 _EPOCH["next"] += 2
@@ -730,7 +739,8 @@ class TreeBuilder:
             self.ctx.depth = depth
             self.ctx.n_slots_host = self.n_slots
             self._bind()
-            self.hist[self.hcur][: self.n_slots * self.slab_words].zero_()
+            if not self._coop:
+                self.hist[self.hcur][: self.n_slots * self.slab_words].zero_()
             self.search_level()
             self._swap_sides()
             self.stats.levels += 1

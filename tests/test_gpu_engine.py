@@ -230,3 +230,47 @@ def test_unbounded_depth_many_small_nodes():
     assert clf.score(X, y) == 1.0  # distinct rows: a fully grown tree memorises the data
     leaves = flat.feature < 0
     assert int(flat.counts[leaves].sum()) == n
+
+
+def test_klogk_device_function_matches_numpy_twin():
+    """g(k) = k log2 k of the gain phase (csrc/impurity.cuh::KlogK) against its numpy twin and plain numpy."""
+    import ctypes
+
+    import torch
+
+    from mpitree_b200.ops import _lib
+    from mpitree_b200.ops.cpu_engine import klogk
+    from mpitree_b200.ops.cuda_engine import klogk_table
+
+    rng = np.random.default_rng(0)
+    k = np.concatenate([np.arange(0, 70000), 2 ** np.arange(32, dtype=np.int64), 2 ** np.arange(1, 33, dtype=np.int64) - 1,
+                        rng.integers(0, 2**32, size=200_000)]).astype(np.uint32)
+    kd = torch.from_numpy(k.view(np.int32)).cuda()
+    out = torch.empty(k.shape[0], dtype=torch.float64, device="cuda")
+    tab = klogk_table(torch.device("cuda", torch.cuda.current_device()))
+    rc = _lib.load().mtb_klogk_eval(ctypes.c_void_p(kd.data_ptr()), ctypes.c_void_p(out.data_ptr()),
+                                    ctypes.c_int64(k.shape[0]), ctypes.c_void_p(tab.data_ptr()),
+                                    ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+    assert rc == 0
+    got = out.cpu().numpy()
+    want = klogk(k)
+    big = k > 1
+    assert np.all(got[~big] == 0.0)
+    assert np.max(np.abs(got[big] - want[big]) / want[big]) < 5e-16  # fused vs separately rounded Horner steps
+    ref = k[big].astype(np.float64) * np.log2(k[big].astype(np.float64))
+    assert np.max(np.abs(got[big] - ref) / ref) < 1e-15
+
+
+@pytest.mark.parametrize("C", [15, 16, 64, 128])
+def test_many_classes_with_256_bins(C):
+    """B = 256 with many classes: the gain slab of one (node, feature) pair is B x C words and must still
+    fit next to (or instead of) the histogram pipeline's shared memory (fewer gain groups, smaller tiles)."""
+    rng = np.random.default_rng(C)
+    n, F = 40_000, 6
+    X = rng.integers(0, 256, size=(n, F), dtype=np.uint8)
+    y = ((X[:, 0].astype(np.int64) * 3 + X[:, 1] + rng.integers(0, 40, size=n)) * C // 1100).clip(0, C - 1)
+    y[:C] = np.arange(C)  # every class occurs
+    g = DecisionTreeClassifier(max_depth=5, device="cuda").fit(X, y)
+    c = DecisionTreeClassifier(max_depth=5, device="cpu").fit(X, y)
+    assert g.engine_ == "cuda"
+    _same_tree(g, c)
