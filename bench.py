@@ -43,6 +43,8 @@ def parse():
     ap.add_argument("--depth", type=int, default=10)
     ap.add_argument("--reduce", default=os.environ.get("MTB_REDUCE", "auto"), choices=["auto", "p2p", "nccl", "nvls"])
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-nccl", action="store_true", help="skip the in-process ncclAllReduce baseline pass (N > 1)")
+    ap.add_argument("--no-same-config", action="store_true", help="skip the 250-row like-for-like record")
     ap.add_argument("--ref-budget-s", type=float, default=float(os.environ.get("MTB_REF_BUDGET_S", "150")))
     return ap.parse_args()
 
@@ -170,21 +172,94 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------ ours
-def synth_shard(torch, dev, rows, features, classes, seed):
-    """Seeded synthetic shard on the device: uint8 bin codes + labels with real structure."""
-    g = torch.Generator(device=dev).manual_seed(seed)
-    X = torch.randint(0, 256, (rows, features), dtype=torch.uint8, device=dev, generator=g)
+BLOCK_ROWS = 1 << 20  # rows per generator block: the data set is a pure function of (seed, global row index)
+
+
+def synth_rows(torch, dev, lo, hi, features, classes, seed=1234):
+    """Rows ``[lo, hi)`` of the seeded synthetic data set, generated on the device.
+
+    Every block of ``BLOCK_ROWS`` global rows has its own generator state ``(seed, block)``, so any
+    sharding of the rows over ranks produces the same global matrix: N = 1, 2, 4, 8 fit one data set
+    and must grow one tree (``tree_sha`` in the JSON line).  uint8 bin codes + labels with real structure.
+    """
     k = min(8, features)
     w = torch.tensor([1.0, -0.8, 0.6, 0.5, -0.4, 0.3, 0.25, -0.2][:k], device=dev)
-    score = torch.zeros(rows, device=dev)
-    for j in range(k):  # column-wise to bound temporary memory
-        score += (X[:, j].float() - 127.5) * w[j]
-    score += 40.0 * torch.randn(rows, device=dev, generator=g)
-    # fixed class boundaries (identical on every rank): quantiles of the analytic score distribution
+    # fixed class boundaries: quantiles of the analytic score distribution
     sd = float((w.pow(2).sum() * (256 ** 2 - 1) / 12.0 + 1600.0).sqrt())
     qs = torch.distributions.Normal(0.0, sd).icdf(torch.linspace(0, 1, classes + 1, device=dev)[1:-1])
-    y = torch.bucketize(score, qs).to(torch.uint8)
+    X = torch.empty((hi - lo, features), dtype=torch.uint8, device=dev)
+    y = torch.empty(hi - lo, dtype=torch.uint8, device=dev)
+    for blk in range(lo // BLOCK_ROWS, (max(hi, lo + 1) - 1) // BLOCK_ROWS + 1):
+        b0 = blk * BLOCK_ROWS
+        g = torch.Generator(device=dev).manual_seed(seed * 1_000_003 + blk)
+        Xb = torch.randint(0, 256, (BLOCK_ROWS, features), dtype=torch.uint8, device=dev, generator=g)
+        score = (Xb[:, :k].float() - 127.5) @ w + 40.0 * torch.randn(BLOCK_ROWS, device=dev, generator=g)
+        yb = torch.bucketize(score, qs).to(torch.uint8)
+        s0, s1 = max(lo, b0), min(hi, b0 + BLOCK_ROWS)
+        if s1 > s0:
+            X[s0 - lo : s1 - lo] = Xb[s0 - b0 : s1 - b0]
+            y[s0 - lo : s1 - lo] = yb[s0 - b0 : s1 - b0]
     return X, y
+
+
+def tree_sha(flat) -> str:
+    """Short hash of the fitted tree (split features, bins, topology, class counts)."""
+    import hashlib
+
+    import numpy as np
+
+    h = hashlib.sha256()
+    for name in ("feature", "bin", "left", "counts"):
+        h.update(np.ascontiguousarray(getattr(flat, name)).astype(np.int64).tobytes())
+    return h.hexdigest()[:16]
+
+
+REF_ROWS = 250  # rows of the like-for-like configuration shared with the reference arm
+
+
+def ref_config_data(n, features, classes):
+    """The numpy data set the reference arm fits (shared by both arms: same generator, same ``n``)."""
+    import numpy as np
+
+    rng = np.random.default_rng(1234)
+    X = rng.integers(0, 256, size=(n, features)).astype(np.float64)
+    w = np.array([1.0, -0.8, 0.6, 0.5, -0.4, 0.3, 0.25, -0.2][: min(8, features)])
+    score = (X[:, : len(w)] - 127.5) @ w + 40.0 * rng.normal(size=n)
+    qs = np.quantile(score, np.linspace(0, 1, classes + 1)[1:-1])
+    return X, np.digitize(score, qs)
+
+
+def same_config_record(a, torch):
+    """Our estimator on exactly the array the reference arm times (``REF_ROWS`` x features, host numpy in,
+    fitted tree out), plus a check that it grows the reference's tree.  Rank 0, outside the timed regions."""
+    from mpitree_b200.tree import DecisionTreeClassifier
+
+    X, y = ref_config_data(REF_ROWS, a.features, a.classes)
+    clf = DecisionTreeClassifier(max_depth=a.depth, device="cuda")
+    for _ in range(2):
+        clf.fit(X, y)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    reps = 5
+    for _ in range(reps):
+        clf.fit(X, y)
+    torch.cuda.synchronize()
+    ms = (time.perf_counter() - t0) / reps * 1e3
+    rec = {"rows": REF_ROWS, "features": a.features, "ms_per_fit_wall": ms, "rows_per_s": REF_ROWS / (ms / 1e3),
+           "engine": clf.engine_, "input": "host numpy float64 (the reference arm's array), tree read back"}
+    try:
+        from baseline.oracle import load_reference
+
+        ref = load_reference()
+        if ref is not None:
+            t0 = time.perf_counter()
+            want = ref.DecisionTreeClassifier(max_depth=a.depth).fit(X, y)
+            rec["reference_fit_s"] = time.perf_counter() - t0
+            rec["tree_equal_to_reference"] = bool(want.export_text() == clf.export_text())
+    except Exception as exc:  # noqa: BLE001
+        rec["tree_equal_to_reference"] = None
+        rec["reference_error"] = str(exc).splitlines()[0][:160]
+    return rec
 
 
 def run_ours(a):
@@ -212,7 +287,7 @@ def run_ours(a):
         init_process_group_from_env("nccl")
 
     lo, hi = a.rows * rank // world, a.rows * (rank + 1) // world
-    X, y = synth_shard(torch, dev, hi - lo, a.features, a.classes, seed=1234 + rank)
+    X, y = synth_rows(torch, dev, lo, hi, a.features, a.classes)
     reduce = a.reduce
     clf = ParallelDecisionTreeClassifier(max_depth=a.depth, data_layout="sharded", device="cuda")
     if reduce != "auto":
@@ -250,8 +325,20 @@ def run_ours(a):
     ms_step = ms_total / a.steps
     value = a.rows / (ms_step / 1e3)
     n_nodes = clf.flat_tree_.n_nodes
+    sha = tree_sha(clf.flat_tree_)
     acc_rows = min(1_000_000, X.shape[0])
     acc = float((clf.predict(X[:acc_rows]) == y[:acc_rows].to(torch.int64)).float().mean().item())
+
+    # ---- the same fit with ncclAllReduce instead of the fused peer reduction (in-house GPU baseline)
+    vs_nccl = None
+    if world > 1 and reduce in ("auto", "p2p", "nvls") and not a.no_nccl:
+        base = ParallelDecisionTreeClassifier(max_depth=a.depth, data_layout="sharded", device="cuda")
+        base.builder_kwargs = {"reduce": "nccl"}
+        n_steps = max(1, min(a.steps, 3))
+        ms_nccl, _, _ = timed(lambda: base.fit(X, y), n_steps, max(1, min(a.warmup, 3)), False)
+        vs_nccl = {"ms_per_step_nccl": ms_nccl / n_steps, "speedup": (ms_nccl / n_steps) / ms_step,
+                   "same_tree": tree_sha(base.flat_tree_) == sha}
+        del base
 
     # ---- end-to-end arm: pinned host inputs, tree read back
     e2e = None
@@ -276,6 +363,12 @@ def run_ours(a):
             "steps": e_steps,
         }
 
+    same_cfg = None
+    if rank == 0 and not a.no_same_config:
+        try:
+            same_cfg = same_config_record(a, torch)
+        except Exception as exc:  # noqa: BLE001
+            same_cfg = {"error": str(exc).splitlines()[0][:200]}
     if rank == 0:
         stats = getattr(cuda_engine.fit_from_torch, "last_stats", None)
         out = {
@@ -291,7 +384,8 @@ def run_ours(a):
             "scaling": "strong",
             "vs_baseline": None,
             "dtype": "u8 bin codes / u32 counts / fp64 gain",
-            "data": "synthetic (seeded, generated on device; random-init, no files)",
+            "data": "synthetic (seeded, generated on device as a function of the global row index: the same "
+                    "matrix for every N; random-init, no files)",
             "impl": "ours",
             "config": {
                 "model": "entropy decision tree, level-wise fused split search",
@@ -302,6 +396,9 @@ def run_ours(a):
                              "are far larger than the 126 MB L2; no explicit flush",
                 "tree_nodes": n_nodes, "train_acc_first_1M": acc,
             },
+            "tree_sha": sha,
+            "vs_nccl": vs_nccl,
+            "same_config": same_cfg,
             "clocks": clocks,
             "e2e": e2e,
             "gpu_launches": launches,
@@ -330,12 +427,7 @@ def run_reference(a):
         return
 
     def data(n):
-        rng = np.random.default_rng(1234)
-        X = rng.integers(0, 256, size=(n, a.features)).astype(np.float64)
-        w = np.array([1.0, -0.8, 0.6, 0.5, -0.4, 0.3, 0.25, -0.2][: min(8, a.features)])
-        score = (X[:, : len(w)] - 127.5) @ w + 40.0 * rng.normal(size=n)
-        qs = np.quantile(score, np.linspace(0, 1, a.classes + 1)[1:-1])
-        return X, np.digitize(score, qs)
+        return ref_config_data(n, a.features, a.classes)
 
     cls = ref.ParallelDecisionTreeClassifier if world > 1 else ref.DecisionTreeClassifier
 
@@ -352,7 +444,9 @@ def run_reference(a):
     t_small = fit_time(base)
     fits = a.steps + a.warmup
     n = base
-    for cand in (8000, 4000, 2000, 1000, 500, 250, 125):
+    # REF_ROWS is the configuration our arm repeats (``same_config``); smaller only if even that
+    # does not fit the time budget
+    for cand in (REF_ROWS, 125):
         est = t_small * (cand / base) ** 1.7
         if est * fits <= a.ref_budget_s:
             n = cand
@@ -389,6 +483,9 @@ def run_reference(a):
                         "whose (steps+warmup) fits fit the time budget, rows/s is for that size",
             },
             "gpu_launches": 0,
+            # the reference runs on the host from host arrays: its timed region already is end to end
+            "e2e": {"value": n / sec, "unit": "rows/s", "ms_per_step": sec * 1e3, "h2d_bytes_per_step": 0,
+                    "d2h_bytes_per_step": 0, "note": "host-only code: inputs and the fitted tree never leave host memory"},
         }))
 
 
