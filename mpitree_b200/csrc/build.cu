@@ -110,8 +110,28 @@ __device__ int block_excl_scan(int v, int* smem_warp /*[33]*/, int& total) {
 }
 
 // ------------------------------------------------------------------------ plan
+// Depth 0: the frontier is the root slot over all local rows.  The kernel writes it (and the scalars)
+// itself, so a fit starts without any host-side fill or copy of the builder's tables.
+__device__ void init_root(const MtbCtx& ctx) {
+  if (threadIdx.x == 0) {
+    ptr_of<int>(ctx.slot_node)[0] = 0;
+    ptr_of<int>(ctx.slot_begin)[0] = 0;
+    ptr_of<int>(ctx.slot_end)[0] = (int)ctx.n_local;
+    ptr_of<int>(ctx.slot_mode)[0] = MTB_MODE_BUILD;
+    ptr_of<int>(ctx.slot_parent)[0] = -1;
+    ptr_of<int>(ctx.slot_sibling)[0] = -1;
+    int* sc = ptr_of<int>(ctx.scalars);
+    sc[0] = 1; sc[1] = 0; sc[2] = 1; sc[3] = 0; sc[4] = 0; sc[5] = 0; sc[6] = 0; sc[7] = 0;
+    ptr_of<int>(ctx.t_left)[0] = -1;
+    ptr_of<int>(ctx.t_parent)[0] = -1;
+    ptr_of<int>(ctx.t_depth)[0] = 0;
+  }
+  __syncthreads();
+}
+
 __device__ void plan_phase(const MtbCtx& ctx, int* smem_warp) {
   View v(ctx);
+  if (ctx.depth == 0) init_root(ctx);
   const int n = v.n_slots();
   const int* mode = ptr_of<const int>(ctx.slot_mode);
   const int* sb = ptr_of<const int>(ctx.slot_begin);
@@ -143,7 +163,7 @@ __device__ void plan_phase(const MtbCtx& ctx, int* smem_warp) {
 
 __global__ void k_plan(const __grid_constant__ MtbCtx ctx) {
   __shared__ int smem_warp[33];
-  if (ptr_of<const int>(ctx.scalars)[0] == 0) {  // empty frontier: leave a consistent "nothing to do"
+  if (ctx.depth > 0 && ptr_of<const int>(ctx.scalars)[0] == 0) {  // empty frontier: leave a consistent "nothing to do"
     if (threadIdx.x == 0) {
       int* sc = ptr_of<int>(ctx.scalars);
       sc[1] = 0; sc[3] = 0; sc[4] = 0; sc[6] = 0; sc[7] = 0;
@@ -1505,13 +1525,13 @@ __global__ void __launch_bounds__(kFusedThreads, 1) k_level_fused(const __grid_c
   __shared__ int smem_warp[33];
   cg::grid_group grid = cg::this_grid();
   // empty frontier (the tree finished at an earlier level): uniform early exit on every CTA of
-  // every rank, before any grid or peer barrier
-  if (ptr_of<const int>(ctx.scalars)[0] == 0) return;
+  // every rank, before any grid or peer barrier.  (Depth 0 starts a fit: CTA 0 writes the root slot.)
+  if (ctx.depth > 0 && ptr_of<const int>(ctx.scalars)[0] == 0) return;
   stamp(ctx, 0);
   if (blockIdx.x == 0) plan_phase(ctx, smem_warp);
   {  // the slabs this level accumulates into start at zero (shared tiles are merged with red.add)
     View v(ctx);
-    zero_slabs(v.hist_cur(), v.slab_words(), v.n_slots());
+    zero_slabs(v.hist_cur(), v.slab_words(), ctx.depth == 0 ? 1 : v.n_slots());
   }
   grid.sync();
   stamp(ctx, 1);

@@ -33,6 +33,7 @@ __all__ = [
     "DeviceDataset",
     "TreeBuilder",
     "KERNEL_LAUNCHES",
+    "clear_caches",
 ]
 
 MAX_CLASSES = 128
@@ -555,21 +556,23 @@ class TreeBuilder:
 
     # ------------------------------------------------------------------ tree
     def _alloc_tree(self, cap: int, old=None) -> None:
+        """Tree arrays (SoA, ``cap`` nodes) as views of one int32 buffer, so that a finished tree comes
+        back in a single device-to-host copy.  No initial fill: the kernels write every field of every
+        node they create (the root's by ``init_root``)."""
         torch = self.torch
         dev = self.data.device
-        new = {
-            "feature": torch.full((cap,), -1, dtype=torch.int32, device=dev),
-            "bin": torch.full((cap,), -1, dtype=torch.int32, device=dev),
-            "left": torch.full((cap,), -1, dtype=torch.int32, device=dev),
-            "parent": torch.full((cap,), -1, dtype=torch.int32, device=dev),
-            "depth": torch.zeros((cap,), dtype=torch.int32, device=dev),
-            "gain": torch.full((cap,), float("nan"), dtype=torch.float64, device=dev),
-            "counts": torch.zeros((cap * self.C,), dtype=torch.int32, device=dev),
-        }
+        C = self.C
+        cap = int(cap)
+        st = _round_up(cap, 64)  # every array starts on a 256-byte boundary
+        buf = torch.empty((7 + C) * st, dtype=torch.int32, device=dev)
+        new = {k: buf[i * st : i * st + cap] for i, k in enumerate(("feature", "bin", "left", "parent", "depth"))}
+        new["gain"] = buf[5 * st : 7 * st].view(torch.float64)[:cap]
+        new["counts"] = buf[7 * st : 7 * st + cap * C]
         if old is not None:
             for k, t in old.items():
                 new[k][: t.shape[0]].copy_(t)
         self.tree = new
+        self._tree_buf = buf
         self.node_cap = cap
 
     def _bind(self) -> None:
@@ -611,16 +614,16 @@ class TreeBuilder:
 
     # ------------------------------------------------------------ level steps
     def start(self) -> None:
-        torch = self.torch
-        cur = self.slots[self.side]
-        init = [0, 0, self.data.n_local, 1, -1, -1]
-        for k, v in zip(("node", "begin", "end", "mode", "parent", "sibling"), init):
-            cur[k][0] = v
-        self.scalars.copy_(torch.tensor([1, 0, 1, 0, 0, 0, 0, 0], dtype=torch.int32))
+        """Begin a fit.  Nothing is written to the device: the level-0 kernel initialises the root slot,
+        the scalars and the root node (``init_root`` in csrc/build.cu)."""
         self.n_slots, self.n_nodes, self.depth = 1, 1, 0
-        self._host_scal = torch.empty(8, dtype=torch.int32).pin_memory()
+        self.side, self.hcur = 0, 0
+        if getattr(self, "_host_scal", None) is None:
+            self._host_scal = self.torch.empty(8, dtype=self.torch.int32).pin_memory()
         self._phase_ns = []
         self._ctx_prev = None
+        self.stats.levels = self.stats.launches = self.stats.handed_off = 0
+        self.stats.level_ms = []
 
     def prepare_level(self) -> None:
         n_slots, n_nodes = self.n_slots, self.n_nodes
@@ -750,10 +753,18 @@ class TreeBuilder:
         return self._download(self.n_nodes)
 
     def _download(self, n_nodes: int) -> FlatTree:
-        t = {k: v[: n_nodes * (self.C if k == "counts" else 1)].cpu().numpy() for k, v in self.tree.items()}
+        cap, C = self.node_cap, self.C
+        st = _round_up(cap, 64)
+        if (7 + C) * st * 4 <= (8 << 20) or cap <= 2 * n_nodes:
+            host = self._tree_buf.cpu().numpy()  # one copy of all seven arrays
+            t = {k: host[i * st : i * st + n_nodes] for i, k in enumerate(("feature", "bin", "left", "parent", "depth"))}
+            t["gain"] = host[5 * st : 7 * st].view(np.float64)[:n_nodes]
+            t["counts"] = host[7 * st : 7 * st + n_nodes * C]
+        else:
+            t = {k: v[: n_nodes * (C if k == "counts" else 1)].cpu().numpy() for k, v in self.tree.items()}
         left = t["left"].astype(np.int32)
         right = np.where(left >= 0, left + 1, -1).astype(np.int32)
-        counts = t["counts"].view(np.uint32).reshape(n_nodes, self.C).astype(np.int64)
+        counts = t["counts"].view(np.uint32).reshape(n_nodes, C).astype(np.int64)
         return FlatTree(
             feature=t["feature"].astype(np.int32),
             bin=t["bin"].astype(np.int32),
@@ -847,6 +858,50 @@ def build_lockstep(builders: List[TreeBuilder]) -> List[FlatTree]:
         for b in builders:
             b.advance_level()
     return [b._download(b.n_nodes) for b in builders]
+
+
+# ---------------------------------------------------------------------------
+# builder cache
+# ---------------------------------------------------------------------------
+_BUILDERS: dict = {}
+_BUILDERS_MAX = 2
+
+
+def _params_key(params: SplitParams):
+    return (params.max_depth, int(params.min_samples_split), params.criterion)
+
+
+def _get_builder(key, data: DeviceDataset, make):
+    """A :class:`TreeBuilder` for ``key``, reused across fits.
+
+    Constructing a builder allocates a few dozen device buffers and (with several ranks) maps peer
+    regions; for repeated fits of the same problem shape that is pure overhead (2.2 ms per fit at two
+    ranks, more than the device time of a small fit).  ``key`` must be built from values every rank
+    agrees on, so that all ranks hit or miss together (a miss runs collectives).  A reused builder
+    only needs the new data set: every table it owns is rewritten by the kernels, starting with
+    ``init_root``.
+    """
+    b = _BUILDERS.pop(key, None)
+    if b is None:
+        b = make()
+        while len(_BUILDERS) >= _BUILDERS_MAX:
+            _BUILDERS.pop(next(iter(_BUILDERS))).close()
+    else:
+        b.data = data
+        b._bound_tree = None  # re-bind the data pointers
+    _BUILDERS[key] = b  # most recently used last
+    return b
+
+
+def clear_caches() -> None:
+    """Drop cached builders, peer regions and workspaces (frees their device memory)."""
+    for b in _BUILDERS.values():
+        b.close()
+    _BUILDERS.clear()
+    _WORKSPACE.clear()
+    for reg in _REGIONS.values():
+        reg.close()
+    _REGIONS.clear()
 
 
 # ---------------------------------------------------------------------------
@@ -1079,23 +1134,36 @@ def fit_from_torch(X, y, params: SplitParams, *, max_bins: int = 256, comm=None,
     y_dev = y.to(dev, non_blocking=True)
     if y_dev.dtype.is_floating_point or y_dev.dtype == torch.bool:
         raise TypeError("class labels must be non-negative integers")
-    if y_dev.numel() == 0:
-        if comm is None or comm.size <= 1:
-            raise ValueError("Found array with 0 sample(s)")
-        y_min, y_max = 0, -1  # a rank of a sharded fit may hold no rows; it still joins every exchange
+    multi = comm is not None and comm.size > 1
+    if y_dev.numel() == 0 and not multi:
+        raise ValueError("Found array with 0 sample(s)")
+    # One read-back per fit: label range, and with several ranks every shard's size and free memory (the
+    # one host-visible exchange of a fit; a rank of a sharded fit may hold no rows and still joins it).
+    # Free memory is only needed when a builder has to be constructed; -1 = "not asked".
+    free_b = -1 if _BUILDERS else int(torch.cuda.mem_get_info(dev)[0])
+    if y_dev.numel():
+        lo_hi = torch.stack(torch.aminmax(y_dev)).to(torch.int64)
     else:
-        lo_hi = torch.stack(torch.aminmax(y_dev)).tolist()  # one reduction, one read-back
-        y_min, y_max = int(lo_hi[0]), int(lo_hi[1])
-    if y_min < 0:
+        lo_hi = torch.tensor([0, -1], dtype=torch.int64, device=dev)
+    gather = getattr(comm, "allgather_device", None) if multi else None
+    gathered = None
+    if gather is not None:
+        gathered = gather(torch.cat([lo_hi, torch.tensor([n, free_b], dtype=torch.int64, device=dev)]))
+    if gathered is not None:
+        meta = gathered.cpu().numpy()  # (size, 4): y_min, y_max, n, free
+    else:
+        y_lo, y_hi = (int(v) for v in lo_hi.tolist())
+        meta = comm.allgather_ints((y_lo, y_hi, n, free_b)) if multi else np.asarray([[y_lo, y_hi, n, free_b]], dtype=np.int64)
+    have_rows = meta[:, 2] > 0
+    y_min = int(meta[have_rows, 0].min()) if have_rows.any() else 0
+    y_max = int(meta[have_rows, 1].max()) if have_rows.any() else -1
+    if y_min < 0:  # decided from the gathered values: every rank raises, nobody is left waiting
         raise ValueError("class labels must be non-negative integers")
     st.mark("labels")
     lazy_classes = False
-    n_global, min_free = n, None
-    if comm is not None and comm.size > 1:
-        # the one host-side exchange of a fit: label range, shard sizes, free memory
-        meta = comm.allgather_ints((y_max, n, int(torch.cuda.mem_get_info(dev)[0])))
-        y_max = int(meta[:, 0].max())
-        n_global, min_free = int(meta[:, 1].sum()), int(meta[:, 2].min())
+    n_global = int(meta[:, 2].sum())
+    min_free = None if not multi else int(meta[:, 3].min())
+    meta = meta[:, 1:]  # (y_max, n, free) as before
     if y_max < MAX_CLASSES:
         # label values are used as class codes; the labels that actually occur are read off the
         # root histogram afterwards (saves a counting pass over y)
@@ -1125,7 +1193,7 @@ def fit_from_torch(X, y, params: SplitParams, *, max_bins: int = 256, comm=None,
         if X.dtype == torch.uint8:
             sample = sample.to(torch.float32)  # edge discovery works on floats; the rows stay bytes
         col_max = X.max(dim=0).values.cpu().numpy() if idx is not None else None
-        if comm is not None and comm.size > 1 and int(meta[:, 1].max()) > SAMPLE_ROWS:
+        if multi and int(meta[:, 1].max()) > SAMPLE_ROWS:
             # some rank sampled its rows: every rank joins the exchange of column maxima (the shard
             # sizes come from the all-gather above, so the decision is the same everywhere)
             if col_max is None and n:
@@ -1148,13 +1216,28 @@ def fit_from_torch(X, y, params: SplitParams, *, max_bins: int = 256, comm=None,
     data.set_labels(y_codes)
     st.mark("encode")
     _dist_group(comm)
-    builder = TreeBuilder(data, int(mapper.n_bins.max()), params, n_global=n_global, comm=comm,
-                          min_free_bytes=min_free, **(builder_kwargs or {}))
+    n_bins = int(mapper.n_bins.max())
+    kw = dict(builder_kwargs or {})
+
+    def make():
+        free = min_free
+        if multi and free is not None and free < 0:
+            # some rank did not look at its free memory (it expected a cached builder): ask again, all together
+            free = int(comm.allgather_ints((int(torch.cuda.mem_get_info(dev)[0]),)).min())
+        return TreeBuilder(data, n_bins, params, n_global=n_global, comm=comm, min_free_bytes=free, **kw)
+
+    # the key holds only values every rank sees identically (shard sizes come from the gather above)
+    key = ("torch", str(dev), tuple(int(v) for v in meta[:, 1]), F, len(classes), n_bins, _params_key(params),
+           0 if comm is None else (comm.size, comm.rank), tuple(sorted(kw.items())), os.environ.get("MTB_TILE"),
+           os.environ.get("MTB_ASYNC"), os.environ.get("MTB_SMALL_ROWS"))
+    cacheable = not kw.get("profile") and "peers" not in kw
+    builder = _get_builder(key, data, make) if cacheable else make()
     st.mark("builder_init")
     try:
         flat = builder.build()
     finally:
-        builder.close()
+        if not cacheable:
+            builder.close()
         data.release()
     st.mark("build")
     st.report()

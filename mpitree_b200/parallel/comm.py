@@ -113,6 +113,21 @@ class TorchComm:
             return out.cpu().numpy().reshape(self.size, len(vals))
         return np.asarray(self.allgather_object(vals), dtype=np.int64)
 
+    def allgather_device(self, t):
+        """All-gather a small device tensor without touching the host: ``(k,)`` -> ``(size, k)``.
+
+        Lets a caller fold device-side reductions (label range, ...) and host integers into one
+        exchange with a single read-back.  Only when this communicator is the NCCL world (the device
+        collective runs on the default group); otherwise ``None`` and callers use :meth:`allgather_ints`."""
+        import torch
+
+        world_is_default = self._ranks == list(range(self._dist.get_world_size()))
+        if not (world_is_default and self._dist.get_backend() == "nccl" and t.is_cuda):
+            return None
+        out = torch.empty(self.size * t.numel(), dtype=t.dtype, device=t.device)
+        self._dist.all_gather_into_tensor(out, t.contiguous())
+        return out.view(self.size, t.numel())
+
     def broadcast_object(self, obj: Any, src: int = 0) -> Any:
         box = [obj]
         self._dist.broadcast_object_list(box, src=self._ranks[src], group=self._group)

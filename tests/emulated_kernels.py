@@ -62,6 +62,11 @@ def search_and_finalize(c, reduce=None):
     """
     criterion = "gini" if c.criterion else "entropy"
     x = Ctx(c)
+    if int(c.depth) == 0:  # ``init_root``: the level-0 kernel writes the root slot and the scalars itself
+        for k, v in zip(("node", "begin", "end", "mode", "parent", "sibling"), (0, 0, int(c.n_local), BUILD, -1, -1)):
+            x.slot[k][0] = v
+        x.scal[:] = (1, 0, 1, 0, 0, 0, 0, 0)
+        x.t["left"][0], x.t["parent"][0], x.t["depth"][0] = -1, -1, 0
     n = int(x.scal[0])
     if n == 0:
         x.scal[1] = 0

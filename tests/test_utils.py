@@ -322,7 +322,7 @@ def test_level_loop_dry_run_launch_sequences(monkeypatch):
         b = ce.TreeBuilder(Data(), 256, SplitParams(max_depth=4), hist_budget_bytes=64 << 20, **kw)
         monkeypatch.setattr(b, "_launch", lambda name: calls.append(name))
         flat = b.build()
-        assert flat.n_nodes == 1  # nothing ran: the zero-initialised tree is a single root
+        assert flat.n_nodes == 0  # nothing ran: the level-0 kernel (not the host) writes the root
         return b.async_levels, list(calls)
 
     assert run() == (True, ["mtb_level_fused"] + ["mtb_level_fused2"] * 3)
