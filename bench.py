@@ -326,6 +326,7 @@ def run_ours(a):
     value = a.rows / (ms_step / 1e3)
     n_nodes = clf.flat_tree_.n_nodes
     sha = tree_sha(clf.flat_tree_)
+    stats = getattr(cuda_engine.fit_from_torch, "last_stats", None)  # of the product path (before the baseline pass)
     acc_rows = min(1_000_000, X.shape[0])
     acc = float((clf.predict(X[:acc_rows]) == y[:acc_rows].to(torch.int64)).float().mean().item())
 
@@ -370,7 +371,6 @@ def run_ours(a):
         except Exception as exc:  # noqa: BLE001
             same_cfg = {"error": str(exc).splitlines()[0][:200]}
     if rank == 0:
-        stats = getattr(cuda_engine.fit_from_torch, "last_stats", None)
         out = {
             "metric": "fit_rows_per_s_depth10_100Mx64",
             "value": value,

@@ -46,7 +46,7 @@ typedef struct MtbCtx {
   int64_t n_local;  /* rows of this rank's shard                               */
   int64_t F;        /* real features                                           */
   int64_t G;        /* feature groups = ceil(F/16)                             */
-  int64_t B;        /* bin stride (multiple of 32, <= 256)                     */
+  int64_t B;        /* bin stride (power of two, 32..256)                      */
   int64_t C;        /* classes                                                 */
   int64_t FT;       /* features per shared-memory histogram tile (1,2,4,8,16)  */
   int64_t max_depth;          /* -1 = unlimited                                */
@@ -60,7 +60,7 @@ typedef struct MtbCtx {
   int64_t codes[2];
   int64_t labels[2];
   int64_t cur;                /* which ping-pong side holds the current level  */
-  /* ---- histograms, ping-pong by level: [m_cap][G*16][B][C] u32 ---- */
+  /* ---- histograms, ping-pong by level: [m_cap][G*16][C][B] u32 (class-major) ---- */
   int64_t hist[2];
   int64_t hcur;               /* side holding the current level's histograms   */
   /* ---- frontier (current level, SoA length m_cap) ---- */
@@ -82,7 +82,8 @@ typedef struct MtbCtx {
   int64_t t_feature, t_bin, t_left, t_parent, t_depth; /* i32 */
   int64_t t_gain;                /* f64 */
   int64_t t_counts;              /* u32 [node_cap][C] */
-  /* ---- device scalars: i32[8] = {n_slots, n_next, n_nodes, units_hist, units_part, overflow, 0, 0} ---- */
+  /* ---- device scalars: i32[8] = {n_slots, n_next, n_nodes, units_hist, units_part, handed-off nodes, 0,
+   *      peer barrier gave up (a rank did not arrive)} ---- */
   int64_t scalars;
   int64_t unit_prefix;           /* i32 [m_cap+1] scratch for work decomposition */
   int64_t depth;                 /* depth of the current level                  */
@@ -137,6 +138,10 @@ typedef struct MtbCtx {
    * kernels skip the peer push and the owners read cross-rank sums with multimem.ld_reduce.  The
    * slabs must then live in a VMM allocation bound to the multicast object (parallel/nvls.py). 0 = off. */
   int64_t mc_hist[2];
+  /* world > 1: how long (ns, %globaltimer) a rank waits for a peer in an in-kernel barrier before it
+   * gives up, sets scalars[7] and raises the abort word (u32 index MTB_MAX_WORLD of every rank's flag
+   * block), after which all barriers of the fit fall through.  0 = wait for ever.                */
+  int64_t barrier_timeout_ns;
 } MtbCtx;
 
 const char* mtb_last_error(void);

@@ -7,7 +7,8 @@
 // Data layout (chosen for 128-bit loads and TMA bulk tiles):
 //   codes  [G][n_cap][16] u8   feature-group planes, rows of a node are contiguous
 //   labels [n_cap] u8
-//   hist   [slot][G*16][B][C] u32, one slab per frontier slot, ping-pong by level
+//   hist   [slot][G*16][C][B] u32 (class-major: a class row of B bins is contiguous), one slab per
+//          frontier slot, ping-pong by level; B is a power of two, 32..256
 //
 // Phases of one level (each also callable on its own; mtb_level_fused runs
 // plan+hist+gain+finalize in a single cooperative launch):
@@ -228,7 +229,7 @@ struct UnitCursor {
 // a feature hitting the same bank with different cells) instead of the ~3.6-way average that
 // random (bin, class) addresses give the [f][B][C] tile.  The row's 16 bytes are rotated once by
 // the lane's offset so that step k reads the statically indexed byte k.
-__device__ __forceinline__ void tile_count_il(uint32_t* tile, uint4 x, uint32_t lab, int C, int lane) {
+__device__ __forceinline__ void tile_count_il(uint32_t* tile, uint4 x, uint32_t lab, int B, int lane) {
   const int rot = lane & 15;
   uint32_t w0 = x.x, w1 = x.y, w2 = x.z, w3 = x.w;
   if (rot & 4) { const uint32_t t = w0; w0 = w1; w1 = w2; w2 = w3; w3 = t; }
@@ -239,8 +240,9 @@ __device__ __forceinline__ void tile_count_il(uint32_t* tile, uint4 x, uint32_t 
   // byte offsets throughout: one byte-extract (PRMT), one add of the lane's feature offset (loop
   // invariant per k, kept in registers across rows) and one multiply-add per increment
   // (shared-window addresses, so the tile base folds into the per-row term)
-  const uint32_t row_base = smem_u32(tile) + lab * 64u;
-  const uint32_t stride_b = (uint32_t)C * 64u;
+  // cell = lab * B + code (class-major, like the slabs): the code's term is a shift
+  const uint32_t row_base = smem_u32(tile) + lab * (uint32_t)B * 64u;
+  const uint32_t stride_b = 64u;
   const uint32_t yw[4] = {y.x, y.y, y.z, y.w};
 #pragma unroll
   for (int k = 0; k < 16; ++k) {
@@ -397,16 +399,16 @@ __device__ void hist_phase(const MtbCtx& ctx, uint8_t* smem) {
       __syncwarp();
       if (lane_id() == 0) mbar_arrive(&empty[st]);  // tile is in registers: release the stage
       if constexpr (IL) {
-        if (r_a < nrows) tile_count_il(tile, va, lab_a, C, tid);
-        if (r_b < nrows) tile_count_il(tile, vb, lab_b, C, tid);
+        if (r_a < nrows) tile_count_il(tile, va, lab_a, B, tid);
+        if (r_b < nrows) tile_count_il(tile, vb, lab_b, B, tid);
       } else {
         if (r_a < nrows) {
 #pragma unroll
-          for (int k = 0; k < FT; ++k) atomicAdd(&tile[(k * B + (int)code_byte(va, sub + k)) * C + (int)lab_a], 1u);
+          for (int k = 0; k < FT; ++k) atomicAdd(&tile[(k * C + (int)lab_a) * B + (int)code_byte(va, sub + k)], 1u);
         }
         if (r_b < nrows) {
 #pragma unroll
-          for (int k = 0; k < FT; ++k) atomicAdd(&tile[(k * B + (int)code_byte(vb, sub + k)) * C + (int)lab_b], 1u);
+          for (int k = 0; k < FT; ++k) atomicAdd(&tile[(k * C + (int)lab_b) * B + (int)code_byte(vb, sub + k)], 1u);
         }
       }
       if (++st == stages) { st = 0; ph ^= 1; }
@@ -444,34 +446,74 @@ __device__ __forceinline__ Mailbox mailbox_at(const MtbCtx& ctx, int64_t base) {
   return m;
 }
 
-// Cross-GPU barrier inside a cooperative kernel.  Every CTA calls it.  Data written to
-// peers before the call is visible to them after it: grid.sync orders the CTAs' writes
-// before thread 0's system-scope fence and release store of the flag.
+// Cross-GPU barrier inside a cooperative kernel.  Every CTA calls it.  Data written to peers before
+// the call is visible to them after it: grid.sync orders the CTAs' writes before CTA 0's system-scope
+// fence and release stores of the flags; every CTA then polls this rank's own flag words itself (no
+// second grid-wide synchronisation) and its bar.sync extends the acquire to the whole CTA.
+//
+// Failure handling: a rank that never arrives (its process died or raised between two launches)
+// would leave the others spinning for ever.  Every spin therefore also watches an abort word in the
+// own flag block and a deadline on %globaltimer; a rank that gives up records the failure in
+// scalars[7], raises the abort word of every peer, and from then on all barriers of the fit fall
+// through, so the launches still queued finish at once (their results are garbage and the host
+// raises on every rank once it has read the scalars back).
+constexpr int kAbortWord = MTB_MAX_WORLD;  // u32 index in a rank's flag block
+
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
 __device__ void peer_barrier(const MtbCtx& ctx, cg::grid_group& grid, uint32_t epoch) {
   grid.sync();
-  if (blockIdx.x == 0 && threadIdx.x < (unsigned)ctx.world) {
-    __threadfence_system();
-    uint32_t* remote = ptr_of<uint32_t>(ctx.peer_flags[threadIdx.x]) + ctx.rank;
-    st_release_sys_u32(remote, epoch);
-    const uint32_t* mine = ptr_of<const uint32_t>(ctx.peer_flags[ctx.rank]) + threadIdx.x;
-    while ((int32_t)(ld_acquire_sys_u32(mine) - epoch) < 0) {
+  const uint32_t* mine = ptr_of<const uint32_t>(ctx.peer_flags[ctx.rank]);
+  if (threadIdx.x < (unsigned)ctx.world) {
+    if (blockIdx.x == 0) {
+      __threadfence_system();
+      st_release_sys_u32(ptr_of<uint32_t>(ctx.peer_flags[threadIdx.x]) + ctx.rank, epoch);
+    }
+    const unsigned long long t0 = globaltimer_ns();
+    unsigned spins = 0;
+    while ((int32_t)(ld_acquire_sys_u32(mine + threadIdx.x) - epoch) < 0) {
+      if ((++spins & 63u) == 0u) {
+        if (ld_acquire_sys_u32(mine + kAbortWord) != 0u) break;
+        if (ctx.barrier_timeout_ns > 0 && globaltimer_ns() - t0 > (unsigned long long)ctx.barrier_timeout_ns) {
+          ptr_of<int>(ctx.scalars)[7] = 1;  // this rank gave up waiting for peer `threadIdx.x`
+          for (int q = 0; q < (int)ctx.world; ++q)
+            st_release_sys_u32(ptr_of<uint32_t>(ctx.peer_flags[q]) + kAbortWord, 1u);
+          break;
+        }
+      }
     }
     __threadfence_system();
   }
-  grid.sync();
+  __syncthreads();
 }
 
-// world > 1: copy this rank's partial counts of every BUILD slot to the owners' staging
-// areas with 128-bit stores over NVLink (the own features stay in the local slab).
-__device__ void push_phase(const MtbCtx& ctx) {
+// world > 1: copy this rank's partial counts of every BUILD slot to the owners' staging areas with
+// 128-bit stores over NVLink (the own features stay in the local slab).  A slot with fewer than
+// 65,536 local rows cannot hold a count that needs more than 16 bits, so its cells travel as u16
+// (half the bytes on the wire: the deep levels, whose pushes are the largest, consist of such slots);
+// a format word per (source, slot) behind the staging cells tells the owner which one it got.
+// `rows_from_cursors`: the slots' row segments are not committed yet (fused partition), their local
+// row counts are the partition cursors.
+__device__ __forceinline__ uint32_t* stage_format_table(const MtbCtx& ctx, int owner) {
+  return ptr_of<uint32_t>(ctx.peer_hist[owner]) + ctx.world * ctx.h_cap * (ctx.fpo * ctx.B * ctx.C);
+}
+
+__device__ void push_phase(const MtbCtx& ctx, int n_slots, bool rows_from_cursors) {
   View v(ctx);
   const int P = (int)ctx.world, r = (int)ctx.rank;
   if (P <= 1) return;
-  const int n_slots = v.n_slots();
   const int F = (int)ctx.F, fpo = (int)ctx.fpo;
   const int64_t BC = ctx.B * ctx.C;
   const int64_t region = (int64_t)fpo * BC;  // words per (source, slot) staging cell
   const int* mode = ptr_of<const int>(ctx.slot_mode);
+  const int* sb = ptr_of<const int>(ctx.slot_begin);
+  const int* se = ptr_of<const int>(ctx.slot_end);
+  const uint32_t* cursors = ptr_of<const uint32_t>(ctx.cursors);
+  const int* src_of = ptr_of<const int>(ctx.nslot_src);  // after the swap: this level's slots as children
   const int64_t items = (int64_t)n_slots * (P - 1);
   // one (slot, owner) region per CTA iteration
   for (int64_t it = blockIdx.x; it < items; it += gridDim.x) {
@@ -482,52 +524,157 @@ __device__ void push_phase(const MtbCtx& ctx) {
     const int f0 = o * fpo;
     if (f0 >= F) continue;
     const int nf = min(fpo, F - f0);
+    const uint32_t rows = rows_from_cursors ? cursors[src_of[slot]] : (uint32_t)(se[slot] - sb[slot]);
+    const bool narrow = rows < 65536u;
     const uint4* src = reinterpret_cast<const uint4*>(v.hist_cur() + (int64_t)slot * v.slab_words() + (int64_t)f0 * BC);
     uint4* dst = reinterpret_cast<uint4*>(ptr_of<uint32_t>(ctx.peer_hist[o]) + ((int64_t)r * ctx.h_cap + slot) * region);
-    const int64_t n16 = (int64_t)nf * BC / 4;
-    for (int64_t i = threadIdx.x; i < n16; i += blockDim.x) st_na_u4(dst + i, ld_nc_u4(src + i));
+    if (threadIdx.x == 0) stage_format_table(ctx, o)[(int64_t)r * ctx.h_cap + slot] = narrow ? 1u : 0u;
+    if (narrow) {
+      const int64_t n16 = (int64_t)nf * BC / 8;  // eight counts per 128-bit store
+      for (int64_t i = threadIdx.x; i < n16; i += blockDim.x) {
+        const uint4 a = ld_cg_u4(src + 2 * i), b = ld_cg_u4(src + 2 * i + 1);
+        st_na_u4(dst + i, make_uint4(a.x | (a.y << 16), a.z | (a.w << 16), b.x | (b.y << 16), b.z | (b.w << 16)));
+      }
+    } else {
+      const int64_t n16 = (int64_t)nf * BC / 4;
+      for (int64_t i = threadIdx.x; i < n16; i += blockDim.x) st_na_u4(dst + i, ld_cg_u4(src + i));
+    }
   }
 }
 
-__global__ void __launch_bounds__(512) k_push(const __grid_constant__ MtbCtx ctx) { push_phase(ctx); }
+__global__ void __launch_bounds__(512) k_push(const __grid_constant__ MtbCtx ctx) {
+  push_phase(ctx, ptr_of<const int>(ctx.scalars)[0], false);
+}
 
 // Gain phase.  One warp per (slot, owned feature) pair, no block-level synchronisation: the warps of
-// an SM work on independent pairs, which is what keeps the issue slots busy when a level has
-// thousands of pairs (a variant with one 256-thread group per pair, thread <-> bin, needed five
-// group barriers per pair and ran at a fifth of the issue rate: 1.30 ms instead of the 0.97 ms of
-// round 1 on the deepest level of 100M x 64).  `slab` is the warp's padded shared-memory copy of the
-// feature's [B][C] counts: lane L owns bins [L*BPL, (L+1)*BPL) at offset L*(BPL*C+1), so
-// lane-sequential walks are bank-conflict free.  Per pair:
-//   load     128-bit loads, four cells per lane in flight together: BUILD = own partial (+ the
-//            peers' staged partials, or one multimem.ld_reduce when the slabs are multicast-mapped),
-//            DERIVE = parent - sibling; the reduced counts also go back to global memory for the
-//            next level's subtraction
-//   scan     lane-local inclusive prefix over the lane's bins, per-class offsets by warp shuffles
-//   cost     float64 (reference rounding for small nodes, k log2 k form for large ones, evaluated
-//            arithmetically: no table gathers, no software log2), first arg-min by (cost, bin)
+// an SM work on independent pairs.  The slabs are class-major ([C][B]); lane L owns the BPL = B/32
+// consecutive bins [L*BPL, (L+1)*BPL) of every class row, so a class row is one fully coalesced
+// 128-bit load per lane (two for 256 bins).  Per pair:
+//   pass 1   for every class (two at a time in flight): load the lane's bins - BUILD = own partial
+//            (+ the peers' staged partials, or one multimem.ld_reduce when the slabs are
+//            multicast-mapped), DERIVE = parent - sibling - write the reduced counts back to global
+//            memory for the next level's subtraction, form the inclusive prefix over bins *in
+//            registers* (lane-local adds + one warp scan of the lane totals) and park it in the
+//            warp's shared-memory slab [C][32*(BPL+1)] (the +1 keeps lane-strided accesses
+//            conflict-free); per-bin row counts and left totals accumulate in registers
+//   pass 2   one candidate per (lane, bin): float64 cost - the reference's operation order for small
+//            nodes, the k log2 k form for large ones with all of a lane's bins evaluated together
+//            (2*BPL independent fp64 chains per class: an fp64 operation has ~40 cycles of latency
+//            on this part) - then the first arg-min by (cost, bin) across the warp
 //   publish  best-split record of the pair into every rank's mailbox
+// History (100M x 64, deepest level, one B200): one warp per pair with [B][C] slabs scattered into
+// shared memory and scanned there 0.97 ms (global-table gathers for k log2 k) / 0.77 ms (arithmetic
+// k log2 k); a 256-thread group per pair with five group barriers 1.30 ms.
 struct GainGeom {
   int warps;       // warps per CTA that take part
   int slab_words;  // shared-memory words per warp
+  int cs;          // words per class row in the slab
 };
 
 constexpr int kGainTabBytes = ((kKlogkTabDoubles * 8 + 127) / 128) * 128;
 
 __host__ __device__ inline GainGeom gain_geom(int B, int C, int warps, int smem_bytes) {
   GainGeom g;
-  g.slab_words = (B * C + 32 + 3) & ~3;
+  g.cs = 32 * (B / 32 + 1);
+  g.slab_words = (C * g.cs + C + 3) & ~3;
   int by_smem = (smem_bytes - kGainTabBytes) / (g.slab_words * 4);
   g.warps = warps < by_smem ? warps : by_smem;
   return g;
 }
 
-template <bool NV = false>
-__device__ void gain_pair(const MtbCtx& ctx, const KlogK& klogk, uint32_t* slab, int slot, int f) {
+// the lane's BPL consecutive words of a class row
+template <int BPL>
+struct Bins {
+  uint32_t v[BPL];
+};
+template <int BPL>
+__device__ __forceinline__ Bins<BPL> ld_bins(const uint32_t* p) {
+  Bins<BPL> r;
+  if constexpr (BPL >= 4) {
+#pragma unroll
+    for (int i = 0; i < BPL / 4; ++i) {
+      const uint4 x = ld_cg_u4(p + 4 * i);
+      r.v[4 * i] = x.x; r.v[4 * i + 1] = x.y; r.v[4 * i + 2] = x.z; r.v[4 * i + 3] = x.w;
+    }
+  } else if constexpr (BPL == 2) {
+    asm volatile("ld.global.cg.v2.u32 {%0,%1}, [%2];" : "=r"(r.v[0]), "=r"(r.v[1]) : "l"(p) : "memory");
+  } else {
+    asm volatile("ld.global.cg.u32 %0, [%1];" : "=r"(r.v[0]) : "l"(p) : "memory");
+  }
+  return r;
+}
+// the same bins from a u16-packed staging cell (`p16` = the class row's first u16)
+template <int BPL>
+__device__ __forceinline__ Bins<BPL> ld_bins_u16(const uint16_t* p16) {
+  Bins<BPL> r;
+  if constexpr (BPL == 8) {
+    const uint4 x = ld_cg_u4(p16);
+    r.v[0] = x.x & 0xffffu; r.v[1] = x.x >> 16; r.v[2] = x.y & 0xffffu; r.v[3] = x.y >> 16;
+    r.v[4] = x.z & 0xffffu; r.v[5] = x.z >> 16; r.v[6] = x.w & 0xffffu; r.v[7] = x.w >> 16;
+  } else if constexpr (BPL == 4) {
+    uint32_t a, b;
+    asm volatile("ld.global.cg.v2.u32 {%0,%1}, [%2];" : "=r"(a), "=r"(b) : "l"(p16) : "memory");
+    r.v[0] = a & 0xffffu; r.v[1] = a >> 16; r.v[2] = b & 0xffffu; r.v[3] = b >> 16;
+  } else if constexpr (BPL == 2) {
+    uint32_t a;
+    asm volatile("ld.global.cg.u32 %0, [%1];" : "=r"(a) : "l"(p16) : "memory");
+    r.v[0] = a & 0xffffu; r.v[1] = a >> 16;
+  } else {
+    uint16_t a;
+    asm volatile("ld.global.cg.u16 %0, [%1];" : "=h"(a) : "l"(p16) : "memory");
+    r.v[0] = a;
+  }
+  return r;
+}
+template <int BPL>
+__device__ __forceinline__ void st_bins(uint32_t* p, const Bins<BPL>& r) {
+  if constexpr (BPL >= 4) {
+#pragma unroll
+    for (int i = 0; i < BPL / 4; ++i)
+      *reinterpret_cast<uint4*>(p + 4 * i) = make_uint4(r.v[4 * i], r.v[4 * i + 1], r.v[4 * i + 2], r.v[4 * i + 3]);
+  } else if constexpr (BPL == 2) {
+    *reinterpret_cast<uint2*>(p) = make_uint2(r.v[0], r.v[1]);
+  } else {
+    *p = r.v[0];
+  }
+}
+template <int BPL>
+__device__ __forceinline__ Bins<BPL> ld_bins_mc(const uint32_t* mc) {  // sum over all ranks, formed in the switch
+  Bins<BPL> r;
+  if constexpr (BPL >= 2) {
+#pragma unroll
+    for (int i = 0; i < BPL / 2; ++i) {
+      uint64_t x;
+      asm volatile("multimem.ld_reduce.relaxed.sys.global.add.u64 %0, [%1];" : "=l"(x) : "l"(mc + 2 * i) : "memory");
+      r.v[2 * i] = (uint32_t)x;
+      r.v[2 * i + 1] = (uint32_t)(x >> 32);
+    }
+  } else {
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.u32 %0, [%1];" : "=r"(r.v[0]) : "l"(mc) : "memory");
+  }
+  return r;
+}
+
+// Cost of one candidate from the parked prefixes (L[c * CS] = left count of class c), for the paths
+// that are not worth inlining eight times: the reference's exact operation order (small nodes) and gini.
+__device__ __noinline__ double slow_pair_cost(const MtbCtx& ctx, const KlogK& klogk, const uint32_t* L, const uint32_t* tot,
+                                              int CS, uint32_t nl, uint32_t nr, bool exact) {
+  const int C = (int)ctx.C, crit = (int)ctx.criterion;
+  if (exact) {
+    const double* plogp = ptr_of<const double>(ctx.plogp);
+    const uint32_t plogp_n = (uint32_t)ctx.plogp_n;
+    const double hl = impurity(C, [&](int c) { return L[c * CS]; }, nl, crit, plogp, plogp_n);
+    const double hr = impurity(C, [&](int c) { return tot[c] - L[c * CS]; }, nr, crit, plogp, plogp_n);
+    return split_cost(nl, nr, hl, hr, (int)ctx.dot_mode);
+  }
+  return fast_split_cost(C, [&](int c) { return L[c * CS]; }, [&](int c) { return tot[c] - L[c * CS]; }, nl, nr, crit, klogk);
+}
+
+template <int BPL, bool NV>
+__device__ void gain_pair(const MtbCtx& ctx, const KlogK& klogk, uint32_t* slab, const GainGeom& gg, int slot, int f) {
   View v(ctx);
   const int B = (int)ctx.B, C = (int)ctx.C, F = (int)ctx.F;
   const int P = (int)ctx.world, r = (int)ctx.rank;
-  const int BPL = B / 32;
-  const int lane_stride = BPL * C + 1;
   const int lane = lane_id();
   const int mode = ptr_of<const int>(ctx.slot_mode)[slot];
   const int64_t rec = (int64_t)slot * F + f;
@@ -539,228 +686,165 @@ __device__ void gain_pair(const MtbCtx& ctx, const KlogK& klogk, uint32_t* slab,
     }
     return;
   }
-  const unsigned divC = ((1u << 24) + (unsigned)C - 1u) / (unsigned)C;  // w / C == (w * divC) >> 24 for w < B*C
-  const unsigned divBPL = (unsigned)(__ffs(BPL) - 1);                   // shift when BPL is a power of two
-  const bool bpl_pow2 = (BPL & (BPL - 1)) == 0;
-  const int words = B * C;
-  const int n4 = words / 4;
-  // scatter 4 consecutive histogram words into the padded per-lane slab layout
-  auto put4 = [&](const uint4& x, int w) {
-    int b = (int)(((unsigned)w * divC) >> 24), c = w - b * C;
-    const uint32_t xs[4] = {x.x, x.y, x.z, x.w};
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const int bl = bpl_pow2 ? (b >> divBPL) : b / BPL;
-      slab[bl * lane_stride + (b - bl * BPL) * C + c] = xs[i];
-      if (++c == C) { c = 0; ++b; }
-    }
-  };
-  const int64_t fBC = (int64_t)f * B * C;
-  constexpr int kBatch = 4;  // 128-bit cells per lane whose loads are issued together
+  const int CS = gg.cs;
+  uint32_t* tot = slab + C * CS;               // [C] class totals of the node
+  uint32_t* mine = slab + lane * (BPL + 1);    // + c * CS + j
+  const bool derive = mode == MTB_MODE_DERIVE;
+  const int64_t BC = (int64_t)B * C;
+  const int64_t lane_off = (int64_t)lane * BPL;
+
+  // ---- sources / sinks of pass 1 (word pointers at class 0, this lane's bins)
+  const uint32_t* own;         // local partial (or the single-rank slab)
+  const uint32_t* par = nullptr;  // DERIVE: the parent's reduced slab
+  uint32_t* out = nullptr;        // where the reduced counts go (nullptr: nowhere)
+  const uint32_t* stage_cell = nullptr;  // staging cell of (source 0, slot), first word
+  int64_t fl_off = 0;                    // counts of the owned feature within a cell
+  uint32_t narrow_mask = 0;              // bit p: source p sent this slot as u16
+  const uint32_t* mc = nullptr;
+  int64_t src_stride = 0;
   if (P > 1) {
     // Multi-rank owner path.  Reduced slabs of the own features live in rstore (ping-pong by level);
     // the local partial slabs are never modified.
     const int fl = f - r * (int)ctx.fpo;
-    const int64_t region = ctx.fpo * ctx.B * ctx.C;
-    const uint32_t* stage = ptr_of<const uint32_t>(ctx.peer_hist[r]) + (int64_t)fl * B * C;
-    const int64_t src_stride = ctx.h_cap * region;
-    uint4* out4 = reinterpret_cast<uint4*>(ptr_of<uint32_t>(ctx.rstore[ctx.hcur]) + (int64_t)slot * region + (int64_t)fl * B * C);
-    const bool derive = mode == MTB_MODE_DERIVE;
+    const int64_t region = ctx.fpo * BC;
     const int src = derive ? ptr_of<const int>(ctx.slot_sibling)[slot] : slot;
-    const uint4* par4 = nullptr;
+    own = v.hist_cur() + (int64_t)src * v.slab_words() + (int64_t)f * BC + lane_off;
+    stage_cell = ptr_of<const uint32_t>(ctx.peer_hist[r]) + (int64_t)src * region;
+    fl_off = (int64_t)fl * BC;
+    src_stride = ctx.h_cap * region;
+    if constexpr (!NV) {
+      const uint32_t* fmt = stage_format_table(ctx, r);
+      if (lane < P && lane != r) narrow_mask = fmt[(int64_t)lane * ctx.h_cap + src] ? 1u << lane : 0u;
+      narrow_mask = __reduce_or_sync(0xffffffffu, narrow_mask);
+    }
+    if constexpr (NV)
+      mc = ptr_of<const uint32_t>(ctx.mc_hist[ctx.hcur]) + (int64_t)src * v.slab_words() + (int64_t)f * BC + lane_off;
+    out = ptr_of<uint32_t>(ctx.rstore[ctx.hcur]) + (int64_t)slot * region + (int64_t)fl * BC + lane_off;
+    if (derive)
+      par = ptr_of<const uint32_t>(ctx.rstore[ctx.hcur ^ 1]) + (int64_t)ptr_of<const int>(ctx.slot_parent)[slot] * region +
+            (int64_t)fl * BC + lane_off;
+  } else if (derive) {
+    own = v.hist_cur() + (int64_t)ptr_of<const int>(ctx.slot_sibling)[slot] * v.slab_words() + (int64_t)f * BC + lane_off;
+    par = v.hist_prev() + (int64_t)ptr_of<const int>(ctx.slot_parent)[slot] * v.slab_words() + (int64_t)f * BC + lane_off;
+    out = v.hist_cur() + (int64_t)slot * v.slab_words() + (int64_t)f * BC + lane_off;
+  } else {
+    own = v.hist_cur() + (int64_t)slot * v.slab_words() + (int64_t)f * BC + lane_off;
+  }
+
+  // ---- pass 1: load, reduce, prefix over bins in registers, park in shared memory
+  uint32_t rows_here[BPL], nl[BPL];
+#pragma unroll
+  for (int j = 0; j < BPL; ++j) rows_here[j] = nl[j] = 0;
+  constexpr int kCB = 2;  // classes in flight together
+  for (int c0 = 0; c0 < C; c0 += kCB) {
+    Bins<BPL> h[kCB];
+#pragma unroll
+    for (int u = 0; u < kCB; ++u) {
+      const int c = min(c0 + u, C - 1);  // a class past the end repeats the last one (discarded below)
+      if constexpr (NV) h[u] = ld_bins_mc<BPL>(mc + (int64_t)c * B);
+      else h[u] = ld_bins<BPL>(own + (int64_t)c * B);
+    }
+    if (P > 1 && !NV) {
+      // staged partials of the peers, one source after the other: the loads of a source do not
+      // depend on the running sums, so several sources overlap in flight
+      for (int p = 0; p < P; ++p) {
+        if (p == r) continue;
+        Bins<BPL> y[kCB];
+        const uint32_t* cell = stage_cell + (int64_t)p * src_stride;  // this source's cell of the slot, class 0
+        if (narrow_mask >> p & 1u) {
+#pragma unroll
+          for (int u = 0; u < kCB; ++u)
+            y[u] = ld_bins_u16<BPL>(reinterpret_cast<const uint16_t*>(cell) + (int64_t)fl_off + (int64_t)min(c0 + u, C - 1) * B + lane_off);
+        } else {
+#pragma unroll
+          for (int u = 0; u < kCB; ++u) y[u] = ld_bins<BPL>(cell + fl_off + (int64_t)min(c0 + u, C - 1) * B + lane_off);
+        }
+#pragma unroll
+        for (int u = 0; u < kCB; ++u)
+#pragma unroll
+          for (int j = 0; j < BPL; ++j) h[u].v[j] += y[u].v[j];
+      }
+    }
     if (derive) {
-      const int par = ptr_of<const int>(ctx.slot_parent)[slot];
-      par4 = reinterpret_cast<const uint4*>(ptr_of<const uint32_t>(ctx.rstore[ctx.hcur ^ 1]) + (int64_t)par * region +
-                                            (int64_t)fl * B * C);
+      Bins<BPL> a[kCB];
+#pragma unroll
+      for (int u = 0; u < kCB; ++u) a[u] = ld_bins<BPL>(par + (int64_t)min(c0 + u, C - 1) * B);
+#pragma unroll
+      for (int u = 0; u < kCB; ++u)
+#pragma unroll
+        for (int j = 0; j < BPL; ++j) h[u].v[j] = a[u].v[j] - h[u].v[j];
     }
-    const uint4* own4 = reinterpret_cast<const uint4*>(v.hist_cur() + (int64_t)src * v.slab_words() + fBC);
-    const uint32_t* cell0 = stage + (int64_t)src * region;
-    for (int q0 = lane; q0 < n4; q0 += kBatch * 32) {
-      uint4 x[kBatch];
 #pragma unroll
-      for (int j = 0; j < kBatch; ++j) {
-        const int q = q0 + j * 32;
-        x[j] = make_uint4(0, 0, 0, 0);
-        if (q < n4) {
-          if constexpr (NV) {
-            const uint64_t* mc = reinterpret_cast<const uint64_t*>(ptr_of<const uint32_t>(ctx.mc_hist[ctx.hcur]) +
-                                                                   (int64_t)src * v.slab_words() + fBC) + 2 * q;
-            uint64_t lo, hi;
-            asm volatile("multimem.ld_reduce.relaxed.sys.global.add.u64 %0, [%1];" : "=l"(lo) : "l"(mc) : "memory");
-            asm volatile("multimem.ld_reduce.relaxed.sys.global.add.u64 %0, [%1];" : "=l"(hi) : "l"(mc + 1) : "memory");
-            x[j] = make_uint4((uint32_t)lo, (uint32_t)(lo >> 32), (uint32_t)hi, (uint32_t)(hi >> 32));
-          } else {
-            x[j] = ld_cg_u4(own4 + q);
-          }
+    for (int u = 0; u < kCB; ++u) {
+      const int c = c0 + u;
+      if (c < C) {
+        if (out) st_bins<BPL>(out + (int64_t)c * B, h[u]);
+        uint32_t run = 0;
+#pragma unroll
+        for (int j = 0; j < BPL; ++j) {
+          rows_here[j] += h[u].v[j];
+          run += h[u].v[j];
+          h[u].v[j] = run;  // lane-local inclusive prefix
         }
-      }
-      if constexpr (!NV) {
-        // staged partials of the peers, one source (x kBatch cells) after the other: the loads of a
-        // source are independent of the running sums, so several sources overlap in flight
-        for (int p = 0; p < P; ++p) {
-          if (p == r) continue;
-          uint4 y[kBatch];
+        const uint32_t inc = warp_incl_scan(run);
+        const uint32_t off = inc - run;
 #pragma unroll
-          for (int j = 0; j < kBatch; ++j) {
-            const int q = q0 + j * 32;
-            y[j] = q < n4 ? ld_cg_u4(cell0 + (int64_t)p * src_stride + q * 4) : make_uint4(0, 0, 0, 0);
-          }
-#pragma unroll
-          for (int j = 0; j < kBatch; ++j) { x[j].x += y[j].x; x[j].y += y[j].y; x[j].z += y[j].z; x[j].w += y[j].w; }
+        for (int j = 0; j < BPL; ++j) {
+          const uint32_t L = h[u].v[j] + off;
+          nl[j] += L;
+          mine[c * CS + j] = L;
         }
-      }
-      if (derive) {
-        uint4 a[kBatch];
-#pragma unroll
-        for (int j = 0; j < kBatch; ++j) {
-          const int q = q0 + j * 32;
-          a[j] = q < n4 ? ld_cg_u4(par4 + q) : make_uint4(0, 0, 0, 0);
-        }
-#pragma unroll
-        for (int j = 0; j < kBatch; ++j)
-          x[j] = make_uint4(a[j].x - x[j].x, a[j].y - x[j].y, a[j].z - x[j].z, a[j].w - x[j].w);
-      }
-#pragma unroll
-      for (int j = 0; j < kBatch; ++j) {
-        const int q = q0 + j * 32;
-        if (q < n4) {
-          out4[q] = x[j];
-          put4(x[j], q * 4);
-        }
+        if (lane == 31) tot[c] = inc;
       }
     }
-  } else if (mode == MTB_MODE_DERIVE) {
-    const int par = ptr_of<const int>(ctx.slot_parent)[slot];
-    const int sib = ptr_of<const int>(ctx.slot_sibling)[slot];
-    const uint4* hp4 = reinterpret_cast<const uint4*>(v.hist_prev() + (int64_t)par * v.slab_words() + fBC);
-    const uint4* hs4 = reinterpret_cast<const uint4*>(v.hist_cur() + (int64_t)sib * v.slab_words() + fBC);
-    uint4* mine4 = reinterpret_cast<uint4*>(v.hist_cur() + (int64_t)slot * v.slab_words() + fBC);
-    for (int q0 = lane; q0 < n4; q0 += kBatch * 32) {
-      uint4 a[kBatch], d[kBatch];
+  }
+  __syncwarp();
+  uint32_t n = 0;
+  for (int c = 0; c < C; ++c) n += tot[c];
+
+  // ---- pass 2: one candidate per (lane, bin)
+  double best = INFINITY;
+  int best_bin = 0x7fffffff;
+  const int crit = (int)ctx.criterion;
+  // small nodes: the reference's exact float64 operation order; large nodes: the cheap form
+  const bool exact = ctx.plogp == 0 || n <= (uint32_t)ctx.plogp_n;
+  if (!exact && crit == 0) {
+    // summation order of fast_split_cost: s = g(nL) + g(nR), then s -= g(kL_c) + g(kR_c) for ascending c
+    double s[BPL];
 #pragma unroll
-      for (int j = 0; j < kBatch; ++j) {
-        const int q = q0 + j * 32;
-        if (q < n4) { a[j] = ld_cg_u4(hp4 + q); d[j] = ld_cg_u4(hs4 + q); }
+    for (int j = 0; j < BPL; ++j) s[j] = __dadd_rn(klogk(nl[j]), klogk(n - nl[j]));
+    for (int c = 0; c < C; ++c) {
+      const uint32_t tc = tot[c];
+      double a[BPL], b[BPL];
+#pragma unroll
+      for (int j = 0; j < BPL; ++j) {
+        const uint32_t l = mine[c * CS + j];
+        a[j] = klogk(l);
+        b[j] = klogk(tc - l);
       }
 #pragma unroll
-      for (int j = 0; j < kBatch; ++j) {
-        const int q = q0 + j * 32;
-        if (q < n4) {
-          const uint4 z = make_uint4(a[j].x - d[j].x, a[j].y - d[j].y, a[j].z - d[j].z, a[j].w - d[j].w);
-          mine4[q] = z;
-          put4(z, q * 4);
+      for (int j = 0; j < BPL; ++j) s[j] = __dsub_rn(s[j], __dadd_rn(a[j], b[j]));
+    }
+    const double dn = u2d(n);
+#pragma unroll
+    for (int j = 0; j < BPL; ++j) {
+      if (rows_here[j] != 0u && nl[j] != n) {  // empty bins repeat a candidate; an empty right side is no split
+        const double cost = __ddiv_rn(s[j], dn);
+        if (cost < best) {  // strict: first (lowest) bin wins ties inside the lane
+          best = cost;
+          best_bin = lane * BPL + j;
         }
       }
     }
   } else {
-    const uint4* mine4 = reinterpret_cast<const uint4*>(v.hist_cur() + (int64_t)slot * v.slab_words() + fBC);
-    for (int q0 = lane; q0 < n4; q0 += kBatch * 32) {
-      uint4 a[kBatch];
 #pragma unroll
-      for (int j = 0; j < kBatch; ++j) {
-        const int q = q0 + j * 32;
-        if (q < n4) a[j] = ld_cg_u4(mine4 + q);
+    for (int j = 0; j < BPL; ++j) {
+      if (rows_here[j] == 0u || nl[j] == n) continue;
+      const double cost = slow_pair_cost(ctx, klogk, mine + j, tot, CS, nl[j], n - nl[j], exact);
+      if (cost < best) {
+        best = cost;
+        best_bin = lane * BPL + j;
       }
-#pragma unroll
-      for (int j = 0; j < kBatch; ++j) {
-        const int q = q0 + j * 32;
-        if (q < n4) put4(a[j], q * 4);
-      }
-    }
-  }
-  __syncwarp();
-
-  uint32_t* my = slab + lane * lane_stride;
-  // per-bin row counts before the scan -> which bins are candidates
-  uint32_t present = 0;
-  for (int j = 0; j < BPL; ++j) {
-    uint32_t s = 0;
-    for (int c = 0; c < C; ++c) s += my[j * C + c];
-    if (s) present |= 1u << j;
-  }
-  // lane-local inclusive scan along bins, then cross-lane offsets per class
-  for (int j = 1; j < BPL; ++j)
-    for (int c = 0; c < C; ++c) my[j * C + c] += my[(j - 1) * C + c];
-  for (int c = 0; c < C; ++c) {
-    uint32_t tot = my[(BPL - 1) * C + c];
-    uint32_t inc = warp_incl_scan(tot);
-    uint32_t off = inc - tot;
-    if (off)
-      for (int j = 0; j < BPL; ++j) my[j * C + c] += off;
-  }
-  __syncwarp();
-  const uint32_t* last = slab + 31 * lane_stride + (BPL - 1) * C;  // totals per class
-  uint32_t n = 0;
-  for (int c = 0; c < C; ++c) n += last[c];
-
-  double best = INFINITY;
-  int best_bin = 0x7fffffff;
-  const int crit = (int)ctx.criterion, dm = (int)ctx.dot_mode;
-  const double* plogp = ptr_of<const double>(ctx.plogp);
-  const uint32_t plogp_n = (uint32_t)ctx.plogp_n;
-  // small nodes: the reference's exact float64 operation order; large nodes: the cheap form
-  const bool exact = plogp == nullptr || n <= plogp_n;
-  if (!exact && crit == 0) {
-    // Entropy, large node.  Four of the lane's bins are evaluated together: an fp64 operation has a
-    // latency of some 40 cycles here, so the eight independent g() chains per class are what keeps
-    // the pipe busy (one bin at a time ran at ~500 cycles per g()).  Per bin the summation order is
-    // that of fast_split_cost: s = g(nL) + g(nR), then s -= g(kL_c) + g(kR_c) for ascending c.
-    const double dn = u2d(n);
-    for (int j0 = 0; j0 < BPL; j0 += 4) {
-      uint32_t nl4[4] = {0, 0, 0, 0};
-      int jj[4];
-#pragma unroll
-      for (int u = 0; u < 4; ++u) jj[u] = min(j0 + u, BPL - 1) * C;
-      for (int c = 0; c < C; ++c) {
-#pragma unroll
-        for (int u = 0; u < 4; ++u) nl4[u] += my[jj[u] + c];
-      }
-      double s4[4];
-#pragma unroll
-      for (int u = 0; u < 4; ++u) s4[u] = __dadd_rn(klogk(nl4[u]), klogk(n - nl4[u]));
-      for (int c = 0; c < C; ++c) {
-        const uint32_t tc = last[c];
-        double a[4], b[4];
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          const uint32_t l = my[jj[u] + c];
-          a[u] = klogk(l);
-          b[u] = klogk(tc - l);
-        }
-#pragma unroll
-        for (int u = 0; u < 4; ++u) s4[u] = __dsub_rn(s4[u], __dadd_rn(a[u], b[u]));
-      }
-#pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const int j = j0 + u;
-        if (j < BPL && (present >> j & 1u) && nl4[u] != n) {  // an empty right side is not a usable split
-          const double cost = __ddiv_rn(s4[u], dn);
-          if (cost < best) {  // strict: first (lowest) bin wins ties inside the lane
-            best = cost;
-            best_bin = lane * BPL + j;
-          }
-        }
-      }
-    }
-  } else
-  for (int j = 0; j < BPL; ++j) {
-    if (!(present >> j & 1u)) continue;
-    const uint32_t* L = my + j * C;
-    uint32_t nl = 0;
-    for (int c = 0; c < C; ++c) nl += L[c];
-    const uint32_t nr = n - nl;
-    if (nr == 0) continue;  // right side empty: not a usable split
-    double cost;
-    if (exact) {
-      double hl = impurity(C, [&](int c) { return L[c]; }, nl, crit, plogp, plogp_n);
-      double hr = impurity(C, [&](int c) { return last[c] - L[c]; }, nr, crit, plogp, plogp_n);
-      cost = split_cost(nl, nr, hl, hr, dm);
-    } else {
-      cost = fast_split_cost(C, [&](int c) { return L[c]; }, [&](int c) { return last[c] - L[c]; }, nl, nr, crit, klogk);
-    }
-    if (cost < best) {  // strict: first (lowest) bin wins ties inside the lane
-      best = cost;
-      best_bin = lane * BPL + j;
     }
   }
 #pragma unroll
@@ -773,7 +857,7 @@ __device__ void gain_pair(const MtbCtx& ctx, const KlogK& klogk, uint32_t* slab,
     }
   }
   const bool ok = best_bin != 0x7fffffff;
-  const uint32_t* Lb = ok ? slab + (best_bin / BPL) * lane_stride + (best_bin % BPL) * C : last;
+  const uint32_t* Lb = slab + (ok ? (best_bin / BPL) * (BPL + 1) + best_bin % BPL : 0);  // + c * CS
   // publish the record to every rank's mailbox (the own one when world == 1)
   for (int q = 0; q < P; ++q) {
     Mailbox m = mailbox_at(ctx, P > 1 ? ctx.peer_rec[q] : ctx.fb_cost);
@@ -782,9 +866,9 @@ __device__ void gain_pair(const MtbCtx& ctx, const KlogK& klogk, uint32_t* slab,
       m.bin[rec] = ok ? best_bin : -1;
     }
     if (ok)
-      for (int c = lane; c < C; c += 32) m.left[rec * C + c] = Lb[c];
+      for (int c = lane; c < C; c += 32) m.left[rec * C + c] = Lb[c * CS];
     if (f == 0)
-      for (int c = lane; c < C; c += 32) m.node_cnt[(int64_t)slot * C + c] = last[c];
+      for (int c = lane; c < C; c += 32) m.node_cnt[(int64_t)slot * C + c] = tot[c];
   }
   __syncwarp();
 }
@@ -793,13 +877,12 @@ __device__ void gain_pair(const MtbCtx& ctx, const KlogK& klogk, uint32_t* slab,
 // available to the phase (fewer warps work when their slabs do not all fit).  pass -1: every pair;
 // 0 / 1: BUILD+NONE / DERIVE slots only (kept for experiments: pairs never depend on one another).
 template <bool NV = false>
-__device__ void gain_phase(const MtbCtx& ctx, uint8_t* smem, int warps, int smem_bytes, int pass) {
-  View v(ctx);
+__device__ void gain_phase(const MtbCtx& ctx, uint8_t* smem, int warps, int smem_bytes, int pass, int n_slots) {
   const int F = (int)ctx.F;
   const int f_lo = (int)(ctx.rank * ctx.fpo);
   const int f_hi = min(F, f_lo + (int)ctx.fpo);
   const int n_own = max(0, f_hi - f_lo);
-  const int n_pairs = v.n_slots() * n_own;
+  const int n_pairs = n_slots * n_own;
   const GainGeom gg = gain_geom((int)ctx.B, (int)ctx.C, warps, smem_bytes);
   // constants of g(k) = k log2 k into shared memory (33 KB), coefficients into registers
   double* tab = reinterpret_cast<double*>(smem);
@@ -813,18 +896,25 @@ __device__ void gain_phase(const MtbCtx& ctx, uint8_t* smem, int warps, int smem
   uint32_t* slab = reinterpret_cast<uint32_t*>(smem + kGainTabBytes) + (size_t)w * gg.slab_words;
   const int* mode = ptr_of<const int>(ctx.slot_mode);
   const int total_warps = gg.warps * (int)gridDim.x;
+  const int bpl = (int)ctx.B / 32;
   // pairs are dealt round-robin, CTAs first: a level with few pairs spreads over the SMs, and the
   // pairs of one slot (equal cost) spread over the warps
   for (int p = w * (int)gridDim.x + (int)blockIdx.x; p < n_pairs; p += total_warps) {
     const int slot = p / n_own;
     if (pass >= 0 && (mode[slot] == MTB_MODE_DERIVE) != (pass == 1)) continue;
-    gain_pair<NV>(ctx, klogk, slab, slot, f_lo + p % n_own);
+    const int f = f_lo + p % n_own;
+    switch (bpl) {
+      case 8: gain_pair<8, NV>(ctx, klogk, slab, gg, slot, f); break;
+      case 4: gain_pair<4, NV>(ctx, klogk, slab, gg, slot, f); break;
+      case 2: gain_pair<2, NV>(ctx, klogk, slab, gg, slot, f); break;
+      default: gain_pair<1, NV>(ctx, klogk, slab, gg, slot, f); break;
+    }
   }
 }
 
 __global__ void __launch_bounds__(kGainWarps * 32) k_gain(const __grid_constant__ MtbCtx ctx, int pass, int smem_bytes) {
   extern __shared__ __align__(128) uint8_t smem[];
-  gain_phase(ctx, smem, kGainWarps, smem_bytes, pass);
+  gain_phase(ctx, smem, kGainWarps, smem_bytes, pass, ptr_of<const int>(ctx.scalars)[0]);
 }
 
 // -------------------------------------------------------------------- finalize
@@ -941,6 +1031,10 @@ __device__ void finalize_phase(const MtbCtx& ctx, int* smem_warp) {
       rec_bin[s] = -1;
       part_flags[s] = 0;
       if (ctx.part_child) ptr_of<int>(ctx.part_child)[s] = -1;
+    }
+    if (s < n) {  // the partition of these slots' rows counts into fresh cursors
+      ptr_of<uint32_t>(ctx.cursors)[2 * s] = 0;
+      ptr_of<uint32_t>(ctx.cursors)[2 * s + 1] = 0;
     }
     int tot_split, tot_pair, tot_units;
     const int ex_split = block_excl_scan(split, smem_warp, tot_split);
@@ -1092,7 +1186,9 @@ __global__ void __launch_bounds__(kPartThreads) k_partition(const __grid_constan
 }
 static_assert(4 * (kPartThreads / 32) == 32, "partition scan assumes 32 cells");
 
-__device__ void commit_phase(const MtbCtx& ctx) {
+// `first`, `stride`: the calling thread's index and the thread count of whoever runs the phase (the
+// whole grid in k_commit, CTA 0 alone in the fused kernel)
+__device__ void commit_phase(const MtbCtx& ctx, int first, int stride) {
   View v(ctx);
   const int n_next = v.scalars()[1];
   const int* ns_src = ptr_of<const int>(ctx.nslot_src);
@@ -1102,7 +1198,7 @@ __device__ void commit_phase(const MtbCtx& ctx) {
   const uint32_t* cursors = ptr_of<const uint32_t>(ctx.cursors);
   int* nb = ptr_of<int>(ctx.nslot_begin);
   int* ne = ptr_of<int>(ctx.nslot_end);
-  for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < n_next; j += gridDim.x * blockDim.x) {
+  for (int j = first; j < n_next; j += stride) {
     const int p = ns_src[j] >> 1, side = ns_src[j] & 1;
     int b = 0, e = 0;
     if (ns_mode[j] != MTB_MODE_NONE) {
@@ -1131,7 +1227,7 @@ __device__ void commit_phase(const MtbCtx& ctx) {
 }
 
 __global__ void k_commit(const __grid_constant__ MtbCtx ctx) {
-  commit_phase(ctx);
+  commit_phase(ctx, blockIdx.x * blockDim.x + threadIdx.x, gridDim.x * blockDim.x);
   // the next level's slot count becomes current (nothing in this kernel reads scalars[0])
   if (blockIdx.x == 0 && threadIdx.x == 0) ptr_of<int>(ctx.scalars)[0] = ptr_of<int>(ctx.scalars)[1];
 }
@@ -1437,16 +1533,16 @@ __device__ void move_hist_phase(const MtbCtx& P, const MtbCtx& C, uint8_t* smem,
     }
     if (build_child >= 0) {
       if constexpr (IL) {
-        if (va_ok && (int)(!la) == build_side) tile_count_il(tile, xa, lab_a, Cn, lane);
-        if (vb_ok && (int)(!lb) == build_side) tile_count_il(tile, xb, lab_b, Cn, lane);
+        if (va_ok && (int)(!la) == build_side) tile_count_il(tile, xa, lab_a, B, lane);
+        if (vb_ok && (int)(!lb) == build_side) tile_count_il(tile, xb, lab_b, B, lane);
       } else {
         if (va_ok && (int)(!la) == build_side) {
 #pragma unroll
-          for (int k = 0; k < FT; ++k) atomicAdd(&tile[(k * B + (int)code_byte(xa, sub + k)) * Cn + (int)lab_a], 1u);
+          for (int k = 0; k < FT; ++k) atomicAdd(&tile[(k * Cn + (int)lab_a) * B + (int)code_byte(xa, sub + k)], 1u);
         }
         if (vb_ok && (int)(!lb) == build_side) {
 #pragma unroll
-          for (int k = 0; k < FT; ++k) atomicAdd(&tile[(k * B + (int)code_byte(xb, sub + k)) * Cn + (int)lab_b], 1u);
+          for (int k = 0; k < FT; ++k) atomicAdd(&tile[(k * Cn + (int)lab_b) * B + (int)code_byte(xb, sub + k)], 1u);
         }
       }
     }
@@ -1484,39 +1580,40 @@ __device__ void zero_slabs(uint32_t* base, int64_t slab_words, int n_slabs) {
 // the other ping-pong side (dead once this level's DERIVE pairs have read their parents); with
 // peers the one side is reused, dead once every rank has passed the second barrier.  The next
 // frontier has at most two slots per current slot.  Runs while CTA 0 finalizes.
-__device__ void zero_next_level(const MtbCtx& ctx) {
+__device__ void zero_next_level(const MtbCtx& ctx, int n_slots) {
   if (ctx.max_depth >= 0 && ctx.depth + 1 >= ctx.max_depth) return;
   View v(ctx);
-  int64_t n = 2 * (int64_t)v.n_slots();
+  int64_t n = 2 * (int64_t)n_slots;
   if (n > ctx.h_cap) n = ctx.h_cap;
   zero_slabs(ptr_of<uint32_t>(ctx.hist[ctx.hcur ^ 1]), v.slab_words(), (int)n);
 }
 
+// Everything after a level's histograms are complete on this rank (the caller has synchronised the
+// grid): [push partial slabs to the owners, peer barrier,] gain on the owned features (records go to
+// every rank's mailbox), [peer barrier | grid sync,] finalize on CTA 0 while the others zero the
+// next level's slabs.
 template <bool NV>
 __device__ __forceinline__ void search_tail(const MtbCtx& ctx, cg::grid_group& grid, uint8_t* smem, int smem_bytes,
-                                            int* smem_warp, bool zero_next) {
+                                            int* smem_warp, int n_slots, bool zero_next, bool rows_from_cursors) {
+  stamp(ctx, 2);
   if (ctx.world > 1) {
-    grid.sync();
-    stamp(ctx, 2);
-    if constexpr (!NV) push_phase(ctx);
+    if constexpr (!NV) push_phase(ctx, n_slots, rows_from_cursors);
     peer_barrier(ctx, grid, (uint32_t)ctx.epoch + 1u);
     stamp(ctx, 3);
-    gain_phase<NV>(ctx, smem, kFusedGainWarps, smem_bytes, -1);
+    gain_phase<NV>(ctx, smem, kFusedGainWarps, smem_bytes, -1, n_slots);
     stamp(ctx, 4);
     peer_barrier(ctx, grid, (uint32_t)ctx.epoch + 2u);
     stamp(ctx, 5);
   } else {
-    grid.sync();
-    stamp(ctx, 2);
     stamp(ctx, 3);
-    gain_phase(ctx, smem, kFusedGainWarps, smem_bytes, -1);
+    gain_phase(ctx, smem, kFusedGainWarps, smem_bytes, -1, n_slots);
     grid.sync();
     stamp(ctx, 4);
     stamp(ctx, 5);
   }
   if (blockIdx.x == 0) finalize_phase(ctx, smem_warp);
   stamp(ctx, 6);
-  if (zero_next) zero_next_level(ctx);
+  if (zero_next) zero_next_level(ctx, n_slots);
 }
 
 template <int FT, bool IL = false, bool NV = false>
@@ -1536,7 +1633,8 @@ __global__ void __launch_bounds__(kFusedThreads, 1) k_level_fused(const __grid_c
   grid.sync();
   stamp(ctx, 1);
   hist_phase<FT, IL>(ctx, smem);
-  search_tail<NV>(ctx, grid, smem, smem_bytes, smem_warp, ctx.zero_next != 0);
+  grid.sync();
+  search_tail<NV>(ctx, grid, smem, smem_bytes, smem_warp, ptr_of<const int>(ctx.scalars)[0], ctx.zero_next != 0, false);
 }
 
 template <int FT, bool IL = false, bool NV = false>
@@ -1546,7 +1644,8 @@ __global__ void __launch_bounds__(kFusedThreads, 1) k_level_fused2(const __grid_
   __shared__ int smem_warp[33];
   cg::grid_group grid = cg::this_grid();
   // nothing to partition and nothing to search: the tree finished at an earlier level
-  if (ptr_of<const int>(P.scalars)[1] == 0) {
+  const int n_children = ptr_of<const int>(P.scalars)[1];  // the children's slot count (finalize overwrites it at the end)
+  if (n_children == 0) {
     if (blockIdx.x == 0 && threadIdx.x == 0) ptr_of<int>(P.scalars)[0] = 0;
     return;
   }
@@ -1573,13 +1672,17 @@ __global__ void __launch_bounds__(kFusedThreads, 1) k_level_fused2(const __grid_
     stamp(C, 8);
     move_hist_phase<FT, IL>(P, C, smem, 1, ring);
   }
-  grid.sync();
-  commit_phase(P);
-  if (blockIdx.x == 0 && threadIdx.x == 0) ptr_of<int>(P.scalars)[0] = ptr_of<int>(P.scalars)[1];
-  grid.sync();
+  grid.sync();  // children's histograms and rows are complete on this rank
   stamp(C, 1);
-  if (blockIdx.x == 0) plan_phase(C, smem_warp);  // resets cursors and the gain work counters
-  search_tail<NV>(C, grid, smem, smem_bytes, smem_warp, true);
+  // CTA 0 turns the partition cursors into the children's row segments while the others go on: only
+  // its own finalize (and the next launch) read them.  The search below takes the slot count as an
+  // argument; scalars[0] is brought up to date for finalize and the zeroing at the end.
+  if (blockIdx.x == 0) {
+    commit_phase(P, threadIdx.x, blockDim.x);
+    if (threadIdx.x == 0) ptr_of<int>(P.scalars)[0] = n_children;
+    __syncthreads();
+  }
+  search_tail<NV>(C, grid, smem, smem_bytes, smem_warp, n_children, true, true);
 }
 
 int g_sm_count = 0;

@@ -356,7 +356,7 @@ class TreeBuilder:
         F, C, G = data.n_features, data.n_classes, data.G
         if C > MAX_CLASSES:
             raise ValueError(f"the CUDA engine supports at most {MAX_CLASSES} classes")
-        B = max(32, ((int(n_bins) + 31) // 32) * 32)
+        B = _bin_stride(n_bins)
         if B > 256:
             raise ValueError("at most 256 bins per feature")
         self.F, self.C, self.G, self.B = F, C, G, B
@@ -378,6 +378,9 @@ class TreeBuilder:
         ctx.klogk, ctx.klogk_n = _p(self._klogk), KLOGK_N
         ctx.world, ctx.rank = (P, self.rank) if peer_mode else (1, 0)
         ctx.fpo = self.fpo
+        # in-kernel peer barriers give up after this long (a rank that died or raised between two
+        # launches would otherwise leave the others spinning for ever); 0 = wait for ever
+        ctx.barrier_timeout_ns = int(float(os.environ.get("MTB_BARRIER_TIMEOUT_S", "30")) * 1e9)
 
         # features per shared-memory tile: the largest that leaves >= 2 TMA stages
         self.stats = BuildStats(reduce=reduce, world=P)
@@ -507,7 +510,8 @@ class TreeBuilder:
         MF = m_cap * F
         self._rec_off = (0, MF * 8, MF * 12, MF * 12 + MF * C * 4)
         rec_bytes = _round_up(self._rec_off[3] + m_cap * C * 4, 256)
-        stage_bytes = _round_up(P * self.h_cap * self.fpo * B * C * 4, 256) if peer_mode else 0
+        # staging cells [source][slot][fpo*B*C] u32 (or u16-packed) + one format word per (source, slot)
+        stage_bytes = _round_up(P * self.h_cap * (self.fpo * B * C + 1) * 4, 256) if peer_mode else 0
         self._layout = (0, stage_bytes, stage_bytes + rec_bytes)  # stage | mailbox | flags
         total = stage_bytes + rec_bytes + 256
         if reduce == "p2p":
@@ -547,7 +551,7 @@ class TreeBuilder:
         MF = m_cap * F
         rec = _round_up(MF * 12 + MF * C * 4 + m_cap * C * 4, 256)
         fpo = (F + world - 1) // world
-        return _round_up(world * h_cap * fpo * B * C * 4, 256) + rec + 256
+        return _round_up(world * h_cap * (fpo * B * C + 1) * 4, 256) + rec + 256
 
     def close(self) -> None:
         if self.region is not None:
@@ -674,8 +678,18 @@ class TreeBuilder:
             if t[8] > t[0]:
                 row["prepass_ms"] = float(t[8] - t[0])
             self._phase_ns.append(row)
+        self._check_peers()
         self.n_next, self.n_nodes = int(self._host_scal[1]), int(self._host_scal[2])
         return self.n_next
+
+    def _check_peers(self) -> None:
+        """Raise when an in-kernel peer barrier gave up (``scalars[7]``, see ``peer_barrier`` in csrc/build.cu)."""
+        if self.reduce == "p2p" and int(self._host_scal[7]) != 0:
+            clear_caches()  # flags, epochs and abort words of the cached regions are no longer in step
+            raise RuntimeError(
+                f"rank {self.rank}: a peer did not reach an in-kernel barrier within "
+                f"{self.ctx.barrier_timeout_ns / 1e9:.0f} s (a rank failed or is far behind); the fit was abandoned"
+            )
 
     def _swap_sides(self) -> None:
         if self.fuse_partition:
@@ -749,6 +763,7 @@ class TreeBuilder:
             self.stats.levels += 1
         self._host_scal.copy_(self.scalars, non_blocking=True)
         self.torch.cuda.current_stream().synchronize()
+        self._check_peers()
         self.n_nodes = int(self._host_scal[2])
         return self._download(self.n_nodes)
 
@@ -820,7 +835,7 @@ def fit_virtual_ranks(shards, n_classes: int, n_bins: int, params: SplitParams, 
 
     P = len(shards)
     F = int(shards[0][0].shape[1])
-    B = max(32, ((int(n_bins) + 31) // 32) * 32)
+    B = _bin_stride(n_bins)
     region = LocalRegion(TreeBuilder.region_bytes(P, F, B, n_classes, h_cap), P)
     n_global = sum(int(x.shape[0]) for x, _ in shards)
     builders = []
@@ -830,6 +845,15 @@ def fit_virtual_ranks(shards, n_classes: int, n_bins: int, params: SplitParams, 
         data.set_labels(y)
         builders.append(TreeBuilder(data, n_bins, params, n_global=n_global, peers=region.view(r), h_cap=h_cap))
     return build_lockstep(builders)
+
+
+def _bin_stride(n_bins: int) -> int:
+    """Bins per class row of a histogram slab: a power of two, at least 32 (a lane of the gain phase
+    owns ``B / 32`` consecutive bins and loads them with one aligned vector load)."""
+    B = 32
+    while B < int(n_bins):
+        B *= 2
+    return B
 
 
 def _round_up(x: int, m: int) -> int:
