@@ -344,6 +344,10 @@ def run_ours(a):
     # ---- end-to-end arm: pinned host inputs, tree read back
     e2e = None
     if not a.no_e2e:
+        # feed the GPU from the host memory next to it (first-touch placement of the pinned buffers)
+        from mpitree_b200.utils.topology import bind_to_gpu_numa
+
+        bound = bind_to_gpu_numa(local)
         Xh = torch.empty(X.shape, dtype=X.dtype).pin_memory()
         yh = torch.empty(y.shape, dtype=y.dtype).pin_memory()
         Xh.copy_(X)
@@ -362,6 +366,7 @@ def run_ours(a):
             "h2d_bytes_per_step": int(Xh.numel() * Xh.element_size() + yh.numel() * yh.element_size()) * world,
             "d2h_bytes_per_step": d2h * world,
             "steps": e_steps,
+            "cpu_binding": f"rank 0 bound to {len(bound)} CPUs local to its GPU" if bound else "none (NVML affinity unavailable or already bound)",
         }
 
     same_cfg = None

@@ -16,7 +16,9 @@
 //   hist      persistent CTAs; a producer warp streams 1024-row x 16-byte tiles with
 //             cp.async.bulk (TMA) through an mbarrier ring; 16 consumer warps do
 //             shared-memory atomic increments into an [FT][B][C] tile; tiles are
-//             flushed with red.global.add (to the owner GPU's slab when world > 1)
+//             written to the slot's local slab (plain stores when one CTA saw all of the tile's
+//             rows, red.global.add otherwise); with world > 1 the slabs are partial sums that the
+//             push phase copies to the owners' staging areas
 //   gain      one warp per (slot, feature): sibling = parent - built child,
 //             prefix over bins, float64 entropy cost with the reference's rounding,
 //             first arg-min
@@ -745,24 +747,36 @@ __device__ void gain_pair(const MtbCtx& ctx, const KlogK& klogk, uint32_t* slab,
       else h[u] = ld_bins<BPL>(own + (int64_t)c * B);
     }
     if (P > 1 && !NV) {
-      // staged partials of the peers, one source after the other: the loads of a source do not
-      // depend on the running sums, so several sources overlap in flight
-      for (int p = 0; p < P; ++p) {
-        if (p == r) continue;
-        Bins<BPL> y[kCB];
-        const uint32_t* cell = stage_cell + (int64_t)p * src_stride;  // this source's cell of the slot, class 0
-        if (narrow_mask >> p & 1u) {
+      // staged partials of the peers, two sources (x kCB classes) in flight together: the pair's
+      // latency is a chain of L2 round trips, one per group of loads
+      constexpr int kPS = 2;  // (four overflow the 96-register budget of the fused kernel into local memory)
+      for (int p0 = 0; p0 < P; p0 += kPS) {
+        Bins<BPL> y[kPS][kCB];
 #pragma unroll
-          for (int u = 0; u < kCB; ++u)
-            y[u] = ld_bins_u16<BPL>(reinterpret_cast<const uint16_t*>(cell) + (int64_t)fl_off + (int64_t)min(c0 + u, C - 1) * B + lane_off);
-        } else {
+        for (int i = 0; i < kPS; ++i) {
+          const int p = p0 + i;
+          const bool live = p < P && p != r;
+          const uint32_t* cell = stage_cell + (int64_t)(live ? p : r) * src_stride;  // this source's cell of the slot
+          if (live && (narrow_mask >> p & 1u)) {
 #pragma unroll
-          for (int u = 0; u < kCB; ++u) y[u] = ld_bins<BPL>(cell + fl_off + (int64_t)min(c0 + u, C - 1) * B + lane_off);
+            for (int u = 0; u < kCB; ++u)
+              y[i][u] = ld_bins_u16<BPL>(reinterpret_cast<const uint16_t*>(cell) + (int64_t)fl_off + (int64_t)min(c0 + u, C - 1) * B + lane_off);
+          } else if (live) {
+#pragma unroll
+            for (int u = 0; u < kCB; ++u) y[i][u] = ld_bins<BPL>(cell + fl_off + (int64_t)min(c0 + u, C - 1) * B + lane_off);
+          } else {
+#pragma unroll
+            for (int u = 0; u < kCB; ++u)
+#pragma unroll
+              for (int j = 0; j < BPL; ++j) y[i][u].v[j] = 0;
+          }
         }
 #pragma unroll
-        for (int u = 0; u < kCB; ++u)
+        for (int i = 0; i < kPS; ++i)
 #pragma unroll
-          for (int j = 0; j < BPL; ++j) h[u].v[j] += y[u].v[j];
+          for (int u = 0; u < kCB; ++u)
+#pragma unroll
+            for (int j = 0; j < BPL; ++j) h[u].v[j] += y[i][u].v[j];
       }
     }
     if (derive) {
@@ -930,7 +944,8 @@ __device__ __forceinline__ bool is_terminal(Cnt cnt, int C, int depth, const Mtb
   return present <= 1 || (ctx.max_depth >= 0 && depth >= ctx.max_depth) || (int64_t)n < ctx.min_samples_split;
 }
 
-__device__ void finalize_phase(const MtbCtx& ctx, int* smem_warp) {
+// `ktab`: the k log2 k constants (the shared-memory copy left by the gain phase in the fused kernels)
+__device__ void finalize_phase(const MtbCtx& ctx, int* smem_warp, const double* ktab) {
   View v(ctx);
   const int n = v.n_slots();
   const int F = (int)ctx.F, C = (int)ctx.C;
@@ -980,18 +995,18 @@ __device__ void finalize_phase(const MtbCtx& ctx, int* smem_warp) {
       if (!is_terminal([&](int c) { return cnt[c]; }, C, depth, ctx, ntot)) {
         const bool exact = ctx.plogp == 0 || ntot <= (uint32_t)ctx.plogp_n;
         KlogK klogk;
-        klogk.bind(ptr_of<const double>(ctx.klogk), ptr_of<const double>(ctx.klogk));  // a handful of evaluations per slot: global table
+        klogk.bind(ktab, ptr_of<const double>(ctx.klogk));
         const double hp = exact ? impurity(C, [&](int c) { return cnt[c]; }, ntot, (int)ctx.criterion,
                                            ptr_of<const double>(ctx.plogp), (uint32_t)ctx.plogp_n)
                                 : fast_impurity(C, [&](int c) { return cnt[c]; }, ntot, (int)ctx.criterion, klogk);
         bool have = false;
-        // costs of eight features are loaded together: the loop is bound by load latency otherwise
-        for (int f0 = 0; f0 < F; f0 += 8) {
-          double cst[8];
+        // costs of sixteen features are loaded together: the loop is bound by load latency otherwise
+        for (int f0 = 0; f0 < F; f0 += 16) {
+          double cst[16];
 #pragma unroll
-          for (int j = 0; j < 8; ++j) cst[j] = f0 + j < F ? fb_cost[(int64_t)s * F + f0 + j] : INFINITY;
+          for (int j = 0; j < 16; ++j) cst[j] = f0 + j < F ? fb_cost[(int64_t)s * F + f0 + j] : INFINITY;
 #pragma unroll
-          for (int j = 0; j < 8; ++j) {
+          for (int j = 0; j < 16; ++j) {
             if (!(cst[j] < INFINITY)) continue;
             const double g = __dsub_rn(hp, cst[j]);
             if (!have || g > bgain) {  // strict: first (lowest) feature wins ties
@@ -1097,7 +1112,7 @@ __device__ void finalize_phase(const MtbCtx& ctx, int* smem_warp) {
 __global__ void __launch_bounds__(1024) k_finalize(const __grid_constant__ MtbCtx ctx) {
   __shared__ int smem_warp[33];
   if (ptr_of<const int>(ctx.scalars)[0] == 0) return;
-  finalize_phase(ctx, smem_warp);
+  finalize_phase(ctx, smem_warp, ptr_of<const double>(ctx.klogk));
 }
 
 // ------------------------------------------------------------------- partition
@@ -1611,7 +1626,7 @@ __device__ __forceinline__ void search_tail(const MtbCtx& ctx, cg::grid_group& g
     stamp(ctx, 4);
     stamp(ctx, 5);
   }
-  if (blockIdx.x == 0) finalize_phase(ctx, smem_warp);
+  if (blockIdx.x == 0) finalize_phase(ctx, smem_warp, reinterpret_cast<const double*>(smem));
   stamp(ctx, 6);
   if (zero_next) zero_next_level(ctx, n_slots);
 }

@@ -27,10 +27,12 @@ from typing import List, Optional, Sequence
 
 import numpy as np
 
-__all__ = ["BinMapper", "FEATURE_GROUP", "padded_features"]
+__all__ = ["BinMapper", "FEATURE_GROUP", "MAX_WIDE_BINS", "padded_features"]
 
 #: features per device tile row chunk (16 one-byte codes = one 128-bit load)
 FEATURE_GROUP = 16
+#: most bins per feature in the wide (exact beyond 256 distinct values) mode, see BinMapper.expand_wide
+MAX_WIDE_BINS = 1 << 16
 
 
 def padded_features(n_features: int) -> int:
@@ -60,6 +62,9 @@ class BinMapper:
     edges: List[np.ndarray]
     lossless: np.ndarray
     max_bins: int = 256
+    #: True where the edges list every distinct value that was seen when they were fitted (on a sample
+    #: of the rows this is a claim about the sample only: see ``cuda_engine._repair_sampled_edges``)
+    enumerated: Optional[np.ndarray] = None
 
     # ----------------------------------------------------------------- build
     @classmethod
@@ -69,6 +74,7 @@ class BinMapper:
         max_bins: int = 256,
         *,
         summaries: Optional[Sequence[Sequence[np.ndarray]]] = None,
+        wide: bool = False,
     ) -> "BinMapper":
         """Compute edges from ``X`` (n_rows, n_features).
 
@@ -77,9 +83,12 @@ class BinMapper:
         the summaries alone, with the same operations in the same order on every rank, so all
         ranks end up with identical bins (the cross-rank "edge agreement" step of K1) whatever
         their local rows are.
+
+        ``wide``: allow up to ``MAX_WIDE_BINS`` bins per feature (codes then need :meth:`expand_wide`
+        before they can be searched with one-byte bin codes).
         """
-        if not 2 <= max_bins <= 256:
-            raise ValueError("max_bins must be in [2, 256]")
+        if not 2 <= max_bins <= (MAX_WIDE_BINS if wide else 256):
+            raise ValueError(f"max_bins must be in [2, {MAX_WIDE_BINS if wide else 256}]")
         n_features = X.shape[1]
         edges, lossless = [], np.zeros(n_features, dtype=bool)
         for f in range(n_features):
@@ -96,7 +105,37 @@ class BinMapper:
                 lossless[f] = True
             else:
                 edges.append(_quantile_edges(values, weighted, max_bins))
-        return cls(edges=edges, lossless=lossless, max_bins=max_bins)
+        return cls(edges=edges, lossless=lossless, max_bins=max_bins, enumerated=lossless.copy())
+
+    # ------------------------------------------------------------- wide bins
+    def expand_wide(self, X: np.ndarray):
+        """Codes for features with more than 256 bins, as several one-byte *virtual* columns.
+
+        The kernels (and the slabs) are built around one-byte bin codes.  A feature with ``U > 256`` edges
+        is therefore presented as ``ceil(U / 255)`` columns: column ``p`` holds ``clip(code - 255 p, 0, 255)``.
+        A split of that column at local bin ``b <= 254`` is exactly the split ``code <= 255 p + b`` of the
+        real feature (smaller codes clip to 0 and go left, larger ones clip to 255 and go right; local bin
+        255 has an empty right side and is never chosen), every global threshold appears in exactly one
+        column, and the columns' order (feature, then chunk, then bin) is the reference's tie-break order
+        (first feature, first threshold).  So the histogram search over the virtual columns is the exact
+        search over all ``U`` candidates; it only costs more columns.
+
+        Returns ``(vcodes uint8 (n, Fv), v_feature int (Fv,), v_chunk int (Fv,), v_nbins int32 (Fv,))``.
+        """
+        n, F = X.shape
+        cols, v_feature, v_chunk, v_nbins = [], [], [], []
+        for f in range(F):
+            e = self.edges[f]
+            U = max(len(e), 1)
+            code = np.zeros(n, dtype=np.int64) if len(e) == 0 else np.minimum(np.searchsorted(e, X[:, f], side="left"), U - 1)
+            for p in range((U + 254) // 255) if U > 256 else range(1):
+                lo = 255 * p
+                cols.append(np.clip(code - lo, 0, 255).astype(np.uint8))
+                v_feature.append(f)
+                v_chunk.append(p)
+                v_nbins.append(min(256, U - lo) if U > 256 else U)
+        return (np.stack(cols, axis=1) if cols else np.zeros((n, 0), np.uint8), np.asarray(v_feature), np.asarray(v_chunk),
+                np.asarray(v_nbins, dtype=np.int32))
 
     @staticmethod
     def local_summary(X: np.ndarray, cap: int = 4096) -> List[np.ndarray]:

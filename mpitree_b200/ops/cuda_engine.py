@@ -28,6 +28,7 @@ __all__ = [
     "available",
     "supports",
     "fit_from_host",
+    "fit_from_codes",
     "fit_from_torch",
     "predict_leaf_ids",
     "DeviceDataset",
@@ -57,8 +58,8 @@ def available() -> bool:
 
 
 def supports(*, numeric: bool, n_classes: int) -> Tuple[bool, str]:
-    if not numeric:
-        return False, "object/string features are handled by the host engine"
+    # (object / string columns are fine: they are ordinal-coded on the host, where the strings live, and the
+    # tree is grown from the codes on the device: ``fit_from_codes``)
     if n_classes > MAX_CLASSES:
         return False, f"more than {MAX_CLASSES} classes"
     return True, ""
@@ -891,6 +892,21 @@ _BUILDERS: dict = {}
 _BUILDERS_MAX = 2
 
 
+def _log_fit(builder, n_global: int, F: int, flat) -> None:
+    """One INFO line per fit on rank 0 (``MTB_LOG=INFO``); per-level rows at DEBUG when the builder profiled."""
+    from ..utils.log import get_logger
+
+    log = get_logger()
+    if not log.isEnabledFor(20):
+        return
+    st = builder.stats
+    log.info("fit: %d rows x %d features, %d classes, %d bins | world %d, reduce %s, tile %s, FT %d, %d slots | "
+             "%d levels, %d launches, %d nodes, %d handed off", n_global, F, builder.C, builder.B, st.world, st.reduce,
+             st.tile_layout, st.FT, st.m_cap, st.levels, st.launches, flat.n_nodes, st.handed_off)
+    for lv, row in enumerate(st.level_ms):
+        log.debug("level %d: %s", lv, " ".join(f"{k}={v:.3f}" if isinstance(v, float) else f"{k}={v}" for k, v in row.items()))
+
+
 def _params_key(params: SplitParams):
     return (params.max_depth, int(params.min_samples_split), params.criterion)
 
@@ -988,6 +1004,10 @@ def _fit_mapper_numpy(X: np.ndarray, max_bins: int, comm=None) -> BinMapper:
                 else:
                     e[-1] = col_max[f]
                 mapper.lossless[f] = False
+    if sampled and X.dtype.kind in "fiu":
+        import torch
+
+        _repair_sampled_edges(torch.from_numpy(X), mapper, max_bins, comm)
     return mapper
 
 
@@ -1037,7 +1057,7 @@ def _merge_edge_candidates(parts, F: int, max_bins: int, np_dtype, col_max) -> B
     """Reduce every rank's ``(distinct counts, distinct values, order statistics)`` to one edge set.
 
     Pure function of ``parts`` (in rank order), so every rank derives identical bins."""
-    edges, lossless = [], np.zeros(F, dtype=bool)
+    edges, lossless, enumerated = [], np.zeros(F, dtype=bool), np.zeros(F, dtype=bool)
     for f in range(F):
         all_small = all(int(p[0][f]) <= 256 for p in parts)
         if all_small:
@@ -1045,6 +1065,7 @@ def _merge_edge_candidates(parts, F: int, max_bins: int, np_dtype, col_max) -> B
             if len(vals) <= max_bins:
                 edges.append(vals.astype(np_dtype))
                 lossless[f] = len(parts) == 1 and col_max is None
+                enumerated[f] = True
                 continue
         merged = np.sort(np.concatenate([p[2][:, f] for p in parts]))
         if len(merged) == 0:  # no rank has any row
@@ -1054,7 +1075,7 @@ def _merge_edge_candidates(parts, F: int, max_bins: int, np_dtype, col_max) -> B
             pick = np.ceil(np.linspace(0.0, 1.0, max_bins + 1)[1:] * (len(merged) - 1)).astype(np.int64)
             merged = merged[pick]
         edges.append(np.unique(merged).astype(np_dtype))
-    mapper = BinMapper(edges=edges, lossless=lossless, max_bins=max_bins)
+    mapper = BinMapper(edges=edges, lossless=lossless, max_bins=max_bins, enumerated=enumerated)
     if col_max is not None:
         for f, e in enumerate(mapper.edges):
             if len(e) and col_max[f] > e[-1]:
@@ -1065,6 +1086,66 @@ def _merge_edge_candidates(parts, F: int, max_bins: int, np_dtype, col_max) -> B
     return mapper
 
 
+def _repair_sampled_edges(X, mapper: BinMapper, max_bins: int, comm=None) -> int:
+    """After edges were fitted on a *sample* of the rows: make sure no value of a low-cardinality column was missed.
+
+    A column whose sample showed at most ``max_bins`` distinct values gets one bin per value, and the
+    search is then exact for it - but only if the sample saw every value.  A rare value the sample
+    missed would silently share the next edge's bin, and candidate thresholds (and printed ones) would
+    differ from the reference and from a fit on all rows.  So every such column is checked against all
+    rows (one ``bucketize`` pass, chunked); columns with strays get their edges refitted from the
+    distinct values of *all* rows of *all* ranks (or, if there turn out to be more than ``max_bins``,
+    keep their edges and lose the ``lossless`` mark).  Every decision is taken from all-gathered
+    values, so ranks stay in step.  ``X``: this rank's rows as a torch tensor (any device).  Returns the
+    number of columns whose edges changed.
+    """
+    import torch
+
+    cand = [f for f in range(mapper.n_features) if mapper.enumerated is not None and mapper.enumerated[f] and len(mapper.edges[f])]
+    multi = comm is not None and comm.size > 1
+    stray = np.zeros(len(cand), dtype=bool)
+    n = int(X.shape[0])
+    step = 1 << 24
+    for i, f in enumerate(cand):
+        e = torch.from_numpy(np.ascontiguousarray(mapper.edges[f])).to(X.device)
+        for r0 in range(0, n, step):
+            col = X[r0 : r0 + step, f].contiguous()
+            if col.dtype != e.dtype:
+                col = col.to(e.dtype)
+            idx = torch.bucketize(col, e).clamp_(max=e.numel() - 1)
+            if bool((e[idx] != col).any()):
+                stray[i] = True
+                break
+    if multi:
+        stray = np.any(np.stack(comm.allgather_object(stray)), axis=0)
+    changed = 0
+    for i, f in enumerate(cand):
+        if not stray[i]:
+            continue
+        u = torch.unique(X[:, f].contiguous())
+        vals = u[: 4 * 256 + 1].cpu().numpy() if u.numel() > 4 * 256 else u.cpu().numpy()  # more than that cannot be enumerated anyway
+        if multi:
+            vals = np.unique(np.concatenate(comm.allgather_object(vals)))
+        vals = vals.astype(mapper.edges[f].dtype, copy=False)
+        if len(vals) <= max_bins:
+            mapper.edges[f] = vals
+            mapper.lossless[f] = not multi
+            changed += 1
+        else:
+            # too many distinct values for one bin each: the sampled edges stay, merged with the column's
+            # extremes so that every value still falls into a bin whose upper edge is a data value
+            hi = vals[-1]
+            e = mapper.edges[f]
+            if hi > e[-1]:
+                mapper.edges[f] = np.append(e[: max_bins - 1], hi).astype(e.dtype)
+                changed += 1
+            mapper.lossless[f] = False
+            mapper.enumerated[f] = False
+    if changed:
+        mapper.__dict__.pop("_edge_table", None)
+    return changed
+
+
 def _byte_lut(mapper: BinMapper) -> np.ndarray:
     """``(F, 256)`` uint8 table: byte value -> bin code (first edge >= value, clamped to the last bin)."""
     lut = np.zeros((mapper.n_features, 256), dtype=np.uint8)
@@ -1072,6 +1153,30 @@ def _byte_lut(mapper: BinMapper) -> np.ndarray:
         if len(e):
             lut[f] = np.minimum(np.searchsorted(e, np.arange(256).astype(e.dtype), side="left"), len(e) - 1)
     return lut
+
+
+_COPY_STREAMS: dict = {}
+
+
+def _copy_stream(dev):
+    import torch
+
+    key = str(dev)
+    if key not in _COPY_STREAMS:
+        _COPY_STREAMS[key] = torch.cuda.Stream(device=dev)
+    return _COPY_STREAMS[key]
+
+
+def _float_dtype_for(dtype):
+    """Floating type that holds every value of ``dtype`` exactly enough to sit on the right side of a
+    threshold: integers wider than 16 bits (and anything unknown) go to float64 - float32 would round
+    values above 2**24 - narrow integers and half-precision floats to float32.  Fit and predict use
+    the same rule (``fit_from_host`` does the same for numpy inputs)."""
+    import torch
+
+    narrow = (torch.int8, torch.int16, torch.float16, torch.bfloat16, torch.bool) + tuple(
+        t for t in (getattr(torch, "uint16", None),) if t is not None)
+    return torch.float32 if dtype in narrow else torch.float64
 
 
 def _device():
@@ -1132,7 +1237,44 @@ def fit_from_host(X: np.ndarray, y_codes: np.ndarray, n_classes: int, params: Sp
         builder.close()
         data.release()
     fit_from_host.last_stats = builder.stats
+    _log_fit(builder, n_global, F, flat)
     return flat, mapper
+
+
+def fit_from_codes(codes: np.ndarray, y_codes: np.ndarray, n_classes: int, n_bins: int, params: SplitParams, *,
+                   comm=None, builder_kwargs=None) -> FlatTree:
+    """Grow the tree from bin codes that were formed on the host (this rank's shard, ``uint8``).
+
+    The path of object / string ("categorical") columns: the reference splits them ordinally with
+    Python's ``<=`` on the sorted distinct values (``decision_tree.py:73-77``), so the host mapper turns
+    every column into ordinal codes in sorted-unique order - strings cannot go to the device, their
+    codes can - and the level-wise kernels take it from there exactly as for numeric data.  ``n_bins``:
+    the largest number of bins of any column (agreed on across ranks).
+    """
+    import torch
+
+    dev = _device()
+    codes = np.ascontiguousarray(codes, dtype=np.uint8)
+    n, F = codes.shape
+    data = DeviceDataset.allocate(n, F, n_classes, dev)
+    for r0 in range(0, n, ENCODE_CHUNK_ROWS):
+        data.encode_u8(torch.from_numpy(codes[r0 : r0 + ENCODE_CHUNK_ROWS]).to(dev), None, r0)
+    data.set_labels(torch.from_numpy(np.asarray(y_codes)).to(dev))
+    n_global, min_free = n, None
+    if comm is not None and comm.size > 1:
+        meta = comm.allgather_ints((n, int(torch.cuda.mem_get_info(dev)[0])))
+        n_global, min_free = int(meta[:, 0].sum()), int(meta[:, 1].min())
+    _dist_group(comm)
+    builder = TreeBuilder(data, int(n_bins), params, n_global=n_global, comm=comm, min_free_bytes=min_free,
+                          **(builder_kwargs or {}))
+    try:
+        flat = builder.build()
+    finally:
+        builder.close()
+        data.release()
+    fit_from_host.last_stats = builder.stats
+    _log_fit(builder, n_global, F, flat)
+    return flat
 
 
 def fit_from_torch(X, y, params: SplitParams, *, max_bins: int = 256, comm=None, replicated: bool = False,
@@ -1152,7 +1294,7 @@ def fit_from_torch(X, y, params: SplitParams, *, max_bins: int = 256, comm=None,
         X, y = X[lo:hi], y[lo:hi]
     n, F = int(X.shape[0]), int(X.shape[1])
     if X.dtype not in (torch.float32, torch.float64, torch.uint8):
-        X = X.to(torch.float32)
+        X = X.to(_float_dtype_for(X.dtype))
 
     # labels -> class codes (classes_ are agreed on globally)
     y_dev = y.to(dev, non_blocking=True)
@@ -1225,6 +1367,8 @@ def fit_from_torch(X, y, params: SplitParams, *, max_bins: int = 256, comm=None,
             maxima = [m for m in comm.allgather_object(col_max) if m is not None]
             col_max = np.max(np.stack(maxima), axis=0)
         mapper = _fit_mapper_device(sample.to(dev, non_blocking=True), max_bins, comm, col_max)
+        if multi and int(meta[:, 1].max()) > SAMPLE_ROWS or idx is not None:
+            _repair_sampled_edges(X, mapper, max_bins, comm)  # (uint8 rows compare against float edges)
         if X.dtype == torch.uint8:
             lut = torch.from_numpy(_byte_lut(mapper)).to(dev)
 
@@ -1233,9 +1377,21 @@ def fit_from_torch(X, y, params: SplitParams, *, max_bins: int = 256, comm=None,
     st.mark("alloc")
     if X.is_cuda:
         (data.encode_u8(X, lut, 0) if X.dtype == torch.uint8 else data.encode_float(X, mapper, 0))
-    else:
+    elif dev.type != "cuda":  # driver tests without a GPU: the "device" is the host
         for r0 in range(0, n, ENCODE_CHUNK_ROWS):
             chunk = X[r0 : r0 + ENCODE_CHUNK_ROWS].to(dev, non_blocking=True)
+            (data.encode_u8(chunk, lut, r0) if X.dtype == torch.uint8 else data.encode_float(chunk, mapper, r0))
+    else:
+        # host rows: the copies run on their own stream, so chunk k+1 is on the wire while chunk k is encoded
+        main = torch.cuda.current_stream()
+        side = _copy_stream(dev)
+        side.wait_stream(main)
+        for r0 in range(0, n, ENCODE_CHUNK_ROWS):
+            with torch.cuda.stream(side):
+                chunk = X[r0 : r0 + ENCODE_CHUNK_ROWS].to(dev, non_blocking=True)
+                arrived = side.record_event()
+            main.wait_event(arrived)
+            chunk.record_stream(main)
             (data.encode_u8(chunk, lut, r0) if X.dtype == torch.uint8 else data.encode_float(chunk, mapper, r0))
     data.set_labels(y_codes)
     st.mark("encode")
@@ -1266,6 +1422,8 @@ def fit_from_torch(X, y, params: SplitParams, *, max_bins: int = 256, comm=None,
     st.mark("build")
     st.report()
     fit_from_torch.last_stats = builder.stats
+    flat.max_shard_rows = int(meta[:, 1].max())  # agreed on by every rank (for decisions that involve collectives)
+    _log_fit(builder, n_global, F, flat)
     if lazy_classes:
         # classes_ = labels that occur: read them off the root's class counts
         seen = np.flatnonzero(flat.counts[0] > 0)
@@ -1320,7 +1478,7 @@ def predict_leaf_ids(flat: FlatTree, X, *, want: str = "leaf"):
     is_np = isinstance(X, np.ndarray)
     Xt = torch.from_numpy(np.ascontiguousarray(X)) if is_np else X
     if Xt.dtype not in (torch.float32, torch.float64, torch.uint8):
-        Xt = Xt.to(torch.float64 if Xt.dtype in (torch.int64,) else torch.float32)
+        Xt = Xt.to(_float_dtype_for(Xt.dtype))
     dtype = {torch.float32: 0, torch.uint8: 1, torch.float64: 2}[Xt.dtype]
     n = int(Xt.shape[0])
     out = torch.empty(n, dtype=torch.int32, device=dev)

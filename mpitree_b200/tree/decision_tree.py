@@ -33,6 +33,8 @@ unchanged wherever the reference succeeds; see DESIGN.md "Quirk policy"):
 
 from __future__ import annotations
 
+import dataclasses
+
 import numbers
 from typing import Optional
 
@@ -171,7 +173,9 @@ class DecisionTreeClassifier(ClassifierMixin, BaseEstimator):
     max_bins : int, default=256
         Features with at most this many distinct values are searched exactly
         (every distinct value is a candidate, like the reference); others are
-        quantile-binned.
+        quantile-binned.  Values above 256 (up to 65,536; numpy inputs) keep the
+        search exact for such features at the price of extra one-byte columns
+        (``BinMapper.expand_wide``).
     device : {"auto", "cpu", "cuda"}, default="auto"
         ``auto`` uses the CUDA engine whenever a GPU is present.
     """
@@ -289,11 +293,49 @@ class DecisionTreeClassifier(ClassifierMixin, BaseEstimator):
         engine = resolve_engine(self.device, numeric=numeric, n_classes=len(classes))
         params = self._params(depth_offset)
 
-        if engine == "cuda":
+        if numeric and self.max_bins > 256:
+            # Exact search beyond 256 distinct values per feature (the reference examines every distinct
+            # value, ``:73``): features with more bins than a one-byte code can name are presented to the
+            # engines as several virtual columns (``BinMapper.expand_wide``); the chosen (column, bin) pairs
+            # are folded back into (feature, global bin) afterwards.
+            summaries = None
+            if comm is not None and comm.size > 1:
+                summaries = comm.allgather_object(BinMapper.local_summary(X, cap=max(4096, int(self.max_bins))))
+            mapper = BinMapper.fit(X, max_bins=self.max_bins, summaries=summaries, wide=True)
+            vcodes, v_feature, v_chunk, v_nbins = mapper.expand_wide(X)
+            if engine == "cuda":
+                from ..ops import cuda_engine
+
+                flat = cuda_engine.fit_from_codes(vcodes, y_codes, len(classes), int(v_nbins.max()), params, comm=comm,
+                                                  builder_kwargs=self._builder_kwargs())
+            else:
+                flat = fit_flat_tree_host(vcodes, y_codes, v_nbins, len(classes), params, comm,
+                                          handoff_rows=getattr(self, "handoff_rows", None))
+            # (new arrays: thread-ranks of one process can share the tree object the scheduler returns)
+            inner = flat.feature >= 0
+            vf = flat.feature[inner]
+            feature, bins = flat.feature.copy(), flat.bin.copy()
+            bins[inner] = 255 * v_chunk[vf] + flat.bin[inner]
+            feature[inner] = v_feature[vf]
+            flat = dataclasses.replace(flat, feature=feature, bin=bins)
+        elif engine == "cuda" and numeric:
             from ..ops import cuda_engine
 
             flat, mapper = cuda_engine.fit_from_host(
                 X, y_codes, len(classes), params, max_bins=self.max_bins, comm=comm,
+                builder_kwargs=self._builder_kwargs(),
+            )
+        elif engine == "cuda":
+            # object / string columns: ordinal codes in sorted-unique order on the host (the order Python's
+            # ``<=`` gives the reference, ``:73-77``), the tree from the codes on the device
+            from ..ops import cuda_engine
+
+            summaries = None
+            if comm is not None and comm.size > 1:
+                summaries = comm.allgather_object(BinMapper.local_summary(X))
+            mapper = BinMapper.fit(X, max_bins=self.max_bins, summaries=summaries)
+            flat = cuda_engine.fit_from_codes(
+                mapper.transform(X), y_codes, len(classes), int(mapper.n_bins.max()), params, comm=comm,
                 builder_kwargs=self._builder_kwargs(),
             )
         else:
@@ -360,7 +402,8 @@ class DecisionTreeClassifier(ClassifierMixin, BaseEstimator):
         self.classes_ = classes
         flat.class_labels = np.asarray(classes, dtype=np.int64)
         flat.thresholds = mapper.thresholds_of(flat.feature, flat.bin)
-        if not X.is_cuda and X.shape[0] <= ZERO_SIGN_ROWS_MAX:
+        # (decided from the largest shard, a value every rank shares: the restore runs collectives)
+        if not X.is_cuda and getattr(flat, "max_shard_rows", X.shape[0]) <= ZERO_SIGN_ROWS_MAX:
             # rows that live on the host can be looked at for free (see _restore_zero_signs); device
             # inputs and very large host inputs keep the sign of the global bin edge.  In the replicated
             # layout every rank holds all rows, so nothing has to be gathered.

@@ -274,3 +274,61 @@ def test_many_classes_with_256_bins(C):
     c = DecisionTreeClassifier(max_depth=5, device="cpu").fit(X, y)
     assert g.engine_ == "cuda"
     _same_tree(g, c)
+
+
+def test_string_and_mixed_columns_run_on_the_gpu_and_match_the_reference(ref):
+    """Object / string ("categorical") columns: ordinal codes on the host, the tree on the device; the
+    reference splits such columns with ``<=`` on the sorted distinct values (decision_tree.py:73-77)."""
+    rng = np.random.default_rng(3)
+    n = 400
+    colour = rng.choice(np.array(["red", "green", "blue", "amber"], dtype=object), size=n)
+    size = rng.choice(np.array(["S", "M", "L"], dtype=object), size=n)
+    x = rng.integers(0, 12, size=n)
+    y = ((colour <= "blue").astype(int) + (x > 6) + (size == "M")).astype(np.int64)
+    X = np.empty((n, 3), dtype=object)
+    X[:, 0], X[:, 1], X[:, 2] = colour, x.astype(object), size
+    ours = DecisionTreeClassifier(max_depth=4, device="cuda").fit(X, y)
+    assert ours.engine_ == "cuda"
+    cpu = DecisionTreeClassifier(max_depth=4, device="cpu").fit(X, y)
+    theirs = ref.DecisionTreeClassifier(max_depth=4).fit(X, y)
+    assert np.array_equal(ours.predict(X), theirs.predict(X))
+    assert np.array_equal(ours.predict_proba(X), theirs.predict_proba(X))
+    a, b = ours.flat_tree_, cpu.flat_tree_
+    assert np.array_equal(a.feature, b.feature) and np.array_equal(a.counts, b.counts) and a.thresholds == b.thresholds
+    # all-string matrix: thresholds are strings (the reference cannot print them; the structure must agree)
+    Xs = np.stack([colour, size], axis=1)
+    g = DecisionTreeClassifier(max_depth=3, device="cuda").fit(Xs, y)
+    r = ref.DecisionTreeClassifier(max_depth=3).fit(Xs, y)
+    assert g.engine_ == "cuda" and np.array_equal(g.predict(Xs), r.predict(Xs))
+
+
+@pytest.mark.parametrize("n,vals,seed", [(1500, 3, 0), (1500, 4, 1), (3000, 3, 2), (3000, 4, 3)])
+def test_large_tie_heavy_nodes_match_the_reference(ref, n, vals, seed):
+    """Root nodes above the 1,024-row limit of the exact-arithmetic path take the k log2 k cost form; with
+    3-4 distinct values per feature and duplicated / mirrored columns many candidates tie exactly, and the
+    reference's tie-breaks (first threshold, first feature) must survive.  CPU engine and CUDA engine."""
+    rng = np.random.default_rng(seed)
+    F = 6
+    X = rng.integers(0, vals, size=(n, F)).astype(np.float64)
+    X[:, 3] = X[:, 0]                 # duplicate column: exact ties between features
+    X[:, 4] = (vals - 1) - X[:, 1]    # mirrored column: the same partitions with left and right swapped
+    y = ((X[:, 0] + X[:, 1] + rng.integers(0, 2, size=n)) % 3).astype(np.int64)
+    theirs = ref.DecisionTreeClassifier(max_depth=3).fit(X, y)
+    for device in ("cpu", "cuda"):
+        ours = DecisionTreeClassifier(max_depth=3, device=device).fit(X, y)
+        assert ours.engine_ == device
+        assert ours.export_text() == theirs.export_text(), device
+        assert np.array_equal(ours.predict(X), theirs.predict(X))
+
+
+def test_wide_bins_on_the_gpu_match_the_reference(ref):
+    rng = np.random.default_rng(1)
+    n = 900
+    X = np.round(rng.normal(size=(n, 4)), 3)
+    X[:, 3] = rng.integers(0, 7, size=n)
+    y = (X[:, 0] - 0.7 * X[:, 2] > 0.05).astype(np.int64) + 2 * (X[:, 3] > 3)
+    theirs = ref.DecisionTreeClassifier(max_depth=4).fit(X, y)
+    ours = DecisionTreeClassifier(max_depth=4, device="cuda", max_bins=2048).fit(X, y)
+    assert ours.engine_ == "cuda"
+    assert ours.export_text() == theirs.export_text()
+    assert np.array_equal(ours.predict(X), theirs.predict(X))

@@ -222,3 +222,29 @@ def test_unusual_parameter_values_act_like_the_reference(ref, kw):
     X = rng.integers(0, 5, size=(40, 3)).astype(float)
     y = rng.integers(0, 3, size=40)
     assert DecisionTreeClassifier(device="cpu", **kw).fit(X, y).export_text() == ref.DecisionTreeClassifier(**kw).fit(X, y).export_text()
+
+
+def test_wide_bins_keep_the_search_exact_beyond_256_distinct_values(ref):
+    """``max_bins > 256``: every distinct value stays a candidate (reference ``:73``) through virtual one-byte
+    columns (``BinMapper.expand_wide``); the default 256 quantile bins cannot reproduce the reference here."""
+    rng = np.random.default_rng(0)
+    n = 700
+    X = np.round(rng.normal(size=(n, 3)), 3)  # ~700 distinct values in two columns
+    X[:, 2] = rng.integers(0, 5, size=n)
+    y = (X[:, 0] + 0.5 * X[:, 1] > 0.1).astype(np.int64) + (X[:, 2] > 2)
+    theirs = ref.DecisionTreeClassifier(max_depth=4).fit(X, y)
+    ours = DecisionTreeClassifier(max_depth=4, device="cpu", max_bins=1024).fit(X, y)
+    assert ours.export_text() == theirs.export_text()
+    assert np.array_equal(ours.predict(X), theirs.predict(X))
+    coarse = DecisionTreeClassifier(max_depth=4, device="cpu").fit(X, y)
+    assert coarse.export_text() != theirs.export_text()  # (what the wide mode is for)
+    # thread ranks with row shards agree with the serial fit
+    from mpitree_b200.parallel.comm import run_threaded
+    from mpitree_b200.tree import ParallelDecisionTreeClassifier
+
+    def work(comm):
+        lo, hi = n * comm.rank // comm.size, n * (comm.rank + 1) // comm.size
+        clf = ParallelDecisionTreeClassifier(max_depth=4, device="cpu", max_bins=1024, data_layout="sharded", comm=comm)
+        return clf.fit(X[lo:hi], y[lo:hi]).export_text()
+
+    assert set(run_threaded(3, work)) == {theirs.export_text()}

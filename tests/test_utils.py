@@ -401,3 +401,41 @@ def test_multi_rank_builder_wiring_dry_run(monkeypatch):
             assert regions[-1].nbytes == b.h_cap * b.slab_words * 4
         else:
             assert not b.nvls and list(b.ctx.mc_hist) == [0, 0]
+
+
+def test_sampled_edges_are_repaired_when_the_sample_missed_a_value():
+    """Edges fitted on a strided sample: a rare value of a low-cardinality column that the sample did not see
+    must get its own bin (otherwise it silently shares the next edge's bin and the search is no longer the
+    exact search the documentation promises for columns with at most ``max_bins`` distinct values)."""
+    import torch
+
+    from mpitree_b200.ops import cuda_engine as ce
+    from mpitree_b200.ops.binning import BinMapper
+
+    rng = np.random.default_rng(0)
+    n = ce.SAMPLE_ROWS * 2 + 11
+    X = rng.normal(size=(n, 3)).astype(np.float32)
+    X[:, 1] = rng.integers(0, 5, size=n)
+    idx = ce._sample_rows(n)
+    missed = int(np.setdiff1d(np.arange(n), idx)[1000])
+    X[missed, 1] = 77.0
+    X[:, 2] = rng.integers(0, 1000, size=n)  # more distinct values than bins: stays quantile-binned
+    mapper = BinMapper.fit(X[idx], max_bins=256)
+    assert list(mapper.edges[1]) == [0, 1, 2, 3, 4]
+    changed = ce._repair_sampled_edges(torch.from_numpy(X), mapper, 256)
+    assert changed == 1 and list(mapper.edges[1]) == [0, 1, 2, 3, 4, 77] and mapper.lossless[1]
+    assert len(mapper.edges[2]) == 256 and not mapper.lossless[2]
+    # the whole front end: the host mapper of a large input finds the stray value too
+    m2 = ce._fit_mapper_numpy(X, 256)
+    assert 77.0 in m2.edges[1]
+    # thread ranks: only one shard holds the stray value, every rank must end with the same edges
+    from mpitree_b200.parallel.comm import run_threaded
+
+    cuts = [0, n // 3, n]
+
+    def work(comm):
+        lo, hi = cuts[comm.rank], cuts[comm.rank + 1]
+        return [e.tolist() for e in ce._fit_mapper_numpy(X[lo:hi], 256, comm).edges]
+
+    got = run_threaded(2, work)
+    assert got[0] == got[1] and 77.0 in got[0][1]
