@@ -686,7 +686,7 @@ class TreeBuilder:
     def _check_peers(self) -> None:
         """Raise when an in-kernel peer barrier gave up (``scalars[7]``, see ``peer_barrier`` in csrc/build.cu)."""
         if self.reduce == "p2p" and int(self._host_scal[7]) != 0:
-            clear_caches()  # flags, epochs and abort words of the cached regions are no longer in step
+            clear_caches(collective=False)  # flags, epochs and abort words of the cached regions are no longer in step
             raise RuntimeError(
                 f"rank {self.rank}: a peer did not reach an in-kernel barrier within "
                 f"{self.ctx.barrier_timeout_ns / 1e9:.0f} s (a rank failed or is far behind); the fit was abandoned"
@@ -933,14 +933,20 @@ def _get_builder(key, data: DeviceDataset, make):
     return b
 
 
-def clear_caches() -> None:
-    """Drop cached builders, peer regions and workspaces (frees their device memory)."""
+def clear_caches(*, collective: bool = True) -> None:
+    """Drop cached builders, peer regions and workspaces (frees their device memory).
+
+    ``collective=False``: do not synchronise with the peers while closing the regions (used after a
+    peer failed)."""
     for b in _BUILDERS.values():
         b.close()
     _BUILDERS.clear()
     _WORKSPACE.clear()
     for reg in _REGIONS.values():
-        reg.close()
+        try:
+            reg.close(collective=collective)
+        except TypeError:  # regions without a collective close
+            reg.close()
     _REGIONS.clear()
 
 

@@ -92,7 +92,9 @@ class IpcRegion:
         comm.barrier()  # everyone has mapped everyone before any kernel writes to a peer
         self._comm = comm
 
-    def close(self) -> None:
+    def close(self, *, collective: bool = True) -> None:
+        """Unmap the peers and free the own region.  ``collective=False`` skips the barrier: the way out
+        after a peer failed (nobody will answer, and nothing that still runs writes here)."""
         from ..ops import _lib as L
 
         lib = L.load()
@@ -100,7 +102,8 @@ class IpcRegion:
             import torch
 
             torch.cuda.synchronize()
-            self._comm.barrier()  # no peer may still be writing into a region that goes away
+            if collective:
+                self._comm.barrier()  # no peer may still be writing into a region that goes away
         except Exception:  # pragma: no cover
             pass
         for p in self._opened:

@@ -106,3 +106,65 @@ def test_real_ranks_p2p_and_nccl(tmp_path):
     res = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=600)
     assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
     assert f"MULTIGPU_OK {world}" in res.stdout
+
+
+_FAILURE_WORKER = r"""
+import os, sys, time
+sys.path.insert(0, os.environ["REPO"])
+import numpy as np, torch, torch.distributed as dist
+from mpitree_b200.ops import cuda_engine
+from mpitree_b200.ops.cpu_engine import SplitParams
+from mpitree_b200.parallel.comm import TorchComm, init_process_group_from_env
+assert init_process_group_from_env("nccl")
+rank, world = dist.get_rank(), dist.get_world_size()
+dev = torch.device("cuda", torch.cuda.current_device())
+g = torch.Generator(device=dev).manual_seed(rank)
+n = 200_000
+X = torch.randint(0, 256, (n, 32), dtype=torch.uint8, device=dev, generator=g)
+y = ((X[:, 0] > 100) ^ (X[:, 5] > 30)).to(torch.uint8)
+data = cuda_engine.DeviceDataset.allocate(n, 32, 2, dev)
+data.encode_u8(X); data.set_labels(y)
+b = cuda_engine.TreeBuilder(data, 256, SplitParams(max_depth=6), comm=TorchComm(), n_global=n * world)
+first = b.build()                       # every rank takes part: works
+assert first.n_nodes > 3
+dist.barrier()
+torch.cuda.synchronize()
+if rank == world - 1:
+    # this rank "fails": it never launches the next fit's kernels
+    time.sleep(float(os.environ["MTB_BARRIER_TIMEOUT_S"]) + 4.0)
+    print("SILENT_RANK_DONE", flush=True)
+    os._exit(0)
+data.cur = 0
+data.encode_u8(X); data.set_labels(y)
+t0 = time.time()
+try:
+    b.build()
+    print("NO_ERROR", rank, flush=True)
+except RuntimeError as exc:
+    took = time.time() - t0
+    assert "did not reach an in-kernel barrier" in str(exc), exc
+    print(f"RAISED rank={rank} after {took:.2f}s", flush=True)
+    assert took < float(os.environ["MTB_BARRIER_TIMEOUT_S"]) + 3.0, took
+os._exit(0)
+"""
+
+
+@pytest.mark.multigpu
+def test_a_missing_rank_makes_the_others_raise_instead_of_hanging(tmp_path):
+    """The reference deadlocks in ``allgather`` when one rank fails (decision_tree.py:456).  Here the level
+    kernels of the surviving ranks give up at their peer barrier after ``MTB_BARRIER_TIMEOUT_S`` and the
+    host raises on every one of them."""
+    import torch
+
+    world = min(torch.cuda.device_count(), 4)
+    if world < 2:
+        pytest.skip("needs at least two GPUs")
+    script = tmp_path / "failure_worker.py"
+    script.write_text(_FAILURE_WORKER)
+    env = dict(os.environ, REPO=os.path.dirname(os.path.dirname(os.path.abspath(__file__))), MTB_BARRIER_TIMEOUT_S="2")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
+           "--master-addr", "127.0.0.1", "--master-port", "29637", str(script)]
+    res = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=120)
+    out = res.stdout + res.stderr
+    assert out.count("RAISED rank=") == world - 1, out[-3000:]
+    assert "NO_ERROR" not in out
