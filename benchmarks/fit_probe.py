@@ -19,6 +19,7 @@ def main():
     ap.add_argument("--unfused", action="store_true")
     ap.add_argument("--informative", type=int, default=8)
     ap.add_argument("--reduce", default="auto")
+    ap.add_argument("--root-cluster", action="store_true", help="hand the builder raw row-major bytes (k_root_cluster)")
     a = ap.parse_args()
     import os
     world, rank = int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("RANK", "0"))
@@ -44,11 +45,14 @@ def main():
     out = []
     for rep in range(a.reps):
         data.cur = 0
-        data.encode_u8(X)
-        data.set_labels(y)
+        if not a.root_cluster:
+            data.encode_u8(X)
+            data.set_labels(y)
         torch.cuda.synchronize()
         b = cuda_engine.TreeBuilder(data, 256, params, fused=not a.unfused, profile=True, comm=comm,
                                     n_global=a.rows * world, reduce=a.reduce)
+        if a.root_cluster:  # retile + labels + root histogram inside the timed build (one cluster kernel)
+            b.root_input = (X, y)
         t0 = time.perf_counter()
         s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         s.record()

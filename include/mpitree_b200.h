@@ -142,6 +142,9 @@ typedef struct MtbCtx {
    * gives up, sets scalars[7] and raises the abort word (u32 index MTB_MAX_WORLD of every rank's flag
    * block), after which all barriers of the fit fall through.  0 = wait for ever.                */
   int64_t barrier_timeout_ns;
+  /* depth 0 only: the root slab already holds the root histogram (mtb_root_retile_hist ran), so
+   * mtb_level_fused skips its zeroing and histogram phase.                                        */
+  int64_t root_hist_done;
 } MtbCtx;
 
 const char* mtb_last_error(void);
@@ -182,6 +185,13 @@ int mtb_level_fused2(const MtbCtx* parents, const MtbCtx* children, void* stream
 /* One cooperative launch doing plan + hist + (peer push + barriers) + gain + finalize.  Zeroes the
  * slabs it accumulates into itself (no host-side fill), and the next level's when ctx->zero_next. */
 int mtb_level_fused(const MtbCtx* ctx, void* stream);
+/* uint8 rows in the user's row-major layout ([n][ldx], ldx == F == 32 / 64 / 128, 16-byte aligned, memory
+ * of the current GPU) -> feature-group planes + labels + root histogram in ONE pass, by clusters of F/16
+ * CTAs that share each row tile through a multicast TMA copy.  ctx: codes / labels / hist / cur / hcur /
+ * n_cap / F / G / B / C / FT == 16 / tile_layout == 1 must be set.  Returns 0 when launched, 1 when the
+ * shape or the pointers do not qualify (nothing was launched: encode and count the usual way), < 0 on a
+ * CUDA error.  Follow with mtb_level_fused(ctx with root_hist_done = 1).                             */
+int mtb_root_retile_hist(const MtbCtx* ctx, const void* X, int64_t ldx, int64_t n, const void* y, void* stream);
 /* Test hook: out[i] = k[i] * log2(k[i]) by the device function of the gain phase (table = ctx.klogk). */
 int mtb_klogk_eval(const uint32_t* k, double* out, int64_t n, const double* table, void* stream);
 /* Shared memory / launch geometry the hist phase will use for this ctx (for reports). */

@@ -29,6 +29,8 @@
 //             grow down from its end)
 //   commit    row segments of the next frontier from the partition cursors
 #include <cooperative_groups.h>
+#include <cuda.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 #include "impurity.cuh"
@@ -394,10 +396,10 @@ __device__ void hist_phase(const MtbCtx& ctx, uint8_t* smem) {
       if (r_a < nrows) lab_a = labels[cur.row0 + r_a];
       if (r_b < nrows) lab_b = labels[cur.row0 + r_b];
       mbar_wait(&full[st], ph);
-      const uint4* rows = reinterpret_cast<const uint4*>(stage_base + (size_t)st * kStageBytes);
+      const uint32_t rows = smem_u32(stage_base) + (uint32_t)st * kStageBytes;  // (explicit shared-space loads: see lds_u4)
       uint4 va = make_uint4(0, 0, 0, 0), vb = va;
-      if (r_a < nrows) va = rows[r_a];
-      if (r_b < nrows) vb = rows[r_b];
+      if (r_a < nrows) va = lds_u4(rows + 16 * r_a);
+      if (r_b < nrows) vb = lds_u4(rows + 16 * r_b);
       __syncwarp();
       if (lane_id() == 0) mbar_arrive(&empty[st]);  // tile is in registers: release the stage
       if constexpr (IL) {
@@ -1513,18 +1515,18 @@ __device__ void move_hist_phase(const MtbCtx& P, const MtbCtx& C, uint8_t* smem,
     const int ra = w * 64 + lane, rb = ra + 32;
     const bool va_ok = ra < cur.nrows, vb_ok = rb < cur.nrows;
     mbar_wait(&avail[ring.st], ring.ph);
-    const uint8_t* sbuf = ms.stage_base + (size_t)ring.st * kStage2Bytes;
-    const uint4* rows = reinterpret_cast<const uint4*>(sbuf);
-    const uint8_t* slab = sbuf + kStageBytes + ((uint32_t)cur.row0 & 15u);
-    const uint32_t* rec = reinterpret_cast<const uint32_t*>(sbuf + kStageBytes + kLabelStage);
+    // (explicit shared-space loads: see lds_u4)
+    const uint32_t sbuf = smem_u32(ms.stage_base) + (uint32_t)ring.st * kStage2Bytes;
+    const uint32_t slab = sbuf + kStageBytes + ((uint32_t)cur.row0 & 15u);
+    const uint32_t rec = sbuf + kStageBytes + kLabelStage;
     // rank rows from the unit's "goes left" bits
-    const uint32_t w0 = rec[2 * w], w1 = rec[2 * w + 1];
-    const uint32_t before0 = rec[32 + 2 * w];  // lefts before word 2w
-    const uint32_t base_l = rec[64], base_r = rec[65];
+    const uint32_t w0 = lds_u32(rec + 8 * w), w1 = lds_u32(rec + 8 * w + 4);
+    const uint32_t before0 = lds_u32(rec + 4 * (32 + 2 * w));  // lefts before word 2w
+    const uint32_t base_l = lds_u32(rec + 4 * 64), base_r = lds_u32(rec + 4 * 65);
     uint4 xa = make_uint4(0, 0, 0, 0), xb = xa;
     uint32_t lab_a = 0, lab_b = 0;
-    if (va_ok) { xa = rows[ra]; lab_a = slab[ra]; }
-    if (vb_ok) { xb = rows[rb]; lab_b = slab[rb]; }
+    if (va_ok) { xa = lds_u4(sbuf + 16 * ra); lab_a = lds_u8(slab + ra); }
+    if (vb_ok) { xb = lds_u4(sbuf + 16 * rb); lab_b = lds_u8(slab + rb); }
     __syncwarp();
     if (lane == 0) mbar_arrive(&ms.empty[ring.st]);
     const uint32_t below = (1u << lane) - 1u;
@@ -1603,6 +1605,219 @@ __device__ void zero_next_level(const MtbCtx& ctx, int n_slots) {
   zero_slabs(ptr_of<uint32_t>(ctx.hist[ctx.hcur ^ 1]), v.slab_words(), (int)n);
 }
 
+// Interleaved tile with two 16-bit counters per word (cells 2i and 2i+1 share word i): half the
+// shared memory of the 32-bit tile, which the root cluster kernel turns into row stages.  The caller
+// flushes before any counter can pass 65,535.
+__device__ __forceinline__ void tile_count_il16(uint32_t* tile, uint4 x, uint32_t lab, int B, int lane) {
+  const int rot = lane & 15;
+  uint32_t w0 = x.x, w1 = x.y, w2 = x.z, w3 = x.w;
+  if (rot & 4) { const uint32_t t = w0; w0 = w1; w1 = w2; w2 = w3; w3 = t; }
+  if (rot & 8) { uint32_t t = w0; w0 = w2; w2 = t; t = w1; w1 = w3; w3 = t; }
+  const uint32_t sel = 0x3210u + 0x1111u * (uint32_t)(rot & 3);
+  const uint4 y = make_uint4(__byte_perm(w0, w1, sel), __byte_perm(w1, w2, sel), __byte_perm(w2, w3, sel),
+                             __byte_perm(w3, w0, sel));  // byte k of y = byte (k + rot) mod 16 of x
+  const uint32_t row_base = smem_u32(tile) + lab * (uint32_t)(B / 2) * 64u;  // cell = lab * B + code, word = cell >> 1
+  const uint32_t yw[4] = {y.x, y.y, y.z, y.w};
+#pragma unroll
+  for (int k = 0; k < 16; ++k) {
+    const uint32_t code = __byte_perm(yw[k >> 2], 0u, 0x4440u | (uint32_t)(k & 3));
+    const uint32_t addr = (code >> 1) * 64u + (row_base + (uint32_t)(((k + rot) & 15) * 4));
+    const uint32_t one = 1u << ((code & 1u) * 16u);
+    asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(addr), "r"(one) : "memory");
+  }
+}
+
+// Merge (and clear) the packed tile of feature group `g` into slot 0's slab with red.global.add.
+__device__ void flush_tile_il16(const MtbCtx& ctx, uint32_t* tile, int g, int tid) {
+  View v(ctx);
+  const int BC = (int)ctx.B * (int)ctx.C;
+  uint32_t* dst = v.hist_cur() + (int64_t)g * 16 * BC;
+  const int lane = tid & 31, w = tid >> 5;
+  const int q = lane & 3, r = lane >> 2;
+  const uint4 zero = make_uint4(0, 0, 0, 0);
+  for (int c0 = w * 32; c0 < BC / 2; c0 += kConsumerWarps * 32) {  // word (= cell pair) index
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int pair = c0 + r + 8 * i;
+      if (pair < BC / 2) {
+        uint4* src = reinterpret_cast<uint4*>(tile + pair * 16 + 4 * q);
+        const uint4 x = *src;
+        *src = zero;
+        const uint32_t e[4] = {x.x, x.y, x.z, x.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          uint32_t* d = dst + (int64_t)(4 * q + j) * BC + 2 * pair;
+          if (e[j] & 0xffffu) red_add_u32(d, e[j] & 0xffffu);
+          if (e[j] >> 16) red_add_u32(d + 1, e[j] >> 16);
+        }
+      }
+    }
+  }
+}
+
+// ------------------------------------------------------ root level from row-major bytes (cluster)
+// The first touch of a uint8 data set: rows arrive row-major ([n][16 G] bytes, the user's layout) and
+// have to become feature-group planes, labels have to be copied, and the root histogram has to be
+// counted.  As three passes (retile kernel, label copy, root histogram) that is 6.4 + 6.4 + 6.4 GB of
+// traffic for 100M x 64; here it is one pass, 6.4 GB in and 6.4 GB out, run by thread-block clusters
+// of G CTAs:
+//   * a unit is 256 whole rows (256 x 16 G bytes, contiguous).  It is loaded ONCE per cluster, by TMA
+//     bulk copies that are multicast into the same stage of all G CTAs (the source is this GPU's own
+//     memory, see tma_load_1d_multicast);
+//   * CTA g of the cluster owns feature group g: its consumers take bytes [16 g, 16 g + 16) of every
+//     row from the shared tile, store them into plane g (one 128-bit store per row, coalesced), and
+//     count them into the CTA's [C*B][16] histogram tile; CTA 0 also writes the labels;
+//   * two consumer groups of eight warps alternate units, so stores and shared-memory atomics of
+//     consecutive units overlap;
+//   * a stage holds the same bytes in all G CTAs, so the bytes a cluster has in flight are bounded by
+//     ONE CTA's spare shared memory: with the 32-bit tile (160 KB at 256 bins x 10 classes) only four
+//     16 KB stages fit and the kernel was latency-bound at 11 ms for 100M x 64.  The tile therefore
+//     packs two 16-bit counters per word (80 KB, nine stages) and is merged into the slab every 240
+//     units, before any counter can overflow;
+//   * stage hand-shake: a CTA's producer thread waits until its own consumers have released the
+//     stage, arms its own `full` barrier with the unit's byte count and arrives on the leader's `go`
+//     barrier; the leader issues the multicast copy once all G CTAs have done so.  The copy is the
+//     tiled (tensor-map) form: the untiled cp.async.bulk with .multicast::cluster was measured at
+//     ~0.34 us + 0.043 us/KB per operation, serialised across the cluster (23 GB/s per cluster).
+// The tiles are merged into the root slab with red.global.add at the end (the entry point zeroes the
+// slab first).  mtb_level_fused then runs with ctx.root_hist_done set and skips its histogram phase.
+constexpr int kRootRows = 256;
+constexpr int kRootGroupWarps = 8;
+
+struct RootArgs {
+  const uint8_t* X;   // [n][ldx] row-major bytes, ldx == 16 * G, 16-byte aligned, this GPU's memory
+  const uint8_t* y;   // [n] labels (class codes)
+  int64_t n;
+  int multicast;      // 1: the leader loads each unit once for the whole cluster; 0: every CTA loads it itself (experiment)
+};
+
+struct RootSmem {
+  uint32_t* tile;
+  uint8_t* stage_base;
+  uint64_t *full, *empty, *go;
+  int stages, stage_bytes;
+};
+
+__host__ __device__ inline int root_stage_bytes(int G) { return kRootRows * 16 * G; }
+constexpr int kRootMaxStages = 12;
+constexpr int kRootFlushUnits = 240;  // 240 x 256 rows < 65,536: no 16-bit counter can overflow between flushes
+__host__ __device__ inline int root_tile_bytes(int B, int C) { return 16 * B * C * 2; }  // two counters per word
+__host__ __device__ inline int root_stages(int B, int C, int G) {
+  int st = (kSmemBudget - root_tile_bytes(B, C) - 512) / root_stage_bytes(G);
+  return st > kRootMaxStages ? kRootMaxStages : st;
+}
+
+__device__ __forceinline__ RootSmem root_smem(uint8_t* smem, int B, int C, int G) {
+  RootSmem m;
+  m.tile = reinterpret_cast<uint32_t*>(smem);
+  m.stage_bytes = root_stage_bytes(G);
+  m.stages = root_stages(B, C, G);
+  m.stage_base = smem + (size_t)root_tile_bytes(B, C);
+  m.full = reinterpret_cast<uint64_t*>(m.stage_base + (size_t)m.stages * m.stage_bytes);
+  m.empty = m.full + kRootMaxStages;
+  m.go = m.empty + kRootMaxStages;
+  return m;
+}
+
+__global__ void __launch_bounds__(kHistThreads, 1) k_root_cluster(const __grid_constant__ MtbCtx ctx, const RootArgs a,
+                                                                  const __grid_constant__ CUtensorMap tmap) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  const int B = (int)ctx.B, C = (int)ctx.C, G = (int)ctx.G;
+  const RootSmem ms = root_smem(smem, B, C, G);
+  const int tid = threadIdx.x;
+  const uint32_t crank = cluster_ctarank();  // == feature group of this CTA
+  const int n_clusters = gridDim.x / G, cluster_id = blockIdx.x / G;
+  const int64_t units = (a.n + kRootRows - 1) / kRootRows;
+  const int64_t u0 = units * cluster_id / n_clusters, u1 = units * (cluster_id + 1) / n_clusters;
+  if (tid == 0) {
+    for (int i = 0; i < ms.stages; ++i) {
+      mbar_init(&ms.full[i], 1);
+      mbar_init(&ms.empty[i], kRootGroupWarps);
+      mbar_init(&ms.go[i], (uint32_t)G);
+    }
+    fence_barrier_init();
+  }
+  for (int i = tid; i < 8 * B * C; i += blockDim.x) ms.tile[i] = 0;
+  __syncthreads();
+  cluster_sync_all();  // every CTA's barriers exist before anybody arrives on them remotely
+
+  if (tid >= kConsumers) {
+    // ===== producer thread of this CTA =====
+    if (tid == kConsumers) {
+      int st = 0;
+      uint32_t ph = 0;
+      for (int64_t u = u0; u < u1; ++u) {
+        const int64_t row0 = u * kRootRows;
+        uint32_t bytes = (uint32_t)min((int64_t)kRootRows, a.n - row0) * 16u * (uint32_t)G;
+        if (a.multicast) bytes = (uint32_t)ms.stage_bytes;  // the tiled copy always delivers the whole box
+        mbar_wait(&ms.empty[st], ph ^ 1);                // own consumers are done with the stage
+        mbar_arrive_expect_tx(&ms.full[st], bytes);      // armed for the unit's bytes
+        if (!a.multicast) {
+          tma_load_1d(ms.stage_base + (size_t)st * ms.stage_bytes, a.X + row0 * 16 * G, bytes, &ms.full[st]);
+          if (++st == ms.stages) { st = 0; ph ^= 1; }
+          continue;
+        }
+        mbar_arrive_cluster(&ms.go[st], 0);              // tell the leader
+        if (crank == 0) {
+          mbar_wait_cluster(&ms.go[st], ph);             // all G CTAs are ready to receive
+          // one tiled copy of the unit (a 16 G x 256 box of the [n][16 G] byte matrix), multicast to the
+          // cluster; rows past the end arrive as zeros, so the byte count is always the full box
+          tma_load_2d_multicast(ms.stage_base + (size_t)st * ms.stage_bytes, &tmap, 0, (int)row0, &ms.full[st],
+                                (uint16_t)((1u << G) - 1u));
+        }
+        if (++st == ms.stages) { st = 0; ph ^= 1; }
+      }
+    }
+  } else {
+    // ===== consumers: group `grp` takes the units u0 + grp, u0 + grp + 2, ... =====
+    const int lane = tid & 31, w = tid >> 5;
+    const int grp = w / kRootGroupWarps, r = (w % kRootGroupWarps) * 32 + lane;  // row of the unit
+    uint4* plane = reinterpret_cast<uint4*>(ptr_of<uint8_t>(ctx.codes[ctx.cur])) + (int64_t)crank * ctx.n_cap;
+    uint8_t* lab_out = ptr_of<uint8_t>(ctx.labels[ctx.cur]);
+    int st = grp % ms.stages;
+    uint32_t ph = (uint32_t)(grp / ms.stages) & 1u;
+    int64_t next_flush = u0 + kRootFlushUnits;
+    // labels come straight from global memory, one unit ahead (a unit is short: the load's latency
+    // would otherwise be paid once per unit)
+    uint32_t lab_next = 0;
+    if (u0 + grp < u1 && (u0 + grp) * kRootRows + r < a.n) lab_next = a.y[(u0 + grp) * kRootRows + r];
+    for (int64_t u = u0 + grp; u < u1; u += 2) {
+      if (u >= next_flush) {  // both groups pass every flush point, each before its first unit beyond it
+        named_bar_sync(1, kConsumers);
+        flush_tile_il16(ctx, ms.tile, (int)crank, tid);
+        named_bar_sync(1, kConsumers);
+        next_flush += kRootFlushUnits;
+      }
+      const int64_t row = u * kRootRows + r;
+      const bool ok = row < a.n;
+      const uint32_t lab = lab_next;
+      if (u + 2 < u1 && row + 2 * kRootRows < a.n) lab_next = a.y[row + 2 * kRootRows];
+      mbar_wait(&ms.full[st], ph);
+      uint4 x = make_uint4(0, 0, 0, 0);
+      if (ok) x = lds_u4(smem_u32(ms.stage_base) + (uint32_t)(st * ms.stage_bytes + r * 16 * G + 16 * (int)crank));
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&ms.empty[st]);  // the tile's bytes are in registers: release the stage
+      if (ok) {
+        st_na_u4(plane + row, x);
+        if (crank == 0) lab_out[row] = (uint8_t)lab;
+        tile_count_il16(ms.tile, x, lab, B, lane);
+      }
+      // two units further on: the ring position advances by two stages
+      st += 2;
+      if (st >= ms.stages) { st -= ms.stages; ph ^= 1; }
+    }
+    // flush points this group did not reach because its units ran out (the other group may have)
+    for (; next_flush < u1; next_flush += kRootFlushUnits) {
+      named_bar_sync(1, kConsumers);
+      flush_tile_il16(ctx, ms.tile, (int)crank, tid);
+      named_bar_sync(1, kConsumers);
+    }
+    named_bar_sync(1, kConsumers);
+    flush_tile_il16(ctx, ms.tile, (int)crank, tid);
+  }
+  cluster_sync_all();  // nobody leaves while a peer may still multicast into it or arrive on its barriers
+}
+
 // Everything after a level's histograms are complete on this rank (the caller has synchronised the
 // grid): [push partial slabs to the owners, peer barrier,] gain on the owned features (records go to
 // every rank's mailbox), [peer barrier | grid sync,] finalize on CTA 0 while the others zero the
@@ -1641,14 +1856,17 @@ __global__ void __launch_bounds__(kFusedThreads, 1) k_level_fused(const __grid_c
   if (ctx.depth > 0 && ptr_of<const int>(ctx.scalars)[0] == 0) return;
   stamp(ctx, 0);
   if (blockIdx.x == 0) plan_phase(ctx, smem_warp);
-  {  // the slabs this level accumulates into start at zero (shared tiles are merged with red.add)
+  const bool have_hist = ctx.depth == 0 && ctx.root_hist_done != 0;  // counted by k_root_cluster
+  if (!have_hist) {  // the slabs this level accumulates into start at zero (shared tiles are merged with red.add)
     View v(ctx);
     zero_slabs(v.hist_cur(), v.slab_words(), ctx.depth == 0 ? 1 : v.n_slots());
   }
   grid.sync();
   stamp(ctx, 1);
-  hist_phase<FT, IL>(ctx, smem);
-  grid.sync();
+  if (!have_hist) {
+    hist_phase<FT, IL>(ctx, smem);
+    grid.sync();
+  }
   search_tail<NV>(ctx, grid, smem, smem_bytes, smem_warp, ptr_of<const int>(ctx.scalars)[0], ctx.zero_next != 0, false);
 }
 
@@ -1905,6 +2123,84 @@ extern "C" int mtb_level_fused2(const MtbCtx* parents, const MtbCtx* children, v
     return -2;
   }
   FT_SWITCH((int)parents->FT, launch_fused2, parents, children, smem, (cudaStream_t)stream);
+}
+
+/* Root level of a uint8 data set in one pass: row-major bytes -> feature-group planes + labels + root
+ * histogram (k_root_cluster).  Returns 1 (nothing launched) when the shape or the pointers do not qualify:
+ * the caller then encodes and counts the usual way.                                              */
+extern "C" int mtb_root_retile_hist(const MtbCtx* ctx, const void* X, int64_t ldx, int64_t n, const void* y, void* stream) {
+  const int G = (int)ctx->G, B = (int)ctx->B, C = (int)ctx->C;
+  if (!(G == 2 || G == 4 || G == 8) || ctx->F != 16 * G || ldx != 16 * G || ctx->FT != 16 || ctx->tile_layout != 1) return 1;
+  if ((reinterpret_cast<uintptr_t>(X) & 15u) != 0 || n <= 0 || n > ctx->n_cap) return 1;
+  if (root_stages(B, C, G) < 2) return 1;
+  // the multicast copy must read this GPU's own memory (see tma_load_1d_multicast)
+  int dev = -1;
+  cudaPointerAttributes attr;
+  if (cudaGetDevice(&dev) != cudaSuccess || cudaPointerGetAttributes(&attr, X) != cudaSuccess ||
+      attr.type != cudaMemoryTypeDevice || attr.device != dev) {
+    cudaGetLastError();
+    return 1;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  const int smem = root_tile_bytes(B, C) + root_stages(B, C, G) * root_stage_bytes(G) + 512;
+  MTB_CHECK(cudaFuncSetAttribute(k_root_cluster, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  MTB_CHECK(cudaMemsetAsync(ptr_of<void>(ctx->hist[ctx->hcur]), 0, (size_t)ctx->G * 16 * B * C * 4, st));
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)((sm_count() / G) * G));
+  cfg.blockDim = dim3(kHistThreads);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = (unsigned)G;
+  at[0].val.clusterDim.y = 1;
+  at[0].val.clusterDim.z = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  // one wave: as many clusters as can be resident at once (a cluster needs G SMs of one GPC)
+  static int max_clusters[9] = {0};
+  if (!max_clusters[G]) {
+    int nc = 0;
+    if (cudaOccupancyMaxActiveClusters(&nc, k_root_cluster, &cfg) != cudaSuccess || nc < 1) {
+      cudaGetLastError();
+      nc = sm_count() / G;
+    }
+    max_clusters[G] = nc;
+  }
+  if ((unsigned)(max_clusters[G] * G) < cfg.gridDim.x) cfg.gridDim = dim3((unsigned)(max_clusters[G] * G));
+  // tensor map of the row-major byte matrix: [n][16 G] uint8, box = 16 G x 256 rows
+  typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                               const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                               CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+  static EncodeFn encode = nullptr;
+  if (!encode) {
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres) != cudaSuccess || !fn) {
+      cudaGetLastError();
+      return 1;
+    }
+    encode = (EncodeFn)fn;
+  }
+  CUtensorMap tmap;
+  {
+    const cuuint64_t gdim[2] = {(cuuint64_t)(16 * G), (cuuint64_t)n};
+    const cuuint64_t gstride[1] = {(cuuint64_t)(16 * G)};
+    const cuuint32_t box[2] = {(cuuint32_t)(16 * G), (cuuint32_t)kRootRows};
+    const cuuint32_t estride[2] = {1, 1};
+    if (encode(&tmap, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void*>(X), gdim, gstride, box, estride,
+               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+      return 1;
+  }
+  static int multicast = -1;
+  if (multicast < 0) {
+    const char* e = getenv("MTB_ROOT_MULTICAST");
+    multicast = (e && e[0] == '0') ? 0 : 1;
+  }
+  RootArgs a{reinterpret_cast<const uint8_t*>(X), reinterpret_cast<const uint8_t*>(y), n, multicast};
+  MTB_CHECK(cudaLaunchKernelEx(&cfg, k_root_cluster, *ctx, a, tmap));
+  return 0;
 }
 
 /* Test hook: out[i] = g(k[i]) = k log2 k evaluated by the device function the gain phase uses

@@ -53,7 +53,7 @@ class MtbCtx(ctypes.Structure):
         + [("rstore", ctypes.c_int64 * 2)]
         + [(n, ctypes.c_int64) for n in
            "small_rows ho_cap ho_node ho_begin ho_end ho_side part_child mask_words zero_next tile_layout".split()]
-        + [("mc_hist", ctypes.c_int64 * 2), ("barrier_timeout_ns", ctypes.c_int64)]
+        + [("mc_hist", ctypes.c_int64 * 2), ("barrier_timeout_ns", ctypes.c_int64), ("root_hist_done", ctypes.c_int64)]
     )
 
 

@@ -653,6 +653,8 @@ class TreeBuilder:
             if self.reduce == "p2p":
                 self.ctx.epoch = _EPOCH["next"]
                 _EPOCH["next"] += 2
+            if self.depth == 0:
+                self._root_pass()
             if self.fuse_partition and self._ctx_prev is not None:
                 # partition of the previous level's rows + this level's histograms + search, one launch
                 _call("mtb_level_fused2", ctypes.byref(self._ctx_prev), ctypes.byref(self.ctx), _stream_ptr())
@@ -668,6 +670,29 @@ class TreeBuilder:
                 dist.all_reduce(self.hist[self.hcur][: self.n_slots * self.slab_words])
             self._launch("mtb_level_gain")
             self._launch("mtb_level_finalize")
+
+    def _root_pass(self) -> None:
+        """Depth 0 of a fit whose rows were handed over as raw row-major bytes (``root_input``): planes,
+        labels and the root histogram in one pass (``k_root_cluster``), or - when the shape does not
+        qualify - the usual retile + label copy, with the histogram left to the level kernel."""
+        self.ctx.root_hist_done = 0
+        src = getattr(self, "root_input", None)
+        if src is None:
+            return
+        self.root_input = None
+        X, y = src
+        rc = self.lib.mtb_root_retile_hist(
+            ctypes.byref(self.ctx), ctypes.c_void_p(_p(X)), ctypes.c_int64(X.stride(0)), ctypes.c_int64(X.shape[0]),
+            ctypes.c_void_p(_p(y)), _stream_ptr()) if X.shape[0] else 1
+        KERNEL_LAUNCHES["count"] += 1
+        if rc == 0:
+            self.ctx.root_hist_done = 1
+            self.stats.launches += 1
+            return
+        if rc < 0:
+            self.L.check(rc, "mtb_root_retile_hist")
+        self.data.encode_u8(X, None, 0)
+        self.data.set_labels(y)
 
     def read_level(self) -> int:
         self._host_scal.copy_(self.scalars, non_blocking=True)
@@ -1381,7 +1406,17 @@ def fit_from_torch(X, y, params: SplitParams, *, max_bins: int = 256, comm=None,
     st.mark("meta+mapper")
     data = DeviceDataset.allocate(n, F, len(classes), dev)
     st.mark("alloc")
-    if X.is_cuda:
+    # uint8 rows that already are bin codes, resident on this GPU, whole 16-feature groups: the builder's
+    # first launch can read them in the caller's row-major layout (planes + labels + root histogram in one
+    # pass by thread-block clusters, k_root_cluster) instead of a retile pass and a label copy here
+    root_input = None
+    if (X.is_cuda and X.device == dev and X.dtype == torch.uint8 and lut is None and F in (32, 64, 128) and X.stride(1) == 1
+            and X.stride(0) == F and y_codes.dtype == torch.uint8 and y_codes.is_contiguous() and y_codes.device == dev
+            and os.environ.get("MTB_ROOT_CLUSTER", "0") == "1"):  # opt-in: measured slower than the separate passes, see DESIGN.md
+        root_input = (X, y_codes)
+    if root_input is not None:
+        pass
+    elif X.is_cuda:
         (data.encode_u8(X, lut, 0) if X.dtype == torch.uint8 else data.encode_float(X, mapper, 0))
     elif dev.type != "cuda":  # driver tests without a GPU: the "device" is the host
         for r0 in range(0, n, ENCODE_CHUNK_ROWS):
@@ -1399,7 +1434,8 @@ def fit_from_torch(X, y, params: SplitParams, *, max_bins: int = 256, comm=None,
             main.wait_event(arrived)
             chunk.record_stream(main)
             (data.encode_u8(chunk, lut, r0) if X.dtype == torch.uint8 else data.encode_float(chunk, mapper, r0))
-    data.set_labels(y_codes)
+    if root_input is None:
+        data.set_labels(y_codes)
     st.mark("encode")
     _dist_group(comm)
     n_bins = int(mapper.n_bins.max())
@@ -1418,6 +1454,10 @@ def fit_from_torch(X, y, params: SplitParams, *, max_bins: int = 256, comm=None,
            os.environ.get("MTB_ASYNC"), os.environ.get("MTB_SMALL_ROWS"))
     cacheable = not kw.get("profile") and "peers" not in kw
     builder = _get_builder(key, data, make) if cacheable else make()
+    builder.root_input = root_input if builder._coop else None
+    if root_input is not None and builder.root_input is None:  # a launch decomposition without the root pass
+        data.encode_u8(X, lut, 0)
+        data.set_labels(y_codes)
     st.mark("builder_init")
     try:
         flat = builder.build()

@@ -276,3 +276,22 @@ def test_handoff_record_exchange_paths(tmp_path):
     res = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=600)
     assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
     assert f"RECORD_EXCHANGE_OK {world}" in res.stdout
+
+
+@pytest.mark.parametrize("F", [32, 64, 128])
+def test_root_cluster_pass_equals_separate_passes(monkeypatch, F):
+    """Opt-in root pass (MTB_ROOT_CLUSTER=1): thread-block clusters of F/16 CTAs share each row tile through a
+    multicast TMA copy and produce planes + labels + root histogram at once; same tree as retile + histogram."""
+    import torch
+
+    from mpitree_b200.tree import DecisionTreeClassifier
+
+    rng = np.random.default_rng(F)
+    trees = {}
+    for n in (999, 70_001, 300_000):
+        X = torch.from_numpy(rng.integers(0, 256, size=(n, F), dtype=np.uint8)).cuda()
+        y = ((X[:, 1] > 90).to(torch.uint8) + (X[:, F - 1] > 200).to(torch.uint8) + (X[:, 17] > 30).to(torch.uint8))
+        for flag in ("1", "0"):
+            monkeypatch.setenv("MTB_ROOT_CLUSTER", flag)
+            trees[flag] = DecisionTreeClassifier(max_depth=6, device="cuda").fit(X, y).flat_tree_
+        _same_tree(trees["1"], trees["0"])
