@@ -58,18 +58,20 @@ def main():
         iters = 200 if size <= (1 << 20) else (50 if size <= (32 << 20) else 10)
         y = x.clone()
         t_nccl = timed(lambda: dist.all_reduce(y), iters, dev)
-        t_one = timed(lambda: ar.launch(n, 0), iters, dev) if size <= (64 << 20) else float("nan")
+        t_one = timed(lambda: ar.launch(n, 0), iters, dev)
         t_two = timed(lambda: ar.launch(n, 1), iters, dev)
         t_nvls = timed(lambda: ar.launch(n, 2), iters, dev) if use_nvls else float("nan")
         bus = lambda ms: 2 * (world - 1) / world * size / (ms * 1e-3) / 1e9  # noqa: E731
-        rows.append({"bytes": size, "nccl_us": t_nccl * 1e3, "oneshot_us": t_one * 1e3, "twoshot_us": t_two * 1e3,
+        t_auto = timed(lambda: ar.launch(n, -1), iters, dev)
+        rows.append({"bytes": size, "auto_us": t_auto * 1e3, "nccl_us": t_nccl * 1e3, "oneshot_us": t_one * 1e3, "twoshot_us": t_two * 1e3,
                      "nccl_busbw_GBs": bus(t_nccl), "oneshot_busbw_GBs": bus(t_one), "twoshot_busbw_GBs": bus(t_two),
                      "nvls_us": t_nvls * 1e3, "nvls_busbw_GBs": bus(t_nvls), "correct": all(ok)})
         if rank == 0:
             r = rows[-1]
             print(f"{size:>10d} B  nccl {r['nccl_us']:9.1f} us  one-shot {r['oneshot_us']:9.1f} us  two-shot {r['twoshot_us']:9.1f} us"
                   f"  busbw nccl/1s/2s = {r['nccl_busbw_GBs']:7.1f} {r['oneshot_busbw_GBs']:7.1f} {r['twoshot_busbw_GBs']:7.1f} GB/s  ok={r['correct']}"
-                  + (f"  nvls {r['nvls_us']:9.1f} us {r['nvls_busbw_GBs']:7.1f} GB/s" if use_nvls else ""),
+                  + (f"  nvls {r['nvls_us']:9.1f} us {r['nvls_busbw_GBs']:7.1f} GB/s" if use_nvls else "")
+                  + f"  auto {r['auto_us']:9.1f} us ({'<=' if r['auto_us'] <= r['nccl_us'] else '>'} nccl)",
                   flush=True)
         size *= 4
     if rank == 0:

@@ -92,6 +92,34 @@ __global__ void __launch_bounds__(512) k_allreduce_oneshot(const __grid_constant
   cta_peer_barrier(a, a.epoch + 2);  // nobody may overwrite its input before all have read it
 }
 
+// sums of elements i0 and i1 (i1 < 0: only i0) over all ranks: both elements' loads of four peers are in
+// flight together (eight remote loads per thread), which is what fills NVLink between 256 KB and 4 MB,
+// where a slice is only a few thousand 16-byte units per rank
+__device__ __forceinline__ void gather_sum2(const ArArgs& a, int64_t i0, int64_t i1, uint4& s0, uint4& s1) {
+  const bool two = i1 >= 0;
+  s0 = reinterpret_cast<const uint4*>(a.bufs[a.rank])[i0];
+  s1 = two ? reinterpret_cast<const uint4*>(a.bufs[a.rank])[i1] : make_uint4(0, 0, 0, 0);
+#pragma unroll
+  for (int p0 = 1; p0 < MTB_MAX_WORLD; p0 += 4) {
+    if (p0 < a.world) {
+      uint4 y0[4], y1[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int p = p0 + j;
+        const int q = (a.rank + p) % a.world;  // stagger peers so links are used evenly
+        const uint4* src = reinterpret_cast<const uint4*>(a.bufs[q]);
+        y0[j] = p < a.world ? ld_nc_u4(src + i0) : make_uint4(0, 0, 0, 0);
+        y1[j] = (p < a.world && two) ? ld_nc_u4(src + i1) : make_uint4(0, 0, 0, 0);
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        s0 = add4(s0, y0[j]);
+        s1 = add4(s1, y1[j]);
+      }
+    }
+  }
+}
+
 __global__ void __launch_bounds__(512) k_allreduce_twoshot(const __grid_constant__ ArArgs a) {
   cta_peer_barrier(a, a.epoch + 1);
   // slice owned by this rank, in 16-byte units
@@ -99,18 +127,21 @@ __global__ void __launch_bounds__(512) k_allreduce_twoshot(const __grid_constant
   const int64_t per = (n4 + a.world - 1) / a.world;
   const int64_t lo = per * a.rank, hi = min(n4, lo + per);
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  for (int64_t i = lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += stride) {
-    const uint4 acc = gather_sum(a, i);
+  for (int64_t i = lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += 2 * stride) {
+    const int64_t i1 = i + stride < hi ? i + stride : -1;
+    uint4 s0, s1;
+    gather_sum2(a, i, i1, s0, s1);
     // reduced slice -> every rank's result area (own one included)
     for (int p = 0; p < a.world; ++p) {
       const int q = (a.rank + p) % a.world;
-      st_na_u4(reinterpret_cast<uint4*>(a.bufs[q] + a.cap) + i, acc);
+      st_na_u4(reinterpret_cast<uint4*>(a.bufs[q] + a.cap) + i, s0);
+      if (i1 >= 0) st_na_u4(reinterpret_cast<uint4*>(a.bufs[q] + a.cap) + i1, s1);
     }
   }
   cta_peer_barrier(a, a.epoch + 2);  // the slices of all peers' CTAs of this index have landed
 }
 
-// ---- NVLS variant (staged: compiled and inspected, not yet run on hardware) ----------------------
+// ---- NVLS variant ---------------------------------------------------------------------------------
 // The symmetric area is also mapped through an NVSwitch multicast object (parallel/nvls.py), so one
 // address names the same word on every rank.  A rank takes its slice, asks the switch for the sum
 // over all ranks (multimem.ld_reduce, SASS LDGMC.ADD) and writes it to every rank's result area
@@ -214,6 +245,9 @@ extern "C" int mtb_allreduce_u32(int algo, int rank, int world, void* const* buf
   // small messages: few CTAs (the two flag round trips dominate); large: fill the machine.
   // Every rank computes the same grid (same count, same GPU model).
   int64_t want = (count / 4 + 511) / 512;  // one 16-byte unit per thread until the machine is full (remote latency bound)
+  // two-shot: a rank only touches its 1/world slice, two units per thread; CTAs beyond that would only add
+  // flag round trips (every CTA index runs its own peer barrier)
+  if (algo != 0) want = ((count / 4 + world - 1) / world + 1023) / 1024;
   int cap_ctas = 2 * sms < kArMaxCtas ? 2 * sms : kArMaxCtas;
   int blocks = (int)(want < 1 ? 1 : (want > cap_ctas ? cap_ctas : want));
   if (algo == 0) {

@@ -9,10 +9,15 @@ from __future__ import annotations
 
 import ctypes
 
-__all__ = ["PeerAllReduce", "ALGO_ONESHOT", "ALGO_TWOSHOT", "ALGO_NVLS"]
+__all__ = ["PeerAllReduce", "ALGO_ONESHOT", "ALGO_TWOSHOT", "ALGO_NVLS", "ALGO_AUTO"]
 
 
 ALGO_ONESHOT, ALGO_TWOSHOT, ALGO_NVLS = 0, 1, 2
+ALGO_AUTO = -1
+#: size policy of ``ALGO_AUTO`` (bytes): one-shot below, two-shot between, in-switch above (when the buffers
+#: are multicast-bound); set from the 8-GPU sweep in profiles/
+AUTO_ONESHOT_MAX_BYTES = 128 << 10
+AUTO_NVLS_MIN_BYTES = 8 << 20
 
 
 class PeerAllReduce:
@@ -21,7 +26,7 @@ class PeerAllReduce:
     Producers can write straight into :meth:`input_view` (zero-copy); :meth:`all_reduce`
     copies from an ordinary tensor first.
 
-    ``nvls=True`` (staged, not yet run on hardware) places the buffers in an
+    ``nvls=True`` places the buffers in an
     :class:`mpitree_b200.parallel.nvls.NvlsRegion` so that ``algo=2`` can reduce inside the
     NVSwitch; algorithms 0 and 1 work on either kind of region.
     """
@@ -64,6 +69,10 @@ class PeerAllReduce:
     def launch(self, count: int, algo: int = 1, out=None) -> None:
         """Reduce what is in :meth:`input_view`; result in ``out`` or :meth:`result_view`."""
         torch = self.torch
+        if algo == ALGO_AUTO:
+            nbytes = 4 * count
+            algo = (ALGO_ONESHOT if nbytes <= AUTO_ONESHOT_MAX_BYTES else
+                    ALGO_NVLS if (self._mc and self.world >= 4 and nbytes >= AUTO_NVLS_MIN_BYTES) else ALGO_TWOSHOT)
         if out is None and algo == 0:  # one-shot writes its sums straight to the destination
             out = self.result_view(count)
         dst = out.data_ptr() if out is not None else 0
