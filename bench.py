@@ -42,6 +42,9 @@ def parse():
     ap.add_argument("--classes", type=int, default=10)
     ap.add_argument("--depth", type=int, default=10)
     ap.add_argument("--reduce", default=os.environ.get("MTB_REDUCE", "auto"), choices=["auto", "p2p", "nccl", "nvls"])
+    ap.add_argument("--input", default="u8", choices=["u8", "f32"],
+                    help="u8: pre-binned codes (the BASELINE.json headline); f32: continuous float32 rows, bin-edge "
+                         "fitting and encoding inside every timed fit")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-nccl", action="store_true", help="skip the in-process ncclAllReduce baseline pass (N > 1)")
     ap.add_argument("--no-same-config", action="store_true", help="skip the 250-row like-for-like record")
@@ -175,7 +178,7 @@ class ClockSampler:
 BLOCK_ROWS = 1 << 20  # rows per generator block: the data set is a pure function of (seed, global row index)
 
 
-def synth_rows(torch, dev, lo, hi, features, classes, seed=1234):
+def synth_rows(torch, dev, lo, hi, features, classes, seed=1234, as_float=False):
     """Rows ``[lo, hi)`` of the seeded synthetic data set, generated on the device.
 
     Every block of ``BLOCK_ROWS`` global rows has its own generator state ``(seed, block)``, so any
@@ -187,7 +190,7 @@ def synth_rows(torch, dev, lo, hi, features, classes, seed=1234):
     # fixed class boundaries: quantiles of the analytic score distribution
     sd = float((w.pow(2).sum() * (256 ** 2 - 1) / 12.0 + 1600.0).sqrt())
     qs = torch.distributions.Normal(0.0, sd).icdf(torch.linspace(0, 1, classes + 1, device=dev)[1:-1])
-    X = torch.empty((hi - lo, features), dtype=torch.uint8, device=dev)
+    X = torch.empty((hi - lo, features), dtype=torch.float32 if as_float else torch.uint8, device=dev)
     y = torch.empty(hi - lo, dtype=torch.uint8, device=dev)
     for blk in range(lo // BLOCK_ROWS, (max(hi, lo + 1) - 1) // BLOCK_ROWS + 1):
         b0 = blk * BLOCK_ROWS
@@ -196,6 +199,8 @@ def synth_rows(torch, dev, lo, hi, features, classes, seed=1234):
         score = (Xb[:, :k].float() - 127.5) @ w + 40.0 * torch.randn(BLOCK_ROWS, device=dev, generator=g)
         yb = torch.bucketize(score, qs).to(torch.uint8)
         s0, s1 = max(lo, b0), min(hi, b0 + BLOCK_ROWS)
+        if as_float:  # continuous values: the byte plus a uniform fraction (binned to 256 quantile bins by the fit)
+            Xb = Xb.float() + torch.rand((BLOCK_ROWS, features), device=dev, generator=g)
         if s1 > s0:
             X[s0 - lo : s1 - lo] = Xb[s0 - b0 : s1 - b0]
             y[s0 - lo : s1 - lo] = yb[s0 - b0 : s1 - b0]
@@ -287,7 +292,7 @@ def run_ours(a):
         init_process_group_from_env("nccl")
 
     lo, hi = a.rows * rank // world, a.rows * (rank + 1) // world
-    X, y = synth_rows(torch, dev, lo, hi, a.features, a.classes)
+    X, y = synth_rows(torch, dev, lo, hi, a.features, a.classes, as_float=a.input == "f32")
     reduce = a.reduce
     clf = ParallelDecisionTreeClassifier(max_depth=a.depth, data_layout="sharded", device="cuda")
     if reduce != "auto":
@@ -377,7 +382,7 @@ def run_ours(a):
             same_cfg = {"error": str(exc).splitlines()[0][:200]}
     if rank == 0:
         out = {
-            "metric": "fit_rows_per_s_depth10_100Mx64",
+            "metric": "fit_rows_per_s_depth10_100Mx64" + ("_f32_input" if a.input == "f32" else ""),
             "value": value,
             "unit": "rows/s",
             "n_gpus": world,
@@ -388,16 +393,17 @@ def run_ours(a):
             "higher_is_better": True,
             "scaling": "strong",
             "vs_baseline": None,
-            "dtype": "u8 bin codes / u32 counts / fp64 gain",
+            "dtype": ("float32 rows -> " if a.input == "f32" else "") + "u8 bin codes / u32 counts / fp64 gain",
             "data": "synthetic (seeded, generated on device as a function of the global row index: the same "
                     "matrix for every N; random-init, no files)",
             "impl": "ours",
             "config": {
                 "model": "entropy decision tree, level-wise fused split search",
                 "rows": a.rows, "features": a.features, "bins": 256, "classes": a.classes, "max_depth": a.depth,
+                "input": "uint8 bin codes" if a.input == "u8" else "float32, 256 quantile bins fitted and encoded inside the timed fit",
                 "global_batch": a.rows, "seq_len": a.features,
                 "parallelism": f"row-sharded dp{world}" + ("" if world == 1 else f" ({getattr(stats, 'reduce', reduce)} histogram reduction)"),
-                "l2_policy": f"inputs ({(hi - lo) * (a.features + 1) / 1e9:.2f} GB per rank per fit, all re-read every level) "
+                "l2_policy": f"inputs ({(hi - lo) * (a.features * (4 if a.input == 'f32' else 1) + 1) / 1e9:.2f} GB per rank per fit; the codes are re-read every level) "
                              "are far larger than the 126 MB L2; no explicit flush",
                 "tree_nodes": n_nodes, "train_acc_first_1M": acc,
             },

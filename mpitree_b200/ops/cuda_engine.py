@@ -1042,45 +1042,84 @@ def _fit_mapper_numpy(X: np.ndarray, max_bins: int, comm=None) -> BinMapper:
     return mapper
 
 
-def _fit_mapper_device(sample, max_bins: int, comm=None, col_max=None) -> BinMapper:
+def _fit_mapper_device(sample, max_bins: int, comm=None, col_max=None, exchange_col_max: bool = False) -> BinMapper:
     """Bin edges from a device-resident sample: one sort, then order statistics (K1, edge discovery).
 
     Per feature: all distinct values when there are at most ``max_bins`` (lossless), otherwise
     ``max_bins`` order statistics ("higher" quantiles, so every edge is a data value).  With
     several ranks each contributes its candidates and the merged set is reduced the same way on
-    every rank (the cross-rank edge agreement of K1).  ``col_max`` (full-data maxima) extends the
-    last edge when the sample missed the maximum.
+    every rank (the cross-rank edge agreement of K1): the candidates of all ranks travel in ONE device
+    all-gather (NCCL over NVLink) followed by one read-back; ``col_max`` (full-data maxima, extends the
+    last edge when the sample missed the maximum) rides along when ``exchange_col_max`` is set (some rank
+    sampled its rows: every rank then contributes its maxima, or -inf when it has no rows).
     """
     import torch
 
     K, F = int(sample.shape[0]), int(sample.shape[1])
+    multi = comm is not None and comm.size > 1
+    np_dtype = np.float64 if sample.dtype == torch.float64 else np.float32
+    dev = sample.device
     if K == 0:  # a rank without rows still takes part in the agreement, with nothing to contribute
-        np_dtype = np.float64 if sample.dtype == torch.float64 else np.float32
-        parts = [(np.zeros(F, np.int64), np.full((F, 256), np.inf, np_dtype), np.zeros((0, F), np_dtype))]
-        if comm is not None and comm.size > 1:
-            parts = comm.allgather_object(parts[0])
-        return _merge_edge_candidates(parts, F, max_bins, np_dtype, col_max)
-    srt = sample.t().contiguous().sort(dim=1).values  # [F, K], rows sorted
-    # sorted rows end in +inf / nan when the input has them: one check on the extremes
-    if not bool(torch.isfinite(srt[:, [0, -1]]).all()):
-        raise ValueError("Input X contains NaN or infinity.")
-    distinct = (srt[:, 1:] != srt[:, :-1]).sum(dim=1) + 1 if K > 1 else torch.ones(F, dtype=torch.int64, device=sample.device)
-    # order statistics ("higher" quantiles): every edge is a data value
-    q = np.linspace(0.0, 1.0, max_bins + 1)[1:]
-    qidx = torch.from_numpy(np.ceil(q * (K - 1)).astype(np.int64).clip(0, K - 1)).to(sample.device)
-    cand_h = srt[:, qidx].t().cpu().numpy()  # [max_bins, F]
-    distinct_h = distinct.cpu().numpy()
-    np_dtype = cand_h.dtype
-    # features with few distinct values keep all of them (lossless bins)
-    uniq_h = np.full((F, 256), np.inf, dtype=np_dtype)
-    for f in np.flatnonzero(distinct_h <= 256):
-        u = torch.unique_consecutive(srt[f]).cpu().numpy()
-        uniq_h[f, : len(u)] = u
-
-    if comm is not None and comm.size > 1:
-        parts = comm.allgather_object((distinct_h, uniq_h, cand_h))
+        distinct = torch.zeros(F, dtype=torch.float64, device=dev)
+        uniq = torch.full((F, 256), float("inf"), dtype=torch.float64, device=dev)
+        cand = torch.zeros((0, F), dtype=torch.float64, device=dev)
     else:
-        parts = [(distinct_h, uniq_h, cand_h)]
+        srt = sample.t().contiguous().sort(dim=1).values  # [F, K], rows sorted
+        # sorted rows end in +inf / nan when the input has them: one check on the extremes
+        finite = torch.isfinite(srt[:, [0, -1]]).all()
+        distinct_t = (srt[:, 1:] != srt[:, :-1]).sum(dim=1) + 1 if K > 1 else torch.ones(F, dtype=torch.int64, device=dev)
+        # order statistics ("higher" quantiles): every edge is a data value
+        q = np.linspace(0.0, 1.0, max_bins + 1)[1:]
+        qidx = torch.from_numpy(np.ceil(q * (K - 1)).astype(np.int64).clip(0, K - 1)).to(dev)
+        cand = srt[:, qidx].t().to(torch.float64)  # [max_bins, F]
+        distinct = distinct_t.to(torch.float64)
+        # features with few distinct values keep all of them (lossless bins): the first 256 distinct values
+        # of every row, compacted on the device (rows with more are not used)
+        first = torch.ones((F, K), dtype=torch.bool, device=dev)
+        if K > 1:
+            first[:, 1:] = srt[:, 1:] != srt[:, :-1]
+        rank_in_row = first.cumsum(dim=1) - 1  # index among the row's distinct values
+        uniq = torch.full((F, 257), float("inf"), dtype=torch.float64, device=dev)
+        tgt = torch.where(first & (rank_in_row < 256), rank_in_row, torch.full_like(rank_in_row, 256))
+        uniq.scatter_(1, tgt, srt.to(torch.float64))
+        uniq = uniq[:, :256].contiguous()
+        uniq[:, 0] = srt[:, 0].to(torch.float64)  # (scatter order among duplicates is unspecified only for column 256)
+    cmax = torch.full((F,), float("-inf"), dtype=torch.float64, device=dev)
+    if col_max is not None:
+        cmax = torch.as_tensor(col_max, device=dev).to(torch.float64)
+    n_cand = int(cand.shape[0])
+    payload = torch.cat([
+        torch.tensor([float(K), float(n_cand), 1.0 if K == 0 else 0.0], dtype=torch.float64, device=dev),
+        (finite.to(torch.float64).reshape(1) if K else torch.ones(1, dtype=torch.float64, device=dev)),
+        distinct, cmax, uniq.reshape(-1),
+        torch.cat([cand, torch.zeros((max_bins - n_cand, F), dtype=torch.float64, device=dev)]).reshape(-1),
+    ])
+    gather = getattr(comm, "allgather_device", None) if multi else None
+    gathered = gather(payload) if gather is not None else None
+    if gathered is not None:
+        table = gathered.cpu().numpy()
+    elif multi:
+        table = np.stack(comm.allgather_object(payload.cpu().numpy()))
+    else:
+        table = payload.cpu().numpy()[None]
+    if not bool((table[:, 3] > 0).all()):
+        raise ValueError("Input X contains NaN or infinity.")
+    parts, maxima = [], []
+    for row in table:
+        k_rows, n_c = int(row[0]), int(row[1])
+        o = 4
+        d = row[o : o + F].astype(np.int64); o += F
+        m = row[o : o + F]; o += F
+        u = row[o : o + F * 256].reshape(F, 256).astype(np_dtype); o += F * 256
+        c = row[o : o + max_bins * F].reshape(max_bins, F)[:n_c].astype(np_dtype)
+        parts.append((d, u, c))
+        if k_rows or np.isfinite(m).any():
+            maxima.append(m)
+    if exchange_col_max or col_max is not None:
+        live = [m for m in maxima if np.isfinite(m).all()]
+        col_max = np.max(np.stack(live), axis=0).astype(np_dtype) if live else None
+    else:
+        col_max = None
     return _merge_edge_candidates(parts, F, max_bins, np_dtype, col_max)
 
 
@@ -1389,15 +1428,11 @@ def fit_from_torch(X, y, params: SplitParams, *, max_bins: int = 256, comm=None,
         sample = X if idx is None else X[torch.from_numpy(idx).to(X.device)]
         if X.dtype == torch.uint8:
             sample = sample.to(torch.float32)  # edge discovery works on floats; the rows stay bytes
-        col_max = X.max(dim=0).values.cpu().numpy() if idx is not None else None
-        if multi and int(meta[:, 1].max()) > SAMPLE_ROWS:
-            # some rank sampled its rows: every rank joins the exchange of column maxima (the shard
-            # sizes come from the all-gather above, so the decision is the same everywhere)
-            if col_max is None and n:
-                col_max = X.max(dim=0).values.cpu().numpy()
-            maxima = [m for m in comm.allgather_object(col_max) if m is not None]
-            col_max = np.max(np.stack(maxima), axis=0)
-        mapper = _fit_mapper_device(sample.to(dev, non_blocking=True), max_bins, comm, col_max)
+        # some rank sampled its rows: every rank contributes its column maxima (the shard sizes come from
+        # the gather above, so the decision is the same everywhere); they ride along with the candidates
+        any_sampled = idx is not None or (multi and int(meta[:, 1].max()) > SAMPLE_ROWS)
+        col_max = X.max(dim=0).values if (any_sampled and n) else None
+        mapper = _fit_mapper_device(sample.to(dev, non_blocking=True), max_bins, comm, col_max, exchange_col_max=any_sampled)
         if multi and int(meta[:, 1].max()) > SAMPLE_ROWS or idx is not None:
             _repair_sampled_edges(X, mapper, max_bins, comm)  # (uint8 rows compare against float edges)
         if X.dtype == torch.uint8:
