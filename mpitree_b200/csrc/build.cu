@@ -241,17 +241,17 @@ __device__ __forceinline__ void tile_count_il(uint32_t* tile, uint4 x, uint32_t 
   const uint32_t sel = 0x3210u + 0x1111u * (uint32_t)(rot & 3);
   const uint4 y = make_uint4(__byte_perm(w0, w1, sel), __byte_perm(w1, w2, sel), __byte_perm(w2, w3, sel),
                              __byte_perm(w3, w0, sel));  // byte k of y = byte (k + rot) mod 16 of x
-  // byte offsets throughout: one byte-extract (PRMT), one add of the lane's feature offset (loop
-  // invariant per k, kept in registers across rows) and one multiply-add per increment
-  // (shared-window addresses, so the tile base folds into the per-row term)
-  // cell = lab * B + code (class-major, like the slabs): the code's term is a shift
+  // byte offsets throughout: one byte extract (PRMT), one add of the lane's feature offset and one
+  // shift-add per increment (shared-window addresses, so the tile base folds into the per-row term).
+  // cell = lab * B + code (class-major, like the slabs).  (Tried: both address terms as integer
+  // multiply-adds with run-time multipliers, to move them off the ALU pipe: 3.06 instead of 2.87 ms per
+  // level.)
   const uint32_t row_base = smem_u32(tile) + lab * (uint32_t)B * 64u;
-  const uint32_t stride_b = 64u;
   const uint32_t yw[4] = {y.x, y.y, y.z, y.w};
 #pragma unroll
   for (int k = 0; k < 16; ++k) {
     const uint32_t code = __byte_perm(yw[k >> 2], 0u, 0x4440u | (uint32_t)(k & 3));
-    const uint32_t addr = code * stride_b + (row_base + (uint32_t)(((k + rot) & 15) * 4));
+    const uint32_t addr = code * 64u + (row_base + (uint32_t)(((k + rot) & 15) * 4));
     asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(addr), "r"(1u) : "memory");
   }
 }
@@ -315,6 +315,56 @@ __device__ void flush_tile(const MtbCtx& ctx, uint32_t* tile, int slot, int gs, 
       if (x) {
         red_add_u32(dst + i, x);
         tile[i] = 0;
+      }
+    }
+  }
+}
+
+// Interleaved tile with two 16-bit counters per word (cells 2i and 2i+1 share word i): half the
+// shared memory of the 32-bit tile, which the root cluster kernel turns into row stages.  The caller
+// flushes before any counter can pass 65,535.
+__device__ __forceinline__ void tile_count_il16(uint32_t* tile, uint4 x, uint32_t lab, int B, int lane) {
+  const int rot = lane & 15;
+  uint32_t w0 = x.x, w1 = x.y, w2 = x.z, w3 = x.w;
+  if (rot & 4) { const uint32_t t = w0; w0 = w1; w1 = w2; w2 = w3; w3 = t; }
+  if (rot & 8) { uint32_t t = w0; w0 = w2; w2 = t; t = w1; w1 = w3; w3 = t; }
+  const uint32_t sel = 0x3210u + 0x1111u * (uint32_t)(rot & 3);
+  const uint4 y = make_uint4(__byte_perm(w0, w1, sel), __byte_perm(w1, w2, sel), __byte_perm(w2, w3, sel),
+                             __byte_perm(w3, w0, sel));  // byte k of y = byte (k + rot) mod 16 of x
+  const uint32_t row_base = smem_u32(tile) + lab * (uint32_t)(B / 2) * 64u;  // cell = lab * B + code, word = cell >> 1
+  const uint32_t yw[4] = {y.x, y.y, y.z, y.w};
+#pragma unroll
+  for (int k = 0; k < 16; ++k) {
+    const uint32_t code = __byte_perm(yw[k >> 2], 0u, 0x4440u | (uint32_t)(k & 3));
+    const uint32_t addr = (code >> 1) * 64u + (row_base + (uint32_t)(((k + rot) & 15) * 4));
+    const uint32_t one = 1u << ((code & 1u) * 16u);
+    asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(addr), "r"(one) : "memory");
+  }
+}
+
+// Merge (and clear) the packed tile of feature group `g` into the slab of `slot` with red.global.add.
+__device__ void flush_tile_il16(const MtbCtx& ctx, uint32_t* tile, int g, int tid, int slot = 0) {
+  View v(ctx);
+  const int BC = (int)ctx.B * (int)ctx.C;
+  uint32_t* dst = v.hist_cur() + (int64_t)slot * v.slab_words() + (int64_t)g * 16 * BC;
+  const int lane = tid & 31, w = tid >> 5;
+  const int q = lane & 3, r = lane >> 2;
+  const uint4 zero = make_uint4(0, 0, 0, 0);
+  for (int c0 = w * 32; c0 < BC / 2; c0 += kConsumerWarps * 32) {  // word (= cell pair) index
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int pair = c0 + r + 8 * i;
+      if (pair < BC / 2) {
+        uint4* src = reinterpret_cast<uint4*>(tile + pair * 16 + 4 * q);
+        const uint4 x = *src;
+        *src = zero;
+        const uint32_t e[4] = {x.x, x.y, x.z, x.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          uint32_t* d = dst + (int64_t)(4 * q + j) * BC + 2 * pair;
+          if (e[j] & 0xffffu) red_add_u32(d, e[j] & 0xffffu);
+          if (e[j] >> 16) red_add_u32(d + 1, e[j] >> 16);
+        }
       }
     }
   }
@@ -1340,9 +1390,11 @@ struct MoveCursor {
 constexpr int kLabelStage = 1056;                               // 1024 labels + alignment slack
 constexpr int kStage2Bytes = kStageBytes + kLabelStage + kMetaWords * 4;  // + unit record (272 B), 16-byte multiple
 
-__host__ __device__ inline HistGeom move_geom(int FT, int B, int C) {
+// `packed`: the interleaved 16-feature tile with two 16-bit counters per word (half the shared memory,
+// so eight row stages fit next to it instead of three; flushed before a counter can overflow)
+__host__ __device__ inline HistGeom move_geom(int FT, int B, int C, bool packed = false) {
   HistGeom g;
-  g.tile_words = FT * B * C;
+  g.tile_words = packed ? FT * B * C / 2 : FT * B * C;
   int tile_bytes = g.tile_words * 4;
   int st = (kSmemBudget - tile_bytes - 256) / kStage2Bytes;
   if (st > kMaxStages) st = kMaxStages;
@@ -1350,6 +1402,7 @@ __host__ __device__ inline HistGeom move_geom(int FT, int B, int C) {
   g.smem_bytes = tile_bytes + st * kStage2Bytes + 256;
   return g;
 }
+constexpr int kPackedFlushUnits = 63;  // 63 x 1,024 rows < 65,536: no 16-bit counter can overflow between flushes
 
 // ring position of a pipeline role, carried from step A to step B
 struct Ring {
@@ -1383,7 +1436,11 @@ template <int FT, bool IL = false>
 __device__ void move_hist_phase(const MtbCtx& P, const MtbCtx& C, uint8_t* smem, int step, Ring& ring) {
   View vp(P);
   const int B = (int)P.B, Cn = (int)P.C;
-  const MoveSmem ms = move_smem(smem, move_geom(FT, B, Cn));
+  // (a 16-bit packed tile - half the shared memory, eight stages instead of three - was measured here:
+  // 4.1 instead of 2.9 ms per level on 100M x 64; its three extra ALU instructions per increment cost more
+  // than the stages gain, the ALU pipe being the busiest unit of this phase)
+  constexpr bool kPacked = false;
+  const MoveSmem ms = move_smem(smem, move_geom(FT, B, Cn, kPacked));
   uint32_t* tile = ms.tile;
   const int stages = ms.stages;
   const int n_slots = vp.n_slots();
@@ -1488,15 +1545,18 @@ __device__ void move_hist_phase(const MtbCtx& P, const MtbCtx& C, uint8_t* smem,
   const int64_t plane = P.n_cap;
   uint64_t* avail = step == 0 ? ms.ready : ms.full;  // step A: the ranker has filled in the unit record
   int cur_slot = -1, cur_j = -1, cur_gs = -1, build_child = -1, build_side = -1, flags = 0;
+  int units_since_flush = 0;
   bool cur_excl = false;
   for (int u = u0; u < u1; ++u) {
     cur.seek(u);
-    if (cur.slot != cur_slot || cur.j != cur_j) {
+    if (cur.slot != cur_slot || cur.j != cur_j || (kPacked && units_since_flush >= kPackedFlushUnits)) {
       if (build_child >= 0) {
         named_bar_sync(1, kConsumers);
-        flush_tile<FT, IL>(C, tile, build_child, cur_gs, tid, cur_excl);
+        if constexpr (kPacked) flush_tile_il16(C, tile, cur_gs / S, tid, build_child);
+        else flush_tile<FT, IL>(C, tile, build_child, cur_gs, tid, cur_excl);
         named_bar_sync(1, kConsumers);
       }
+      units_since_flush = 0;
       cur_slot = cur.slot;
       cur_j = cur.j;
       cur_gs = tile_of(cur.slot, cur.j);
@@ -1549,7 +1609,11 @@ __device__ void move_hist_phase(const MtbCtx& P, const MtbCtx& C, uint8_t* smem,
       }
     }
     if (build_child >= 0) {
-      if constexpr (IL) {
+      ++units_since_flush;
+      if constexpr (IL && kPacked) {
+        if (va_ok && (int)(!la) == build_side) tile_count_il16(tile, xa, lab_a, B, lane);
+        if (vb_ok && (int)(!lb) == build_side) tile_count_il16(tile, xb, lab_b, B, lane);
+      } else if constexpr (IL) {
         if (va_ok && (int)(!la) == build_side) tile_count_il(tile, xa, lab_a, B, lane);
         if (vb_ok && (int)(!lb) == build_side) tile_count_il(tile, xb, lab_b, B, lane);
       } else {
@@ -1567,7 +1631,8 @@ __device__ void move_hist_phase(const MtbCtx& P, const MtbCtx& C, uint8_t* smem,
   }
   if (build_child >= 0) {
     named_bar_sync(1, kConsumers);
-    flush_tile<FT, IL>(C, tile, build_child, cur_gs, tid, cur_excl);
+    if constexpr (kPacked) flush_tile_il16(C, tile, cur_gs / S, tid, build_child);
+    else flush_tile<FT, IL>(C, tile, build_child, cur_gs, tid, cur_excl);
   }
 }
 
@@ -1603,56 +1668,6 @@ __device__ void zero_next_level(const MtbCtx& ctx, int n_slots) {
   int64_t n = 2 * (int64_t)n_slots;
   if (n > ctx.h_cap) n = ctx.h_cap;
   zero_slabs(ptr_of<uint32_t>(ctx.hist[ctx.hcur ^ 1]), v.slab_words(), (int)n);
-}
-
-// Interleaved tile with two 16-bit counters per word (cells 2i and 2i+1 share word i): half the
-// shared memory of the 32-bit tile, which the root cluster kernel turns into row stages.  The caller
-// flushes before any counter can pass 65,535.
-__device__ __forceinline__ void tile_count_il16(uint32_t* tile, uint4 x, uint32_t lab, int B, int lane) {
-  const int rot = lane & 15;
-  uint32_t w0 = x.x, w1 = x.y, w2 = x.z, w3 = x.w;
-  if (rot & 4) { const uint32_t t = w0; w0 = w1; w1 = w2; w2 = w3; w3 = t; }
-  if (rot & 8) { uint32_t t = w0; w0 = w2; w2 = t; t = w1; w1 = w3; w3 = t; }
-  const uint32_t sel = 0x3210u + 0x1111u * (uint32_t)(rot & 3);
-  const uint4 y = make_uint4(__byte_perm(w0, w1, sel), __byte_perm(w1, w2, sel), __byte_perm(w2, w3, sel),
-                             __byte_perm(w3, w0, sel));  // byte k of y = byte (k + rot) mod 16 of x
-  const uint32_t row_base = smem_u32(tile) + lab * (uint32_t)(B / 2) * 64u;  // cell = lab * B + code, word = cell >> 1
-  const uint32_t yw[4] = {y.x, y.y, y.z, y.w};
-#pragma unroll
-  for (int k = 0; k < 16; ++k) {
-    const uint32_t code = __byte_perm(yw[k >> 2], 0u, 0x4440u | (uint32_t)(k & 3));
-    const uint32_t addr = (code >> 1) * 64u + (row_base + (uint32_t)(((k + rot) & 15) * 4));
-    const uint32_t one = 1u << ((code & 1u) * 16u);
-    asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(addr), "r"(one) : "memory");
-  }
-}
-
-// Merge (and clear) the packed tile of feature group `g` into slot 0's slab with red.global.add.
-__device__ void flush_tile_il16(const MtbCtx& ctx, uint32_t* tile, int g, int tid) {
-  View v(ctx);
-  const int BC = (int)ctx.B * (int)ctx.C;
-  uint32_t* dst = v.hist_cur() + (int64_t)g * 16 * BC;
-  const int lane = tid & 31, w = tid >> 5;
-  const int q = lane & 3, r = lane >> 2;
-  const uint4 zero = make_uint4(0, 0, 0, 0);
-  for (int c0 = w * 32; c0 < BC / 2; c0 += kConsumerWarps * 32) {  // word (= cell pair) index
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const int pair = c0 + r + 8 * i;
-      if (pair < BC / 2) {
-        uint4* src = reinterpret_cast<uint4*>(tile + pair * 16 + 4 * q);
-        const uint4 x = *src;
-        *src = zero;
-        const uint32_t e[4] = {x.x, x.y, x.z, x.w};
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          uint32_t* d = dst + (int64_t)(4 * q + j) * BC + 2 * pair;
-          if (e[j] & 0xffffu) red_add_u32(d, e[j] & 0xffffu);
-          if (e[j] >> 16) red_add_u32(d + 1, e[j] >> 16);
-        }
-      }
-    }
-  }
 }
 
 // ------------------------------------------------------ root level from row-major bytes (cluster)
@@ -1884,7 +1899,7 @@ __global__ void __launch_bounds__(kFusedThreads, 1) k_level_fused2(const __grid_
   }
   stamp(C, 0);
   {
-    const HistGeom geom = move_geom(FT, (int)P.B, (int)P.C);
+    const HistGeom geom = move_geom(FT, (int)P.B, (int)P.C, false);
     const MoveSmem ms = move_smem(smem, geom);
     if (threadIdx.x == 0) {
       for (int i = 0; i < geom.stages; ++i) {
@@ -2019,7 +2034,7 @@ static int fused_smem(const MtbCtx* ctx, bool with_move) {
   HistGeom g = hist_geom((int)ctx->FT, (int)ctx->B, (int)ctx->C);
   int smem = g.smem_bytes;
   if (with_move) {
-    HistGeom mg = move_geom((int)ctx->FT, (int)ctx->B, (int)ctx->C);
+    HistGeom mg = move_geom((int)ctx->FT, (int)ctx->B, (int)ctx->C, false);
     if (mg.smem_bytes > smem) smem = mg.smem_bytes;
   }
   GainGeom gg = gain_geom((int)ctx->B, (int)ctx->C, kFusedGainWarps, smem);
