@@ -198,7 +198,7 @@ class DeviceDataset:
             and X.data_ptr() % 16 == 0
         ):
             _call(
-                "mtb_encode_f32_quads",
+                "mtb_encode_f32_quads" if os.environ.get("MTB_ENCODE") == "quads" else "mtb_encode_f32_slots",
                 ctypes.c_void_p(_p(X)),
                 ctypes.c_int64(X.shape[0]),
                 ctypes.c_int64(self.n_features),
@@ -1428,12 +1428,13 @@ def fit_from_torch(X, y, params: SplitParams, *, max_bins: int = 256, comm=None,
         sample = X if idx is None else X[torch.from_numpy(idx).to(X.device)]
         if X.dtype == torch.uint8:
             sample = sample.to(torch.float32)  # edge discovery works on floats; the rows stay bytes
-        # some rank sampled its rows: every rank contributes its column maxima (the shard sizes come from
-        # the gather above, so the decision is the same everywhere); they ride along with the candidates
+        # Some rank sampled its rows (the shard sizes come from the gather above, so the decision is the same
+        # everywhere).  No pass over all rows for the column maxima: a value above the last sampled edge is
+        # clamped into the last bin by the encoders, the last edge is never a threshold (its right side is
+        # empty), and columns that are enumerated value by value are checked against all rows below.
         any_sampled = idx is not None or (multi and int(meta[:, 1].max()) > SAMPLE_ROWS)
-        col_max = X.max(dim=0).values if (any_sampled and n) else None
-        mapper = _fit_mapper_device(sample.to(dev, non_blocking=True), max_bins, comm, col_max, exchange_col_max=any_sampled)
-        if multi and int(meta[:, 1].max()) > SAMPLE_ROWS or idx is not None:
+        mapper = _fit_mapper_device(sample.to(dev, non_blocking=True), max_bins, comm)
+        if any_sampled:
             _repair_sampled_edges(X, mapper, max_bins, comm)  # (uint8 rows compare against float edges)
         if X.dtype == torch.uint8:
             lut = torch.from_numpy(_byte_lut(mapper)).to(dev)

@@ -31,7 +31,7 @@ def test_encode_f32_quads_equals_scalar_kernel(monkeypatch, F, max_bins):
     mapper = BinMapper.fit(np.nan_to_num(X[: n // 2], nan=0.0), max_bins=max_bins)  # values beyond the edges exist
     Xd = torch.from_numpy(X).cuda()
     out = []
-    for mode in ("scalar", "quads"):
+    for mode in ("scalar", "quads", "slots"):
         monkeypatch.setenv("MTB_ENCODE", mode)
         data = DeviceDataset.allocate(n, F, 2, torch.device("cuda"))
         data.codes[0].zero_()
@@ -39,6 +39,7 @@ def test_encode_f32_quads_equals_scalar_kernel(monkeypatch, F, max_bins):
         out.append(data.codes_rowmajor().cpu().numpy().copy())
         data.release()
     assert np.array_equal(out[0], out[1])
+    assert np.array_equal(out[0], out[2])
     finite = np.isfinite(X).all(axis=1)
     assert np.array_equal(out[1][finite], mapper.transform(X[finite]))
 
