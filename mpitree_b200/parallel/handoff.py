@@ -14,7 +14,7 @@ subtrees return as flat arrays (:class:`FlatTree` rows), not pickled graphs.
 
 This module holds the policy and the stitching, which are engine independent
 and unit-testable on CPU; the GPU row movement itself is kernel K6
-(``mpitree_b200/csrc/handoff.cu``).
+(``k_gather_rows`` in ``mpitree_b200/csrc/subtree.cu``, driven by ``ops/subtree_phase.py``).
 """
 
 from __future__ import annotations
@@ -61,8 +61,10 @@ def halving_groups(ranks: Sequence[int]) -> Tuple[List[int], List[int]]:
     """The reference's parity split of a rank group (``decision_tree.py:336-338``).
 
     ``Split(color=rank % 2, key=rank // 2)``: even positions take the ``<=``
-    child, odd positions the ``>`` child.  Kept for users who want the
-    reference's schedule; :func:`assign_owners` is the sized default.
+    child, odd positions the ``>`` child.  The host scheduler halves its communicator this
+    way when nodes become too small to be worth sharing among all ranks
+    (``scheduler.fit_flat_tree_host``, phase 2); which nodes go to which half is decided by
+    size (:func:`assign_owners` over two bins), not by the side of the split.
     """
     ranks = list(ranks)
     return ranks[0::2], ranks[1::2]

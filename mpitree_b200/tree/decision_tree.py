@@ -310,7 +310,8 @@ class DecisionTreeClassifier(ClassifierMixin, BaseEstimator):
                                                   builder_kwargs=self._builder_kwargs())
             else:
                 flat = fit_flat_tree_host(vcodes, y_codes, v_nbins, len(classes), params, comm,
-                                          handoff_rows=getattr(self, "handoff_rows", None))
+                                          handoff_rows=getattr(self, "handoff_rows", None),
+                                          group_rows=getattr(self, "group_rows", None))
             # (new arrays: thread-ranks of one process can share the tree object the scheduler returns)
             inner = flat.feature >= 0
             vf = flat.feature[inner]
@@ -351,7 +352,7 @@ class DecisionTreeClassifier(ClassifierMixin, BaseEstimator):
             else:
                 flat = fit_flat_tree_host(
                     codes, y_codes, mapper.n_bins, len(classes), params, comm,
-                    handoff_rows=getattr(self, "handoff_rows", None),
+                    handoff_rows=getattr(self, "handoff_rows", None), group_rows=getattr(self, "group_rows", None),
                 )
         flat.class_labels = np.asarray(classes, dtype=np.int64)
         flat.thresholds = mapper.thresholds_of(flat.feature, flat.bin)
@@ -549,6 +550,12 @@ class ParallelDecisionTreeClassifier(DecisionTreeClassifier):
     handoff_rows : int, optional
         Global row count below which a subtree is handed to a single owner rank
         (``None`` = automatic, ``0`` = never).
+    group_rows : int, optional
+        Global row count below which a node leaves the all-ranks build for a rank
+        *subgroup*: the communicator is halved the way the reference halves it
+        (``:336-338``, ``:446-466``), the node's rows move to its half and the half goes
+        on cooperatively, halving again further down (host engine, four ranks or
+        more; ``None`` = four times ``handoff_rows``, ``0`` = never).
     comm : communicator, optional
         Defaults to the world group at ``fit`` time.
     """
@@ -567,6 +574,7 @@ class ParallelDecisionTreeClassifier(DecisionTreeClassifier):
         device: str = "auto",
         data_layout: str = "replicated",
         handoff_rows: Optional[int] = None,
+        group_rows: Optional[int] = None,
         comm=None,
     ):
         super().__init__(
@@ -578,6 +586,7 @@ class ParallelDecisionTreeClassifier(DecisionTreeClassifier):
         )
         self.data_layout = data_layout
         self.handoff_rows = handoff_rows
+        self.group_rows = group_rows
         self.comm = comm
 
     def _communicator(self):

@@ -349,3 +349,44 @@ def test_torch_front_end_dry_run_on_thread_ranks(monkeypatch):
     # (the outlier 55.0 is not in every rank's sample: it is clamped into the last bin, whose upper edge is never a
     # threshold, so the last edge need not be the column maximum; what matters is that all ranks agree)
     assert out[0][1] == [0, 1000, 2000] and out[0][0][2][-1] <= 55.0
+
+
+@pytest.mark.parametrize("world", [4, 5, 8])
+def test_rank_subgroups_keep_cooperating_on_medium_nodes(world, ref):
+    """Phase 2 of the host scheduler: nodes below ``group_rows`` leave the all-ranks build for one half of the
+    communicator (the reference's parity halving, decision_tree.py:336-338, :446-466), the half continues
+    cooperatively on its own sub-communicator and halves again; nodes below ``handoff_rows`` end on single
+    owners.  Every rank must end with the serial tree, which is the reference's tree."""
+    from mpitree_b200.parallel import scheduler
+    from mpitree_b200.parallel.comm import run_threaded
+    from mpitree_b200.tree import DecisionTreeClassifier, ParallelDecisionTreeClassifier
+
+    rng = np.random.default_rng(world)
+    n = 1500
+    X = rng.integers(0, 9, size=(n, 5)).astype(np.float64)
+    y = ((X[:, 0] + X[:, 1] * X[:, 2] + rng.integers(0, 5, size=n)) % 3).astype(np.int64)
+    want = DecisionTreeClassifier(device="cpu").fit(X, y).export_text()
+    assert want == ref.DecisionTreeClassifier().fit(X, y).export_text()
+    splits = []
+    real_split = scheduler.halving_groups
+
+    def spy(ranks):
+        splits.append(len(list(ranks)))
+        return real_split(ranks)
+
+    scheduler.halving_groups = spy
+    try:
+        cuts = [n * r // world for r in range(world + 1)]
+
+        def work(comm):
+            lo, hi = cuts[comm.rank], cuts[comm.rank + 1]
+            clf = ParallelDecisionTreeClassifier(device="cpu", data_layout="sharded", handoff_rows=40, group_rows=600, comm=comm)
+            return clf.fit(X[lo:hi], y[lo:hi]).export_text()
+
+        out = run_threaded(world, work)
+    finally:
+        scheduler.halving_groups = real_split
+    assert set(out) == {want}
+    assert world in splits  # the world was halved ...
+    if world >= 8:
+        assert any(s < world for s in splits)  # ... and a half of four ranks halved again
