@@ -411,7 +411,7 @@ __device__ void hist_phase(const MtbCtx& ctx, uint8_t* smem) {
       for (int u = u0; u < u1; ++u) {
         cur.seek(u);
         const int g = cur.gs / S;
-        mbar_wait(&empty[st], ph ^ 1);
+        mbar_wait_sleepy(&empty[st], ph ^ 1, 1000u);
         const uint32_t bytes = (uint32_t)cur.nrows * 16u;
         mbar_arrive_expect_tx(&full[st], bytes);
         tma_load_1d(stage_base + (size_t)st * kStageBytes, codes + ((int64_t)g * ctx.n_cap + cur.row0) * 16, bytes,
@@ -445,7 +445,7 @@ __device__ void hist_phase(const MtbCtx& ctx, uint8_t* smem) {
       uint32_t lab_a = 0, lab_b = 0;
       if (r_a < nrows) lab_a = labels[cur.row0 + r_a];
       if (r_b < nrows) lab_b = labels[cur.row0 + r_b];
-      mbar_wait(&full[st], ph);
+      mbar_wait_sleepy(&full[st], ph, 500u);
       const uint32_t rows = smem_u32(stage_base) + (uint32_t)st * kStageBytes;  // (explicit shared-space loads: see lds_u4)
       uint4 va = make_uint4(0, 0, 0, 0), vb = va;
       if (r_a < nrows) va = lds_u4(rows + 16 * r_a);
@@ -1476,7 +1476,7 @@ __device__ void move_hist_phase(const MtbCtx& P, const MtbCtx& C, uint8_t* smem,
     for (int u = u0 + rk; u < u1; u += kRankers) {
       cur.seek_to(u);
       const int f = rec_feature[cur.slot], bin = rec_bin[cur.slot];
-      mbar_wait(&ms.full[mine_ring.st], mine_ring.ph);
+      mbar_wait_sleepy(&ms.full[mine_ring.st], mine_ring.ph, 1000u);
       uint8_t* sbuf = ms.stage_base + (size_t)mine_ring.st * kStage2Bytes;
       const uint8_t* col = sbuf + (f & 15);
       uint32_t mine = 0, nl = 0;
@@ -1519,7 +1519,7 @@ __device__ void move_hist_phase(const MtbCtx& P, const MtbCtx& C, uint8_t* smem,
       for (int u = u0; u < u1; ++u) {
         cur.seek(u);
         const int g = tile_of(cur.slot, cur.j) / S;
-        mbar_wait(&ms.empty[ring.st], ring.ph ^ 1);
+        mbar_wait_sleepy(&ms.empty[ring.st], ring.ph ^ 1, 1000u);
         uint8_t* sbuf = ms.stage_base + (size_t)ring.st * kStage2Bytes;
         const uint32_t cbytes = (uint32_t)cur.nrows * 16u;
         const uint32_t loff = (uint32_t)cur.row0 & 15u;
@@ -1574,7 +1574,7 @@ __device__ void move_hist_phase(const MtbCtx& P, const MtbCtx& C, uint8_t* smem,
     const bool mover = (cur_gs % S) == 0;  // one feature tile per plane moves the plane's bytes
     const int ra = w * 64 + lane, rb = ra + 32;
     const bool va_ok = ra < cur.nrows, vb_ok = rb < cur.nrows;
-    mbar_wait(&avail[ring.st], ring.ph);
+    mbar_wait_sleepy(&avail[ring.st], ring.ph, 500u);
     // (explicit shared-space loads: see lds_u4)
     const uint32_t sbuf = smem_u32(ms.stage_base) + (uint32_t)ring.st * kStage2Bytes;
     const uint32_t slab = sbuf + kStageBytes + ((uint32_t)cur.row0 & 15u);
