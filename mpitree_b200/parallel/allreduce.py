@@ -14,10 +14,12 @@ __all__ = ["PeerAllReduce", "ALGO_ONESHOT", "ALGO_TWOSHOT", "ALGO_NVLS", "ALGO_A
 
 ALGO_ONESHOT, ALGO_TWOSHOT, ALGO_NVLS = 0, 1, 2
 ALGO_AUTO = -1
-#: size policy of ``ALGO_AUTO`` (bytes): one-shot below, two-shot between, in-switch above (when the buffers
-#: are multicast-bound); set from the 8-GPU sweep in profiles/
-AUTO_ONESHOT_MAX_BYTES = 128 << 10
-AUTO_NVLS_MIN_BYTES = 8 << 20
+#: size policy of ``ALGO_AUTO`` (bytes), from the 8-GPU sweep (profiles/r2/allreduce_sweep_8gpu.txt): with
+#: multicast-bound buffers and four ranks or more the in-switch kernel is the fastest of ours at every size
+#: (16.7 us at 4 KB ... 770 GB/s bus bandwidth at 256 MB; NCCL: 25.5 us ... 644 GB/s); otherwise one-shot up
+#: to 16 KB and two-shot above
+AUTO_ONESHOT_MAX_BYTES = 16 << 10
+AUTO_NVLS_MIN_BYTES = 0
 
 
 class PeerAllReduce:
@@ -71,8 +73,8 @@ class PeerAllReduce:
         torch = self.torch
         if algo == ALGO_AUTO:
             nbytes = 4 * count
-            algo = (ALGO_ONESHOT if nbytes <= AUTO_ONESHOT_MAX_BYTES else
-                    ALGO_NVLS if (self._mc and self.world >= 4 and nbytes >= AUTO_NVLS_MIN_BYTES) else ALGO_TWOSHOT)
+            algo = (ALGO_NVLS if (self._mc and self.world >= 4 and nbytes >= AUTO_NVLS_MIN_BYTES) else
+                    ALGO_ONESHOT if nbytes <= AUTO_ONESHOT_MAX_BYTES else ALGO_TWOSHOT)
         if out is None and algo == 0:  # one-shot writes its sums straight to the destination
             out = self.result_view(count)
         dst = out.data_ptr() if out is not None else 0
