@@ -121,7 +121,8 @@ def build(force: bool = False, verbose: bool = False) -> pathlib.Path:
 
 
 def lib_path() -> pathlib.Path:
-    return LIBDIR / LIBNAME
+    override = os.environ.get("MTB_LIB")  # development: an experimental build of the same sources
+    return pathlib.Path(override) if override else LIBDIR / LIBNAME
 
 
 def load() -> ctypes.CDLL:
