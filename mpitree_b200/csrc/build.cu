@@ -227,31 +227,35 @@ struct UnitCursor {
 };
 
 // Interleaved-tile histogram update of one row (16 codes in `x`, label `lab`).  Lane l takes the
-// features in the order l, l+1, ... (mod 16): in every one of the 16 instructions the 32 lanes of
-// a warp address 16 different features, two lanes each, and a feature's counters live in banks
-// f and 16 + f only.  Worst case per instruction is therefore a 2-way conflict (the two lanes of
-// a feature hitting the same bank with different cells) instead of the ~3.6-way average that
-// random (bin, class) addresses give the [f][B][C] tile.  The row's 16 bytes are rotated once by
-// the lane's offset so that step k reads the statically indexed byte k.
+// features in the order l ^ 0, l ^ 1, ... l ^ 15 (l taken mod 16): in every one of the 16
+// instructions the 32 lanes of a warp address 16 different features, two lanes each, and a
+// feature's counters live in banks f and 16 + f only.  Worst case per instruction is therefore a
+// 2-way conflict (the two lanes of a feature hitting the same bank with different cells) instead
+// of the ~3.6-way average that random (bin, class) addresses give the [f][B][C] tile.  The row's
+// 16 bytes are permuted once by the lane's offset so that step k reads the statically indexed
+// byte k.
+//
+// Three instructions per increment, one per pipe: with the exclusive-or order the lane's feature
+// offset is (4 l) ^ (4 k), so the per-row term (tile base + class offset + 4 l, 64-byte aligned
+// apart from the 4 l) needs one LOP3 with the immediate 4 k; a byte dot product (IDP.4A with the
+// multiplier 64 in byte k & 3) extracts the code, scales it and adds that term in one
+// instruction; the shared-memory increment is the third.  (The additive order l + k mod 16 took
+// six: add, mask, add, byte extract, multiply-add, increment.  Both address terms as integer
+// multiply-adds with run-time multipliers: 3.06 instead of 2.87 ms per level.)
 __device__ __forceinline__ void tile_count_il(uint32_t* tile, uint4 x, uint32_t lab, int B, int lane) {
-  const int rot = lane & 15;
+  const uint32_t r = (uint32_t)lane & 15u;
   uint32_t w0 = x.x, w1 = x.y, w2 = x.z, w3 = x.w;
-  if (rot & 4) { const uint32_t t = w0; w0 = w1; w1 = w2; w2 = w3; w3 = t; }
-  if (rot & 8) { uint32_t t = w0; w0 = w2; w2 = t; t = w1; w1 = w3; w3 = t; }
-  const uint32_t sel = 0x3210u + 0x1111u * (uint32_t)(rot & 3);
-  const uint4 y = make_uint4(__byte_perm(w0, w1, sel), __byte_perm(w1, w2, sel), __byte_perm(w2, w3, sel),
-                             __byte_perm(w3, w0, sel));  // byte k of y = byte (k + rot) mod 16 of x
-  // byte offsets throughout: one byte extract (PRMT), one add of the lane's feature offset and one
-  // shift-add per increment (shared-window addresses, so the tile base folds into the per-row term).
-  // cell = lab * B + code (class-major, like the slabs).  (Tried: both address terms as integer
-  // multiply-adds with run-time multipliers, to move them off the ALU pipe: 3.06 instead of 2.87 ms per
-  // level.)
-  const uint32_t row_base = smem_u32(tile) + lab * (uint32_t)B * 64u;
-  const uint32_t yw[4] = {y.x, y.y, y.z, y.w};
+  if (r & 4u) { uint32_t t = w0; w0 = w1; w1 = t; t = w2; w2 = w3; w3 = t; }
+  if (r & 8u) { uint32_t t = w0; w0 = w2; w2 = t; t = w1; w1 = w3; w3 = t; }
+  const uint32_t sel = 0x3210u ^ (0x1111u * (r & 3u));
+  // byte k of y = byte k ^ r of x
+  const uint32_t yw[4] = {__byte_perm(w0, 0u, sel), __byte_perm(w1, 0u, sel), __byte_perm(w2, 0u, sel),
+                          __byte_perm(w3, 0u, sel)};
+  // cell = lab * B + code (class-major, like the slabs); shared-window byte addresses
+  const uint32_t row_base = smem_u32(tile) + lab * (uint32_t)B * 64u + 4u * r;
 #pragma unroll
   for (int k = 0; k < 16; ++k) {
-    const uint32_t code = __byte_perm(yw[k >> 2], 0u, 0x4440u | (uint32_t)(k & 3));
-    const uint32_t addr = code * 64u + (row_base + (uint32_t)(((k + rot) & 15) * 4));
+    const uint32_t addr = __dp4a(yw[k >> 2], 0x40u << (8 * (k & 3)), row_base ^ (uint32_t)(4 * k));
     asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(addr), "r"(1u) : "memory");
   }
 }
@@ -1484,7 +1488,9 @@ __device__ void move_hist_phase(const MtbCtx& P, const MtbCtx& C, uint8_t* smem,
     // left" bits themselves), so neither the ranker's atomic round trip nor its reads are part of a row
     // stage's cycle.  Records go through a ring of kRecRing entries.  (Measured per plane of the 100M-row
     // fit: 0.88 ms with the record on the stage's critical path, 0.83 ms with the rankers reading global
-    // memory ahead of the copies, 0.67 ms for step B.)
+    // memory ahead of the copies, 0.75 ms as here, 0.67 ms for step B.  Letting the consumers post the bit
+    // words of their own rows, so that a ranker only scans and reserves, took 1.20 ms: the record then
+    // waits for the slowest consumer warp to reach the unit.)
     Ring mine_ring = ring;
     for (int i = 0; i < rk; ++i) mine_ring.next(stages);
     for (int u = u0 + rk; u < u1; u += kRankers) {
