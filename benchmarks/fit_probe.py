@@ -19,7 +19,8 @@ def main():
     ap.add_argument("--unfused", action="store_true")
     ap.add_argument("--informative", type=int, default=8)
     ap.add_argument("--reduce", default="auto")
-    ap.add_argument("--root-cluster", action="store_true", help="hand the builder raw row-major bytes (k_root_cluster)")
+    ap.add_argument("--root-input", "--root-cluster", dest="root_cluster", action="store_true",
+                    help="hand the builder raw row-major bytes: the root pass (MTB_ROOT=direct|cluster) is timed inside the build")
     a = ap.parse_args()
     import os
     world, rank = int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("RANK", "0"))

@@ -197,6 +197,10 @@ int mtb_level_fused(const MtbCtx* ctx, void* stream);
  * shape or the pointers do not qualify (nothing was launched: encode and count the usual way), < 0 on a
  * CUDA error.  Follow with mtb_level_fused(ctx with root_hist_done = 1).                             */
 int mtb_root_retile_hist(const MtbCtx* ctx, const void* X, int64_t ldx, int64_t n, const void* y, void* stream);
+/* The same pass without staging or clusters: CTA b takes feature group b mod G of a row range with 128-bit
+ * loads from the row-major matrix (ldx == F == 16 G, any G up to the SM count).  Same contract and
+ * return values.                                                                                      */
+int mtb_root_direct_hist(const MtbCtx* ctx, const void* X, int64_t ldx, int64_t n, const void* y, void* stream);
 /* Test hook: out[i] = k[i] * log2(k[i]) by the device function of the gain phase (table = ctx.klogk). */
 int mtb_klogk_eval(const uint32_t* k, double* out, int64_t n, const double* table, void* stream);
 /* Shared memory / launch geometry the hist phase will use for this ctx (for reports). */

@@ -1895,6 +1895,58 @@ __global__ void __launch_bounds__(kHistThreads, 1) k_root_cluster(const __grid_c
   cluster_sync_all();  // nobody leaves while a peer may still multicast into it or arrive on its barriers
 }
 
+// Root level of row-major uint8 input without staging (k_root_direct): CTA b works on feature group
+// b mod G of the rows of row range b / G.  A lane loads the 16 bytes of its row's group straight from
+// the caller's matrix (128-bit loads, four rows per lane in flight), stores them into the plane,
+// and counts them into the CTA's 32-bit [C*B][16] tile; the CTAs of group 0 also write the labels.
+// The G CTAs of a row range read the same lines at about the same time, so DRAM sees the input once
+// (the others hit in L2); each CTA uses half of every 32-byte sector it receives.  Against the
+// separate passes (retile: read + write; root histogram: read the planes again) one read of the
+// data set is saved.  The tiles are merged into the root slab with red.global.add (the entry point
+// zeroes the slab first); mtb_level_fused then runs with ctx.root_hist_done set.
+constexpr int kRootDirectThreads = 1024;
+constexpr int kRootDirectUnroll = 4;
+
+__global__ void __launch_bounds__(kRootDirectThreads, 1) k_root_direct(const __grid_constant__ MtbCtx ctx, const RootArgs a) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  uint32_t* tile = reinterpret_cast<uint32_t*>(smem);
+  const int B = (int)ctx.B, C = (int)ctx.C, G = (int)ctx.G;
+  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5, nw = kRootDirectThreads / 32;
+  const int g = (int)(blockIdx.x % (unsigned)G), range = (int)(blockIdx.x / (unsigned)G), n_ranges = (int)(gridDim.x / (unsigned)G);
+  for (int i = tid; i < 16 * B * C; i += kRootDirectThreads) tile[i] = 0;
+  __syncthreads();
+  const int64_t blocks = (a.n + 31) / 32;  // 32 rows: one per lane
+  const int64_t b0 = blocks * range / n_ranges, b1 = blocks * (range + 1) / n_ranges;
+  const uint4* src = reinterpret_cast<const uint4*>(a.X) + g;  // row r of the group: src[r * G]
+  uint4* plane = reinterpret_cast<uint4*>(ptr_of<uint8_t>(ctx.codes[ctx.cur])) + (int64_t)g * ctx.n_cap;
+  uint8_t* lab_out = ptr_of<uint8_t>(ctx.labels[ctx.cur]);
+  for (int64_t b = b0 + w; b < b1; b += (int64_t)nw * kRootDirectUnroll) {
+    uint4 x[kRootDirectUnroll];
+    uint32_t lab[kRootDirectUnroll];
+#pragma unroll
+    for (int j = 0; j < kRootDirectUnroll; ++j) {
+      const int64_t row = (b + (int64_t)j * nw) * 32 + lane;
+      x[j] = make_uint4(0, 0, 0, 0);
+      lab[j] = 0;
+      if (b + (int64_t)j * nw < b1 && row < a.n) {
+        x[j] = ld_cg_u4(src + row * G);
+        lab[j] = __ldg(a.y + row);
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < kRootDirectUnroll; ++j) {
+      const int64_t row = (b + (int64_t)j * nw) * 32 + lane;
+      if (b + (int64_t)j * nw < b1 && row < a.n) {
+        st_na_u4(plane + row, x[j]);
+        if (g == 0) lab_out[row] = (uint8_t)lab[j];
+        tile_count_il(tile, x[j], lab[j], B, lane);
+      }
+    }
+  }
+  __syncthreads();
+  if (tid < kConsumers) flush_tile<16, true>(ctx, tile, 0, g, tid, false);
+}
+
 // Everything after a level's histograms are complete on this rank (the caller has synchronised the
 // grid): [push partial slabs to the owners, peer barrier,] gain on the owned features (records go to
 // every rank's mailbox), [peer barrier | grid sync,] finalize on CTA 0 while the others zero the
@@ -2281,6 +2333,22 @@ extern "C" int mtb_root_retile_hist(const MtbCtx* ctx, const void* X, int64_t ld
   }
   RootArgs a{reinterpret_cast<const uint8_t*>(X), reinterpret_cast<const uint8_t*>(y), n, multicast};
   MTB_CHECK(cudaLaunchKernelEx(&cfg, k_root_cluster, *ctx, a, tmap));
+  return 0;
+}
+
+/* The same pass without staging and without clusters (k_root_direct): any whole number of 16-feature groups.  */
+extern "C" int mtb_root_direct_hist(const MtbCtx* ctx, const void* X, int64_t ldx, int64_t n, const void* y, void* stream) {
+  const int G = (int)ctx->G, B = (int)ctx->B, C = (int)ctx->C;
+  if (G < 1 || G > sm_count() || ctx->F != 16 * G || ldx != 16 * G || ctx->FT != 16 || ctx->tile_layout != 1) return 1;
+  if ((reinterpret_cast<uintptr_t>(X) & 15u) != 0 || n <= 0 || n > ctx->n_cap) return 1;
+  const int smem = 16 * B * C * 4;
+  if (smem > kSmemBudget) return 1;
+  cudaStream_t st = (cudaStream_t)stream;
+  MTB_CHECK(cudaFuncSetAttribute(k_root_direct, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  MTB_CHECK(cudaMemsetAsync(ptr_of<void>(ctx->hist[ctx->hcur]), 0, (size_t)G * 16 * B * C * 4, st));
+  RootArgs a{reinterpret_cast<const uint8_t*>(X), reinterpret_cast<const uint8_t*>(y), n, 0};
+  k_root_direct<<<(unsigned)((sm_count() / G) * G), kRootDirectThreads, smem, st>>>(*ctx, a);
+  MTB_CHECK(cudaGetLastError());
   return 0;
 }
 

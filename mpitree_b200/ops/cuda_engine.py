@@ -686,7 +686,8 @@ class TreeBuilder:
             return
         self.root_input = None
         X, y = src
-        rc = self.lib.mtb_root_retile_hist(
+        entry = self.lib.mtb_root_retile_hist if _root_mode() == "cluster" else self.lib.mtb_root_direct_hist
+        rc = entry(
             ctypes.byref(self.ctx), ctypes.c_void_p(_p(X)), ctypes.c_int64(X.stride(0)), ctypes.c_int64(X.shape[0]),
             ctypes.c_void_p(_p(y)), _stream_ptr()) if X.shape[0] else 1
         KERNEL_LAUNCHES["count"] += 1
@@ -1233,6 +1234,18 @@ def _byte_lut(mapper: BinMapper) -> np.ndarray:
 _COPY_STREAMS: dict = {}
 
 
+def _root_mode() -> str:
+    """How the first level reads uint8 rows that already are bin codes: ``direct`` (default: planes, labels and
+    root histogram in one pass straight from the row-major matrix, ``k_root_direct``), ``cluster`` (the same
+    by thread-block clusters and a multicast TMA copy, ``k_root_cluster``: measured slower) or
+    ``off`` (retile pass + label copy, histogram by the level kernel).  ``MTB_ROOT`` selects;
+    ``MTB_ROOT_CLUSTER=1`` is the older spelling of ``cluster``."""
+    if os.environ.get("MTB_ROOT_CLUSTER", "0") == "1":
+        return "cluster"
+    mode = os.environ.get("MTB_ROOT", "direct")
+    return mode if mode in ("direct", "cluster", "off") else "direct"
+
+
 def _copy_stream(dev):
     import torch
 
@@ -1451,9 +1464,10 @@ def fit_from_torch(X, y, params: SplitParams, *, max_bins: int = 256, comm=None,
     # first launch can read them in the caller's row-major layout (planes + labels + root histogram in one
     # pass by thread-block clusters, k_root_cluster) instead of a retile pass and a label copy here
     root_input = None
-    if (X.is_cuda and X.device == dev and X.dtype == torch.uint8 and lut is None and F in (32, 64, 128) and X.stride(1) == 1
+    mode = _root_mode()
+    if (X.is_cuda and X.device == dev and X.dtype == torch.uint8 and lut is None and X.stride(1) == 1
             and X.stride(0) == F and y_codes.dtype == torch.uint8 and y_codes.is_contiguous() and y_codes.device == dev
-            and os.environ.get("MTB_ROOT_CLUSTER", "0") == "1"):  # opt-in: measured slower than the separate passes, see DESIGN.md
+            and (F in (32, 64, 128) if mode == "cluster" else (mode == "direct" and F % 16 == 0 and F > 0))):
         root_input = (X, y_codes)
     if root_input is not None:
         pass

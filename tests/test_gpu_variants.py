@@ -279,20 +279,24 @@ def test_handoff_record_exchange_paths(tmp_path):
     assert f"RECORD_EXCHANGE_OK {world}" in res.stdout
 
 
-@pytest.mark.parametrize("F", [32, 64, 128])
-def test_root_cluster_pass_equals_separate_passes(monkeypatch, F):
-    """Opt-in root pass (MTB_ROOT_CLUSTER=1): thread-block clusters of F/16 CTAs share each row tile through a
-    multicast TMA copy and produce planes + labels + root histogram at once; same tree as retile + histogram."""
+@pytest.mark.parametrize("F", [16, 32, 48, 64, 128])
+def test_root_pass_variants_equal_separate_passes(monkeypatch, F):
+    """First level of uint8 rows that already are bin codes, three ways: ``direct`` (the default: planes + labels
+    + root histogram in one pass of 128-bit loads from the row-major matrix), ``cluster`` (opt-in: thread-block
+    clusters of F/16 CTAs share each row tile through a multicast TMA copy; F = 32 / 64 / 128 only) and ``off``
+    (retile + label copy, histogram by the level kernel).  Same tree."""
     import torch
 
     from mpitree_b200.tree import DecisionTreeClassifier
 
+    monkeypatch.delenv("MTB_ROOT_CLUSTER", raising=False)
     rng = np.random.default_rng(F)
-    trees = {}
     for n in (999, 70_001, 300_000):
         X = torch.from_numpy(rng.integers(0, 256, size=(n, F), dtype=np.uint8)).cuda()
-        y = ((X[:, 1] > 90).to(torch.uint8) + (X[:, F - 1] > 200).to(torch.uint8) + (X[:, 17] > 30).to(torch.uint8))
-        for flag in ("1", "0"):
-            monkeypatch.setenv("MTB_ROOT_CLUSTER", flag)
-            trees[flag] = DecisionTreeClassifier(max_depth=6, device="cuda").fit(X, y).flat_tree_
-        _same_tree(trees["1"], trees["0"])
+        y = ((X[:, 1] > 90).to(torch.uint8) + (X[:, F - 1] > 200).to(torch.uint8) + (X[:, F // 2 + 1] > 30).to(torch.uint8))
+        trees = {}
+        for mode in ("off", "direct", "cluster"):
+            monkeypatch.setenv("MTB_ROOT", mode)
+            trees[mode] = DecisionTreeClassifier(max_depth=6, device="cuda").fit(X, y).flat_tree_
+        _same_tree(trees["direct"], trees["off"])
+        _same_tree(trees["cluster"], trees["off"])
