@@ -1662,7 +1662,9 @@ __device__ void move_hist_phase(const MtbCtx& P, const MtbCtx& C, uint8_t* smem,
     // (Tried: compacting the rows to count - the lanes list their rows of the built child in shared memory
     // and lane i reads the i-th listed row from the stage again, so that a warp issues one full pass of
     // increments instead of two half-empty ones.  2.67 instead of 2.50 ms per level: with near-even splits
-    // a second pass is still needed for almost half of the units, and full passes conflict more.)
+    // a second pass is still needed for almost half of the units, and full passes conflict more.  Also
+    // tried: first pass = a lane's first row that counts, second pass = lanes with two; 2.57 ms.  The
+    // cost of the shared-memory increments follows the number of active lanes, not of instructions.)
     if (build_child >= 0) {
       ++units_since_flush;
       if constexpr (IL && kPacked) {
