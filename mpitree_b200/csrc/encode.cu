@@ -66,6 +66,7 @@ __global__ void __launch_bounds__(kThreads) k_encode_float(const T* __restrict__
 // `rd(e) >= x`, so the codes equal k_encode_float's.  Rows of the table are padded to 257 words so
 // that the same search step of different features falls into different banks.
 constexpr int kEdgeStride = MTB_MAX_BINS + 1;
+static_assert(MTB_MAX_BINS <= 256, "k_encode_f32_slots packs two bin codes into a 16-bit table entry");
 
 __global__ void __launch_bounds__(kThreads) k_encode_f32_quads(const float4* __restrict__ X, int64_t n, int F,
                                                                int64_t ldx4, const double* __restrict__ edges,
@@ -158,8 +159,7 @@ __global__ void __launch_bounds__(kThreads) k_encode_f32_slots(const float4* __r
     s_inv[threadIdx.x] = (w > 0.0f && w < INFINITY) ? 1.0f / w : 0.0f;
   }
   __syncthreads();
-  // lut[k][s] = number of edges whose slot is below s (the edges' slots ascend: bisection per entry);
-  // entry s also carries lut[s + 1] in its upper half
+  // below(k, s) = number of edges whose slot is below s (the edges' slots ascend: bisection per entry)
   auto below = [&](int k, int sl) {
     const float* e = s_edges + k * kEdgeStride;
     const float mn = s_mn[k], inv = s_inv[k];
@@ -170,9 +170,13 @@ __global__ void __launch_bounds__(kThreads) k_encode_f32_slots(const float4* __r
     }
     return (uint32_t)lo;
   };
+  // one 16-bit entry per slot: first candidate code in the low byte, last one (capped at the last bin) in the
+  // high byte, so a value costs one table load before its probes (codes are < 256 = MTB_MAX_BINS)
   for (int i = threadIdx.x; i < 16 * (kSlots + 1); i += kThreads) {
     const int k = i / (kSlots + 1), sl = i % (kSlots + 1);
-    s_lut[k][sl] = (uint16_t)below(k, sl);
+    const uint32_t lo = below(k, sl);
+    const uint32_t hi = min(sl < kSlots ? below(k, sl + 1) : (uint32_t)s_last[k] + 1u, (uint32_t)s_last[k]);
+    s_lut[k][sl] = (uint16_t)(lo | (hi << 8));
   }
   __syncthreads();
   const int quads = min(4, (F - g * 16 + 3) / 4);  // quads of this group that exist in X
@@ -195,7 +199,8 @@ __global__ void __launch_bounds__(kThreads) k_encode_f32_slots(const float4* __r
       const int k = q * 4 + j;
       const float* e = s_edges + k * kEdgeStride;
       const int sl = slot_of(x[j], mn[j], inv[j]);
-      int lo = s_lut[k][sl], hi = min((int)s_lut[k][sl + 1], last[j]);
+      const uint32_t ent = s_lut[k][sl];
+      int lo = (int)(ent & 255u), hi = (int)(ent >> 8);
       while (hi - lo > 4) {
         const int mid = (lo + hi) >> 1;
         if (e[mid] >= x[j]) hi = mid; else lo = mid + 1;
