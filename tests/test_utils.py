@@ -189,41 +189,50 @@ def test_tree_builder_host_setup_runs_without_a_gpu():
 
 
 def test_interleaved_tile_index_arithmetic_host_emulation():
-    """Host emulation of ``tile_count_il`` + the interleaved ``flush_tile`` (csrc/build.cu, staged path).
+    """Host emulation of ``tile_count_il`` + the interleaved ``flush_tile`` (csrc/build.cu).
 
-    Mirrors the kernel's integer arithmetic step by step: the per-lane byte rotation
-    (word swaps + ``__byte_perm``), the ``[cell][16]`` tile address, and the flush's lane -> (cell, feature
-    quad) mapping.  Checks that every (feature, bin, class) count lands in the ``[f][B][C]`` slab exactly
-    once.  It pins the index algebra, not the CUDA code itself (that is ``tests/test_gpu_variants.py``).
+    Mirrors the kernel's integer arithmetic step by step: the per-lane byte permutation (word swaps +
+    ``__byte_perm``) of the exclusive-or feature order, the address formed by one ``LOP3`` (row term ^ 4k) and
+    one byte dot product (``__dp4a`` with the multiplier 64 in byte k & 3), the ``[cell = class*B + bin][16]``
+    tile, and the flush's lane -> (cell, feature quad) mapping.  Checks that every (feature, class, bin) count
+    lands in the ``[f][C][B]`` slab exactly once.  It pins the index algebra, not the CUDA code itself (that is
+    ``tests/test_gpu_variants.py``).
     """
 
     def byte_perm(a, b, sel):
         by = [(a >> (8 * i)) & 255 for i in range(4)] + [(b >> (8 * i)) & 255 for i in range(4)]
         return sum(by[(sel >> (4 * n)) & 7] << (8 * n) for n in range(4))
 
+    def dp4a(a, b, c):
+        return (sum(((a >> (8 * i)) & 255) * ((b >> (8 * i)) & 255) for i in range(4)) + c) & 0xFFFFFFFF
+
     rng = np.random.default_rng(0)
     B, C = 256, 10
     BC = B * C
+    tile_base = 0x400  # shared-window byte address of the tile: 128-byte aligned
     tile = np.zeros(BC * 16, np.int64)
-    want = np.zeros((16, B, C), np.int64)
+    want = np.zeros((16, C, B), np.int64)
     for row in range(1500):
         lane = row % 32
         codes = rng.integers(0, 256, 16)
         lab = int(rng.integers(0, C))
         w = [int(sum(int(codes[4 * i + j]) << (8 * j) for j in range(4))) for i in range(4)]
-        rot = lane & 15
-        if rot & 4:
-            w = [w[1], w[2], w[3], w[0]]
-        if rot & 8:
+        r = lane & 15
+        if r & 4:
+            w = [w[1], w[0], w[3], w[2]]
+        if r & 8:
             w = [w[2], w[3], w[0], w[1]]
-        sel = 0x3210 + 0x1111 * (rot & 3)
-        y = [byte_perm(w[i], w[(i + 1) & 3], sel) for i in range(4)]
+        sel = 0x3210 ^ (0x1111 * (r & 3))
+        y = [byte_perm(w[i], 0, sel) for i in range(4)]
+        row_base = tile_base + lab * B * 64 + 4 * r
         for k in range(16):
-            f = (k + rot) & 15
-            code = (y[k >> 2] >> ((k & 3) * 8)) & 255
-            assert code == codes[f]
-            tile[lab * 16 + code * C * 16 + f] += 1
-        want[np.arange(16), codes, lab] += 1
+            addr = dp4a(y[k >> 2], 0x40 << (8 * (k & 3)), row_base ^ (4 * k))
+            word, rem = divmod(addr - tile_base, 4)
+            assert rem == 0
+            cell, f = divmod(word, 16)
+            assert f == k ^ r and cell == lab * B + int(codes[f])
+            tile[word] += 1
+        want[np.arange(16), lab, codes] += 1
     slab = np.zeros(16 * BC, np.int64)
     hits = np.zeros(16 * BC, np.int64)
     for warp in range(16):
@@ -237,11 +246,11 @@ def test_interleaved_tile_index_arithmetic_host_emulation():
                             slab[(4 * q + j) * BC + cell] += tile[cell * 16 + 4 * q + j]
                             hits[(4 * q + j) * BC + cell] += 1
     assert (hits == 1).all()
-    assert np.array_equal(slab.reshape(16, B, C), want)
+    assert np.array_equal(slab.reshape(16, C, B), want)
     # bank view: in one instruction (fixed k) the 32 lanes touch 16 features, two lanes each,
     # and feature f only ever maps to banks f and 16 + f
     for k in range(16):
-        feats = [(k + (lane & 15)) & 15 for lane in range(32)]
+        feats = [k ^ (lane & 15) for lane in range(32)]
         assert sorted(feats) == sorted(list(range(16)) * 2)
     cells = rng.integers(0, BC, 1000)
     for f in range(16):
@@ -439,3 +448,46 @@ def test_sampled_edges_are_repaired_when_the_sample_missed_a_value():
 
     got = run_threaded(2, work)
     assert got[0] == got[1] and 77.0 in got[0][1]
+
+
+def test_root_mode_switch(monkeypatch):
+    """``MTB_ROOT`` picks how the first level reads uint8 code input; the older ``MTB_ROOT_CLUSTER=1`` still means
+    the cluster pass; anything unknown falls back to the default."""
+    from mpitree_b200.ops import cuda_engine
+
+    monkeypatch.delenv("MTB_ROOT", raising=False)
+    monkeypatch.delenv("MTB_ROOT_CLUSTER", raising=False)
+    assert cuda_engine._root_mode() == "direct"
+    for mode in ("direct", "cluster", "off"):
+        monkeypatch.setenv("MTB_ROOT", mode)
+        assert cuda_engine._root_mode() == mode
+    monkeypatch.setenv("MTB_ROOT", "nonsense")
+    assert cuda_engine._root_mode() == "direct"
+    monkeypatch.setenv("MTB_ROOT", "off")
+    monkeypatch.setenv("MTB_ROOT_CLUSTER", "1")
+    assert cuda_engine._root_mode() == "cluster"
+
+
+def test_root_direct_row_ranges_cover_every_row_once():
+    """Row assignment of ``k_root_direct`` (csrc/build.cu): CTA b takes feature group b mod G of row range b / G;
+    a range is a run of 32-row blocks dealt to the CTA's warps four blocks per pass.  Every (row, group) pair
+    must be visited exactly once for any n and G."""
+    nw, unroll = 32, 4
+    for n, G, sms in ((999, 4, 148), (70_001, 3, 148), (5, 1, 148), (300_000, 8, 148), (4097, 4, 6)):
+        n_ranges = sms // G
+        seen = np.zeros((n, G), np.int64)
+        blocks = (n + 31) // 32
+        for b in range(n_ranges * G):
+            g, rng_ = b % G, b // G
+            b0, b1 = blocks * rng_ // n_ranges, blocks * (rng_ + 1) // n_ranges
+            for w in range(nw):
+                blk = b0 + w
+                while blk < b1:
+                    for j in range(unroll):
+                        bj = blk + j * nw
+                        if bj < b1:
+                            lo, hi = bj * 32, min(bj * 32 + 32, n)
+                            if lo < hi:
+                                seen[lo:hi, g] += 1
+                    blk += nw * unroll
+        assert (seen == 1).all(), (n, G)
