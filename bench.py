@@ -371,7 +371,7 @@ def run_ours(a):
             "h2d_bytes_per_step": int(Xh.numel() * Xh.element_size() + yh.numel() * yh.element_size()) * world,
             "d2h_bytes_per_step": d2h * world,
             "steps": e_steps,
-            "cpu_binding": f"rank 0 bound to {len(bound)} CPUs local to its GPU" if bound else "none (NVML affinity unavailable or already bound)",
+            "cpu_binding": f"rank 0 bound to {len(bound)} CPUs local to its GPU" if bound else "none (no GPU-local CPU set from NVML or sysfs, or it is the whole allowed set)",
         }
 
     same_cfg = None

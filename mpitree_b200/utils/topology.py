@@ -34,12 +34,39 @@ def gpu_cpu_affinity(device_index: int) -> Optional[List[int]]:
         return None
 
 
+def parse_cpulist(text: str) -> List[int]:
+    """``"0-3,8,10-11"`` (the kernel's cpulist format) -> ``[0, 1, 2, 3, 8, 10, 11]``."""
+    cpus: List[int] = []
+    for part in text.strip().split(","):
+        part = part.strip()
+        if not part:
+            continue
+        lo, _, hi = part.partition("-")
+        cpus.extend(range(int(lo), int(hi or lo) + 1))
+    return cpus
+
+
+def gpu_cpu_affinity_sysfs(device_index: int, sysfs_root: str = "/sys/bus/pci/devices") -> Optional[List[int]]:
+    """The same from the kernel's PCI topology (``<device>/local_cpulist``) for the GPU torch calls
+    ``device_index``: works where NVML will not report an affinity (some containers)."""
+    try:
+        import torch
+
+        p = torch.cuda.get_device_properties(device_index)
+        bdf = f"{p.pci_domain_id:04x}:{p.pci_bus_id:02x}:{p.pci_device_id:02x}.0"
+        with open(os.path.join(sysfs_root, bdf, "local_cpulist")) as fh:
+            cpus = parse_cpulist(fh.read())
+        return cpus or None
+    except Exception:  # noqa: BLE001  (no CUDA device, no sysfs entry, unreadable file)
+        return None
+
+
 def bind_to_gpu_numa(device_index: int) -> Optional[List[int]]:
     """Restrict this process to the CPUs local to its GPU; returns them (``None``: nothing was changed).
 
     Only CPUs the process is already allowed to use are kept, so a container's CPU set is respected.
     """
-    cpus = gpu_cpu_affinity(device_index)
+    cpus = gpu_cpu_affinity(device_index) or gpu_cpu_affinity_sysfs(device_index)
     if not cpus or not hasattr(os, "sched_setaffinity"):
         return None
     try:

@@ -491,3 +491,19 @@ def test_root_direct_row_ranges_cover_every_row_once():
                                 seen[lo:hi, g] += 1
                     blk += nw * unroll
         assert (seen == 1).all(), (n, G)
+
+
+def test_cpulist_parsing_and_binding_is_a_no_op_without_topology():
+    from mpitree_b200.utils import topology
+
+    assert topology.parse_cpulist("0-3,8,10-11\n") == [0, 1, 2, 3, 8, 10, 11]
+    assert topology.parse_cpulist("") == []
+    assert topology.parse_cpulist("5") == [5]
+    # no CUDA device here: neither source reports anything and the process keeps its CPU set
+    import os
+
+    before = os.sched_getaffinity(0) if hasattr(os, "sched_getaffinity") else None
+    assert topology.gpu_cpu_affinity_sysfs(0) is None
+    assert topology.bind_to_gpu_numa(0) is None
+    if before is not None:
+        assert os.sched_getaffinity(0) == before
