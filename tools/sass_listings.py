@@ -15,7 +15,7 @@ ROOT = pathlib.Path(__file__).resolve().parents[1]
 LIB = ROOT / "mpitree_b200" / "lib" / "libmpitree_b200.so"
 OUT = ROOT / "profiles" / "sass"
 
-OPS = ["UBLKCP", "UTMALDG", "SYNCS", "ATOMS", "LDGMC", "REDG", "ATOMG", "RED", "LDG", "STG", "LDS", "STS", "LDL", "STL",
+OPS = ["UBLKCP", "UTMALDG", "SYNCS", "ATOMS", "IDP", "LDGMC", "REDG", "ATOMG", "RED", "LDG", "STG", "LDS", "STS", "LDL", "STL",
        "DADD", "DMUL", "DFMA", "MUFU", "PRMT", "BAR", "SHFL", "MEMBAR", "VOTE", "POPC", "UCGABAR", "CCTL"]
 
 # mangled-name fragment -> file stem
@@ -24,12 +24,13 @@ WANT = [
     ("k_level_fused2ILi16ELb1ELb1E", "k_level_fused2_FT16_interleaved_nvls"),
     ("k_level_fused2ILi16ELb0ELb0E", "k_level_fused2_FT16_planar"),
     ("k_level_fusedILi16ELb1ELb0E", "k_level_fused_FT16_interleaved"),
+    ("k_root_direct", "k_root_direct"),
     ("k_root_cluster", "k_root_cluster"),
     ("k_histILi16ELb1E", "k_hist_FT16_interleaved"),
     ("k_histILi16ELb0E", "k_hist_FT16_planar"),
     ("k_gainE", "k_gain"), ("k_finalize", "k_finalize"), ("k_plan", "k_plan"), ("k_partition", "k_partition"),
     ("k_commit", "k_commit"), ("k_push", "k_push"), ("k_klogk_eval", "k_klogk_eval"),
-    ("k_encode_f32_quads", "k_encode_f32_quads"), ("k_encode_floatIfE", "k_encode_float_f32"),
+    ("k_encode_f32_slots", "k_encode_f32_slots"), ("k_encode_f32_quads", "k_encode_f32_quads"), ("k_encode_floatIfE", "k_encode_float_f32"),
     ("k_encode_u8", "k_encode_u8"), ("k_retile_u8", "k_retile_u8"),
     ("k_predict_u8_compact", "k_predict_u8_compact"), ("k_predict_stagedIffE", "k_predict_staged_f32"),
     ("k_subtreeILi8E", "k_subtree_FT8"), ("k_gather_rows", "k_gather_rows"),
@@ -80,6 +81,7 @@ def main():
             fh.write(f"| `{stem}` | {n} | {ops} |\n")
         fh.write("\n`UBLKCP` = `cp.async.bulk` (TMA bulk copy), `UTMALDG` = `cp.async.bulk.tensor` (tiled TMA load, the multicast copy of\n"
                  "`k_root_cluster`), `SYNCS` = mbarrier operations, `ATOMS` = shared-memory atomics (`red.shared.add` / `ATOMS.POPC.INC`),\n"
+                 "`IDP` = `IDP.4A` (byte dot product: forms a histogram address - byte extract, scale, add - in one instruction),\n"
                  "`REDG` = `red.global.add`, `LDGMC` = `multimem.ld_reduce` (in-switch reduction), `UCGABAR` = cluster barrier;\n"
                  "`MEMBAR.SYS` + `ST.E.STRONG.SYS` / `LD.E.STRONG.SYS` form the peer barrier.  No tcgen05 / `UTC*MMA` by design: the\n"
                  "workload has no GEMM (DESIGN.md §2).\n")
